@@ -301,10 +301,17 @@ int main(int argc, char **argv) {
     w.put("scaffold_nodes", sc_nodes);
     w.put("scaffold_slots", sc_slots);
 
+    uint8_t fasta_ok = 0;
     if (have_scaffold && pos.size() == 6) {
         Scaffolder scaff(scaffold);
         if (!scaff.load(pos[3]) || !scaff.load(pos[4])) return 1;
-        if (!scaff.write(pos[5])) return 1;
+        try {  // the reference's substr calls throw on some scaffolds (src/Scaffolder.cpp:62,111)
+            fasta_ok = scaff.write(pos[5]) ? 1 : 0;
+        } catch (const std::exception &e) {
+            std::cerr << "Scaffolder::write threw: " << e.what() << "\n";
+            std::remove(pos[5]);
+        }
     }
+    w.scalar<uint8_t>("fasta_ok", fasta_ok);
     return 0;
 }
