@@ -1,0 +1,171 @@
+/*
+ * hera_b200.h -- C ABI of the B200-native HERA repeat-resolution hot path.
+ *
+ * The reference (lirfu/Telomeri) has no plugin/FFI layer: its hot path is reached only through
+ * the C++ classes main() calls (src/Main.cpp:211-352).  This header is the boundary a binding
+ * would use instead; each entry point names the reference member function(s) it replaces.
+ * Plain pointers and sizes only.  Every function returns 0 on success; on failure it returns a
+ * non-zero code and hera_last_error() describes it.  There is no CPU fallback: without a CUDA
+ * device hera_create() fails.
+ *
+ * One host thread per context.  "View" structs hold HOST pointers owned by the context
+ * (pinned memory), valid until the next call that mutates the same object or hera_destroy().
+ */
+#ifndef HERA_B200_H
+#define HERA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hera_ctx hera_ctx;
+
+/* OverlapGraph::LengthCalculationMode, include/OverlapGraph.hpp:56-65 */
+enum { HERA_MODE_MIN = 0, HERA_MODE_MAX = 1, HERA_MODE_AVG = 2, HERA_MODE_SUM = 3 };
+/* Utils::Metrics, include/Utils.hpp:43-45 */
+enum { HERA_EXTENSION_SCORE = 0, HERA_OVERLAP_SCORE = 1, HERA_EXTENSION_SCORE_SQRT = 2, HERA_OVERLAP_SCORE_SQRT = 3 };
+
+/* OverlapGraph::FilterParameters, include/OverlapGraph.hpp:67-78 (defaults src/Main.cpp:56-62) */
+typedef struct {
+    int32_t mode;
+    uint64_t min_overlap_length;
+    float min_overlap_percentage;
+    uint64_t max_overhang_length;
+    float max_overhang_percentage;
+} hera_filter_params;
+
+/* PathManager::Parameters, include/PathManager.hpp:27-40 (defaults src/Main.cpp:63-69) */
+typedef struct {
+    int32_t rebuild_attempts;
+    int32_t backtrack_attempts;
+    int64_t len_threshold;
+    uint64_t window_size;
+    float ratio_threshold;
+} hera_path_params;
+
+typedef struct {
+    uint64_t records;      /* "ctr": records consumed from this input (src/OverlapGraph.cpp:128) */
+    uint64_t kept;         /* overlaps of this input that passed the filter */
+    uint64_t kept_total;   /* cumulative, what "Loaded a/b edges" prints (src/OverlapGraph.cpp:150) */
+    uint64_t bytes;
+    float parse_ms;        /* device time of the tokenizer/filter/score kernels (CUDA events) */
+    float h2d_ms;          /* host->device copy time, 0 for hera_graph_load_device */
+} hera_load_result;
+
+typedef struct {
+    uint64_t nodes, anchors, edges, slots;   /* slots = 2 * edges adjacency entries */
+    float intern_ms, csr_ms, rank_ms;
+} hera_graph_info;
+
+/* Host mirror of the graph.  Edge-like tables are structure-of-arrays; index e = kept overlap
+ * in file order (OverlapGraph::edges_), index s = adjacency slot (nodes_[x].edges[k] has
+ * s = adj_off[x] + k).  For slots the fields are as the owner's list stores them after the
+ * q/t swap of src/OverlapGraph.cpp:245-248: q_* belong to the neighbour, t_* to the owner. */
+typedef struct {
+    uint64_t nodes, edges, slots;
+    const uint32_t *node_len;
+    const uint8_t *node_anchor;
+    const uint64_t *node_name_off;   /* nodes + 1 */
+    const char *node_names;
+    const uint32_t *e_q, *e_t, *e_qs, *e_qe, *e_ts, *e_te;
+    const float *e_os, *e_si, *e_es;
+    const uint8_t *e_strand;
+    const uint64_t *adj_off;         /* nodes + 1 */
+    const uint32_t *adj_rec;         /* slot -> kept overlap */
+    const uint8_t *adj_side;         /* 0 = owner is the PAF target, 1 = owner is the PAF query (swapped copy) */
+    const uint32_t *rank_es, *rank_os, *rank_es_sqrt, *rank_os_sqrt;  /* per-node stable descending order, absolute slots; NULL if not built */
+    const uint32_t *canon;           /* first slot of the owner with the same neighbour */
+} hera_graph_view;
+
+/* Paths in the order of PathManager::paths_.  Path i owns nodes [off[i], off[i+1]) and slots
+ * [off[i] - i, off[i+1] - (i+1)). */
+typedef struct {
+    uint64_t paths, total_nodes;
+    const uint64_t *off;
+    const uint32_t *nodes;
+    const uint32_t *slots;
+    const int64_t *len;              /* Path::length(), src/Path.cpp:6-16 */
+    uint64_t calls;                  /* build calls so far */
+    const uint32_t *call_kind;       /* 0 = Monte Carlo, 1 = deterministic */
+    const uint32_t *call_metric;
+    const uint64_t *call_found;      /* "Found N paths." per call */
+    uint64_t mc_walks;
+    const uint32_t *mc_draws_per_walk;  /* random draws each Monte-Carlo walk consumed, canonical walk order */
+} hera_paths_view;
+
+typedef struct {
+    uint64_t pairs, groups, sorted_total, pig_total;
+    const uint32_t *pair_a1, *pair_a2;   /* anchor node ids, map order of getPathsBetweenAnchors */
+    const uint64_t *pair_off;            /* pairs + 1, into pair_sorted */
+    const uint32_t *pair_sorted;         /* unique-path ids per pair in the order constructGroups leaves them */
+    const uint32_t *grp_pair;
+    const uint32_t *grp_size0;           /* members before discardNotFrequent: consecutive ranges of pair_sorted */
+    const uint64_t *grp_pig_off;         /* groups + 1 */
+    const uint32_t *grp_pig;             /* members after discardNotFrequent */
+    const int64_t *grp_consensus;        /* path id or -1 */
+    const int32_t *grp_valid;            /* valid_path_number */
+    const int64_t *pair_consensus;       /* inter-group pick (src/Main.cpp:306-332), path id or -1 */
+    float ms;
+} hera_groups_view;
+
+/* Timing of the last walk call, for bench.py. */
+typedef struct {
+    uint64_t walks;        /* walks started by the call */
+    uint64_t found;
+    uint64_t steps;        /* adjacency entries examined (sum over walks) */
+    float ms;
+    uint32_t launches;     /* kernels launched by the call */
+} hera_walk_stats;
+
+/* ---- lifetime ---------------------------------------------------------------------------- */
+hera_ctx *hera_create(int device);               /* NULL if the device cannot be used */
+void hera_destroy(hera_ctx *ctx);
+const char *hera_last_error(hera_ctx *ctx);      /* ctx may be NULL: error of the last failed hera_create */
+uint64_t hera_kernel_launches(hera_ctx *ctx);    /* kernels launched by this context so far */
+
+/* ---- OverlapGraph ------------------------------------------------------------------------ */
+/* graph.filter_params_ = ... (src/Main.cpp:213-217) */
+int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp);
+/* OverlapGraph::load(filepath, anchors) (src/OverlapGraph.cpp:97-154): reads the file, copies it
+ * to the device, tokenizes / filters / scores there, appends to the graph.  test_load_num as
+ * OverlapGraph::test_load_num_ (0 = whole file).  A file that cannot be opened returns 1. */
+int hera_graph_load_file(hera_ctx *ctx, const char *path, int anchors, uint32_t test_load_num, hera_load_result *out);
+/* Same, PAF text already in host memory (copied H2D inside) ... */
+int hera_graph_load_bytes(hera_ctx *ctx, const void *host_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out);
+/* ... or already resident in device memory (n bytes at a cudaMalloc'ed address; the library
+ * copies it device-to-device into its own padded buffer). */
+int hera_graph_load_device(hera_ctx *ctx, const void *device_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out);
+/* Drops all loaded overlaps (a fresh OverlapGraph). */
+int hera_graph_reset(hera_ctx *ctx);
+/* Node numbering (OverlapGraph::nodeIndex + node creation, src/OverlapGraph.cpp:208-218,251-258),
+ * adjacency lists (src/OverlapGraph.cpp:241-248) as CSR, per-metric rank permutations and
+ * canonical slots used by the greedy walks.  metrics_mask: bit m set = build ranks for metric m.
+ * May be called again after further loads. */
+int hera_graph_finalize(hera_ctx *ctx, uint32_t metrics_mask, hera_graph_info *out);
+/* nodes_ / edges_ / nodes_[i].edges as flat host arrays. */
+int hera_graph_export(hera_ctx *ctx, hera_graph_view *out);
+
+/* ---- PathManager ------------------------------------------------------------------------- */
+/* PathManager::buildMonteCarlo (src/PathManager.cpp:12-177).  Draws come from Philox4x32-10 with
+ * counter (anchor node, attempt, draw number, metric) and key = seed instead of one shared
+ * std::mt19937 stream, so walks are independent of execution order. */
+int hera_paths_monte_carlo(hera_ctx *ctx, int metric, const hera_path_params *pp, uint64_t seed, hera_walk_stats *out);
+/* PathManager::buildDeterministic (src/PathManager.cpp:179-430). */
+int hera_paths_deterministic(hera_ctx *ctx, int metric, hera_walk_stats *out);
+/* PathManager::filterUnique (src/PathManager.cpp:432-438). */
+int hera_paths_unique(hera_ctx *ctx, uint64_t *n_unique);
+/* Forget all paths (a fresh PathManager). */
+int hera_paths_reset(hera_ctx *ctx);
+int hera_paths_export(hera_ctx *ctx, hera_paths_view *out);
+
+/* getPathsBetweenAnchors + constructGroups + PathWindow + PathGroup::{discardNotFrequent,
+ * calculateConsensusPath, calculateValidPathNumber} + the inter-group pick
+ * (src/PathManager.cpp:508-645, src/PathWindow.cpp, src/PathGroup.cpp, src/Main.cpp:277-342). */
+int hera_groups(hera_ctx *ctx, const hera_path_params *pp, hera_groups_view *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

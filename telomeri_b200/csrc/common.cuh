@@ -1,0 +1,94 @@
+// Shared plumbing of the hera_b200 library: context, growable device/pinned buffers, error
+// handling, launch accounting.  Kernels live in the other .cu files of this directory.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "../../include/hera_b200.h"
+
+namespace hera {
+
+struct Error {
+    int code;
+    std::string msg;
+};
+
+#define HERA_CUDA(expr)                                                                                   \
+    do {                                                                                                  \
+        cudaError_t err__ = (expr);                                                                       \
+        if (err__ != cudaSuccess)                                                                         \
+            throw ::hera::Error{2, std::string(#expr) + ": " + cudaGetErrorString(err__) + " (" + __FILE__ + ":" + std::to_string(__LINE__) + ")"}; \
+    } while (0)
+
+#define HERA_REQUIRE(cond, code, text)                 \
+    do {                                               \
+        if (!(cond)) throw ::hera::Error{(code), (text)}; \
+    } while (0)
+
+// Growable device array.  grow() keeps the contents when asked to.
+template <typename T>
+struct DBuf {
+    T *p = nullptr;
+    size_t cap = 0;
+    ~DBuf() { release(); }
+    DBuf() = default;
+    DBuf(const DBuf &) = delete;
+    DBuf &operator=(const DBuf &) = delete;
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    void reserve(size_t n, bool keep = false, size_t keep_n = 0, cudaStream_t s = 0) {
+        if (n <= cap) return;
+        size_t ncap = n + n / 4 + 64;
+        T *np = nullptr;
+        HERA_CUDA(cudaMalloc(&np, ncap * sizeof(T)));
+        if (keep && p && keep_n) HERA_CUDA(cudaMemcpyAsync(np, p, keep_n * sizeof(T), cudaMemcpyDeviceToDevice, s));
+        if (p) {
+            HERA_CUDA(cudaStreamSynchronize(s));
+            cudaFree(p);
+        }
+        p = np;
+        cap = ncap;
+    }
+};
+
+// Growable pinned host array (export views point into these).
+template <typename T>
+struct HBuf {
+    T *p = nullptr;
+    size_t cap = 0;
+    ~HBuf() { if (p) cudaFreeHost(p); }
+    HBuf() = default;
+    HBuf(const HBuf &) = delete;
+    HBuf &operator=(const HBuf &) = delete;
+    void reserve(size_t n) {
+        if (n <= cap) return;
+        if (p) cudaFreeHost(p);
+        cap = n + n / 4 + 64;
+        HERA_CUDA(cudaMallocHost(&p, cap * sizeof(T)));
+    }
+};
+
+struct Launches {
+    uint64_t count = 0;
+};
+
+// Launch helper: counts the launch and checks the launch status.
+#define HERA_LAUNCH(ctx, kernel, grid, block, smem, ...)                      \
+    do {                                                                      \
+        kernel<<<(grid), (block), (smem), (ctx).stream>>>(__VA_ARGS__);       \
+        (ctx).launches.count++;                                               \
+        HERA_CUDA(cudaGetLastError());                                        \
+    } while (0)
+
+inline unsigned div_up(uint64_t a, uint64_t b) { return static_cast<unsigned>((a + b - 1) / b); }
+
+}  // namespace hera

@@ -1,0 +1,140 @@
+// Context of the hera_b200 library: every device-resident table of the hot path.
+#pragma once
+
+#include <memory>
+
+#include "common.cuh"
+
+namespace hera {
+
+// Bits of KeptTable::flags
+constexpr uint8_t KF_MINUS = 1;     // relative strand '-' (src/OverlapGraph.cpp:240)
+constexpr uint8_t KF_CR = 2;        // record came from the contig-read load (anchors == true)
+constexpr uint8_t KF_QCTG = 4;      // query name starts with "ctg" (case-insensitive), src/OverlapGraph.cpp:134
+
+// Name reference: which loaded text, byte offset, length.
+__host__ __device__ inline uint64_t pack_name(uint32_t file, uint64_t off, uint32_t len) {
+    return (static_cast<uint64_t>(file) << 60) | (off << 16) | (len & 0xffffu);
+}
+__host__ __device__ inline uint32_t name_file(uint64_t r) { return static_cast<uint32_t>(r >> 60); }
+__host__ __device__ inline uint64_t name_off(uint64_t r) { return (r >> 16) & ((1ull << 44) - 1); }
+__host__ __device__ inline uint32_t name_len(uint64_t r) { return static_cast<uint32_t>(r & 0xffffu); }
+
+// Overlaps that passed the filter, file order, rr load(s) first ("edges_" before node ids exist).
+struct KeptTable {
+    uint64_t n = 0;
+    DBuf<uint32_t> qs, qe, ts, te, qlen, tlen, rec;
+    DBuf<float> os, si, es;
+    DBuf<uint8_t> flags;
+    DBuf<uint64_t> qhash, thash, qname, tname;
+    void reserve(uint64_t total, cudaStream_t s) {
+        qs.reserve(total, true, n, s); qe.reserve(total, true, n, s); ts.reserve(total, true, n, s); te.reserve(total, true, n, s);
+        qlen.reserve(total, true, n, s); tlen.reserve(total, true, n, s); rec.reserve(total, true, n, s);
+        os.reserve(total, true, n, s); si.reserve(total, true, n, s); es.reserve(total, true, n, s);
+        flags.reserve(total, true, n, s);
+        qhash.reserve(total, true, n, s); thash.reserve(total, true, n, s); qname.reserve(total, true, n, s); tname.reserve(total, true, n, s);
+    }
+};
+
+// Raw pointers of KeptTable for kernels.
+struct KeptPtrs {
+    uint32_t *qs, *qe, *ts, *te, *qlen, *tlen, *rec;
+    float *os, *si, *es;
+    uint8_t *flags;
+    uint64_t *qhash, *thash, *qname, *tname;
+};
+
+struct LoadedText {
+    DBuf<uint8_t> bytes;  // padded with '\n' up to a multiple of the tile size plus one tile
+    uint64_t n = 0;
+};
+
+struct GraphTables {
+    bool ready = false;
+    uint64_t N = 0, anchors = 0, E = 0, S = 0;
+    DBuf<uint32_t> e_q, e_t;                 // node ids per kept overlap
+    DBuf<uint32_t> node_len;
+    DBuf<uint8_t> node_anchor;
+    DBuf<uint64_t> node_name;                // packed name reference of the first appearance
+    DBuf<uint32_t> adj_off;                  // N + 1
+    DBuf<uint32_t> adj_pay;                  // slot -> 2 * kept + side
+    // walk-facing structure of arrays
+    DBuf<uint32_t> a_nbr;                    // neighbour id, bit 31 = neighbour is an anchor
+    DBuf<float> a_es, a_os;
+    DBuf<int32_t> a_delta;                   // q_start - t_start of the slot (src/Path.cpp:13)
+    DBuf<uint32_t> rank[4];                  // per metric; empty if not built
+    bool rank_ready[4] = {false, false, false, false};
+    DBuf<uint32_t> canon;
+    DBuf<uint32_t> anchor_ids;               // anchor node ids in node order
+};
+
+struct PathStore {
+    uint64_t paths = 0, nodes = 0;
+    DBuf<uint64_t> off;      // paths + 1
+    DBuf<uint32_t> node, slot;
+    DBuf<int64_t> len;
+};
+
+struct Ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    Launches launches;
+    std::string err;
+    hera_filter_params fp{HERA_MODE_AVG, 0, 0.0f, UINT64_MAX, 1.0f};
+
+    std::vector<std::unique_ptr<LoadedText>> texts;
+    KeptTable kept;
+    GraphTables g;
+
+    PathStore all, uniq;
+    bool uniq_ready = false;
+    std::vector<uint32_t> call_kind, call_metric;
+    std::vector<uint64_t> call_found;
+    std::vector<uint32_t> mc_draws;  // host copy, canonical walk order
+
+    // scratch
+    DBuf<uint8_t> scratch_a, scratch_b, scratch_c, scratch_d;
+    DBuf<uint64_t> counters;     // small device counter block
+    HBuf<uint64_t> h_counters;
+
+    // export mirrors (pinned)
+    struct GraphMirror {
+        HBuf<uint32_t> node_len, e_q, e_t, e_qs, e_qe, e_ts, e_te, adj_rec, rank[4], canon;
+        HBuf<uint8_t> node_anchor, e_strand, adj_side;
+        HBuf<uint64_t> node_name_off, adj_off;
+        HBuf<char> node_names;
+        HBuf<float> e_os, e_si, e_es;
+    } gm;
+    struct PathMirror {
+        HBuf<uint64_t> off;
+        HBuf<uint32_t> nodes, slots;
+        HBuf<int64_t> len;
+    } pm;
+    struct GroupMirror {
+        std::vector<uint32_t> pair_a1, pair_a2, pair_sorted, grp_pair, grp_size0, grp_pig;
+        std::vector<uint64_t> pair_off, grp_pig_off;
+        std::vector<int64_t> grp_consensus, pair_consensus;
+        std::vector<int32_t> grp_valid;
+    } grm;
+};
+
+// ---- host-side helpers implemented in primitives.cu -----------------------------------------
+// out[i] = sum of in[0..i), all on device; returns nothing, *d_total (device, may be null) gets the sum.
+void exclusive_scan_u32(Ctx &c, const uint32_t *in, uint64_t n, uint32_t *out, uint32_t *d_total);
+void exclusive_scan_u8_to_u32(Ctx &c, const uint8_t *in, uint64_t n, uint32_t *out, uint32_t *d_total);
+void exclusive_scan_u32_to_u64(Ctx &c, const uint32_t *in, uint64_t n, uint64_t *out, uint64_t *d_total);
+// Stable sort of (key, value) by the low `bits` bits of key.  Result ends up in keys/vals (the
+// alt buffers are scratch of the same size).
+void radix_sort_pairs(Ctx &c, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt, uint32_t *vals_alt, uint64_t n, int bits);
+
+// ---- stages ------------------------------------------------------------------------------
+void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, hera_load_result *out);
+void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out);
+void export_graph(Ctx &c, hera_graph_view *out);
+void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);
+void walk_deterministic(Ctx &c, int metric, hera_walk_stats *out);
+void unique_paths(Ctx &c, uint64_t *n_unique);
+void export_paths(Ctx &c, hera_paths_view *out);
+void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out);
+
+}  // namespace hera

@@ -1,0 +1,395 @@
+// K3 + K4: node interning, CSR adjacency, per-metric rank permutations, canonical slots.
+//
+// K3 replaces OverlapGraph::nodeIndex and the node creation in buildFrom (reference
+// src/OverlapGraph.cpp:208-218, 251-258): node id = rank of the name's first appearance among
+// kept records (query before target, rr load before cr load).  Names are interned through an
+// open-addressing table keyed by the 64-bit name hash; every occurrence does an atomicMin of its
+// position; positions that equal the table minimum are first appearances, and an exclusive scan
+// over those flags is the node id.  A verification pass compares every occurrence's bytes with
+// its node's name, so a 64-bit hash collision is detected, never silently merged.
+//
+// K4 replaces the adjacency pushes (src/OverlapGraph.cpp:241-248): each kept overlap e yields
+// entry 2e (owner = target, stored as read) and 2e+1 (owner = query, q/t swapped).  A stable LSD
+// radix sort by owner keeps record order inside each node's list, which is the reference's
+// insertion order.  Rank permutations restate the per-step stable_sort of the greedy walk
+// (src/PathManager.cpp:289-296); canon[] its first-parallel-edge lookup (:340-347).
+#include "ctx.cuh"
+#include "primitives.cuh"
+
+namespace hera {
+
+struct TextPtrs {
+    const uint8_t *p[16];
+};
+
+__global__ void intern_insert_kernel(uint64_t occ, const uint64_t *__restrict__ qhash, const uint64_t *__restrict__ thash,
+                                     unsigned long long *keys, uint32_t *minpos, uint64_t mask, uint32_t *__restrict__ occ_slot,
+                                     unsigned int *distinct, unsigned int *overflow) {
+    const uint64_t pos = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (pos >= occ) return;
+    const uint64_t e = pos >> 1;
+    const unsigned long long h = (pos & 1) ? thash[e] : qhash[e];
+    uint64_t slot = h & mask;
+    for (uint64_t probes = 0; probes <= mask; probes++) {
+        unsigned long long cur = keys[slot];
+        if (cur == 0) {
+            cur = atomicCAS(&keys[slot], 0ull, h);
+            if (cur == 0) { atomicAdd(distinct, 1u); cur = h; }
+        }
+        if (cur == h) {
+            atomicMin(&minpos[slot], static_cast<uint32_t>(pos));
+            occ_slot[pos] = static_cast<uint32_t>(slot);
+            return;
+        }
+        slot = (slot + 1) & mask;
+    }
+    *overflow = 1;
+}
+
+__global__ void intern_first_flags_kernel(uint64_t occ, const uint32_t *__restrict__ occ_slot, const uint32_t *__restrict__ minpos, uint8_t *__restrict__ first) {
+    const uint64_t pos = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (pos >= occ) return;
+    first[pos] = minpos[occ_slot[pos]] == pos ? 1 : 0;
+}
+
+// First appearances create the node: length and anchor flag of THAT record (src/OverlapGraph.cpp:209-218).
+__global__ void intern_create_nodes_kernel(uint64_t occ, const uint8_t *__restrict__ first, const uint32_t *__restrict__ first_scan,
+                                           const uint32_t *__restrict__ occ_slot, uint32_t *__restrict__ slot_id, const uint32_t *__restrict__ qlen,
+                                           const uint32_t *__restrict__ tlen, const uint8_t *__restrict__ flags, const uint64_t *__restrict__ qname,
+                                           const uint64_t *__restrict__ tname, uint32_t *__restrict__ node_len, uint8_t *__restrict__ node_anchor,
+                                           uint64_t *__restrict__ node_name) {
+    const uint64_t pos = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (pos >= occ || !first[pos]) return;
+    const uint64_t e = pos >> 1;
+    const uint32_t id = first_scan[pos];
+    slot_id[occ_slot[pos]] = id;
+    const uint8_t f = flags[e];
+    const bool cr = f & KF_CR, qctg = f & KF_QCTG;
+    if (pos & 1) {
+        node_len[id] = tlen[e];
+        node_anchor[id] = (cr && !qctg) ? 1 : 0;   // ContigPosition::TARGET
+        node_name[id] = tname[e];
+    } else {
+        node_len[id] = qlen[e];
+        node_anchor[id] = (cr && qctg) ? 1 : 0;    // ContigPosition::QUERY
+        node_name[id] = qname[e];
+    }
+}
+
+__global__ void intern_assign_kernel(uint64_t E, const uint32_t *__restrict__ occ_slot, const uint32_t *__restrict__ slot_id, uint32_t *__restrict__ e_q,
+                                     uint32_t *__restrict__ e_t, const uint64_t *__restrict__ qname, const uint64_t *__restrict__ tname,
+                                     const uint64_t *__restrict__ node_name, TextPtrs texts, unsigned int *collision) {
+    const uint64_t e = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    const uint32_t q = slot_id[occ_slot[2 * e]], t = slot_id[occ_slot[2 * e + 1]];
+    e_q[e] = q;
+    e_t[e] = t;
+    // verification: same bytes as the node's name
+    const uint64_t mine[2] = {qname[e], tname[e]};
+    const uint32_t ids[2] = {q, t};
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+        const uint64_t ref = node_name[ids[s]];
+        if (ref == mine[s]) continue;
+        bool same = name_len(ref) == name_len(mine[s]);
+        if (same) {
+            const uint8_t *a = texts.p[name_file(ref)] + name_off(ref);
+            const uint8_t *b = texts.p[name_file(mine[s])] + name_off(mine[s]);
+            for (uint32_t i = 0; i < name_len(ref); i++) if (a[i] != b[i]) { same = false; break; }
+        }
+        if (!same) *collision = 1;
+    }
+}
+
+__global__ void csr_entries_kernel(uint64_t E, const uint32_t *__restrict__ e_q, const uint32_t *__restrict__ e_t, uint32_t *__restrict__ keys,
+                                   uint32_t *__restrict__ vals) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= 2 * E) return;
+    const uint64_t e = i >> 1;
+    keys[i] = (i & 1) ? e_q[e] : e_t[e];
+    vals[i] = static_cast<uint32_t>(i);
+}
+
+__global__ void csr_offsets_kernel(uint64_t S, uint64_t N, const uint32_t *__restrict__ keys, uint32_t *__restrict__ off) {
+    const uint64_t s = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (s > S) return;
+    if (s == S) { off[N] = static_cast<uint32_t>(S); return; }
+    if (s == 0 || keys[s] != keys[s - 1]) off[keys[s]] = static_cast<uint32_t>(s);
+}
+
+__global__ void csr_gather_kernel(uint64_t S, const uint32_t *__restrict__ pay, const uint32_t *__restrict__ e_q, const uint32_t *__restrict__ e_t,
+                                  const uint32_t *__restrict__ qs, const uint32_t *__restrict__ ts, const float *__restrict__ es,
+                                  const float *__restrict__ os, const uint8_t *__restrict__ node_anchor, uint32_t *__restrict__ a_nbr,
+                                  float *__restrict__ a_es, float *__restrict__ a_os, int32_t *__restrict__ a_delta) {
+    const uint64_t s = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    const uint32_t p = pay[s], e = p >> 1, side = p & 1;
+    const uint32_t nbr = side ? e_t[e] : e_q[e];
+    a_nbr[s] = nbr | (node_anchor[nbr] ? 0x80000000u : 0u);
+    a_es[s] = es[e];
+    a_os[s] = os[e];
+    const int64_t d = side ? static_cast<int64_t>(ts[e]) - static_cast<int64_t>(qs[e]) : static_cast<int64_t>(qs[e]) - static_cast<int64_t>(ts[e]);
+    a_delta[s] = static_cast<int32_t>(d);
+}
+
+__global__ void anchor_list_kernel(uint64_t N, const uint8_t *__restrict__ node_anchor, const uint32_t *__restrict__ anchor_scan, uint32_t *__restrict__ anchor_ids) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < N && node_anchor[i]) anchor_ids[anchor_scan[i]] = static_cast<uint32_t>(i);
+}
+
+// One CTA per node.  rank by counting: position of slot i in the stable descending order =
+// #{j : m[j] > m[i]} + #{j < i : m[j] == m[i]}.  Values are staged in shared memory when the
+// list fits; longer lists are read through L1/L2.
+constexpr int RK_THREADS = 128;
+constexpr int RK_SMEM = 4096;
+
+__device__ __forceinline__ float metric_value(int metric, float es, float os) {
+    switch (metric) {
+        case HERA_EXTENSION_SCORE: return es;
+        case HERA_OVERLAP_SCORE: return os;
+        case HERA_EXTENSION_SCORE_SQRT: return __fsqrt_rn(es);
+        default: return __fsqrt_rn(os);
+    }
+}
+
+__global__ void __launch_bounds__(RK_THREADS) rank_kernel(const uint32_t *__restrict__ off, const float *__restrict__ a_es, const float *__restrict__ a_os,
+                                                          int metric, uint32_t *__restrict__ rank) {
+    __shared__ float sm[RK_SMEM];
+    const uint32_t x = blockIdx.x;
+    const uint32_t base = off[x], deg = off[x + 1] - base;
+    const bool staged = deg <= RK_SMEM;
+    if (staged) {
+        for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) sm[i] = metric_value(metric, a_es[base + i], a_os[base + i]);
+        __syncthreads();
+    }
+    for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) {
+        const float mi = staged ? sm[i] : metric_value(metric, a_es[base + i], a_os[base + i]);
+        uint32_t r = 0;
+        if (staged) {
+            for (uint32_t j = 0; j < deg; j++) { const float mj = sm[j]; r += (mj > mi) || (mj == mi && j < i); }
+        } else {
+            for (uint32_t j = 0; j < deg; j++) { const float mj = metric_value(metric, a_es[base + j], a_os[base + j]); r += (mj > mi) || (mj == mi && j < i); }
+        }
+        rank[base + r] = base + i;
+    }
+}
+
+__global__ void __launch_bounds__(RK_THREADS) canon_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr, uint32_t *__restrict__ canon) {
+    __shared__ uint32_t sm[RK_SMEM];
+    const uint32_t x = blockIdx.x;
+    const uint32_t base = off[x], deg = off[x + 1] - base;
+    const bool staged = deg <= RK_SMEM;
+    if (staged) {
+        for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) sm[i] = a_nbr[base + i];
+        __syncthreads();
+    }
+    for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) {
+        const uint32_t ni = staged ? sm[i] : a_nbr[base + i];
+        uint32_t j = 0;
+        if (staged) { while (sm[j] != ni) j++; } else { while (a_nbr[base + j] != ni) j++; }
+        canon[base + i] = base + j;
+    }
+}
+
+static int bits_for(uint64_t n) {
+    int b = 1;
+    while ((1ull << b) < n) b++;
+    return b;
+}
+
+void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
+    GraphTables &g = c.g;
+    const uint64_t E = c.kept.n, occ = 2 * E;
+    HERA_REQUIRE(occ < (1ull << 32), 4, "too many kept overlaps for 32-bit slots");
+    cudaEvent_t ev[4];
+    for (auto &e : ev) HERA_CUDA(cudaEventCreate(&e));
+    HERA_CUDA(cudaEventRecord(ev[0], c.stream));
+    g.ready = false;
+    g.E = E; g.S = occ; g.N = 0; g.anchors = 0;
+    for (bool &r : g.rank_ready) r = false;
+    float intern_ms = 0, csr_ms = 0, rank_ms = 0;
+    if (E > 0) {
+        // ---- K3
+        uint32_t *occ_slot = nullptr, *first_scan = nullptr, *d_small = nullptr;
+        uint8_t *first = nullptr;
+        HERA_CUDA(cudaMallocAsync(&occ_slot, occ * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&first_scan, occ * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&first, occ, c.stream));
+        HERA_CUDA(cudaMallocAsync(&d_small, 8 * sizeof(uint32_t), c.stream));
+        uint64_t cap = 1024;
+        while (cap < 4 * E && cap < (1ull << 22)) cap <<= 1;
+        unsigned long long *keys = nullptr;
+        uint32_t *minpos = nullptr, *slot_id = nullptr;
+        uint32_t h_small[8];
+        for (;;) {
+            HERA_CUDA(cudaMallocAsync(&keys, cap * sizeof(unsigned long long), c.stream));
+            HERA_CUDA(cudaMallocAsync(&minpos, cap * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMemsetAsync(keys, 0, cap * sizeof(unsigned long long), c.stream));
+            HERA_CUDA(cudaMemsetAsync(minpos, 0xff, cap * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMemsetAsync(d_small, 0, 8 * sizeof(uint32_t), c.stream));
+            HERA_LAUNCH(c, intern_insert_kernel, div_up(occ, 256), 256, 0, occ, c.kept.qhash.p, c.kept.thash.p, keys, minpos, cap - 1, occ_slot, d_small, d_small + 1);
+            HERA_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            if (!h_small[1] && static_cast<uint64_t>(h_small[0]) * 2 <= cap) break;
+            HERA_CUDA(cudaFreeAsync(keys, c.stream));
+            HERA_CUDA(cudaFreeAsync(minpos, c.stream));
+            cap <<= 2;  // table too full: probe chains get long, rebuild four times larger
+        }
+        const uint64_t N = h_small[0];
+        g.N = N;
+        HERA_CUDA(cudaMallocAsync(&slot_id, cap * sizeof(uint32_t), c.stream));
+        HERA_LAUNCH(c, intern_first_flags_kernel, div_up(occ, 256), 256, 0, occ, occ_slot, minpos, first);
+        exclusive_scan_u8_to_u32(c, first, occ, first_scan, nullptr);
+        g.node_len.reserve(N); g.node_anchor.reserve(N); g.node_name.reserve(N);
+        g.e_q.reserve(E); g.e_t.reserve(E);
+        HERA_LAUNCH(c, intern_create_nodes_kernel, div_up(occ, 256), 256, 0, occ, first, first_scan, occ_slot, slot_id, c.kept.qlen.p, c.kept.tlen.p,
+                    c.kept.flags.p, c.kept.qname.p, c.kept.tname.p, g.node_len.p, g.node_anchor.p, g.node_name.p);
+        TextPtrs tp{};
+        HERA_REQUIRE(c.texts.size() <= 16, 5, "more than 16 loads per graph are not supported");
+        for (size_t i = 0; i < c.texts.size(); i++) tp.p[i] = c.texts[i]->bytes.p;
+        HERA_LAUNCH(c, intern_assign_kernel, div_up(E, 256), 256, 0, E, occ_slot, slot_id, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p, g.node_name.p, tp, d_small + 2);
+        // anchors in node order
+        uint32_t *anchor_scan = nullptr;
+        HERA_CUDA(cudaMallocAsync(&anchor_scan, N * sizeof(uint32_t), c.stream));
+        exclusive_scan_u8_to_u32(c, g.node_anchor.p, N, anchor_scan, d_small + 3);
+        HERA_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        HERA_REQUIRE(!h_small[2], 6, "64-bit name hash collision detected while interning node names");
+        g.anchors = h_small[3];
+        g.anchor_ids.reserve(g.anchors + 1);
+        HERA_LAUNCH(c, anchor_list_kernel, div_up(N, 256), 256, 0, N, g.node_anchor.p, anchor_scan, g.anchor_ids.p);
+        HERA_CUDA(cudaFreeAsync(anchor_scan, c.stream));
+        HERA_CUDA(cudaFreeAsync(keys, c.stream)); HERA_CUDA(cudaFreeAsync(minpos, c.stream)); HERA_CUDA(cudaFreeAsync(slot_id, c.stream));
+        HERA_CUDA(cudaFreeAsync(occ_slot, c.stream)); HERA_CUDA(cudaFreeAsync(first_scan, c.stream)); HERA_CUDA(cudaFreeAsync(first, c.stream));
+        HERA_CUDA(cudaFreeAsync(d_small, c.stream));
+        HERA_CUDA(cudaEventRecord(ev[1], c.stream));
+
+        // ---- K4
+        uint32_t *keys32 = nullptr, *keys_alt = nullptr, *vals_alt = nullptr;
+        HERA_CUDA(cudaMallocAsync(&keys32, occ * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&keys_alt, occ * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&vals_alt, occ * sizeof(uint32_t), c.stream));
+        g.adj_pay.reserve(occ); g.adj_off.reserve(N + 1);
+        g.a_nbr.reserve(occ); g.a_es.reserve(occ); g.a_os.reserve(occ); g.a_delta.reserve(occ); g.canon.reserve(occ);
+        HERA_LAUNCH(c, csr_entries_kernel, div_up(occ, 256), 256, 0, E, g.e_q.p, g.e_t.p, keys32, g.adj_pay.p);
+        radix_sort_pairs(c, keys32, g.adj_pay.p, keys_alt, vals_alt, occ, bits_for(N));
+        HERA_LAUNCH(c, csr_offsets_kernel, div_up(occ + 1, 256), 256, 0, occ, N, keys32, g.adj_off.p);
+        HERA_LAUNCH(c, csr_gather_kernel, div_up(occ, 256), 256, 0, occ, g.adj_pay.p, g.e_q.p, g.e_t.p, c.kept.qs.p, c.kept.ts.p, c.kept.es.p, c.kept.os.p,
+                    g.node_anchor.p, g.a_nbr.p, g.a_es.p, g.a_os.p, g.a_delta.p);
+        HERA_CUDA(cudaFreeAsync(keys32, c.stream)); HERA_CUDA(cudaFreeAsync(keys_alt, c.stream)); HERA_CUDA(cudaFreeAsync(vals_alt, c.stream));
+        HERA_CUDA(cudaEventRecord(ev[2], c.stream));
+
+        // ---- rank permutations + canonical slots
+        HERA_LAUNCH(c, canon_kernel, static_cast<unsigned>(N), RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.canon.p);
+        for (int m = 0; m < 4; m++) {
+            if (!(metrics_mask & (1u << m))) continue;
+            g.rank[m].reserve(occ);
+            HERA_LAUNCH(c, rank_kernel, static_cast<unsigned>(N), RK_THREADS, 0, g.adj_off.p, g.a_es.p, g.a_os.p, m, g.rank[m].p);
+            g.rank_ready[m] = true;
+        }
+        HERA_CUDA(cudaEventRecord(ev[3], c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        HERA_CUDA(cudaEventElapsedTime(&intern_ms, ev[0], ev[1]));
+        HERA_CUDA(cudaEventElapsedTime(&csr_ms, ev[1], ev[2]));
+        HERA_CUDA(cudaEventElapsedTime(&rank_ms, ev[2], ev[3]));
+    }
+    g.ready = true;
+    for (auto &e : ev) cudaEventDestroy(e);
+    if (out) {
+        out->nodes = g.N; out->anchors = g.anchors; out->edges = g.E; out->slots = g.S;
+        out->intern_ms = intern_ms; out->csr_ms = csr_ms; out->rank_ms = rank_ms;
+    }
+}
+
+// ---- export ---------------------------------------------------------------------------------
+__global__ void name_len_kernel(uint64_t N, const uint64_t *__restrict__ node_name, uint32_t *__restrict__ lens) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < N) lens[i] = name_len(node_name[i]);
+}
+
+__global__ void name_copy_kernel(uint64_t N, const uint64_t *__restrict__ node_name, const uint64_t *__restrict__ offs, TextPtrs texts, char *__restrict__ blob) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const uint64_t r = node_name[i];
+    const uint8_t *src = texts.p[name_file(r)] + name_off(r);
+    char *dst = blob + offs[i];
+    for (uint32_t k = 0; k < name_len(r); k++) dst[k] = static_cast<char>(src[k]);
+}
+
+__global__ void export_adj_kernel(uint64_t S, const uint32_t *__restrict__ pay, uint32_t *__restrict__ rec, uint8_t *__restrict__ side) {
+    const uint64_t s = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (s < S) { rec[s] = pay[s] >> 1; side[s] = pay[s] & 1; }
+}
+
+__global__ void export_strand_kernel(uint64_t E, const uint8_t *__restrict__ flags, uint8_t *__restrict__ strand) {
+    const uint64_t e = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (e < E) strand[e] = (flags[e] & KF_MINUS) ? 1 : 0;
+}
+
+__global__ void widen_kernel(uint64_t n, const uint32_t *__restrict__ in, uint64_t *__restrict__ out) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i];
+}
+
+template <typename T>
+static void d2h(Ctx &c, HBuf<T> &dst, const T *src, uint64_t n) {
+    dst.reserve(n + 1);
+    if (n) HERA_CUDA(cudaMemcpyAsync(dst.p, src, n * sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+}
+
+void export_graph(Ctx &c, hera_graph_view *out) {
+    GraphTables &g = c.g;
+    HERA_REQUIRE(g.ready, 7, "hera_graph_export: call hera_graph_finalize first");
+    const uint64_t N = g.N, E = g.E, S = g.S;
+    auto &m = c.gm;
+    *out = hera_graph_view{};
+    out->nodes = N; out->edges = E; out->slots = S;
+    m.node_name_off.reserve(N + 1); m.adj_off.reserve(N + 1); m.node_names.reserve(1);
+    m.node_name_off.p[0] = 0; m.adj_off.p[0] = 0;
+    if (E > 0) {
+        d2h(c, m.node_len, g.node_len.p, N);
+        d2h(c, m.node_anchor, g.node_anchor.p, N);
+        // names
+        uint32_t *lens = nullptr; uint64_t *offs = nullptr; char *blob = nullptr; uint8_t *tmp8 = nullptr; uint32_t *tmp32 = nullptr;
+        HERA_CUDA(cudaMallocAsync(&lens, (N + 1) * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&offs, (N + 1) * sizeof(uint64_t), c.stream));
+        HERA_LAUNCH(c, name_len_kernel, div_up(N, 256), 256, 0, N, g.node_name.p, lens);
+        exclusive_scan_u32_to_u64(c, lens, N, offs, offs + N);
+        uint64_t blob_bytes = 0;
+        HERA_CUDA(cudaMemcpyAsync(&blob_bytes, offs + N, sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        HERA_CUDA(cudaMallocAsync(&blob, blob_bytes + 1, c.stream));
+        TextPtrs tp{};
+        for (size_t i = 0; i < c.texts.size(); i++) tp.p[i] = c.texts[i]->bytes.p;
+        HERA_LAUNCH(c, name_copy_kernel, div_up(N, 256), 256, 0, N, g.node_name.p, offs, tp, blob);
+        d2h(c, m.node_name_off, offs, N + 1);
+        m.node_names.reserve(blob_bytes + 1);
+        HERA_CUDA(cudaMemcpyAsync(m.node_names.p, blob, blob_bytes, cudaMemcpyDeviceToHost, c.stream));
+        // edges
+        d2h(c, m.e_q, g.e_q.p, E); d2h(c, m.e_t, g.e_t.p, E);
+        d2h(c, m.e_qs, c.kept.qs.p, E); d2h(c, m.e_qe, c.kept.qe.p, E); d2h(c, m.e_ts, c.kept.ts.p, E); d2h(c, m.e_te, c.kept.te.p, E);
+        d2h(c, m.e_os, c.kept.os.p, E); d2h(c, m.e_si, c.kept.si.p, E); d2h(c, m.e_es, c.kept.es.p, E);
+        HERA_CUDA(cudaMallocAsync(&tmp8, S + 1, c.stream));
+        HERA_CUDA(cudaMallocAsync(&tmp32, (S + 1) * sizeof(uint32_t), c.stream));
+        HERA_LAUNCH(c, export_strand_kernel, div_up(E, 256), 256, 0, E, c.kept.flags.p, tmp8);
+        d2h(c, m.e_strand, tmp8, E);
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        HERA_LAUNCH(c, export_adj_kernel, div_up(S, 256), 256, 0, S, g.adj_pay.p, tmp32, tmp8);
+        d2h(c, m.adj_rec, tmp32, S); d2h(c, m.adj_side, tmp8, S);
+        HERA_LAUNCH(c, widen_kernel, div_up(N + 1, 256), 256, 0, N + 1, g.adj_off.p, offs);
+        d2h(c, m.adj_off, offs, N + 1);
+        d2h(c, m.canon, g.canon.p, S);
+        for (int k = 0; k < 4; k++) if (g.rank_ready[k]) d2h(c, m.rank[k], g.rank[k].p, S);
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        HERA_CUDA(cudaFreeAsync(lens, c.stream)); HERA_CUDA(cudaFreeAsync(offs, c.stream)); HERA_CUDA(cudaFreeAsync(blob, c.stream));
+        HERA_CUDA(cudaFreeAsync(tmp8, c.stream)); HERA_CUDA(cudaFreeAsync(tmp32, c.stream));
+    }
+    out->node_len = m.node_len.p; out->node_anchor = m.node_anchor.p; out->node_name_off = m.node_name_off.p; out->node_names = m.node_names.p;
+    out->e_q = m.e_q.p; out->e_t = m.e_t.p; out->e_qs = m.e_qs.p; out->e_qe = m.e_qe.p; out->e_ts = m.e_ts.p; out->e_te = m.e_te.p;
+    out->e_os = m.e_os.p; out->e_si = m.e_si.p; out->e_es = m.e_es.p; out->e_strand = m.e_strand.p;
+    out->adj_off = m.adj_off.p; out->adj_rec = m.adj_rec.p; out->adj_side = m.adj_side.p; out->canon = m.canon.p;
+    out->rank_es = g.rank_ready[0] ? m.rank[0].p : nullptr; out->rank_os = g.rank_ready[1] ? m.rank[1].p : nullptr;
+    out->rank_es_sqrt = g.rank_ready[2] ? m.rank[2].p : nullptr; out->rank_os_sqrt = g.rank_ready[3] ? m.rank[3].p : nullptr;
+}
+
+}  // namespace hera

@@ -1,0 +1,579 @@
+// K5 + K6: path search, one warp per walk.
+//
+// K5 replaces PathManager::buildMonteCarlo (reference src/PathManager.cpp:12-177): from every
+// anchor, rebuild_attempts roulette walks.  The reference shares one std::mt19937 stream over
+// all walks; here draw number k of walk (anchor, attempt) is Philox4x32-10 with counter
+// (anchor node id, attempt, k, metric) and key = seed, turned into [0,1) the way libstdc++'s
+// generate_canonical does, so a walk does not depend on any other walk.
+// K6 replaces PathManager::buildDeterministic (src/PathManager.cpp:179-430): one walk per
+// (anchor, first edge), greedy by the precomputed rank permutation.
+//
+// The 32 lanes of a warp stream the current node's CSR slice (neighbour ids with the anchor flag
+// in bit 31, fp32 metric) and probe the walk's visited bitmap.  The roulette needs the fp64 sum
+// of the candidate metrics in list order (src/PathManager.cpp:50-66,104-114).  A warp reduction
+// associates differently, so it is used only when every partial sum is provably exact (all
+// addends non-negative finite multiples of 2^k and the total below 2^(k+53)): then any order
+// gives the sequential result bit for bit.  Otherwise the warp accumulates in list order.
+#include "ctx.cuh"
+#include "primitives.cuh"
+
+namespace hera {
+
+constexpr int WK_THREADS = 128;
+constexpr int WK_WARPS = WK_THREADS / 32;
+constexpr int WK_CACHE = 512;   // candidates cached in shared memory per warp between the two roulette passes
+
+struct WalkGraph {
+    const uint32_t *off, *nbr, *canon, *rank, *node_len, *anchor_ids;
+    const float *metric;      // a_es or a_os
+    const int32_t *delta;
+    uint32_t N, anchors;
+    int sqrt_metric;
+};
+
+struct WalkScratch {
+    uint32_t *bitmap;     // warps * words
+    uint32_t *nodes, *slots, *vlog;   // warps * cap
+    uint32_t words, cap;
+};
+
+struct WalkOut {
+    // per walk
+    uint32_t *res_n;       // nodes of the accepted path, 0 = none
+    uint64_t *res_off;     // offset into the pool
+    int64_t *res_len;
+    uint32_t *res_draws;
+    // pool
+    uint32_t *pool_nodes, *pool_slots;
+    unsigned long long pool_cap;
+    unsigned long long *pool_used;    // also keeps counting past the capacity
+    unsigned long long *steps;        // adjacency entries examined
+    unsigned int *next_walk;
+};
+
+__device__ __forceinline__ void philox_round(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t k0, uint32_t k1) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+}
+
+__device__ __forceinline__ double mc_draw(uint64_t seed, uint32_t metric, uint32_t anchor, uint32_t attempt, uint32_t draw) {
+    uint32_t c0 = anchor, c1 = attempt, c2 = draw, c3 = metric;
+    uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        philox_round(c0, c1, c2, c3, k0, k1);
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    // generate_canonical<double,53> over a 32-bit engine: (x0 + x1 * 2^32) / 2^64, one rounding in the sum
+    const double sum = __dadd_rn(__uint2double_rn(c0), __dmul_rn(__uint2double_rn(c1), 4294967296.0));
+    double u = __dmul_rn(sum, 5.42101086242752217e-20);  // exact: 2^-64
+    if (u >= 1.0) u = 0.99999999999999988897769753748434595763683319091796875;
+    return u;
+}
+
+__device__ __forceinline__ float walk_metric(const WalkGraph &g, uint32_t s) {
+    const float v = g.metric[s];
+    return g.sqrt_metric ? __fsqrt_rn(v) : v;
+}
+
+__device__ __forceinline__ bool bit_get(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1u; }
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v = __dadd_rn(v, __shfl_xor_sync(0xffffffffu, v, d));
+    return v;
+}
+
+__device__ __forceinline__ void emit_path(const WalkOut &o, uint32_t walk, const uint32_t *nodes, const uint32_t *slots, uint32_t n_nodes, int64_t len) {
+    const uint32_t lane = lane_id();
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(o.pool_used, static_cast<unsigned long long>(n_nodes));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (lane == 0) { o.res_n[walk] = n_nodes; o.res_off[walk] = base; o.res_len[walk] = len; }
+    if (base + n_nodes <= o.pool_cap) {
+        for (uint32_t i = lane; i < n_nodes; i += 32) o.pool_nodes[base + i] = nodes[i];
+        for (uint32_t i = lane; i + 1 < n_nodes; i += 32) o.pool_slots[base + i] = slots[i];
+    }
+}
+
+__device__ __forceinline__ void clear_visited(uint32_t *bm, uint32_t words, const uint32_t *vlog, uint32_t nlog) {
+    const uint32_t lane = lane_id();
+    if (nlog * 4u < words) {
+        for (uint32_t i = lane; i < nlog; i += 32) bm[vlog[i] >> 5] = 0;
+    } else {
+        for (uint32_t i = lane; i < words; i += 32) bm[i] = 0;
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkScratch sc, WalkOut o, uint32_t total_walks, uint32_t attempts,
+                                                             int backtrack_attempts, long long len_threshold, uint64_t seed, uint32_t metric_id) {
+    __shared__ uint32_t s_cslot[WK_WARPS][WK_CACHE];
+    __shared__ float s_cval[WK_WARPS][WK_CACHE];
+    const uint32_t lane = lane_id(), wib = warp_id();
+    const uint32_t wslot = blockIdx.x * WK_WARPS + wib;
+    uint32_t *bm = sc.bitmap + static_cast<uint64_t>(wslot) * sc.words;
+    uint32_t *nodes = sc.nodes + static_cast<uint64_t>(wslot) * sc.cap;
+    uint32_t *slots = sc.slots + static_cast<uint64_t>(wslot) * sc.cap;
+    uint32_t *vlog = sc.vlog + static_cast<uint64_t>(wslot) * sc.cap;
+    unsigned long long examined = 0;
+
+    for (;;) {
+        uint32_t walk = 0;
+        if (lane == 0) walk = atomicAdd(o.next_walk, 1u);
+        walk = __shfl_sync(0xffffffffu, walk, 0);
+        if (walk >= total_walks) break;
+        const uint32_t start = g.anchor_ids[walk / attempts], attempt = walk % attempts;
+
+        uint32_t n_nodes = 1, nlog = 1, draws = 0;
+        int backtracks = 0;
+        long long sum_all = g.node_len[start];   // first node's length + every edge delta on the path
+        uint32_t cur = start;
+        bool accepted = false;
+        if (lane == 0) { nodes[0] = start; vlog[0] = start; bm[start >> 5] |= 1u << (start & 31); }
+        __syncwarp();
+
+        for (;;) {
+            const uint32_t base = g.off[cur], deg = g.off[cur + 1] - base;
+            // ---- pass 1: forced anchor edge, candidate set, exactness bookkeeping (src/PathManager.cpp:53-67)
+            int forced = -1;
+            double part = 0.0;
+            uint32_t ncand = 0;
+            int min_exp = 1 << 20;
+            bool weird = false;
+            for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
+                const uint32_t k = c0 + lane;
+                const bool valid = k < deg;
+                const uint32_t nbw = valid ? g.nbr[base + k] : 0u;
+                const uint32_t nb = nbw & 0x7fffffffu;
+                const bool force = valid && (nbw >> 31) && nb != start;
+                const uint32_t fb = __ballot_sync(0xffffffffu, force);
+                if (fb) { forced = static_cast<int>(c0) + __ffs(fb) - 1; break; }
+                const bool cand = valid && !bit_get(bm, nb);
+                const uint32_t cb = __ballot_sync(0xffffffffu, cand);
+                if (cand) {
+                    const float v = walk_metric(g, base + k);
+                    const uint32_t bits = __float_as_uint(v);
+                    const uint32_t ex = (bits >> 23) & 0xffu;
+                    if ((bits >> 31) || ex == 0xffu) weird = true;                 // negative, inf, nan
+                    else if (bits != 0) min_exp = min(min_exp, static_cast<int>(ex ? ex : 1u) - 150);  // exponent of the lowest mantissa bit
+                    part = __dadd_rn(part, static_cast<double>(v));
+                    const uint32_t idx = ncand + __popc(cb & ((1u << lane) - 1u));
+                    if (idx < WK_CACHE) { s_cslot[wib][idx] = k; s_cval[wib][idx] = v; }
+                }
+                ncand += __popc(cb);
+            }
+            examined += deg;
+            int pick = -1;
+            if (forced >= 0) {
+                pick = forced;
+            } else if (ncand == 0) {
+                // ---- dead end: backtrack (src/PathManager.cpp:72-101)
+                if (backtracks < backtrack_attempts && n_nodes > 2) {
+                    bool open = false;
+                    do {
+                        n_nodes--;
+                        sum_all -= g.delta[slots[n_nodes - 1]];
+                        const uint32_t back = nodes[n_nodes - 1];
+                        const uint32_t bb = g.off[back], bd = g.off[back + 1] - bb;
+                        for (uint32_t c0 = 0; c0 < bd && !open; c0 += 32) {
+                            const uint32_t k = c0 + lane;
+                            const bool un = k < bd && !bit_get(bm, g.nbr[bb + k] & 0x7fffffffu);
+                            open = __any_sync(0xffffffffu, un);
+                        }
+                        examined += bd;
+                    } while (n_nodes > 1 && !open);
+                    if (n_nodes == 1) break;
+                    backtracks++;
+                    cur = nodes[n_nodes - 1];
+                    continue;
+                }
+                break;
+            } else {
+                // ---- roulette (src/PathManager.cpp:102-115)
+                __syncwarp();
+                const double u = mc_draw(seed, metric_id, start, attempt, draws);
+                draws++;
+                const uint32_t weird_any = __any_sync(0xffffffffu, weird);
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) min_exp = min(min_exp, __shfl_xor_sync(0xffffffffu, min_exp, d));
+                double total = warp_sum(part);
+                // exact in any order?  total < 2^(min_exp + 53)
+                bool exact = !weird_any;
+                if (exact && total > 0.0) {
+                    const int total_exp = static_cast<int>((__double_as_longlong(total) >> 52) & 0x7ff) - 1023;
+                    exact = total_exp < min_exp + 53;
+                }
+                const bool cached = ncand <= WK_CACHE;
+                if (exact && cached) {
+                    const double target = __dmul_rn(u, total);
+                    double carry = 0.0;
+                    for (uint32_t c0 = 0; c0 < ncand && pick < 0; c0 += 32) {
+                        const uint32_t i = c0 + lane;
+                        double v = i < ncand ? static_cast<double>(s_cval[wib][i]) : 0.0;
+#pragma unroll
+                        for (int d = 1; d < 32; d <<= 1) {
+                            const double up = __shfl_up_sync(0xffffffffu, v, d);
+                            if (lane >= static_cast<uint32_t>(d)) v = __dadd_rn(v, up);
+                        }
+                        const double incl = __dadd_rn(carry, v);
+                        const uint32_t hit = __ballot_sync(0xffffffffu, i < ncand && incl >= target);
+                        if (hit) pick = static_cast<int>(s_cslot[wib][c0 + __ffs(hit) - 1]);
+                        carry = __shfl_sync(0xffffffffu, incl, 31);
+                    }
+                } else {
+                    // list-order accumulation: every lane replays the same sequence of additions
+                    double seq = 0.0;
+                    if (!exact) {
+                        for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
+                            const uint32_t k = c0 + lane;
+                            const bool valid = k < deg;
+                            const bool cand = valid && !bit_get(bm, g.nbr[base + k] & 0x7fffffffu);
+                            const float v = cand ? walk_metric(g, base + k) : 0.0f;
+                            const uint32_t cb = __ballot_sync(0xffffffffu, cand);
+                            for (uint32_t m = cb; m; m &= m - 1) seq = __dadd_rn(seq, static_cast<double>(__shfl_sync(0xffffffffu, v, __ffs(m) - 1)));
+                        }
+                        total = seq;
+                    }
+                    const double target = __dmul_rn(u, total);
+                    seq = 0.0;
+                    for (uint32_t c0 = 0; c0 < deg && pick < 0; c0 += 32) {
+                        const uint32_t k = c0 + lane;
+                        const bool valid = k < deg;
+                        const bool cand = valid && !bit_get(bm, g.nbr[base + k] & 0x7fffffffu);
+                        const float v = cand ? walk_metric(g, base + k) : 0.0f;
+                        const uint32_t cb = __ballot_sync(0xffffffffu, cand);
+                        for (uint32_t m = cb; m; m &= m - 1) {
+                            const int src = __ffs(m) - 1;
+                            seq = __dadd_rn(seq, static_cast<double>(__shfl_sync(0xffffffffu, v, src)));
+                            if (seq >= target) { pick = static_cast<int>(c0) + src; break; }
+                        }
+                    }
+                    examined += 2ull * deg;
+                }
+                if (pick < 0) break;  // only with NaN metrics; the reference dereferences null here
+            }
+            // ---- take the edge (src/PathManager.cpp:117-142)
+            const uint32_t slot = base + static_cast<uint32_t>(pick);
+            const uint32_t nbw = g.nbr[slot];
+            cur = nbw & 0x7fffffffu;
+            const int32_t dl = g.delta[slot];
+            if (n_nodes >= sc.cap) break;  // cannot happen: a walk visits every node at most once
+            if (lane == 0) {
+                nodes[n_nodes] = cur; slots[n_nodes - 1] = slot; vlog[nlog] = cur;
+                bm[cur >> 5] |= 1u << (cur & 31);
+            }
+            __syncwarp();
+            n_nodes++; nlog++;
+            sum_all += dl;
+            const long long len = sum_all - dl;   // last edge excluded (src/Path.cpp:12-15)
+            if (len <= 0) break;
+            if (nbw >> 31) { accepted = true; break; }
+            if (len >= len_threshold) break;
+        }
+        if (lane == 0) o.res_draws[walk] = draws;
+        if (accepted) {
+            const long long len = sum_all - g.delta[slots[n_nodes - 2]];
+            if (len >= 0) emit_path(o, walk, nodes, slots, n_nodes, len);
+        }
+        clear_visited(bm, sc.words, vlog, nlog);
+    }
+    if (lane == 0 && examined) atomicAdd(o.steps, examined);
+}
+
+// Greedy walk ids: prefix over anchors of the number of first edges tried
+// (src/PathManager.cpp:204,224-229: the first edge that lands on an anchor ends the loop).
+__global__ void det_count_kernel(WalkGraph g, uint32_t *first_edges) {
+    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= g.anchors) return;
+    const uint32_t x = g.anchor_ids[a], base = g.off[x], deg = g.off[x + 1] - base;
+    uint32_t n = deg;
+    for (uint32_t k = 0; k < deg; k++) if (g.nbr[base + k] >> 31) { n = k + 1; break; }
+    first_edges[a] = n;
+}
+
+__global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkScratch sc, WalkOut o, uint32_t total_walks, const uint32_t *__restrict__ walk_base) {
+    const uint32_t lane = lane_id(), wib = warp_id();
+    const uint32_t wslot = blockIdx.x * WK_WARPS + wib;
+    uint32_t *bm = sc.bitmap + static_cast<uint64_t>(wslot) * sc.words;
+    uint32_t *nodes = sc.nodes + static_cast<uint64_t>(wslot) * sc.cap;
+    uint32_t *slots = sc.slots + static_cast<uint64_t>(wslot) * sc.cap;
+    uint32_t *vlog = sc.vlog + static_cast<uint64_t>(wslot) * sc.cap;
+    unsigned long long examined = 0;
+    for (;;) {
+        uint32_t walk = 0;
+        if (lane == 0) walk = atomicAdd(o.next_walk, 1u);
+        walk = __shfl_sync(0xffffffffu, walk, 0);
+        if (walk >= total_walks) break;
+        // anchor = last a with walk_base[a] <= walk
+        uint32_t lo = 0, hi = g.anchors;
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (walk_base[mid] <= walk) lo = mid; else hi = mid; }
+        const uint32_t start = g.anchor_ids[lo];
+        const uint32_t fs = g.off[start] + (walk - walk_base[lo]);
+        const uint32_t nbw0 = g.nbr[fs];
+        uint32_t cur = nbw0 & 0x7fffffffu;
+        uint32_t n_nodes = 2, nlog = 2;
+        if (lane == 0) {
+            nodes[0] = start; nodes[1] = cur; slots[0] = fs; vlog[0] = start; vlog[1] = cur;
+            bm[start >> 5] |= 1u << (start & 31);
+            bm[cur >> 5] |= 1u << (cur & 31);
+        }
+        __syncwarp();
+        bool reached = false;
+        if (nbw0 >> 31) {
+            emit_path(o, walk, nodes, slots, 2, static_cast<int64_t>(g.node_len[start]));
+        } else {
+            int step = 0;
+            uint32_t skip = 0;
+            bool went_back = false;
+            for (;;) {
+                const uint32_t base = g.off[cur], deg = g.off[cur + 1] - base;
+                int chosen = -1;
+                if (deg != 0 && skip < deg - 1) {
+                    for (uint32_t c0 = skip; c0 < deg - 1 && chosen < 0; c0 += 32) {
+                        const uint32_t k = c0 + lane;
+                        uint32_t s = 0;
+                        bool un = false;
+                        if (k < deg - 1) { s = g.rank[base + k]; un = !bit_get(bm, g.nbr[s] & 0x7fffffffu); }
+                        const uint32_t ub = __ballot_sync(0xffffffffu, un);
+                        if (ub) chosen = static_cast<int>(__shfl_sync(0xffffffffu, s, __ffs(ub) - 1));
+                        examined += 32;
+                    }
+                }
+                if (chosen < 0) {
+                    if (step == 0 || went_back) break;
+                    went_back = true;
+                    step--;
+                    skip++;
+                    n_nodes--;
+                    cur = nodes[n_nodes - 1];
+                    if (lane == 0) bm[cur >> 5] &= ~(1u << (cur & 31));
+                    __syncwarp();
+                    continue;
+                }
+                const uint32_t nbw = g.nbr[chosen];
+                const uint32_t next = nbw & 0x7fffffffu;
+                if (n_nodes >= sc.cap) break;
+                if (lane == 0) {
+                    slots[n_nodes - 1] = g.canon[chosen];
+                    bm[cur >> 5] |= 1u << (cur & 31);
+                    nodes[n_nodes] = next;
+                    vlog[nlog] = next;
+                }
+                __syncwarp();
+                // the node just left is in the log already (it was logged when it was entered)
+                cur = next;
+                n_nodes++; nlog++;
+                if (nbw >> 31) { reached = true; break; }
+                step++;
+            }
+            if (reached) {
+                // src/Path.cpp:6-16 over the final edge list
+                long long part = 0;
+                for (uint32_t i = lane; i + 2 < n_nodes; i += 32) part += g.delta[slots[i]];
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+                const long long len = static_cast<long long>(g.node_len[start]) + part;
+                if (len >= 0) emit_path(o, walk, nodes, slots, n_nodes, len);
+            }
+        }
+        if (lane == 0) o.res_draws[walk] = 0;
+        clear_visited(bm, sc.words, vlog, nlog);
+    }
+    if (lane == 0 && examined) atomicAdd(o.steps, examined);
+}
+
+// Copies accepted paths from the pool to the path store in walk order.
+__global__ void __launch_bounds__(WK_THREADS) gather_paths_kernel(uint32_t total_walks, const uint32_t *__restrict__ res_n, const uint64_t *__restrict__ res_off,
+                                                                  const int64_t *__restrict__ res_len, const uint32_t *__restrict__ accepted_scan,
+                                                                  const uint64_t *__restrict__ node_scan, const uint32_t *__restrict__ pool_nodes,
+                                                                  const uint32_t *__restrict__ pool_slots, uint64_t path_base, uint64_t node_base,
+                                                                  uint64_t *__restrict__ off, uint32_t *__restrict__ nodes, uint32_t *__restrict__ slots,
+                                                                  int64_t *__restrict__ len) {
+    const uint32_t walk = (blockIdx.x * WK_THREADS + threadIdx.x) >> 5, lane = lane_id();
+    if (walk >= total_walks) return;
+    const uint32_t n = res_n[walk];
+    if (!n) return;
+    const uint64_t p = path_base + accepted_scan[walk];
+    const uint64_t dst = node_base + node_scan[walk];
+    const uint64_t src = res_off[walk];
+    if (lane == 0) { off[p + 1] = dst + n; len[p] = res_len[walk]; }
+    for (uint32_t i = lane; i < n; i += 32) nodes[dst + i] = pool_nodes[src + i];
+    for (uint32_t i = lane; i + 1 < n; i += 32) slots[dst - p + i] = pool_slots[src + i];
+}
+
+__global__ void flag_nonzero_kernel(uint32_t n, const uint32_t *__restrict__ in, uint8_t *__restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i] ? 1 : 0;
+}
+
+namespace {
+
+struct WalkRun {
+    uint32_t *res_n = nullptr, *res_draws = nullptr, *pool_nodes = nullptr, *pool_slots = nullptr;
+    uint64_t *res_off = nullptr;
+    int64_t *res_len = nullptr;
+    unsigned long long *d_ctr = nullptr;  // [0] pool_used [1] steps [2] next_walk (low 32 bits)
+    uint32_t *bitmap = nullptr, *nodes = nullptr, *slots = nullptr, *vlog = nullptr;
+};
+
+WalkGraph make_walk_graph(Ctx &c, int metric) {
+    GraphTables &g = c.g;
+    WalkGraph w{};
+    w.off = g.adj_off.p; w.nbr = g.a_nbr.p; w.canon = g.canon.p; w.rank = g.rank_ready[metric] ? g.rank[metric].p : nullptr;
+    w.node_len = g.node_len.p; w.anchor_ids = g.anchor_ids.p;
+    w.metric = (metric == HERA_EXTENSION_SCORE || metric == HERA_EXTENSION_SCORE_SQRT) ? g.a_es.p : g.a_os.p;
+    w.delta = g.a_delta.p;
+    w.N = static_cast<uint32_t>(g.N); w.anchors = static_cast<uint32_t>(g.anchors);
+    w.sqrt_metric = (metric == HERA_EXTENSION_SCORE_SQRT || metric == HERA_OVERLAP_SCORE_SQRT) ? 1 : 0;
+    return w;
+}
+
+// Runs one walk kernel over `total_walks` walks and appends the accepted paths to c.all.
+template <typename LaunchFn>
+void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_stats *out, LaunchFn launch) {
+    GraphTables &g = c.g;
+    const uint64_t launches_before = c.launches.count;
+    cudaEvent_t ev0, ev1;
+    HERA_CUDA(cudaEventCreate(&ev0));
+    HERA_CUDA(cudaEventCreate(&ev1));
+    uint64_t found = 0, steps = 0;
+    float ms = 0;
+    if (total_walks > 0) {
+        int sms = 148;
+        HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
+        const uint32_t cap = static_cast<uint32_t>(g.N + 1), words = static_cast<uint32_t>((g.N + 31) / 32);
+        const uint64_t per_warp = (3ull * cap + words) * sizeof(uint32_t);
+        uint64_t warps = static_cast<uint64_t>(sms) * 32;
+        while (warps > WK_WARPS && warps * per_warp > (8ull << 30)) warps /= 2;
+        if (warps > total_walks) warps = (total_walks + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
+        const unsigned blocks = static_cast<unsigned>((warps + WK_WARPS - 1) / WK_WARPS);
+        warps = static_cast<uint64_t>(blocks) * WK_WARPS;
+
+        WalkRun r;
+        HERA_CUDA(cudaMallocAsync(&r.res_n, total_walks * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.res_draws, total_walks * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.res_off, total_walks * sizeof(uint64_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.res_len, total_walks * sizeof(int64_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.d_ctr, 4 * sizeof(unsigned long long), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.bitmap, warps * words * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.nodes, warps * cap * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.slots, warps * cap * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.vlog, warps * cap * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMemsetAsync(r.bitmap, 0, warps * words * sizeof(uint32_t), c.stream));
+        uint64_t pool_cap = std::max<uint64_t>(1u << 16, std::min<uint64_t>(static_cast<uint64_t>(total_walks) * 128, 1ull << 28));
+        unsigned long long h_ctr[4];
+        for (;;) {
+            HERA_CUDA(cudaMallocAsync(&r.pool_nodes, pool_cap * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMallocAsync(&r.pool_slots, pool_cap * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMemsetAsync(r.d_ctr, 0, 4 * sizeof(unsigned long long), c.stream));
+            HERA_CUDA(cudaMemsetAsync(r.res_n, 0, total_walks * sizeof(uint32_t), c.stream));
+            WalkScratch sc{r.bitmap, r.nodes, r.slots, r.vlog, words, cap};
+            WalkOut wo{r.res_n, r.res_off, r.res_len, r.res_draws, r.pool_nodes, r.pool_slots, pool_cap, r.d_ctr, r.d_ctr + 1,
+                       reinterpret_cast<unsigned int *>(r.d_ctr + 2)};
+            HERA_CUDA(cudaEventRecord(ev0, c.stream));
+            launch(blocks, sc, wo);
+            HERA_CUDA(cudaEventRecord(ev1, c.stream));
+            HERA_CUDA(cudaMemcpyAsync(h_ctr, r.d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            if (h_ctr[0] <= pool_cap) break;
+            HERA_CUDA(cudaFreeAsync(r.pool_nodes, c.stream));   // pool too small: walks are deterministic, run again with room
+            HERA_CUDA(cudaFreeAsync(r.pool_slots, c.stream));
+            pool_cap = h_ctr[0] + 1024;
+        }
+        HERA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+        steps = h_ctr[1];
+        const uint64_t new_nodes = h_ctr[0];
+
+        // order by walk id and append to the path store
+        uint8_t *flags = nullptr;
+        uint32_t *acc_scan = nullptr, *d_found = nullptr;
+        uint64_t *node_scan = nullptr;
+        HERA_CUDA(cudaMallocAsync(&flags, total_walks, c.stream));
+        HERA_CUDA(cudaMallocAsync(&acc_scan, total_walks * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&node_scan, total_walks * sizeof(uint64_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&d_found, sizeof(uint32_t), c.stream));
+        HERA_LAUNCH(c, flag_nonzero_kernel, div_up(total_walks, 256), 256, 0, total_walks, r.res_n, flags);
+        exclusive_scan_u8_to_u32(c, flags, total_walks, acc_scan, d_found);
+        exclusive_scan_u32_to_u64(c, r.res_n, total_walks, node_scan, nullptr);
+        uint32_t h_found = 0;
+        HERA_CUDA(cudaMemcpyAsync(&h_found, d_found, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        found = h_found;
+        PathStore &ps = c.all;
+        ps.off.reserve(ps.paths + found + 1, true, ps.paths + 1, c.stream);
+        ps.len.reserve(ps.paths + found, true, ps.paths, c.stream);
+        ps.node.reserve(ps.nodes + new_nodes, true, ps.nodes, c.stream);
+        ps.slot.reserve(ps.nodes + new_nodes, true, ps.nodes > ps.paths ? ps.nodes - ps.paths : 0, c.stream);
+        if (ps.paths == 0) HERA_CUDA(cudaMemsetAsync(ps.off.p, 0, sizeof(uint64_t), c.stream));
+        if (found) {
+            HERA_LAUNCH(c, gather_paths_kernel, div_up(static_cast<uint64_t>(total_walks) * 32, WK_THREADS), WK_THREADS, 0, total_walks, r.res_n, r.res_off,
+                        r.res_len, acc_scan, node_scan, r.pool_nodes, r.pool_slots, ps.paths, ps.nodes, ps.off.p, ps.node.p, ps.slot.p, ps.len.p);
+        }
+        ps.paths += found;
+        ps.nodes += new_nodes;
+        if (kind == 0) {
+            const size_t before = c.mc_draws.size();
+            c.mc_draws.resize(before + total_walks);
+            HERA_CUDA(cudaMemcpyAsync(c.mc_draws.data() + before, r.res_draws, total_walks * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+        }
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        for (void *p : {static_cast<void *>(flags), static_cast<void *>(acc_scan), static_cast<void *>(node_scan), static_cast<void *>(d_found),
+                        static_cast<void *>(r.res_n), static_cast<void *>(r.res_draws), static_cast<void *>(r.res_off), static_cast<void *>(r.res_len),
+                        static_cast<void *>(r.d_ctr), static_cast<void *>(r.bitmap), static_cast<void *>(r.nodes), static_cast<void *>(r.slots),
+                        static_cast<void *>(r.vlog), static_cast<void *>(r.pool_nodes), static_cast<void *>(r.pool_slots)})
+            HERA_CUDA(cudaFreeAsync(p, c.stream));
+    }
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    c.uniq_ready = false;
+    c.call_kind.push_back(static_cast<uint32_t>(kind));
+    c.call_metric.push_back(static_cast<uint32_t>(metric));
+    c.call_found.push_back(found);
+    if (out) {
+        out->walks = total_walks; out->found = found; out->steps = steps; out->ms = ms;
+        out->launches = static_cast<uint32_t>(c.launches.count - launches_before);
+    }
+}
+
+}  // namespace
+
+void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out) {
+    HERA_REQUIRE(c.g.ready, 7, "hera_paths_monte_carlo: call hera_graph_finalize first");
+    HERA_REQUIRE(metric >= 0 && metric < 4, 8, "unknown metric");
+    const uint64_t total = c.g.anchors * static_cast<uint64_t>(pp.rebuild_attempts > 0 ? pp.rebuild_attempts : 0);
+    HERA_REQUIRE(total < (1ull << 32), 9, "too many Monte-Carlo walks for one call");
+    WalkGraph wg = make_walk_graph(c, metric);
+    run_walks(c, static_cast<uint32_t>(total), 0, metric, out, [&](unsigned blocks, WalkScratch sc, WalkOut wo) {
+        HERA_LAUNCH(c, walk_mc_kernel, blocks, WK_THREADS, 0, wg, sc, wo, static_cast<uint32_t>(total), static_cast<uint32_t>(pp.rebuild_attempts),
+                    pp.backtrack_attempts, static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
+    });
+}
+
+void walk_deterministic(Ctx &c, int metric, hera_walk_stats *out) {
+    HERA_REQUIRE(c.g.ready, 7, "hera_paths_deterministic: call hera_graph_finalize first");
+    HERA_REQUIRE(metric >= 0 && metric < 4, 8, "unknown metric");
+    HERA_REQUIRE(c.g.E == 0 || c.g.rank_ready[metric], 10, "rank permutation for this metric was not built (metrics_mask of hera_graph_finalize)");
+    WalkGraph wg = make_walk_graph(c, metric);
+    uint32_t total = 0;
+    uint32_t *first_edges = nullptr, *walk_base = nullptr, *d_total = nullptr;
+    if (c.g.anchors) {
+        HERA_CUDA(cudaMallocAsync(&first_edges, c.g.anchors * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&walk_base, c.g.anchors * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&d_total, sizeof(uint32_t), c.stream));
+        HERA_LAUNCH(c, det_count_kernel, div_up(c.g.anchors, 128), 128, 0, wg, first_edges);
+        exclusive_scan_u32(c, first_edges, c.g.anchors, walk_base, d_total);
+        HERA_CUDA(cudaMemcpyAsync(&total, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+    }
+    run_walks(c, total, 1, metric, out, [&](unsigned blocks, WalkScratch sc, WalkOut wo) {
+        HERA_LAUNCH(c, walk_det_kernel, blocks, WK_THREADS, 0, wg, sc, wo, total, walk_base);
+    });
+    if (first_edges) {
+        HERA_CUDA(cudaFreeAsync(first_edges, c.stream)); HERA_CUDA(cudaFreeAsync(walk_base, c.stream)); HERA_CUDA(cudaFreeAsync(d_total, c.stream));
+    }
+}
+
+}  // namespace hera
