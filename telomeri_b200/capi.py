@@ -1,0 +1,247 @@
+"""ctypes binding of libhera_b200.so (include/hera_b200.h).  No compute happens in Python: every
+method is one C-ABI call; results come back as numpy views copied out of the library's pinned
+mirrors.  Importing this module without the built library raises -- there is no CPU fallback."""
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libhera_b200.so"
+
+MODE = {"min": 0, "max": 1, "avg": 2, "sum": 3}
+METRIC = {"es": 0, "os": 1, "es_sqrt": 2, "os_sqrt": 3}
+
+u8p, u32p, u64p, i64p, i32p, f32p = (C.POINTER(t) for t in (C.c_uint8, C.c_uint32, C.c_uint64, C.c_int64, C.c_int32, C.c_float))
+
+
+class FilterParams(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("min_overlap_length", C.c_uint64), ("min_overlap_percentage", C.c_float),
+                ("max_overhang_length", C.c_uint64), ("max_overhang_percentage", C.c_float)]
+
+
+class PathParams(C.Structure):
+    _fields_ = [("rebuild_attempts", C.c_int32), ("backtrack_attempts", C.c_int32), ("len_threshold", C.c_int64),
+                ("window_size", C.c_uint64), ("ratio_threshold", C.c_float)]
+
+
+class LoadResult(C.Structure):
+    _fields_ = [("records", C.c_uint64), ("kept", C.c_uint64), ("kept_total", C.c_uint64), ("bytes", C.c_uint64),
+                ("parse_ms", C.c_float), ("h2d_ms", C.c_float)]
+
+
+class GraphInfo(C.Structure):
+    _fields_ = [("nodes", C.c_uint64), ("anchors", C.c_uint64), ("edges", C.c_uint64), ("slots", C.c_uint64),
+                ("intern_ms", C.c_float), ("csr_ms", C.c_float), ("rank_ms", C.c_float)]
+
+
+class GraphView(C.Structure):
+    _fields_ = [("nodes", C.c_uint64), ("edges", C.c_uint64), ("slots", C.c_uint64),
+                ("node_len", u32p), ("node_anchor", u8p), ("node_name_off", u64p), ("node_names", C.POINTER(C.c_char)),
+                ("e_q", u32p), ("e_t", u32p), ("e_qs", u32p), ("e_qe", u32p), ("e_ts", u32p), ("e_te", u32p),
+                ("e_os", f32p), ("e_si", f32p), ("e_es", f32p), ("e_strand", u8p),
+                ("adj_off", u64p), ("adj_rec", u32p), ("adj_side", u8p),
+                ("rank_es", u32p), ("rank_os", u32p), ("rank_es_sqrt", u32p), ("rank_os_sqrt", u32p), ("canon", u32p)]
+
+
+class PathsView(C.Structure):
+    _fields_ = [("paths", C.c_uint64), ("total_nodes", C.c_uint64), ("off", u64p), ("nodes", u32p), ("slots", u32p), ("len", i64p),
+                ("calls", C.c_uint64), ("call_kind", u32p), ("call_metric", u32p), ("call_found", u64p),
+                ("mc_walks", C.c_uint64), ("mc_draws_per_walk", u32p)]
+
+
+class GroupsView(C.Structure):
+    _fields_ = [("pairs", C.c_uint64), ("groups", C.c_uint64), ("sorted_total", C.c_uint64), ("pig_total", C.c_uint64),
+                ("pair_a1", u32p), ("pair_a2", u32p), ("pair_off", u64p), ("pair_sorted", u32p),
+                ("grp_pair", u32p), ("grp_size0", u32p), ("grp_pig_off", u64p), ("grp_pig", u32p),
+                ("grp_consensus", i64p), ("grp_valid", i32p), ("pair_consensus", i64p), ("ms", C.c_float)]
+
+
+class WalkStats(C.Structure):
+    _fields_ = [("walks", C.c_uint64), ("found", C.c_uint64), ("steps", C.c_uint64), ("ms", C.c_float), ("launches", C.c_uint32)]
+
+
+# name -> (restype, argtypes); must list every symbol of include/hera_b200.h
+SIGNATURES = {
+    "hera_create": (C.c_void_p, [C.c_int]),
+    "hera_destroy": (None, [C.c_void_p]),
+    "hera_last_error": (C.c_char_p, [C.c_void_p]),
+    "hera_kernel_launches": (C.c_uint64, [C.c_void_p]),
+    "hera_graph_set_filter": (C.c_int, [C.c_void_p, C.POINTER(FilterParams)]),
+    "hera_graph_load_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
+    "hera_graph_load_bytes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
+    "hera_graph_load_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
+    "hera_graph_reset": (C.c_int, [C.c_void_p]),
+    "hera_graph_finalize": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(GraphInfo)]),
+    "hera_graph_export": (C.c_int, [C.c_void_p, C.POINTER(GraphView)]),
+    "hera_paths_monte_carlo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PathParams), C.c_uint64, C.POINTER(WalkStats)]),
+    "hera_paths_deterministic": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(WalkStats)]),
+    "hera_paths_unique": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "hera_paths_reset": (C.c_int, [C.c_void_p]),
+    "hera_paths_export": (C.c_int, [C.c_void_p, C.POINTER(PathsView)]),
+    "hera_groups": (C.c_int, [C.c_void_p, C.POINTER(PathParams), C.POINTER(GroupsView)]),
+}
+
+_lib = None
+
+
+def load_library():
+    """dlopen the in-tree CUDA library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is missing: run `python -m telomeri_b200.build` (nvcc, sm_100a). There is no CPU fallback.")
+        lib = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+class HeraError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"hera error {code}: {msg}")
+        self.code = code
+
+
+def _arr(ptr, n, dtype):
+    if n == 0 or not ptr:
+        return np.zeros(0, dtype=dtype)
+    return np.ctypeslib.as_array(ptr, shape=(int(n),)).astype(dtype, copy=True)
+
+
+def default_filter(mode="avg", min_oll=0, min_olp=0.0, max_ohl=2 ** 64 - 1, max_ohp=1.0):
+    return FilterParams(MODE[mode], min_oll, min_olp, max_ohl, max_ohp)
+
+
+def default_path_params(rb_att=2000, bt_att=60, len_thr=4700000, w_size=1000, r_thr=0.9):
+    return PathParams(rb_att, bt_att, len_thr, w_size, r_thr)
+
+
+class Hera:
+    """Thin object wrapper: one hera_ctx."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        self.h = self.lib.hera_create(device)
+        if not self.h:
+            raise HeraError(-1, self.lib.hera_last_error(None).decode())
+
+    def close(self):
+        if self.h:
+            self.lib.hera_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc):
+        if rc != 0:
+            raise HeraError(rc, self.lib.hera_last_error(self.h).decode())
+
+    @property
+    def launches(self):
+        return int(self.lib.hera_kernel_launches(self.h))
+
+    def set_filter(self, fp):
+        self._check(self.lib.hera_graph_set_filter(self.h, C.byref(fp)))
+
+    def load_file(self, path, anchors, test_load_num=0):
+        r = LoadResult()
+        self._check(self.lib.hera_graph_load_file(self.h, str(path).encode(), int(anchors), test_load_num, C.byref(r)))
+        return r
+
+    def load_bytes(self, data, anchors, test_load_num=0):
+        r = LoadResult()
+        buf = (C.c_char * len(data)).from_buffer_copy(data) if len(data) else None
+        self._check(self.lib.hera_graph_load_bytes(self.h, buf, len(data), int(anchors), test_load_num, C.byref(r)))
+        return r
+
+    def load_host_ptr(self, ptr, n, anchors, test_load_num=0):
+        r = LoadResult()
+        self._check(self.lib.hera_graph_load_bytes(self.h, C.c_void_p(ptr), n, int(anchors), test_load_num, C.byref(r)))
+        return r
+
+    def load_device_ptr(self, ptr, n, anchors, test_load_num=0):
+        r = LoadResult()
+        self._check(self.lib.hera_graph_load_device(self.h, C.c_void_p(ptr), n, int(anchors), test_load_num, C.byref(r)))
+        return r
+
+    def graph_reset(self):
+        self._check(self.lib.hera_graph_reset(self.h))
+
+    def finalize(self, metrics=("es", "os")):
+        mask = 0
+        for m in metrics:
+            mask |= 1 << (METRIC[m] if isinstance(m, str) else int(m))
+        info = GraphInfo()
+        self._check(self.lib.hera_graph_finalize(self.h, mask, C.byref(info)))
+        return info
+
+    def export_graph(self):
+        v = GraphView()
+        self._check(self.lib.hera_graph_export(self.h, C.byref(v)))
+        N, E, S = v.nodes, v.edges, v.slots
+        out = {
+            "node_len": _arr(v.node_len, N, np.uint32), "node_anchor": _arr(v.node_anchor, N, np.uint8),
+            "node_name_off": _arr(v.node_name_off, N + 1, np.uint64),
+            "adj_off": _arr(v.adj_off, N + 1, np.uint64), "adj_rec": _arr(v.adj_rec, S, np.uint32), "adj_side": _arr(v.adj_side, S, np.uint8),
+            "canon": _arr(v.canon, S, np.uint32),
+        }
+        nbytes = int(out["node_name_off"][-1]) if N else 0
+        out["node_names"] = np.frombuffer(C.string_at(v.node_names, nbytes), dtype=np.uint8).copy() if nbytes else np.zeros(0, np.uint8)
+        for k in ("e_q", "e_t", "e_qs", "e_qe", "e_ts", "e_te"):
+            out[k] = _arr(getattr(v, k), E, np.uint32)
+        for k in ("e_os", "e_si", "e_es"):
+            out[k] = _arr(getattr(v, k), E, np.float32)
+        out["e_strand"] = _arr(v.e_strand, E, np.uint8)
+        for i, k in enumerate(("rank_es", "rank_os", "rank_es_sqrt", "rank_os_sqrt")):
+            if getattr(v, k):
+                out[f"rank_{i}"] = _arr(getattr(v, k), S, np.uint32)
+        return out
+
+    def monte_carlo(self, metric, pp, seed=0):
+        s = WalkStats()
+        self._check(self.lib.hera_paths_monte_carlo(self.h, METRIC[metric] if isinstance(metric, str) else metric, C.byref(pp), seed, C.byref(s)))
+        return s
+
+    def deterministic(self, metric):
+        s = WalkStats()
+        self._check(self.lib.hera_paths_deterministic(self.h, METRIC[metric] if isinstance(metric, str) else metric, C.byref(s)))
+        return s
+
+    def unique(self):
+        n = C.c_uint64()
+        self._check(self.lib.hera_paths_unique(self.h, C.byref(n)))
+        return n.value
+
+    def paths_reset(self):
+        self._check(self.lib.hera_paths_reset(self.h))
+
+    def export_paths(self, prefix=""):
+        v = PathsView()
+        self._check(self.lib.hera_paths_export(self.h, C.byref(v)))
+        P = v.paths
+        return {
+            prefix + "off": _arr(v.off, P + 1, np.uint64), prefix + "nodes": _arr(v.nodes, v.total_nodes, np.uint32),
+            prefix + "slots": _arr(v.slots, v.total_nodes - P, np.uint32), prefix + "len": _arr(v.len, P, np.int64),
+            "call_kind": _arr(v.call_kind, v.calls, np.uint32), "call_metric": _arr(v.call_metric, v.calls, np.uint32),
+            "call_found": _arr(v.call_found, v.calls, np.uint64), "mc_draws_per_walk": _arr(v.mc_draws_per_walk, v.mc_walks, np.uint32),
+        }
+
+    def groups(self, pp):
+        v = GroupsView()
+        self._check(self.lib.hera_groups(self.h, C.byref(pp), C.byref(v)))
+        K, G = v.pairs, v.groups
+        return {
+            "pair_a1": _arr(v.pair_a1, K, np.uint32), "pair_a2": _arr(v.pair_a2, K, np.uint32), "pair_off": _arr(v.pair_off, K + 1, np.uint64),
+            "pair_sorted": _arr(v.pair_sorted, v.sorted_total, np.uint32), "grp_pair": _arr(v.grp_pair, G, np.uint32),
+            "grp_size0": _arr(v.grp_size0, G, np.uint32), "grp_pig_off": _arr(v.grp_pig_off, G + 1, np.uint64),
+            "grp_pig": _arr(v.grp_pig, v.pig_total, np.uint32), "grp_consensus": _arr(v.grp_consensus, G, np.int64),
+            "grp_valid": _arr(v.grp_valid, G, np.int32), "pair_consensus": _arr(v.pair_consensus, K, np.int64), "ms": float(v.ms),
+        }

@@ -1,0 +1,202 @@
+// extern "C" entry points of libhera_b200.so (declared in include/hera_b200.h).
+#include <algorithm>
+#include <cstring>
+#include <fstream>
+
+#include "ctx.cuh"
+
+namespace hera {
+uint64_t padded_text_size(uint64_t n);  // paf_parse.cu
+static std::string g_create_error;
+}  // namespace hera
+
+struct hera_ctx {
+    hera::Ctx c;
+};
+
+using hera::Ctx;
+
+#define HERA_API_BEGIN(ctxp)                                   \
+    if (!(ctxp)) return 100;                                   \
+    Ctx &c = (ctxp)->c;                                        \
+    try {                                                      \
+        if (cudaSetDevice(c.device) != cudaSuccess) throw hera::Error{2, "cudaSetDevice failed"};
+
+#define HERA_API_END                                           \
+        return 0;                                              \
+    } catch (const hera::Error &e) {                           \
+        c.err = e.msg;                                         \
+        cudaGetLastError();                                    \
+        return e.code;                                         \
+    } catch (const std::exception &e) {                        \
+        c.err = e.what();                                      \
+        return 99;                                             \
+    }
+
+extern "C" {
+
+hera_ctx *hera_create(int device) {
+    int count = 0;
+    cudaError_t err = cudaGetDeviceCount(&count);
+    if (err != cudaSuccess || device < 0 || device >= count) {
+        hera::g_create_error = err != cudaSuccess ? std::string("no usable CUDA device: ") + cudaGetErrorString(err)
+                                                  : "device index out of range (" + std::to_string(count) + " devices)";
+        cudaGetLastError();
+        return nullptr;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) { hera::g_create_error = "cudaSetDevice failed"; return nullptr; }
+    hera_ctx *h = new hera_ctx();
+    h->c.device = device;
+    if (cudaStreamCreateWithFlags(&h->c.stream, cudaStreamNonBlocking) != cudaSuccess) {
+        hera::g_create_error = "cudaStreamCreate failed";
+        delete h;
+        return nullptr;
+    }
+    // keep freed stream-ordered allocations cached instead of returning them to the driver
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        uint64_t threshold = UINT64_MAX;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+    }
+    return h;
+}
+
+void hera_destroy(hera_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->c.device);
+    cudaStreamSynchronize(ctx->c.stream);
+    cudaStream_t s = ctx->c.stream;
+    delete ctx;
+    cudaStreamDestroy(s);
+}
+
+const char *hera_last_error(hera_ctx *ctx) { return ctx ? ctx->c.err.c_str() : hera::g_create_error.c_str(); }
+
+uint64_t hera_kernel_launches(hera_ctx *ctx) { return ctx ? ctx->c.launches.count : 0; }
+
+int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(fp != nullptr, 101, "null filter parameters");
+    c.fp = *fp;
+    HERA_API_END
+}
+
+static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind, int anchors, uint32_t test_load_num, hera_load_result *out) {
+    std::unique_ptr<hera::LoadedText> t(new hera::LoadedText());
+    t->n = n;
+    t->bytes.reserve(hera::padded_text_size(n));
+    cudaEvent_t e0, e1;
+    HERA_CUDA(cudaEventCreate(&e0));
+    HERA_CUDA(cudaEventCreate(&e1));
+    HERA_CUDA(cudaEventRecord(e0, c.stream));
+    if (n) HERA_CUDA(cudaMemcpyAsync(t->bytes.p, src, n, kind, c.stream));
+    HERA_CUDA(cudaEventRecord(e1, c.stream));
+    const uint32_t file_id = static_cast<uint32_t>(c.texts.size());
+    HERA_REQUIRE(file_id < 16, 5, "more than 16 loads per graph are not supported");
+    c.texts.push_back(std::move(t));
+    hera_load_result tmp{};
+    hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, &tmp);
+    float copy_ms = 0;
+    HERA_CUDA(cudaEventElapsedTime(&copy_ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    tmp.h2d_ms = kind == cudaMemcpyHostToDevice ? copy_ms : 0.0f;
+    if (out) *out = tmp;
+}
+
+int hera_graph_load_bytes(hera_ctx *ctx, const void *host_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(host_text != nullptr || n == 0, 101, "null text");
+    load_common(c, host_text, n, cudaMemcpyHostToDevice, anchors, test_load_num, out);
+    HERA_API_END
+}
+
+int hera_graph_load_device(hera_ctx *ctx, const void *device_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(device_text != nullptr || n == 0, 101, "null text");
+    load_common(c, device_text, n, cudaMemcpyDeviceToDevice, anchors, test_load_num, out);
+    HERA_API_END
+}
+
+int hera_graph_load_file(hera_ctx *ctx, const char *path, int anchors, uint32_t test_load_num, hera_load_result *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(path != nullptr, 101, "null path");
+    std::ifstream f(path, std::ios::binary | std::ios::ate);
+    if (!f) throw hera::Error{1, std::string("Cannot open file: ") + path};
+    const uint64_t n = static_cast<uint64_t>(f.tellg());
+    f.seekg(0);
+    hera::HBuf<char> staging;
+    staging.reserve(n + 1);
+    if (n) f.read(staging.p, static_cast<std::streamsize>(n));
+    HERA_REQUIRE(static_cast<uint64_t>(f.gcount()) == n || n == 0, 1, std::string("short read on ") + path);
+    load_common(c, staging.p, n, cudaMemcpyHostToDevice, anchors, test_load_num, out);
+    HERA_API_END
+}
+
+int hera_graph_reset(hera_ctx *ctx) {
+    HERA_API_BEGIN(ctx)
+    HERA_CUDA(cudaStreamSynchronize(c.stream));
+    c.texts.clear();
+    c.kept.n = 0;
+    c.g.ready = false;
+    c.g.N = c.g.E = c.g.S = c.g.anchors = 0;
+    HERA_API_END
+}
+
+int hera_graph_finalize(hera_ctx *ctx, uint32_t metrics_mask, hera_graph_info *out) {
+    HERA_API_BEGIN(ctx)
+    hera::finalize_graph(c, metrics_mask, out);
+    HERA_API_END
+}
+
+int hera_graph_export(hera_ctx *ctx, hera_graph_view *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(out != nullptr, 101, "null output");
+    hera::export_graph(c, out);
+    HERA_API_END
+}
+
+int hera_paths_monte_carlo(hera_ctx *ctx, int metric, const hera_path_params *pp, uint64_t seed, hera_walk_stats *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(pp != nullptr, 101, "null path parameters");
+    hera::walk_monte_carlo(c, metric, *pp, seed, out);
+    HERA_API_END
+}
+
+int hera_paths_deterministic(hera_ctx *ctx, int metric, hera_walk_stats *out) {
+    HERA_API_BEGIN(ctx)
+    hera::walk_deterministic(c, metric, out);
+    HERA_API_END
+}
+
+int hera_paths_unique(hera_ctx *ctx, uint64_t *n_unique) {
+    HERA_API_BEGIN(ctx)
+    hera::unique_paths(c, n_unique);
+    HERA_API_END
+}
+
+int hera_paths_reset(hera_ctx *ctx) {
+    HERA_API_BEGIN(ctx)
+    HERA_CUDA(cudaStreamSynchronize(c.stream));
+    c.all.paths = c.all.nodes = 0;
+    c.uniq.paths = c.uniq.nodes = 0;
+    c.uniq_ready = false;
+    c.call_kind.clear(); c.call_metric.clear(); c.call_found.clear(); c.mc_draws.clear();
+    HERA_API_END
+}
+
+int hera_paths_export(hera_ctx *ctx, hera_paths_view *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(out != nullptr, 101, "null output");
+    hera::export_paths(c, out);
+    HERA_API_END
+}
+
+int hera_groups(hera_ctx *ctx, const hera_path_params *pp, hera_groups_view *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(pp != nullptr && out != nullptr, 101, "null argument");
+    hera::group_paths(c, *pp, out);
+    HERA_API_END
+}
+
+}  // extern "C"

@@ -4,6 +4,69 @@
 
 namespace hera {
 
+// hist[d * nblocks + b] = number of keys of tile b whose current digit is d.
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t *__restrict__ keys, uint64_t n, int shift, uint32_t *__restrict__ hist) {
+    __shared__ uint32_t h[RS_BINS];
+    for (int i = threadIdx.x; i < RS_BINS; i += RS_THREADS) h[i] = 0;
+    __syncthreads();
+    const uint64_t base = static_cast<uint64_t>(blockIdx.x) * RS_TILE;
+#pragma unroll 4
+    for (int k = 0; k < RS_ITEMS; k++) {
+        uint64_t i = base + static_cast<uint64_t>(k) * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & (RS_BINS - 1)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < RS_BINS; i += RS_THREADS) hist[static_cast<uint64_t>(i) * gridDim.x + blockIdx.x] = h[i];
+}
+
+// Stable scatter: elements of a tile keep their relative order inside each digit.  Ranking is
+// staged in shared memory: per chunk of RS_THREADS elements every warp ranks its lanes with
+// match.any, warps are ordered through a per-warp digit table, chunks through a running count.
+__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                                                                uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n,
+                                                                int shift, const uint32_t *__restrict__ hist_scanned) {
+    __shared__ uint32_t run[RS_BINS];                 // global destination of the next key of each digit
+    __shared__ uint16_t warp_cnt[RS_WARPS][RS_BINS];  // per-warp digit counts of the current chunk
+    for (int i = threadIdx.x; i < RS_BINS; i += RS_THREADS) run[i] = hist_scanned[static_cast<uint64_t>(i) * gridDim.x + blockIdx.x];
+    for (int i = threadIdx.x; i < RS_WARPS * RS_BINS; i += RS_THREADS) (&warp_cnt[0][0])[i] = 0;
+    __syncthreads();
+    const uint64_t base = static_cast<uint64_t>(blockIdx.x) * RS_TILE;
+    const uint32_t lane = lane_id(), warp = warp_id();
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const uint64_t i = base + static_cast<uint64_t>(k) * RS_THREADS + threadIdx.x;
+        const bool live = i < n;
+        uint32_t key = 0, val = 0, d = RS_BINS;  // dead lanes get a digit nobody else has
+        if (live) {
+            key = keys_in[i];
+            val = vals_in[i];
+            d = (key >> shift) & (RS_BINS - 1);
+        }
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+        if (live && rank_in_warp == 0) warp_cnt[warp][d] = static_cast<uint16_t>(__popc(peers));
+        __syncthreads();
+        uint32_t dst = 0;
+        if (live) {
+            uint32_t before = 0;
+            for (uint32_t w = 0; w < warp; w++) before += warp_cnt[w][d];
+            dst = run[d] + before + rank_in_warp;
+        }
+        __syncthreads();
+        // one thread per digit folds the chunk into the running count and clears the table
+        for (int b = threadIdx.x; b < RS_BINS; b += RS_THREADS) {
+            uint32_t s = 0;
+#pragma unroll
+            for (int w = 0; w < RS_WARPS; w++) { s += warp_cnt[w][b]; warp_cnt[w][b] = 0; }
+            run[b] += s;
+        }
+        if (live) {
+            keys_out[dst] = key;
+            vals_out[dst] = val;
+        }
+        __syncthreads();
+    }
+}
+
 namespace {
 
 template <typename TIn, typename TOut>

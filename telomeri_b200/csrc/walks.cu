@@ -14,6 +14,8 @@
 // associates differently, so it is used only when every partial sum is provably exact (all
 // addends non-negative finite multiples of 2^k and the total below 2^(k+53)): then any order
 // gives the sequential result bit for bit.  Otherwise the warp accumulates in list order.
+#include <algorithm>
+
 #include "ctx.cuh"
 #include "primitives.cuh"
 
