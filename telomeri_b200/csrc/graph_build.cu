@@ -293,6 +293,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         HERA_CUDA(cudaEventElapsedTime(&csr_ms, ev[1], ev[2]));
         HERA_CUDA(cudaEventElapsedTime(&rank_ms, ev[2], ev[3]));
     }
+    if (E == 0) for (int m = 0; m < 4; m++) g.rank_ready[m] = (metrics_mask >> m) & 1u;  // empty permutations
     g.ready = true;
     for (auto &e : ev) cudaEventDestroy(e);
     if (out) {
@@ -346,6 +347,8 @@ void export_graph(Ctx &c, hera_graph_view *out) {
     out->nodes = N; out->edges = E; out->slots = S;
     m.node_name_off.reserve(N + 1); m.adj_off.reserve(N + 1); m.node_names.reserve(1);
     m.node_name_off.p[0] = 0; m.adj_off.p[0] = 0;
+    m.canon.reserve(1);
+    for (int k = 0; k < 4; k++) if (g.rank_ready[k]) m.rank[k].reserve(1);
     if (E > 0) {
         d2h(c, m.node_len, g.node_len.p, N);
         d2h(c, m.node_anchor, g.node_anchor.p, N);
