@@ -124,6 +124,13 @@ hera_ctx *hera_create(int device);               /* NULL if the device cannot be
 void hera_destroy(hera_ctx *ctx);
 const char *hera_last_error(hera_ctx *ctx);      /* ctx may be NULL: error of the last failed hera_create */
 uint64_t hera_kernel_launches(hera_ctx *ctx);    /* kernels launched by this context so far */
+/* Measurement helpers (no reference counterpart; the reference only has Stopwatch, src/Stopwatch.cpp):
+ * a CUDA-event pair on the context's own stream, and integer knobs.
+ * Options: "flush_l2" (1 = write a buffer larger than L2 before every event-timed kernel region,
+ * outside the timed region), "walk_warps_per_sm" (resident walk warps per SM, default 32). */
+int hera_timer_start(hera_ctx *ctx);
+int hera_timer_stop(hera_ctx *ctx, float *ms);   /* synchronises the stream */
+int hera_set_option(hera_ctx *ctx, const char *key, int64_t value);
 
 /* ---- OverlapGraph ------------------------------------------------------------------------ */
 /* graph.filter_params_ = ... (src/Main.cpp:213-217) */

@@ -67,6 +67,9 @@ SIGNATURES = {
     "hera_destroy": (None, [C.c_void_p]),
     "hera_last_error": (C.c_char_p, [C.c_void_p]),
     "hera_kernel_launches": (C.c_uint64, [C.c_void_p]),
+    "hera_timer_start": (C.c_int, [C.c_void_p]),
+    "hera_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "hera_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "hera_graph_set_filter": (C.c_int, [C.c_void_p, C.POINTER(FilterParams)]),
     "hera_graph_load_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_bytes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
@@ -147,6 +150,17 @@ class Hera:
     @property
     def launches(self):
         return int(self.lib.hera_kernel_launches(self.h))
+
+    def timer_start(self):
+        self._check(self.lib.hera_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._check(self.lib.hera_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def set_option(self, key, value):
+        self._check(self.lib.hera_set_option(self.h, key.encode(), int(value)))
 
     def set_filter(self, fp):
         self._check(self.lib.hera_graph_set_filter(self.h, C.byref(fp)))

@@ -7,6 +7,18 @@
 
 namespace hera {
 uint64_t padded_text_size(uint64_t n);  // paf_parse.cu
+
+__global__ void l2_flush_kernel(uint4 *p, uint64_t n) {
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<uint64_t>(gridDim.x) * blockDim.x) p[i] = make_uint4(i, 0, 0, 0);
+}
+
+void maybe_flush_l2(Ctx &c) {
+    if (!c.opt_flush_l2) return;
+    const uint64_t bytes = 512ull << 20;
+    c.l2_flush_buf.reserve(bytes);
+    l2_flush_kernel<<<1184, 256, 0, c.stream>>>(reinterpret_cast<uint4 *>(c.l2_flush_buf.p), bytes / 16);
+    HERA_CUDA(cudaGetLastError());
+}
 static std::string g_create_error;
 }  // namespace hera
 
@@ -73,6 +85,32 @@ void hera_destroy(hera_ctx *ctx) {
 const char *hera_last_error(hera_ctx *ctx) { return ctx ? ctx->c.err.c_str() : hera::g_create_error.c_str(); }
 
 uint64_t hera_kernel_launches(hera_ctx *ctx) { return ctx ? ctx->c.launches.count : 0; }
+
+int hera_timer_start(hera_ctx *ctx) {
+    HERA_API_BEGIN(ctx)
+    if (!c.timer0) { HERA_CUDA(cudaEventCreate(&c.timer0)); HERA_CUDA(cudaEventCreate(&c.timer1)); }
+    HERA_CUDA(cudaEventRecord(c.timer0, c.stream));
+    HERA_API_END
+}
+
+int hera_timer_stop(hera_ctx *ctx, float *ms) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(c.timer0 != nullptr && ms != nullptr, 101, "hera_timer_stop without hera_timer_start");
+    HERA_CUDA(cudaEventRecord(c.timer1, c.stream));
+    HERA_CUDA(cudaEventSynchronize(c.timer1));
+    HERA_CUDA(cudaEventElapsedTime(ms, c.timer0, c.timer1));
+    HERA_API_END
+}
+
+int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(key != nullptr, 101, "null option name");
+    const std::string k(key);
+    if (k == "flush_l2") c.opt_flush_l2 = value != 0;
+    else if (k == "walk_warps_per_sm") c.opt_walk_warps_per_sm = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(64, value)));
+    else throw hera::Error{102, "unknown option: " + k};
+    HERA_API_END
+}
 
 int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp) {
     HERA_API_BEGIN(ctx)

@@ -81,6 +81,11 @@ struct Ctx {
     Launches launches;
     std::string err;
     hera_filter_params fp{HERA_MODE_AVG, 0, 0.0f, UINT64_MAX, 1.0f};
+    // measurement helpers / knobs
+    cudaEvent_t timer0 = nullptr, timer1 = nullptr;
+    int opt_flush_l2 = 0;
+    int opt_walk_warps_per_sm = 32;
+    DBuf<uint8_t> l2_flush_buf;
 
     std::vector<std::unique_ptr<LoadedText>> texts;
     KeptTable kept;
@@ -126,6 +131,9 @@ void exclusive_scan_u32_to_u64(Ctx &c, const uint32_t *in, uint64_t n, uint64_t 
 // Stable sort of (key, value) by the low `bits` bits of key.  Result ends up in keys/vals (the
 // alt buffers are scratch of the same size).
 void radix_sort_pairs(Ctx &c, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt, uint32_t *vals_alt, uint64_t n, int bits);
+
+// Writes a buffer larger than L2 when the flush_l2 option is on (call before an event-timed region).
+void maybe_flush_l2(Ctx &c);
 
 // ---- stages ------------------------------------------------------------------------------
 void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, hera_load_result *out);

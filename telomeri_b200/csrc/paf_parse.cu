@@ -544,6 +544,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     cudaEvent_t ev0, ev1;
     HERA_CUDA(cudaEventCreate(&ev0));
     HERA_CUDA(cudaEventCreate(&ev1));
+    maybe_flush_l2(c);
     HERA_CUDA(cudaEventRecord(ev0, c.stream));
     ParseArgs a{text.bytes.p, n, tiles, file_id, anchors ? 1 : 0, rec_limit, c.kept.n, fd, kept_ptrs(c.kept), tok_state, kept_state, ctr};
     HERA_LAUNCH(c, paf_parse_kernel, tiles, PF_THREADS, 0, a);

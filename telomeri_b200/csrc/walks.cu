@@ -448,7 +448,7 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
         const uint32_t cap = static_cast<uint32_t>(g.N + 1), words = static_cast<uint32_t>((g.N + 31) / 32);
         const uint64_t per_warp = (3ull * cap + words) * sizeof(uint32_t);
-        uint64_t warps = static_cast<uint64_t>(sms) * 32;
+        uint64_t warps = static_cast<uint64_t>(sms) * c.opt_walk_warps_per_sm;
         while (warps > WK_WARPS && warps * per_warp > (8ull << 30)) warps /= 2;
         if (warps > total_walks) warps = (total_walks + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
         const unsigned blocks = static_cast<unsigned>((warps + WK_WARPS - 1) / WK_WARPS);

@@ -23,7 +23,7 @@ def declared_symbols():
 def test_header_symbols_are_exported(lib_path):
     lib = ctypes.CDLL(str(lib_path))
     names = declared_symbols()
-    assert len(names) >= 17
+    assert len(names) >= 20
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/hera_b200.h but not exported"
 
