@@ -85,6 +85,7 @@ struct Ctx {
     cudaEvent_t timer0 = nullptr, timer1 = nullptr;
     int opt_flush_l2 = 0;
     int opt_walk_warps_per_sm = 32;
+    uint64_t walk_pool_hint = 0;   // largest path pool a walk call needed so far (avoids the overflow re-run)
     DBuf<uint8_t> l2_flush_buf;
 
     std::vector<std::unique_ptr<LoadedText>> texts;

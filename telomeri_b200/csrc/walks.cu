@@ -465,7 +465,7 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         HERA_CUDA(cudaMallocAsync(&r.slots, warps * cap * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&r.vlog, warps * cap * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMemsetAsync(r.bitmap, 0, warps * words * sizeof(uint32_t), c.stream));
-        uint64_t pool_cap = std::max<uint64_t>(1u << 16, std::min<uint64_t>(static_cast<uint64_t>(total_walks) * 128, 1ull << 28));
+        uint64_t pool_cap = std::max<uint64_t>(std::max<uint64_t>(1u << 16, c.walk_pool_hint), std::min<uint64_t>(static_cast<uint64_t>(total_walks) * 256, 1ull << 28));
         unsigned long long h_ctr[4];
         for (;;) {
             HERA_CUDA(cudaMallocAsync(&r.pool_nodes, pool_cap * sizeof(uint32_t), c.stream));
@@ -487,6 +487,7 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         }
         HERA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
         steps = h_ctr[1];
+        c.walk_pool_hint = std::max<uint64_t>(c.walk_pool_hint, h_ctr[0] + h_ctr[0] / 8);
         const uint64_t new_nodes = h_ctr[0];
 
         // order by walk id and append to the path store
