@@ -67,7 +67,31 @@ def build_tools():
     subprocess.run(["make", "-s", "-C", str(ROOT / "oracle"), "bin/hera_oracle", "ref"], check=True)
 
 
+def build_host():
+    """Drop-in command-line binary: reference class surface (telomeri_b200/host) over the C ABI.
+    bin/Telomeri uses this repo's Main.cpp; bin/Telomeri_refmain is the REFERENCE's own, unmodified
+    src/Main.cpp compiled against our headers (only where /root/reference exists; output is
+    git-ignored and travels to the GPU box like the other built files)."""
+    host = PKG / "host"
+    out_dir = PKG / "bin"
+    out_dir.mkdir(exist_ok=True)
+    srcs = sorted((host / "src").glob("*.cpp"))
+    deps = srcs + sorted((host / "include").glob("*.hpp")) + [ROOT / "include" / "hera_b200.h", LIB]
+    common = ["g++", "-O2", "-std=c++17", f"-I{host / 'include'}", f"-I{ROOT / 'include'}"]
+    link = [f"-L{PKG}", "-lhera_b200", "-Wl,-rpath,$ORIGIN/.."]
+    exe = out_dir / "Telomeri"
+    if _newer(exe, deps):
+        subprocess.run(common + ["-Wall", "-o", str(exe)] + [str(s) for s in srcs] + link, check=True)
+    ref_main = Path("/root/reference/src/Main.cpp")
+    if ref_main.exists():
+        exe2 = out_dir / "Telomeri_refmain"
+        if _newer(exe2, deps + [ref_main]):
+            subprocess.run(common + ["-w", "-o", str(exe2), str(ref_main)] + [str(s) for s in srcs if s.name != "Main.cpp"] + link, check=True)
+    return exe
+
+
 if __name__ == "__main__":
     build_library(force="--force" in sys.argv, verbose="-v" in sys.argv)
     build_tools()
+    build_host()
     print(LIB)
