@@ -64,7 +64,7 @@ def build_tools():
     gen = tools_bin / "gen_dataset"
     if _newer(gen, [ROOT / "tools" / "gen_dataset.cpp"]):
         subprocess.run(["g++", "-O2", "-std=c++17", "-o", str(gen), str(ROOT / "tools" / "gen_dataset.cpp")], check=True)
-    subprocess.run(["make", "-s", "-C", str(ROOT / "oracle"), "bin/hera_oracle", "ref"], check=True)
+    subprocess.run(["make", "-s", "-C", str(ROOT / "oracle"), "bin/hera_oracle", "ref"], check=True, stdout=sys.stderr)
 
 
 def build_host():

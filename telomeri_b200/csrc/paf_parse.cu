@@ -29,12 +29,12 @@
 namespace hera {
 
 constexpr int PF_THREADS = 256;
-constexpr int PF_TILE = 8192;
-constexpr int PF_HALO = 512;
+constexpr int PF_TILE = 24576;
+constexpr int PF_HALO = 1024;
 constexpr int PF_WIN = PF_TILE + PF_HALO;
 constexpr int PF_CHUNKS = PF_WIN / 16;
-constexpr int PF_MAXTOK = PF_WIN / 2 + 1;
-constexpr int PF_MAXREC = PF_TILE / 2 / 16 + 2;
+constexpr int PF_CPT = (PF_TILE / 16 + PF_THREADS - 1) / PF_THREADS;   // tile chunks owned by one thread
+constexpr int PF_MAXREC = PF_TILE / 32 + 2;   // a record is at least 16 tokens + 16 separators
 
 struct FilterDev {
     int mode;
@@ -65,8 +65,12 @@ __device__ __forceinline__ uint64_t hash_finish(uint64_t h) {
     h ^= h >> 33; h *= 0xff51afd7ed558ccdull; h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ull; h ^= h >> 33;
     return h ? h : 1;  // 0 is the empty marker of the interning table
 }
-constexpr uint64_t HASH_SEED = 0xcbf29ce484222325ull;
-constexpr uint64_t HASH_MUL = 0x100000001b3ull;
+// Name hash: two 32-bit multiplicative lanes (cheap per byte), mixed to 64 bits at the end.
+struct NameHash {
+    uint32_t x = 0x811C9DC5u, y = 0x9747B28Cu;
+    __device__ __forceinline__ void add(uint32_t c) { x = (x ^ c) * 0x01000193u; y = (y ^ c) * 0x85EBCA6Bu; }
+    __device__ __forceinline__ uint64_t finish() const { return hash_finish((static_cast<uint64_t>(y) << 32) | x); }
+};
 
 // fp32 filter, reference src/OverlapGraph.cpp:156-202 (name equality is checked by the caller).
 __device__ __forceinline__ bool filter_fields(const FilterDev &f, int qlen, int qs, int qe, int tlen, int ts, int te) {
@@ -122,10 +126,10 @@ struct SerialCursor {
         skip();
         if (p >= n) return good = false;
         off = p;
-        uint64_t h = HASH_SEED;
-        while (p < n && !dev_is_space(t[p])) { h = (h ^ t[p]) * HASH_MUL; p++; }
+        NameHash h;
+        while (p < n && !dev_is_space(t[p])) { h.add(t[p]); p++; }
         len = static_cast<uint32_t>(p - off);
-        hash = hash_finish(h);
+        hash = h.finish();
         return true;
     }
     __device__ bool integer(int &out) {
@@ -259,13 +263,98 @@ struct ParseArgs {
     ParseCounters *ctr;
 };
 
+// Exact reader for a record that does not fit the shared-memory window (very long names).
+// Returns 1 = regular record in r, 0 = irregular (the tail kernel will deal with it).
+__device__ int slow_path_record(const ParseArgs &a, uint64_t start, SerialRecord &r) {
+    SerialCursor cur{a.text, a.n, start, true};
+    if (!serial_read_record(cur, r)) return 0;
+    // regular iff every typed token ended at white space
+    SerialCursor chk{a.text, a.n, start, true};
+    uint64_t o, hh; uint32_t l; int iv; uint32_t chh;
+    bool whole = true;
+    chk.word(o, l, hh);
+    for (int f = 0; f < 3 && whole; f++) { chk.integer(iv); whole = chk.p >= a.n || dev_is_space(a.text[chk.p]); }
+    if (whole) { chk.single(chh); whole = chk.p >= a.n || dev_is_space(a.text[chk.p]); }
+    if (whole) chk.word(o, l, hh);
+    for (int f = 0; f < 6 && whole; f++) { chk.integer(iv); whole = chk.p >= a.n || dev_is_space(a.text[chk.p]); }
+    return whole ? 1 : 0;
+}
+
+// One thread reads one record from the staged window.  Returns the keep flag.
+__device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, uint32_t p0, uint64_t tile_byte0, bool reaches_eof,
+                                          uint64_t rec_idx, StagedRecord &out) {
+    if (rec_idx >= a.rec_limit) return false;
+    SerialRecord r;
+    uint32_t p = p0;
+    int status = 1;  // 1 regular, 0 irregular, 2 window exhausted
+    auto read_name = [&](uint64_t &off, uint32_t &len, uint64_t &hash) {
+        NameHash h;
+        const uint32_t b = p;
+        uint32_t c;
+        while (p < PF_WIN && !dev_is_space(c = s[p])) { h.add(c); p++; }
+        if (p >= PF_WIN) status = 2;
+        off = tile_byte0 + b; len = p - b; hash = h.finish();
+    };
+    auto skip_space = [&]() {
+        while (p < PF_WIN && dev_is_space(s[p])) p++;
+        if (p >= PF_WIN) status = 2;
+    };
+    auto read_int = [&](int &v) {
+        uint32_t c = s[p];
+        bool neg = false;
+        if (c == '+' || c == '-') { neg = c == '-'; p++; c = p < PF_WIN ? s[p] : ' '; }
+        unsigned long long acc = 0;
+        uint32_t digits = 0, d;
+        while ((d = c - '0') <= 9u) {
+            if (acc <= 4294967295ull) acc = acc * 10 + d;
+            digits++; p++;
+            if (p >= PF_WIN) { status = 2; return; }
+            c = s[p];
+        }
+        if (!dev_is_space(c) || digits == 0 || acc > (neg ? 2147483648ull : 2147483647ull)) { status = 0; return; }
+        v = neg ? static_cast<int>(0u - static_cast<uint32_t>(acc)) : static_cast<int>(static_cast<uint32_t>(acc));
+    };
+    read_name(r.qoff, r.qnlen, r.qhash);
+    int *ints3[3] = {&r.qlen, &r.qs, &r.qe};
+#pragma unroll
+    for (int f = 0; f < 3 && status == 1; f++) { skip_space(); if (status == 1) read_int(*ints3[f]); }
+    if (status == 1) skip_space();
+    if (status == 1) {  // strand: exactly one character
+        r.strand = s[p++];
+        if (p >= PF_WIN) status = 2; else if (!dev_is_space(s[p])) status = 0;
+    }
+    if (status == 1) skip_space();
+    if (status == 1) read_name(r.toff, r.tnlen, r.thash);
+    int *ints6[6] = {&r.tlen, &r.ts, &r.te, &r.matches, &r.block, &r.mapq};
+#pragma unroll
+    for (int f = 0; f < 6 && status == 1; f++) { skip_space(); if (status == 1) read_int(*ints6[f]); }
+    if (status == 2) {
+        if (reaches_eof) return false;  // trailing record with fewer than 12 tokens: not a record
+        status = slow_path_record(a, tile_byte0 + p0, r);
+    }
+    if (status == 0) {
+        atomicMin(&a.ctr->first_bad_rec, static_cast<unsigned long long>(rec_idx));
+        atomicMin(&a.ctr->first_bad_off, static_cast<unsigned long long>(tile_byte0 + p0));
+        return false;
+    }
+    return make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), out);
+}
+
+// 4 bits: byte b of w is not white space (SWAR, no per-byte loop).
+__device__ __forceinline__ uint32_t nonspace4(uint32_t w) {
+    const uint32_t low7 = w & 0x7f7f7f7fu;
+    const uint32_t x = w ^ 0x20202020u;
+    const uint32_t is20 = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x) & 0x80808080u;          // byte == 0x20
+    const uint32_t ge9 = low7 + 0x77777777u, ge14 = low7 + 0x72727272u;                      // bit 7: low7 >= 9 / >= 14
+    const uint32_t ctl = ge9 & ~ge14 & ~w & 0x80808080u;                                     // 9 <= byte <= 13
+    const uint32_t ns = ~(is20 | ctl) & 0x80808080u;
+    return (((ns >> 7) * 0x00204081u) >> 21) & 0xfu;
+}
+
 __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a) {
     __shared__ __align__(16) uint8_t s_text[PF_WIN];
     __shared__ uint16_t s_nonws[PF_CHUNKS + 1];
-    __shared__ uint16_t s_chunk_pre[PF_CHUNKS + 1];
-    __shared__ uint16_t s_tok_off[PF_MAXTOK];
-    __shared__ StagedRecord s_rec[PF_MAXREC];
-    __shared__ uint8_t s_keep[PF_MAXREC];
+    __shared__ uint16_t s_rec_off[PF_MAXREC];
     __shared__ uint32_t s_scan[33];
     __shared__ unsigned int s_tile;
     __shared__ unsigned long long s_tok_base, s_kept_base;
@@ -276,196 +365,84 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
     const uint32_t tile = s_tile;
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
 
-    // 1. stage tile + halo, classify bytes
+    // 1. stage tile + halo with 128-bit loads, classify bytes
     const uint4 *src = reinterpret_cast<const uint4 *>(a.text + tile_byte0);
+#pragma unroll 2
     for (int ch = tid; ch < PF_CHUNKS; ch += PF_THREADS) {
         const uint4 v = __ldg(src + ch);
         reinterpret_cast<uint4 *>(s_text)[ch] = v;
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-        uint32_t m = 0;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-#pragma unroll
-            for (int b = 0; b < 4; b++) {
-                const uint32_t c = (w[j] >> (8 * b)) & 0xffu;
-                m |= (dev_is_space(c) ? 0u : 1u) << (4 * j + b);
-            }
-        }
-        s_nonws[ch + 1] = static_cast<uint16_t>(m);
+        s_nonws[ch + 1] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
     }
     if (tid == 0) {
-        // byte before the tile decides whether the tile's first byte starts a token
-        uint32_t prev_nonws = 0;
+        uint32_t prev_nonws = 0;  // does the byte before the tile belong to a token?
         if (tile_byte0 > 0) prev_nonws = dev_is_space(a.text[tile_byte0 - 1]) ? 0u : 1u;
         s_nonws[0] = static_cast<uint16_t>(prev_nonws << 15);
     }
     __syncthreads();
 
-    // token-start masks and per-chunk counts; chunks of the tile proper count towards the chain
-    uint32_t my_cnt[(PF_CHUNKS + PF_THREADS - 1) / PF_THREADS];
-    uint32_t my_mask[(PF_CHUNKS + PF_THREADS - 1) / PF_THREADS];
-    uint32_t tile_tokens_local = 0;
-    // thread t owns chunks [t*3, t*3+3) so that the chunk order equals the thread order
-    constexpr int CPT = (PF_CHUNKS + PF_THREADS - 1) / PF_THREADS;
+    // 2. token starts of the chunks this thread owns (consecutive chunks, so thread order = text order)
+    uint32_t my_mask[PF_CPT];
+    uint32_t my_tokens = 0;
 #pragma unroll
-    for (int k = 0; k < CPT; k++) {
-        const int ch = tid * CPT + k;
+    for (int k = 0; k < PF_CPT; k++) {
+        const int ch = tid * PF_CPT + k;
         uint32_t starts = 0;
-        if (ch < PF_CHUNKS) {
+        if (ch < PF_TILE / 16) {
             const uint32_t cur = s_nonws[ch + 1];
-            const uint32_t prev_top = (s_nonws[ch] >> 15) & 1u;
-            starts = cur & ~((cur << 1) | prev_top) & 0xffffu;
+            starts = cur & ~((cur << 1) | ((s_nonws[ch] >> 15) & 1u)) & 0xffffu;
         }
         my_mask[k] = starts;
-        my_cnt[k] = __popc(starts);
-        if (ch < PF_TILE / 16) tile_tokens_local += my_cnt[k];
+        my_tokens += __popc(starts);
     }
-    uint32_t thread_total = 0;
-#pragma unroll
-    for (int k = 0; k < CPT; k++) thread_total += my_cnt[k];
-    uint32_t win_tokens;
-    uint32_t excl = block_exclusive_scan<uint32_t>(thread_total, s_scan, &win_tokens);
     uint32_t tile_tokens;
-    block_exclusive_scan<uint32_t>(tile_tokens_local, s_scan, &tile_tokens);
-
-    // 2. first chain: global index of the tile's first token
-    if (warp == 0) {
-        unsigned long long base = chain_exclusive(a.tok_state, tile, tile_tokens);
+    const uint32_t excl = block_exclusive_scan<uint32_t>(my_tokens, s_scan, &tile_tokens);
+    if (warp == 0) {  // first chain: global index of the tile's first token
+        const unsigned long long base = chain_exclusive(a.tok_state, tile, tile_tokens);
         if (lane == 0) {
             s_tok_base = base;
             if (tile == a.tiles - 1) a.ctr->total_tokens = base + tile_tokens;
-        }
-    }
-    // 3a. compact token starts to offsets (all tokens of the window)
-    {
-        uint32_t pos = excl;
-#pragma unroll
-        for (int k = 0; k < CPT; k++) {
-            const int ch = tid * CPT + k;
-            uint32_t m = my_mask[k];
-            while (m) {
-                const int b = __ffs(m) - 1;
-                m &= m - 1;
-                if (pos < PF_MAXTOK) s_tok_off[pos] = static_cast<uint16_t>(ch * 16 + b);
-                pos++;
-            }
         }
     }
     __syncthreads();
     const unsigned long long tok_base = s_tok_base;
     const uint32_t first_rec_ord = static_cast<uint32_t>((16 - (tok_base & 15)) & 15);
     const uint32_t nrec = tile_tokens > first_rec_ord ? (tile_tokens - first_rec_ord + 15) / 16 : 0;  // records starting in this tile
-    const bool window_reaches_eof = tile_byte0 + PF_WIN >= a.n;
+    const bool reaches_eof = tile_byte0 + PF_WIN >= a.n;
 
-    // 3b. one half-warp per record
-    const uint32_t half = tid >> 4, k = tid & 15;
-    for (uint32_t j0 = 0; j0 < nrec; j0 += PF_THREADS / 16) {
-        const uint32_t j = j0 + half;
-        const bool have_rec = j < nrec;
-        const uint32_t ord = first_rec_ord + j * 16 + k;
-        const bool exists = have_rec && ord < win_tokens;
-        uint32_t off = exists ? s_tok_off[ord] : 0;
-        // parse my token
-        uint64_t h = HASH_SEED;
-        unsigned long long val = 0;
-        uint32_t len = 0, digits = 0, bad = 0, neg = 0, first_ch = 0;
-        if (exists) {
-            uint32_t c = s_text[off];
-            first_ch = c;
-            while (!dev_is_space(c)) {
-                h = (h ^ c) * HASH_MUL;
-                const uint32_t dgt = c - '0';
-                if (dgt <= 9u) {
-                    if (val <= 4294967295ull) val = val * 10 + dgt;
-                    digits++;
-                } else if (len == 0 && (c == '-' || c == '+')) {
-                    neg = c == '-';
-                } else {
-                    bad = 1;
-                }
-                len++;
-                if (off + len >= PF_WIN) break;
-                c = s_text[off + len];
+    // 3. every 16th token opens a record: note its offset
+    {
+        uint32_t o = excl;
+#pragma unroll
+        for (int k = 0; k < PF_CPT; k++) {
+            const uint32_t cnt = __popc(my_mask[k]);
+            const uint32_t rem = static_cast<uint32_t>((16 - ((tok_base + o) & 15)) & 15);
+            if (rem < cnt) {  // a 16-byte chunk holds at most 8 token starts, so at most one record start
+                const uint32_t bit = __fns(my_mask[k], 0, static_cast<int>(rem) + 1);
+                s_rec_off[(o + rem - first_rec_ord) >> 4] = static_cast<uint16_t>((tid * PF_CPT + k) * 16 + bit);
             }
-        }
-        const bool unterminated = exists && (off + len >= PF_WIN) && !window_reaches_eof;
-        const bool int_ok = exists && !bad && digits > 0 && val <= (neg ? 2147483648ull : 2147483647ull);
-        const int ival = neg ? static_cast<int>(0u - static_cast<uint32_t>(val)) : static_cast<int>(static_cast<uint32_t>(val));
-        const bool is_int_tok = (k >= 1 && k <= 3) || (k >= 6 && k <= 11);
-        const bool tok_ok = k >= 12 ? true : (is_int_tok ? int_ok : (k == 4 ? (exists && len == 1) : exists));
-        const uint32_t hw_mask = 0xffffu << (lane & 16);
-        const uint32_t ok_ballot = __ballot_sync(0xffffffffu, tok_ok) & hw_mask;
-        const uint32_t exist_ballot = __ballot_sync(0xffffffffu, exists) & hw_mask;
-        const uint32_t unterm_ballot = __ballot_sync(0xffffffffu, unterminated && k < 12) & hw_mask;
-        const uint32_t base_lane = lane & 16;
-        // gather
-        SerialRecord r;
-        r.qlen = __shfl_sync(0xffffffffu, ival, base_lane + 1); r.qs = __shfl_sync(0xffffffffu, ival, base_lane + 2);
-        r.qe = __shfl_sync(0xffffffffu, ival, base_lane + 3); r.strand = __shfl_sync(0xffffffffu, first_ch, base_lane + 4);
-        r.tlen = __shfl_sync(0xffffffffu, ival, base_lane + 6); r.ts = __shfl_sync(0xffffffffu, ival, base_lane + 7);
-        r.te = __shfl_sync(0xffffffffu, ival, base_lane + 8); r.matches = __shfl_sync(0xffffffffu, ival, base_lane + 9);
-        const uint64_t hf = hash_finish(h);
-        r.qhash = __shfl_sync(0xffffffffu, hf, base_lane + 0); r.thash = __shfl_sync(0xffffffffu, hf, base_lane + 5);
-        r.qnlen = __shfl_sync(0xffffffffu, len, base_lane + 0); r.tnlen = __shfl_sync(0xffffffffu, len, base_lane + 5);
-        const uint32_t qoff_l = __shfl_sync(0xffffffffu, off, base_lane + 0), toff_l = __shfl_sync(0xffffffffu, off, base_lane + 5);
-        r.qoff = tile_byte0 + qoff_l; r.toff = tile_byte0 + toff_l;
-        if (k == 0 && have_rec) {
-            const uint64_t rec_idx = (tok_base + first_rec_ord) / 16 + j;
-            const uint32_t twelve = 0x0fffu << base_lane;
-            bool keep = false;
-            if (rec_idx < a.rec_limit) {
-                const bool all_exist = (exist_ballot & twelve) == twelve;
-                bool regular = all_exist && ((ok_ballot & twelve) == twelve);
-                bool complete = all_exist;
-                if ((!all_exist && !window_reaches_eof) || (unterm_ballot & twelve)) {
-                    // record does not fit the window (very long names): exact serial reader from its first byte
-                    SerialCursor cur{a.text, a.n, r.qoff, true};
-                    SerialRecord sr;
-                    const bool got = serial_read_record(cur, sr);
-                    // regular iff the reader consumed whole tokens only; otherwise flag it for the tail kernel
-                    bool whole = got;
-                    if (got) {
-                        // re-check token regularity: each integer token must end at white space
-                        SerialCursor chk{a.text, a.n, r.qoff, true};
-                        uint64_t o, hh; uint32_t l; int iv; uint32_t chh;
-                        chk.word(o, l, hh);
-                        for (int f = 0; f < 3 && whole; f++) { chk.integer(iv); whole = chk.p >= a.n || dev_is_space(a.text[chk.p]); }
-                        if (whole) { chk.single(chh); whole = chk.p >= a.n || dev_is_space(a.text[chk.p]); }
-                        if (whole) chk.word(o, l, hh);
-                        for (int f = 0; f < 6 && whole; f++) { chk.integer(iv); whole = chk.p >= a.n || dev_is_space(a.text[chk.p]); }
-                    }
-                    complete = true;
-                    regular = whole;
-                    r = sr;
-                }
-                if (complete) {
-                    if (!regular) {
-                        atomicMin(&a.ctr->first_bad_rec, static_cast<unsigned long long>(rec_idx));
-                        atomicMin(&a.ctr->first_bad_off, static_cast<unsigned long long>(tile_byte0 + s_tok_off[first_rec_ord + j * 16]));
-                    } else {
-                        keep = make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), s_rec[j]);
-                    }
-                }
-            }
-            s_keep[j] = keep ? 1 : 0;
+            o += cnt;
         }
     }
     __syncthreads();
 
-    // 4. compact kept records of the tile, second chain, store
-    uint32_t mine = 0;
-    for (uint32_t j = tid; j < nrec; j += PF_THREADS) mine += s_keep[j];  // nrec <= PF_MAXREC <= 2 * PF_THREADS
-    uint32_t tile_kept;
-    // thread t owns records t and t + PF_THREADS; to keep file order, scan the two rounds separately
-    uint32_t k0 = tid < nrec ? s_keep[tid] : 0;
-    uint32_t k1 = tid + PF_THREADS < nrec ? s_keep[tid + PF_THREADS] : 0;
-    uint32_t tot0, tot1;
-    const uint32_t e0 = block_exclusive_scan<uint32_t>(k0, s_scan, &tot0);
-    const uint32_t e1 = block_exclusive_scan<uint32_t>(k1, s_scan, &tot1);
-    tile_kept = tot0 + tot1;
-    (void) mine;
-    if (warp == 0) {
-        unsigned long long base = chain_exclusive(a.kept_state, tile, tile_kept);
+    // 4. one thread per record: parse, filter, score.  Tiles with more than PF_THREADS records (tiny records) take
+    //    further rounds; their records are parsed again after the chain instead of being kept in registers.
+    const uint64_t first_rec = (tok_base + first_rec_ord) >> 4;
+    StagedRecord mine;
+    bool keep0 = false;
+    uint32_t e0 = 0, tot0 = 0, tile_kept = 0;
+    for (uint32_t b0 = 0; b0 < nrec; b0 += PF_THREADS) {
+        const uint32_t j = b0 + tid;
+        StagedRecord r;
+        bool keep = false;
+        if (j < nrec) keep = parse_one(a, s_text, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+        uint32_t tot;
+        const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
+        if (b0 == 0) { mine = r; keep0 = keep; e0 = ex; tot0 = tot; }
+        tile_kept += tot;
+    }
+    if (warp == 0) {  // second chain: where the tile's kept overlaps go
+        const unsigned long long base = chain_exclusive(a.kept_state, tile, tile_kept);
         if (lane == 0) {
             s_kept_base = base;
             if (tile == a.tiles - 1) a.ctr->kept = base + tile_kept;
@@ -473,8 +450,18 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
     }
     __syncthreads();
     const uint64_t out0 = a.kept_base + s_kept_base;
-    if (k0) store_record(a.kept, out0 + e0, s_rec[tid]);
-    if (k1) store_record(a.kept, out0 + tot0 + e1, s_rec[tid + PF_THREADS]);
+    if (keep0) store_record(a.kept, out0 + e0, mine);
+    uint32_t run = tot0;
+    for (uint32_t b0 = PF_THREADS; b0 < nrec; b0 += PF_THREADS) {
+        const uint32_t j = b0 + tid;
+        StagedRecord r;
+        bool keep = false;
+        if (j < nrec) keep = parse_one(a, s_text, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+        uint32_t tot;
+        const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
+        if (keep) store_record(a.kept, out0 + run + ex, r);
+        run += tot;
+    }
 }
 
 // Finds how many kept records of this load precede the first irregular record.
