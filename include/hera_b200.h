@@ -132,6 +132,41 @@ int hera_timer_start(hera_ctx *ctx);
 int hera_timer_stop(hera_ctx *ctx, float *ms);   /* synchronises the stream */
 int hera_set_option(hera_ctx *ctx, const char *key, int64_t value);
 
+/* ---- sharded runs: one rank per GPU ---------------------------------------------
+ * No reference counterpart (the reference is single-threaded, src/Main.cpp).  A communicator is
+ * attached to a context once; afterwards hera_graph_load_file / hera_graph_load_shard,
+ * hera_graph_finalize, hera_paths_monte_carlo and hera_paths_deterministic are COLLECTIVE: every
+ * rank must call them with the same arguments.  The PAF text is parsed by byte range (each rank
+ * tokenizes, filters and scores its slice), kept overlaps are all-gathered in file order, walks are
+ * dealt out by walk id and the accepted paths all-gathered in the reference's path order, so every
+ * rank ends up with the same graph and the same paths_, bit for bit what one GPU produces.
+ *   NCCL transport: one process per GPU.  Rank 0 calls hera_nccl_unique_id, the launcher hands the
+ *   128 bytes to every rank (torch.distributed broadcast, MPI_Bcast, a file), each rank calls
+ *   hera_comm_init_nccl.  libnccl.so.2 is loaded on demand.
+ *   Local transport: several contexts of one process, one host thread per rank
+ *   (hera_comm_local_create once, hera_comm_attach_local per context). */
+typedef struct hera_local_gang hera_local_gang;
+int hera_nccl_unique_id(void *out128, char *err, uint64_t err_cap);      /* 0 = ok; err gets a message otherwise */
+int hera_comm_init_nccl(hera_ctx *ctx, int rank, int nranks, const void *id128);
+hera_local_gang *hera_comm_local_create(int nranks);
+void hera_comm_local_destroy(hera_local_gang *gang);
+int hera_comm_attach_local(hera_ctx *ctx, hera_local_gang *gang, int rank);
+int hera_comm_rank(hera_ctx *ctx);   /* 0 without a communicator */
+int hera_comm_size(hera_ctx *ctx);   /* 1 without a communicator */
+/* The slice of a `file_bytes` long PAF file rank `rank` of `nranks` must hand to hera_graph_load_shard:
+ * it OWNS the tokens starting in [*begin, *end) and must also provide the bytes up to *avail_end
+ * (so that a record that starts in the slice can be finished) and the byte before *begin. */
+void hera_shard_range(uint64_t file_bytes, int rank, int nranks, uint64_t *begin, uint64_t *end, uint64_t *avail_end);
+/* OverlapGraph::load over a byte-range slice (collective).  text = bytes [begin, avail_end) of the
+ * file in host (on_device = 0) or device memory; owned = end - begin, avail = avail_end - begin;
+ * prev_byte = the file byte before `begin`, or -1 at the start of the file; at_eof = avail_end is the
+ * end of the file.  Results (records, kept, kept_total) are global.  Returns 20 (and changes nothing)
+ * when some slice holds a record formatted extraction would fail on (non-numeric field, strand of
+ * two characters, more than 16 columns ...): reload that file unsharded with
+ * hera_graph_load_bytes / hera_graph_load_device on every rank -- hera_graph_load_file does so itself. */
+int hera_graph_load_shard(hera_ctx *ctx, const void *text, int on_device, uint64_t owned, uint64_t avail, int prev_byte, int at_eof,
+                          int anchors, uint32_t test_load_num, hera_load_result *out);
+
 /* ---- OverlapGraph ------------------------------------------------------------------------ */
 /* graph.filter_params_ = ... (src/Main.cpp:213-217) */
 int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp);

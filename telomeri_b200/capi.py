@@ -74,6 +74,15 @@ SIGNATURES = {
     "hera_graph_load_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_bytes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
+    "hera_nccl_unique_id": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64]),
+    "hera_comm_init_nccl": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "hera_comm_local_create": (C.c_void_p, [C.c_int]),
+    "hera_comm_local_destroy": (None, [C.c_void_p]),
+    "hera_comm_attach_local": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "hera_comm_rank": (C.c_int, [C.c_void_p]),
+    "hera_comm_size": (C.c_int, [C.c_void_p]),
+    "hera_shard_range": (None, [C.c_uint64, C.c_int, C.c_int, u64p, u64p, u64p]),
+    "hera_graph_load_shard": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_reset": (C.c_int, [C.c_void_p]),
     "hera_graph_finalize": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(GraphInfo)]),
     "hera_graph_export": (C.c_int, [C.c_void_p, C.POINTER(GraphView)]),
@@ -186,6 +195,30 @@ class Hera:
         self._check(self.lib.hera_graph_load_device(self.h, C.c_void_p(ptr), n, int(anchors), test_load_num, C.byref(r)))
         return r
 
+    # ---- sharded runs (one rank per GPU) -------------------------------------------------------
+    @property
+    def rank(self):
+        return int(self.lib.hera_comm_rank(self.h))
+
+    @property
+    def size(self):
+        return int(self.lib.hera_comm_size(self.h))
+
+    def comm_init_nccl(self, rank, nranks, unique_id):
+        """unique_id: the 128 bytes rank 0 got from nccl_unique_id(), handed to every rank by the launcher."""
+        buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
+        self._check(self.lib.hera_comm_init_nccl(self.h, rank, nranks, buf))
+
+    def comm_attach_local(self, gang, rank):
+        self._check(self.lib.hera_comm_attach_local(self.h, gang, rank))
+
+    def load_shard_ptr(self, ptr, on_device, owned, avail, prev_byte, at_eof, anchors, test_load_num=0):
+        """Collective.  ptr = this rank's slice (see shard_range); returns global counts."""
+        r = LoadResult()
+        self._check(self.lib.hera_graph_load_shard(self.h, C.c_void_p(ptr), int(on_device), owned, avail, int(prev_byte), int(at_eof), int(anchors),
+                                                   test_load_num, C.byref(r)))
+        return r
+
     def graph_reset(self):
         self._check(self.lib.hera_graph_reset(self.h))
 
@@ -259,3 +292,59 @@ class Hera:
             "grp_pig": _arr(v.grp_pig, v.pig_total, np.uint32), "grp_consensus": _arr(v.grp_consensus, G, np.int64),
             "grp_valid": _arr(v.grp_valid, G, np.int32), "pair_consensus": _arr(v.pair_consensus, K, np.int64), "ms": float(v.ms),
         }
+
+
+def nccl_unique_id():
+    """128-byte NCCL id (rank 0 calls this, every rank passes it to Hera.comm_init_nccl)."""
+    lib = load_library()
+    out = (C.c_char * 128)()
+    err = C.create_string_buffer(512)
+    rc = lib.hera_nccl_unique_id(out, err, 512)
+    if rc != 0:
+        raise HeraError(rc, err.value.decode())
+    return bytes(out)
+
+
+def shard_range(file_bytes, rank, nranks):
+    """(begin, end, avail_end) of rank's slice of a file_bytes long PAF file (hera_shard_range)."""
+    lib = load_library()
+    b, e, a = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    lib.hera_shard_range(file_bytes, rank, nranks, C.byref(b), C.byref(e), C.byref(a))
+    return b.value, e.value, a.value
+
+
+class LocalGang:
+    """Several contexts of ONE process that run the sharded path together (local transport): one
+    host thread per rank; every method call is made on all ranks at once.  Used for single-process
+    multi-GPU runs and to exercise the sharded path on a single GPU."""
+
+    def __init__(self, nranks, devices=None):
+        import concurrent.futures
+        self.lib = load_library()
+        self.n = nranks
+        self.gang = self.lib.hera_comm_local_create(nranks)
+        devices = devices or [0] * nranks
+        self.ranks = [Hera(d) for d in devices]
+        for r, h in enumerate(self.ranks):
+            h.comm_attach_local(self.gang, r)
+        self.pool = concurrent.futures.ThreadPoolExecutor(max_workers=nranks)
+
+    def each(self, fn):
+        """fn(rank, hera) on every rank concurrently (ctypes calls release the GIL); returns the list of results."""
+        futs = [self.pool.submit(fn, r, h) for r, h in enumerate(self.ranks)]
+        return [f.result() for f in futs]
+
+    def close(self):
+        for h in self.ranks:
+            h.close()
+        self.ranks = []
+        if self.gang:
+            self.lib.hera_comm_local_destroy(self.gang)
+            self.gang = None
+        self.pool.shutdown()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()

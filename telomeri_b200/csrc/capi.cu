@@ -26,6 +26,10 @@ struct hera_ctx {
     hera::Ctx c;
 };
 
+struct hera_local_gang {
+    std::shared_ptr<hera::LocalHub> hub;
+};
+
 using hera::Ctx;
 
 #define HERA_API_BEGIN(ctxp)                                   \
@@ -39,9 +43,11 @@ using hera::Ctx;
     } catch (const hera::Error &e) {                           \
         c.err = e.msg;                                         \
         cudaGetLastError();                                    \
+        if (c.xch && e.code != 20) c.xch->abort();             \
         return e.code;                                         \
     } catch (const std::exception &e) {                        \
         c.err = e.what();                                      \
+        if (c.xch) c.xch->abort();                             \
         return 99;                                             \
     }
 
@@ -119,7 +125,8 @@ int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp) {
     HERA_API_END
 }
 
-static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind, int anchors, uint32_t test_load_num, hera_load_result *out) {
+static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard,
+                        hera_load_result *out) {
     std::unique_ptr<hera::LoadedText> t(new hera::LoadedText());
     t->n = n;
     t->bytes.reserve(hera::padded_text_size(n));
@@ -133,7 +140,15 @@ static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind
     HERA_REQUIRE(file_id < 16, 5, "more than 16 loads per graph are not supported");
     c.texts.push_back(std::move(t));
     hera_load_result tmp{};
-    hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, &tmp);
+    try {
+        hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, shard, &tmp);
+    } catch (...) {
+        cudaStreamSynchronize(c.stream);
+        c.texts.pop_back();   // the failed load leaves no trace
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        throw;
+    }
     float copy_ms = 0;
     HERA_CUDA(cudaEventElapsedTime(&copy_ms, e0, e1));
     cudaEventDestroy(e0);
@@ -145,14 +160,38 @@ static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind
 int hera_graph_load_bytes(hera_ctx *ctx, const void *host_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out) {
     HERA_API_BEGIN(ctx)
     HERA_REQUIRE(host_text != nullptr || n == 0, 101, "null text");
-    load_common(c, host_text, n, cudaMemcpyHostToDevice, anchors, test_load_num, out);
+    load_common(c, host_text, n, cudaMemcpyHostToDevice, anchors, test_load_num, nullptr, out);
     HERA_API_END
 }
 
 int hera_graph_load_device(hera_ctx *ctx, const void *device_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out) {
     HERA_API_BEGIN(ctx)
     HERA_REQUIRE(device_text != nullptr || n == 0, 101, "null text");
-    load_common(c, device_text, n, cudaMemcpyDeviceToDevice, anchors, test_load_num, out);
+    load_common(c, device_text, n, cudaMemcpyDeviceToDevice, anchors, test_load_num, nullptr, out);
+    HERA_API_END
+}
+
+void hera_shard_range(uint64_t file_bytes, int rank, int nranks, uint64_t *begin, uint64_t *end, uint64_t *avail_end) {
+    const uint64_t look_ahead = 1ull << 20;   // a record that starts in the slice must end within this many bytes after it
+    if (nranks < 1) nranks = 1;
+    if (rank < 0) rank = 0;
+    if (rank >= nranks) rank = nranks - 1;
+    // 16-byte aligned cuts keep the 128-bit loads of the tokenizer aligned when slices are views into one buffer
+    auto cut = [&](int r) { return r >= nranks ? file_bytes : (file_bytes / nranks * r) & ~15ull; };
+    const uint64_t b = cut(rank), e = cut(rank + 1);
+    if (begin) *begin = b;
+    if (end) *end = e;
+    if (avail_end) *avail_end = std::min(file_bytes, e + look_ahead);
+}
+
+int hera_graph_load_shard(hera_ctx *ctx, const void *text, int on_device, uint64_t owned, uint64_t avail, int prev_byte, int at_eof, int anchors,
+                          uint32_t test_load_num, hera_load_result *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(text != nullptr || avail == 0, 101, "null text");
+    HERA_REQUIRE(owned <= avail, 101, "shard: owned > avail");
+    const bool prev_nonws = prev_byte >= 0 && !(prev_byte == ' ' || (prev_byte >= 9 && prev_byte <= 13));
+    hera::ShardSpec sp{owned, prev_nonws, at_eof != 0};
+    load_common(c, text, avail, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, anchors, test_load_num, &sp, out);
     HERA_API_END
 }
 
@@ -162,19 +201,81 @@ int hera_graph_load_file(hera_ctx *ctx, const char *path, int anchors, uint32_t 
     std::ifstream f(path, std::ios::binary | std::ios::ate);
     if (!f) throw hera::Error{1, std::string("Cannot open file: ") + path};
     const uint64_t n = static_cast<uint64_t>(f.tellg());
-    f.seekg(0);
     hera::HBuf<char> staging;
-    staging.reserve(n + 1);
-    if (n) f.read(staging.p, static_cast<std::streamsize>(n));
-    HERA_REQUIRE(static_cast<uint64_t>(f.gcount()) == n || n == 0, 1, std::string("short read on ") + path);
-    load_common(c, staging.p, n, cudaMemcpyHostToDevice, anchors, test_load_num, out);
+    auto read_range = [&](uint64_t b, uint64_t e) {
+        staging.reserve(e - b + 1);
+        f.clear();
+        f.seekg(static_cast<std::streamoff>(b));
+        if (e > b) f.read(staging.p, static_cast<std::streamsize>(e - b));
+        HERA_REQUIRE(static_cast<uint64_t>(f.gcount()) == e - b || e == b, 1, std::string("short read on ") + path);
+    };
+    bool whole = hera::xch_size(c) == 1;
+    if (!whole) {
+        // every rank reads only its byte range (+ the byte before it and the look-ahead)
+        uint64_t b, e, a;
+        hera_shard_range(n, hera::xch_rank(c), hera::xch_size(c), &b, &e, &a);
+        const uint64_t from = b ? b - 1 : 0;
+        read_range(from, a);
+        const int prev = b ? static_cast<unsigned char>(staging.p[0]) : -1;
+        const bool prev_nonws = prev >= 0 && !(prev == ' ' || (prev >= 9 && prev <= 13));
+        hera::ShardSpec sp{e - b, prev_nonws, a == n};
+        try {
+            load_common(c, staging.p + (b - from), a - b, cudaMemcpyHostToDevice, anchors, test_load_num, &sp, out);
+        } catch (const hera::Error &err) {
+            if (err.code != 20) throw;
+            whole = true;   // an irregular record: all ranks fall back to the exact whole-file reader (same decision on every rank)
+        }
+    }
+    if (whole) {
+        read_range(0, n);
+        load_common(c, staging.p, n, cudaMemcpyHostToDevice, anchors, test_load_num, nullptr, out);
+    }
     HERA_API_END
 }
+
+int hera_nccl_unique_id(void *out128, char *err, uint64_t err_cap) {
+    try {
+        if (!out128) throw hera::Error{101, "null output"};
+        hera::nccl_unique_id(out128);
+        return 0;
+    } catch (const hera::Error &e) {
+        if (err && err_cap) { std::strncpy(err, e.msg.c_str(), err_cap - 1); err[err_cap - 1] = 0; }
+        return e.code;
+    }
+}
+
+int hera_comm_init_nccl(hera_ctx *ctx, int rank, int nranks, const void *id128) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(!c.xch, 36, "a communicator is already attached to this context");
+    c.xch = hera::make_nccl_exchange(c, rank, nranks, id128);
+    HERA_API_END
+}
+
+hera_local_gang *hera_comm_local_create(int nranks) {
+    if (nranks < 1) return nullptr;
+    hera_local_gang *g = new hera_local_gang();
+    g->hub = hera::make_local_hub(nranks);
+    return g;
+}
+
+void hera_comm_local_destroy(hera_local_gang *gang) { delete gang; }
+
+int hera_comm_attach_local(hera_ctx *ctx, hera_local_gang *gang, int rank) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(gang != nullptr, 101, "null gang");
+    HERA_REQUIRE(!c.xch, 36, "a communicator is already attached to this context");
+    c.xch = hera::make_local_exchange(gang->hub, rank);
+    HERA_API_END
+}
+
+int hera_comm_rank(hera_ctx *ctx) { return ctx ? hera::xch_rank(ctx->c) : 0; }
+int hera_comm_size(hera_ctx *ctx) { return ctx ? hera::xch_size(ctx->c) : 1; }
 
 int hera_graph_reset(hera_ctx *ctx) {
     HERA_API_BEGIN(ctx)
     HERA_CUDA(cudaStreamSynchronize(c.stream));
     c.texts.clear();
+    c.own_rows.clear();
     c.kept.n = 0;
     c.g.ready = false;
     c.g.N = c.g.E = c.g.S = c.g.anchors = 0;

@@ -4,6 +4,7 @@
 #include <memory>
 
 #include "common.cuh"
+#include "exchange.cuh"
 
 namespace hera {
 
@@ -27,12 +28,14 @@ struct KeptTable {
     DBuf<float> os, si, es;
     DBuf<uint8_t> flags;
     DBuf<uint64_t> qhash, thash, qname, tname;
-    void reserve(uint64_t total, cudaStream_t s) {
-        qs.reserve(total, true, n, s); qe.reserve(total, true, n, s); ts.reserve(total, true, n, s); te.reserve(total, true, n, s);
-        qlen.reserve(total, true, n, s); tlen.reserve(total, true, n, s); rec.reserve(total, true, n, s);
-        os.reserve(total, true, n, s); si.reserve(total, true, n, s); es.reserve(total, true, n, s);
-        flags.reserve(total, true, n, s);
-        qhash.reserve(total, true, n, s); thash.reserve(total, true, n, s); qname.reserve(total, true, n, s); tname.reserve(total, true, n, s);
+    // keep = rows whose contents must survive a reallocation (default: the n committed rows)
+    void reserve(uint64_t total, cudaStream_t s, uint64_t keep = ~0ull) {
+        const uint64_t k = keep == ~0ull ? n : keep;
+        qs.reserve(total, true, k, s); qe.reserve(total, true, k, s); ts.reserve(total, true, k, s); te.reserve(total, true, k, s);
+        qlen.reserve(total, true, k, s); tlen.reserve(total, true, k, s); rec.reserve(total, true, k, s);
+        os.reserve(total, true, k, s); si.reserve(total, true, k, s); es.reserve(total, true, k, s);
+        flags.reserve(total, true, k, s);
+        qhash.reserve(total, true, k, s); thash.reserve(total, true, k, s); qname.reserve(total, true, k, s); tname.reserve(total, true, k, s);
     }
 };
 
@@ -42,6 +45,17 @@ struct KeptPtrs {
     float *os, *si, *es;
     uint8_t *flags;
     uint64_t *qhash, *thash, *qname, *tname;
+};
+
+// A byte-range slice of a PAF file (sharded load): which of its tokens are this rank's.
+struct ShardSpec {
+    uint64_t owned;     // tokens starting at a byte >= owned belong to the next rank
+    bool prev_nonws;    // the file byte before the slice is part of a token
+    bool at_eof;        // the slice (with its look-ahead) ends at the end of the file
+};
+
+struct RowRange {
+    uint64_t begin, end;
 };
 
 struct LoadedText {
@@ -55,7 +69,11 @@ struct GraphTables {
     DBuf<uint32_t> e_q, e_t;                 // node ids per kept overlap
     DBuf<uint32_t> node_len;
     DBuf<uint8_t> node_anchor;
-    DBuf<uint64_t> node_name;                // packed name reference of the first appearance
+    DBuf<uint64_t> node_name;                // packed name reference of the first appearance (valid on the rank that parsed that row)
+    DBuf<uint32_t> node_row;                 // kept row that created the node
+    DBuf<uint64_t> node_name_off;            // N + 1, into node_names
+    DBuf<char> node_names;                   // every node's name, node order (complete on every rank)
+    uint64_t name_bytes = 0;
     DBuf<uint32_t> adj_off;                  // N + 1
     DBuf<uint32_t> adj_pay;                  // slot -> 2 * kept + side
     // walk-facing structure of arrays
@@ -87,9 +105,11 @@ struct Ctx {
     int opt_walk_warps_per_sm = 32;
     uint64_t walk_pool_hint = 0;   // largest path pool a walk call needed so far (avoids the overflow re-run)
     DBuf<uint8_t> l2_flush_buf;
+    std::unique_ptr<Exchange> xch;   // null = single rank
 
     std::vector<std::unique_ptr<LoadedText>> texts;
     KeptTable kept;
+    std::vector<RowRange> own_rows;   // per load: the kept rows this rank parsed itself (their name references point into ITS texts)
     GraphTables g;
 
     PathStore all, uniq;
@@ -137,7 +157,7 @@ void radix_sort_pairs(Ctx &c, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt
 void maybe_flush_l2(Ctx &c);
 
 // ---- stages ------------------------------------------------------------------------------
-void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, hera_load_result *out);
+void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out);
 void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out);
 void export_graph(Ctx &c, hera_graph_view *out);
 void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);

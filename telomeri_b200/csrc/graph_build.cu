@@ -13,6 +13,8 @@
 // radix sort by owner keeps record order inside each node's list, which is the reference's
 // insertion order.  Rank permutations restate the per-step stable_sort of the greedy walk
 // (src/PathManager.cpp:289-296); canon[] its first-parallel-edge lookup (:340-347).
+#include <vector>
+
 #include "ctx.cuh"
 #include "primitives.cuh"
 
@@ -57,7 +59,7 @@ __global__ void intern_create_nodes_kernel(uint64_t occ, const uint8_t *__restri
                                            const uint32_t *__restrict__ occ_slot, uint32_t *__restrict__ slot_id, const uint32_t *__restrict__ qlen,
                                            const uint32_t *__restrict__ tlen, const uint8_t *__restrict__ flags, const uint64_t *__restrict__ qname,
                                            const uint64_t *__restrict__ tname, uint32_t *__restrict__ node_len, uint8_t *__restrict__ node_anchor,
-                                           uint64_t *__restrict__ node_name) {
+                                           uint64_t *__restrict__ node_name, uint32_t *__restrict__ node_row) {
     const uint64_t pos = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (pos >= occ || !first[pos]) return;
     const uint64_t e = pos >> 1;
@@ -65,6 +67,7 @@ __global__ void intern_create_nodes_kernel(uint64_t occ, const uint8_t *__restri
     slot_id[occ_slot[pos]] = id;
     const uint8_t f = flags[e];
     const bool cr = f & KF_CR, qctg = f & KF_QCTG;
+    node_row[id] = static_cast<uint32_t>(e);
     if (pos & 1) {
         node_len[id] = tlen[e];
         node_anchor[id] = (cr && !qctg) ? 1 : 0;   // ContigPosition::TARGET
@@ -76,26 +79,67 @@ __global__ void intern_create_nodes_kernel(uint64_t occ, const uint8_t *__restri
     }
 }
 
+// Kept rows a rank parsed itself: only their name references point into texts it holds.
+struct OwnRows {
+    uint64_t begin[16], end[16];
+    int n;
+    __device__ bool has(uint64_t e) const {
+        for (int i = 0; i < n; i++) if (e >= begin[i] && e < end[i]) return true;
+        return false;
+    }
+};
+
 __global__ void intern_assign_kernel(uint64_t E, const uint32_t *__restrict__ occ_slot, const uint32_t *__restrict__ slot_id, uint32_t *__restrict__ e_q,
-                                     uint32_t *__restrict__ e_t, const uint64_t *__restrict__ qname, const uint64_t *__restrict__ tname,
-                                     const uint64_t *__restrict__ node_name, TextPtrs texts, unsigned int *collision) {
+                                     uint32_t *__restrict__ e_t) {
     const uint64_t e = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (e >= E) return;
-    const uint32_t q = slot_id[occ_slot[2 * e]], t = slot_id[occ_slot[2 * e + 1]];
-    e_q[e] = q;
-    e_t[e] = t;
-    // verification: same bytes as the node's name
+    e_q[e] = slot_id[occ_slot[2 * e]];
+    e_t[e] = slot_id[occ_slot[2 * e + 1]];
+}
+
+__global__ void name_len_kernel(uint64_t N, const uint64_t *__restrict__ node_name, uint32_t *__restrict__ lens) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < N) lens[i] = name_len(node_name[i]);
+}
+
+// Name bytes of the nodes whose creating row this rank parsed (the other ranks fill the rest).
+__global__ void name_copy_kernel(uint64_t N, const uint64_t *__restrict__ node_name, const uint32_t *__restrict__ node_row, OwnRows own,
+                                 const uint64_t *__restrict__ offs, TextPtrs texts, char *__restrict__ blob) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= N || !own.has(node_row[i])) return;
+    const uint64_t r = node_name[i];
+    const uint8_t *src = texts.p[name_file(r)] + name_off(r);
+    char *dst = blob + offs[i];
+    for (uint32_t k = 0; k < name_len(r); k++) dst[k] = static_cast<char>(src[k]);
+}
+
+// blob |= part[1..parts): every byte is non-zero in exactly one part.
+__global__ void name_merge_kernel(uint64_t bytes, int parts, const char *__restrict__ gathered, char *__restrict__ blob) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= bytes) return;
+    char v = 0;
+    for (int p = 0; p < parts; p++) v |= gathered[static_cast<uint64_t>(p) * bytes + i];
+    blob[i] = v;
+}
+
+// Verification: every occurrence this rank parsed has the same bytes as its node's name, so a
+// 64-bit hash collision is an error, never a silent merge.
+__global__ void intern_verify_kernel(OwnRows own, int range, const uint32_t *__restrict__ e_q, const uint32_t *__restrict__ e_t,
+                                     const uint64_t *__restrict__ qname, const uint64_t *__restrict__ tname, const uint64_t *__restrict__ name_off_tab,
+                                     const char *__restrict__ blob, TextPtrs texts, unsigned int *collision) {
+    const uint64_t e = own.begin[range] + static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (e >= own.end[range]) return;
     const uint64_t mine[2] = {qname[e], tname[e]};
-    const uint32_t ids[2] = {q, t};
+    const uint32_t ids[2] = {e_q[e], e_t[e]};
 #pragma unroll
     for (int s = 0; s < 2; s++) {
-        const uint64_t ref = node_name[ids[s]];
-        if (ref == mine[s]) continue;
-        bool same = name_len(ref) == name_len(mine[s]);
+        const uint64_t o = name_off_tab[ids[s]];
+        const uint32_t len = static_cast<uint32_t>(name_off_tab[ids[s] + 1] - o);
+        bool same = len == name_len(mine[s]);
         if (same) {
-            const uint8_t *a = texts.p[name_file(ref)] + name_off(ref);
+            const char *a = blob + o;
             const uint8_t *b = texts.p[name_file(mine[s])] + name_off(mine[s]);
-            for (uint32_t i = 0; i < name_len(ref); i++) if (a[i] != b[i]) { same = false; break; }
+            for (uint32_t i = 0; i < len; i++) if (static_cast<uint8_t>(a[i]) != b[i]) { same = false; break; }
         }
         if (!same) *collision = 1;
     }
@@ -240,21 +284,61 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         HERA_CUDA(cudaMallocAsync(&slot_id, cap * sizeof(uint32_t), c.stream));
         HERA_LAUNCH(c, intern_first_flags_kernel, div_up(occ, 256), 256, 0, occ, occ_slot, minpos, first);
         exclusive_scan_u8_to_u32(c, first, occ, first_scan, nullptr);
-        g.node_len.reserve(N); g.node_anchor.reserve(N); g.node_name.reserve(N);
+        g.node_len.reserve(N); g.node_anchor.reserve(N); g.node_name.reserve(N); g.node_row.reserve(N); g.node_name_off.reserve(N + 1);
         g.e_q.reserve(E); g.e_t.reserve(E);
         HERA_LAUNCH(c, intern_create_nodes_kernel, div_up(occ, 256), 256, 0, occ, first, first_scan, occ_slot, slot_id, c.kept.qlen.p, c.kept.tlen.p,
-                    c.kept.flags.p, c.kept.qname.p, c.kept.tname.p, g.node_len.p, g.node_anchor.p, g.node_name.p);
+                    c.kept.flags.p, c.kept.qname.p, c.kept.tname.p, g.node_len.p, g.node_anchor.p, g.node_name.p, g.node_row.p);
+        HERA_LAUNCH(c, intern_assign_kernel, div_up(E, 256), 256, 0, E, occ_slot, slot_id, g.e_q.p, g.e_t.p);
+        // node names: one blob in node order.  A rank holds the text of the rows it parsed; the blob is
+        // completed by gathering every rank's part (names are short: N * ~10 bytes).
         TextPtrs tp{};
-        HERA_REQUIRE(c.texts.size() <= 16, 5, "more than 16 loads per graph are not supported");
+        HERA_REQUIRE(c.texts.size() <= 16 && c.own_rows.size() <= 16, 5, "more than 16 loads per graph are not supported");
         for (size_t i = 0; i < c.texts.size(); i++) tp.p[i] = c.texts[i]->bytes.p;
-        HERA_LAUNCH(c, intern_assign_kernel, div_up(E, 256), 256, 0, E, occ_slot, slot_id, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p, g.node_name.p, tp, d_small + 2);
+        OwnRows own{};
+        own.n = static_cast<int>(c.own_rows.size());
+        for (int i = 0; i < own.n; i++) { own.begin[i] = c.own_rows[i].begin; own.end[i] = c.own_rows[i].end; }
+        {
+            uint32_t *lens = nullptr;
+            HERA_CUDA(cudaMallocAsync(&lens, (N + 1) * sizeof(uint32_t), c.stream));
+            HERA_LAUNCH(c, name_len_kernel, div_up(N, 256), 256, 0, N, g.node_name.p, lens);
+            exclusive_scan_u32_to_u64(c, lens, N, g.node_name_off.p, g.node_name_off.p + N);
+            uint64_t blob_bytes = 0;
+            HERA_CUDA(cudaMemcpyAsync(&blob_bytes, g.node_name_off.p + N, sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            HERA_CUDA(cudaFreeAsync(lens, c.stream));
+            g.name_bytes = blob_bytes;
+            g.node_names.reserve(blob_bytes + 1);
+            const int ranks = xch_size(c);
+            if (ranks > 1) HERA_CUDA(cudaMemsetAsync(g.node_names.p, 0, blob_bytes + 1, c.stream));
+            HERA_LAUNCH(c, name_copy_kernel, div_up(N, 256), 256, 0, N, g.node_name.p, g.node_row.p, own, g.node_name_off.p, tp, g.node_names.p);
+            if (ranks > 1 && blob_bytes) {
+                char *parts = nullptr;
+                HERA_CUDA(cudaMallocAsync(&parts, blob_bytes * ranks, c.stream));
+                std::vector<uint64_t> counts(ranks, blob_bytes), displs(ranks);
+                for (int r = 0; r < ranks; r++) displs[r] = static_cast<uint64_t>(r) * blob_bytes;
+                c.xch->all_gatherv(c, g.node_names.p, parts, counts.data(), displs.data(), 1);
+                HERA_LAUNCH(c, name_merge_kernel, div_up(blob_bytes, 256), 256, 0, blob_bytes, ranks, parts, g.node_names.p);
+                HERA_CUDA(cudaFreeAsync(parts, c.stream));
+            }
+        }
+        for (int i = 0; i < own.n; i++) {
+            const uint64_t rows = own.end[i] - own.begin[i];
+            if (rows) HERA_LAUNCH(c, intern_verify_kernel, div_up(rows, 256), 256, 0, own, i, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p,
+                                  g.node_name_off.p, g.node_names.p, tp, d_small + 2);
+        }
         // anchors in node order
         uint32_t *anchor_scan = nullptr;
         HERA_CUDA(cudaMallocAsync(&anchor_scan, N * sizeof(uint32_t), c.stream));
         exclusive_scan_u8_to_u32(c, g.node_anchor.p, N, anchor_scan, d_small + 3);
         HERA_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
-        HERA_REQUIRE(!h_small[2], 6, "64-bit name hash collision detected while interning node names");
+        uint64_t collided = h_small[2];
+        if (xch_size(c) > 1) {
+            std::vector<uint64_t> all(xch_size(c));
+            c.xch->all_gather_host(c, &collided, 1, all.data());
+            for (uint64_t v : all) collided |= v;
+        }
+        HERA_REQUIRE(!collided, 6, "64-bit name hash collision detected while interning node names");
         g.anchors = h_small[3];
         g.anchor_ids.reserve(g.anchors + 1);
         HERA_LAUNCH(c, anchor_list_kernel, div_up(N, 256), 256, 0, N, g.node_anchor.p, anchor_scan, g.anchor_ids.p);
@@ -303,20 +387,6 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
 }
 
 // ---- export ---------------------------------------------------------------------------------
-__global__ void name_len_kernel(uint64_t N, const uint64_t *__restrict__ node_name, uint32_t *__restrict__ lens) {
-    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i < N) lens[i] = name_len(node_name[i]);
-}
-
-__global__ void name_copy_kernel(uint64_t N, const uint64_t *__restrict__ node_name, const uint64_t *__restrict__ offs, TextPtrs texts, char *__restrict__ blob) {
-    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= N) return;
-    const uint64_t r = node_name[i];
-    const uint8_t *src = texts.p[name_file(r)] + name_off(r);
-    char *dst = blob + offs[i];
-    for (uint32_t k = 0; k < name_len(r); k++) dst[k] = static_cast<char>(src[k]);
-}
-
 __global__ void export_adj_kernel(uint64_t S, const uint32_t *__restrict__ pay, uint32_t *__restrict__ rec, uint8_t *__restrict__ side) {
     const uint64_t s = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (s < S) { rec[s] = pay[s] >> 1; side[s] = pay[s] & 1; }
@@ -353,21 +423,11 @@ void export_graph(Ctx &c, hera_graph_view *out) {
         d2h(c, m.node_len, g.node_len.p, N);
         d2h(c, m.node_anchor, g.node_anchor.p, N);
         // names
-        uint32_t *lens = nullptr; uint64_t *offs = nullptr; char *blob = nullptr; uint8_t *tmp8 = nullptr; uint32_t *tmp32 = nullptr;
-        HERA_CUDA(cudaMallocAsync(&lens, (N + 1) * sizeof(uint32_t), c.stream));
+        uint64_t *offs = nullptr; uint8_t *tmp8 = nullptr; uint32_t *tmp32 = nullptr;
         HERA_CUDA(cudaMallocAsync(&offs, (N + 1) * sizeof(uint64_t), c.stream));
-        HERA_LAUNCH(c, name_len_kernel, div_up(N, 256), 256, 0, N, g.node_name.p, lens);
-        exclusive_scan_u32_to_u64(c, lens, N, offs, offs + N);
-        uint64_t blob_bytes = 0;
-        HERA_CUDA(cudaMemcpyAsync(&blob_bytes, offs + N, sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
-        HERA_CUDA(cudaStreamSynchronize(c.stream));
-        HERA_CUDA(cudaMallocAsync(&blob, blob_bytes + 1, c.stream));
-        TextPtrs tp{};
-        for (size_t i = 0; i < c.texts.size(); i++) tp.p[i] = c.texts[i]->bytes.p;
-        HERA_LAUNCH(c, name_copy_kernel, div_up(N, 256), 256, 0, N, g.node_name.p, offs, tp, blob);
-        d2h(c, m.node_name_off, offs, N + 1);
-        m.node_names.reserve(blob_bytes + 1);
-        HERA_CUDA(cudaMemcpyAsync(m.node_names.p, blob, blob_bytes, cudaMemcpyDeviceToHost, c.stream));
+        d2h(c, m.node_name_off, g.node_name_off.p, N + 1);
+        m.node_names.reserve(g.name_bytes + 1);
+        if (g.name_bytes) HERA_CUDA(cudaMemcpyAsync(m.node_names.p, g.node_names.p, g.name_bytes, cudaMemcpyDeviceToHost, c.stream));
         // edges
         d2h(c, m.e_q, g.e_q.p, E); d2h(c, m.e_t, g.e_t.p, E);
         d2h(c, m.e_qs, c.kept.qs.p, E); d2h(c, m.e_qe, c.kept.qe.p, E); d2h(c, m.e_ts, c.kept.ts.p, E); d2h(c, m.e_te, c.kept.te.p, E);
@@ -384,7 +444,7 @@ void export_graph(Ctx &c, hera_graph_view *out) {
         d2h(c, m.canon, g.canon.p, S);
         for (int k = 0; k < 4; k++) if (g.rank_ready[k]) d2h(c, m.rank[k], g.rank[k].p, S);
         HERA_CUDA(cudaStreamSynchronize(c.stream));
-        HERA_CUDA(cudaFreeAsync(lens, c.stream)); HERA_CUDA(cudaFreeAsync(offs, c.stream)); HERA_CUDA(cudaFreeAsync(blob, c.stream));
+        HERA_CUDA(cudaFreeAsync(offs, c.stream));
         HERA_CUDA(cudaFreeAsync(tmp8, c.stream)); HERA_CUDA(cudaFreeAsync(tmp32, c.stream));
     }
     out->node_len = m.node_len.p; out->node_anchor = m.node_anchor.p; out->node_name_off = m.node_name_off.p; out->node_names = m.node_names.p;

@@ -23,6 +23,8 @@
 // strand token is one character.  The first irregular record (stream extraction would fail or
 // desynchronise there) ends the parallel part; a one-thread tail kernel continues from its byte
 // offset with the exact character-stream rules of formatted extraction.
+#include <algorithm>
+
 #include "ctx.cuh"
 #include "primitives.cuh"
 
@@ -251,7 +253,11 @@ __device__ unsigned long long chain_exclusive(unsigned long long *state, unsigne
 
 struct ParseArgs {
     const uint8_t *text;        // padded: readable up to tiles * PF_TILE + PF_HALO, bytes >= n are '\n'
-    uint64_t n;
+    uint64_t n;                 // bytes of text available (whole file, or slice + look-ahead)
+    uint64_t owned;             // tokens that start at a byte >= owned belong to the next rank (== n for a whole file)
+    uint64_t tok_base0;         // global index of the first token that starts in this text (0 for a whole file)
+    int prev_nonws;             // the byte before text[0] is part of a token
+    int at_eof;                 // text[n] is the end of the file
     uint32_t tiles;
     uint32_t file_id;
     int anchors;
@@ -374,7 +380,7 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
         s_nonws[ch + 1] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
     }
     if (tid == 0) {
-        uint32_t prev_nonws = 0;  // does the byte before the tile belong to a token?
+        uint32_t prev_nonws = a.prev_nonws ? 1u : 0u;  // does the byte before the tile belong to a token?
         if (tile_byte0 > 0) prev_nonws = dev_is_space(a.text[tile_byte0 - 1]) ? 0u : 1u;
         s_nonws[0] = static_cast<uint16_t>(prev_nonws << 15);
     }
@@ -390,6 +396,8 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
         if (ch < PF_TILE / 16) {
             const uint32_t cur = s_nonws[ch + 1];
             starts = cur & ~((cur << 1) | ((s_nonws[ch] >> 15) & 1u)) & 0xffffu;
+            const uint64_t b0 = tile_byte0 + static_cast<uint64_t>(ch) * 16;
+            if (b0 + 16 > a.owned) starts = b0 >= a.owned ? 0u : (starts & ((1u << static_cast<uint32_t>(a.owned - b0)) - 1u));
         }
         my_mask[k] = starts;
         my_tokens += __popc(starts);
@@ -404,10 +412,10 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
         }
     }
     __syncthreads();
-    const unsigned long long tok_base = s_tok_base;
+    const unsigned long long tok_base = a.tok_base0 + s_tok_base;
     const uint32_t first_rec_ord = static_cast<uint32_t>((16 - (tok_base & 15)) & 15);
     const uint32_t nrec = tile_tokens > first_rec_ord ? (tile_tokens - first_rec_ord + 15) / 16 : 0;  // records starting in this tile
-    const bool reaches_eof = tile_byte0 + PF_WIN >= a.n;
+    const bool reaches_eof = a.at_eof && tile_byte0 + PF_WIN >= a.n;
 
     // 3. every 16th token opens a record: note its offset
     {
@@ -492,6 +500,25 @@ __global__ void paf_tail_kernel(const uint8_t *text, uint64_t n, uint64_t start_
     ctr->tail_kept = nk;
 }
 
+// Tokens that start in text[0, owned): what a rank of a sharded load tells the others before anyone
+// can know where its records begin (record boundary = global token index % 16 == 0).
+__global__ void __launch_bounds__(256) paf_count_tokens_kernel(const uint8_t *__restrict__ text, uint64_t owned, int prev_nonws, unsigned long long *out) {
+    const uint64_t chunks = (owned + 15) / 16;
+    unsigned long long mine = 0;
+    for (uint64_t ch = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; ch < chunks; ch += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(text) + ch);
+        const uint32_t cur = nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12);
+        const uint32_t prev = ch ? (dev_is_space(text[ch * 16 - 1]) ? 0u : 1u) : (prev_nonws ? 1u : 0u);
+        uint32_t starts = cur & ~((cur << 1) | prev) & 0xffffu;
+        const uint64_t b0 = ch * 16;
+        if (b0 + 16 > owned) starts &= (1u << static_cast<uint32_t>(owned - b0)) - 1u;
+        mine += __popc(starts);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+    if (lane_id() == 0 && mine) atomicAdd(out, mine);
+}
+
 __global__ void pad_text_kernel(uint8_t *text, uint64_t n, uint64_t padded) {
     const uint64_t i = n + static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < padded) text[i] = '\n';
@@ -503,15 +530,33 @@ static KeptPtrs kept_ptrs(KeptTable &k) {
 
 uint64_t padded_text_size(uint64_t n) { return (n / PF_TILE + 2) * static_cast<uint64_t>(PF_TILE); }
 
-void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, hera_load_result *out) {
+// Moves this rank's new kept rows [n0, n0 + counts[rank]) to their global place n0 + displs[rank] and
+// receives the other ranks' rows: one variable-size all-gather per column of the kept table.
+template <typename T>
+static void gather_column(Ctx &c, T *col, uint64_t n0, const uint64_t *counts, const uint64_t *displs, void *tmp) {
+    const int r = xch_rank(c);
+    const void *send = col + n0;
+    if (displs[r] != 0 && counts[r]) {   // my rows move up: stage them so that no receive window overlaps the source
+        HERA_CUDA(cudaMemcpyAsync(tmp, col + n0, counts[r] * sizeof(T), cudaMemcpyDeviceToDevice, c.stream));
+        send = tmp;
+    }
+    c.xch->all_gatherv(c, send, col + n0, counts, displs, sizeof(T));
+}
+
+void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out) {
     const uint64_t n = text.n;
     const uint64_t padded = padded_text_size(n);
     HERA_REQUIRE(text.bytes.cap >= padded, 3, "internal: text buffer not padded");
     HERA_LAUNCH(c, pad_text_kernel, div_up(padded - n, 256), 256, 0, text.bytes.p, n, padded);
+    const bool sharded = shard != nullptr;
+    const int ranks = xch_size(c), me = xch_rank(c);
+    HERA_REQUIRE(!sharded || c.xch, 21, "hera_graph_load_shard needs a communicator (hera_comm_init_nccl / hera_comm_attach_local)");
+    const uint64_t owned = sharded ? shard->owned : n;
+    HERA_REQUIRE(owned <= n, 101, "shard: owned bytes exceed the bytes provided");
 
-    const uint32_t tiles = static_cast<uint32_t>(n / PF_TILE + 1);
+    const uint32_t tiles = static_cast<uint32_t>(owned / PF_TILE + 1);
     // worst case every record is kept: records <= bytes / 24 (12 one-byte tokens + separators)
-    const uint64_t max_new = n / 24 + 2;
+    const uint64_t max_new = owned / 24 + 2;
     c.kept.reserve(c.kept.n + max_new, c.stream);
 
     c.counters.reserve(64 + 2ull * tiles);
@@ -523,6 +568,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     init.first_bad_rec = ~0ull;
     init.first_bad_off = ~0ull;
     HERA_CUDA(cudaMemcpyAsync(ctr, &init, sizeof(init), cudaMemcpyHostToDevice, c.stream));
+    c.h_counters.reserve(16);
 
     FilterDev fd{c.fp.mode, static_cast<float>(c.fp.min_overlap_length), c.fp.min_overlap_percentage,
                  static_cast<float>(c.fp.max_overhang_length), c.fp.max_overhang_percentage};
@@ -533,20 +579,68 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     HERA_CUDA(cudaEventCreate(&ev1));
     maybe_flush_l2(c);
     HERA_CUDA(cudaEventRecord(ev0, c.stream));
-    ParseArgs a{text.bytes.p, n, tiles, file_id, anchors ? 1 : 0, rec_limit, c.kept.n, fd, kept_ptrs(c.kept), tok_state, kept_state, ctr};
+
+    // sharded: where do my records start?  tokens before my slice = sum over the earlier ranks
+    uint64_t tok_base0 = 0, tokens_all = 0;
+    std::vector<uint64_t> gathered(static_cast<size_t>(ranks) * 2);
+    if (sharded) {
+        unsigned long long *d_tok = reinterpret_cast<unsigned long long *>(c.counters.p + 13);
+        if (owned) HERA_LAUNCH(c, paf_count_tokens_kernel, std::min<unsigned>(div_up(div_up(owned, 16), 256), 148 * 8), 256, 0, text.bytes.p, owned, shard->prev_nonws ? 1 : 0, d_tok);
+        HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 13, d_tok, sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        const uint64_t mine = c.h_counters.p[13];
+        c.xch->all_gather_host(c, &mine, 1, gathered.data());
+        for (int r = 0; r < ranks; r++) { if (r < me) tok_base0 += gathered[r]; tokens_all += gathered[r]; }
+    }
+
+    ParseArgs a{text.bytes.p, n, owned, tok_base0, sharded && shard->prev_nonws ? 1 : 0, (!sharded || shard->at_eof) ? 1 : 0,
+                tiles, file_id, anchors ? 1 : 0, rec_limit, c.kept.n, fd, kept_ptrs(c.kept), tok_state, kept_state, ctr};
     HERA_LAUNCH(c, paf_parse_kernel, tiles, PF_THREADS, 0, a);
     HERA_CUDA(cudaEventRecord(ev1, c.stream));
 
-    c.h_counters.reserve(16);
     HERA_CUDA(cudaMemcpyAsync(c.h_counters.p, ctr, sizeof(ParseCounters), cudaMemcpyDeviceToHost, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
     ParseCounters hc = *reinterpret_cast<ParseCounters *>(c.h_counters.p);
 
-    const uint64_t T = hc.total_tokens;
+    const uint64_t T = sharded ? tokens_all : hc.total_tokens;
     uint64_t records = T / 16 + ((T % 16) >= 12 ? 1 : 0);
     if (records > rec_limit) records = rec_limit;
     uint64_t kept_new = hc.kept;
-    if (hc.first_bad_rec < records) {
+    if (sharded) {
+        // every rank learns every rank's kept count and whether anybody met an irregular record
+        const uint64_t mine[2] = {hc.kept, hc.first_bad_rec};
+        c.xch->all_gather_host(c, mine, 2, gathered.data());
+        std::vector<uint64_t> counts(ranks), displs(ranks);
+        uint64_t total = 0, first_bad = ~0ull;
+        for (int r = 0; r < ranks; r++) {
+            counts[r] = gathered[2 * r];
+            displs[r] = total;
+            total += counts[r];
+            first_bad = std::min(first_bad, gathered[2 * r + 1]);
+        }
+        if (first_bad < records) {
+            cudaEventDestroy(ev0);
+            cudaEventDestroy(ev1);
+            throw Error{20, "irregular PAF record " + std::to_string(first_bad) + ": formatted extraction leaves the 16-token grid there; load this file unsharded"};
+        }
+        c.kept.reserve(c.kept.n + total, c.stream, c.kept.n + counts[me]);
+        KeptTable &k = c.kept;
+        const uint64_t n0 = k.n;
+        void *tmp = nullptr;
+        HERA_CUDA(cudaMallocAsync(&tmp, std::max<uint64_t>(counts[me], 1) * sizeof(uint64_t), c.stream));
+        gather_column(c, k.qs.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.qe.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.ts.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.te.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.qlen.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.tlen.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.rec.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.os.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.si.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.es.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.flags.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.qhash.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.thash.p, n0, counts.data(), displs.data(), tmp);
+        gather_column(c, k.qname.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.tname.p, n0, counts.data(), displs.data(), tmp);
+        HERA_CUDA(cudaFreeAsync(tmp, c.stream));
+        c.own_rows.push_back({n0 + displs[me], n0 + displs[me] + counts[me]});
+        kept_new = total;
+    } else if (hc.first_bad_rec < records) {
         // truncate to the records before the irregular one, then continue serially from there
         unsigned long long *d_cut = reinterpret_cast<unsigned long long *>(c.counters.p + 12);
         HERA_CUDA(cudaMemsetAsync(d_cut, 0, sizeof(unsigned long long), c.stream));
@@ -562,6 +656,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         records = hc.first_bad_rec + hc.tail_records;
         kept_new += hc.tail_kept;
     }
+    if (!sharded) c.own_rows.push_back({c.kept.n, c.kept.n + kept_new});
     c.kept.n += kept_new;
     c.g.ready = false;
     if (out) {

@@ -15,6 +15,7 @@
 // addends non-negative finite multiples of 2^k and the total below 2^(k+53)): then any order
 // gives the sequential result bit for bit.  Otherwise the warp accumulates in list order.
 #include <algorithm>
+#include <vector>
 
 #include "ctx.cuh"
 #include "primitives.cuh"
@@ -51,6 +52,8 @@ struct WalkOut {
     unsigned long long *pool_used;    // also keeps counting past the capacity
     unsigned long long *steps;        // adjacency entries examined
     unsigned int *next_walk;
+    // walks are dealt out by id: this rank runs walk ids part_rank, part_rank + part_size, ... ; results are indexed by the local ordinal
+    uint32_t part_rank, part_size;
 };
 
 __device__ __forceinline__ void philox_round(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t k0, uint32_t k1) {
@@ -88,12 +91,12 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-__device__ __forceinline__ void emit_path(const WalkOut &o, uint32_t walk, const uint32_t *nodes, const uint32_t *slots, uint32_t n_nodes, int64_t len) {
+__device__ __forceinline__ void emit_path(const WalkOut &o, uint32_t local, const uint32_t *nodes, const uint32_t *slots, uint32_t n_nodes, int64_t len) {
     const uint32_t lane = lane_id();
     unsigned long long base = 0;
     if (lane == 0) base = atomicAdd(o.pool_used, static_cast<unsigned long long>(n_nodes));
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (lane == 0) { o.res_n[walk] = n_nodes; o.res_off[walk] = base; o.res_len[walk] = len; }
+    if (lane == 0) { o.res_n[local] = n_nodes; o.res_off[local] = base; o.res_len[local] = len; }
     if (base + n_nodes <= o.pool_cap) {
         for (uint32_t i = lane; i < n_nodes; i += 32) o.pool_nodes[base + i] = nodes[i];
         for (uint32_t i = lane; i + 1 < n_nodes; i += 32) o.pool_slots[base + i] = slots[i];
@@ -123,10 +126,11 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
     unsigned long long examined = 0;
 
     for (;;) {
-        uint32_t walk = 0;
-        if (lane == 0) walk = atomicAdd(o.next_walk, 1u);
-        walk = __shfl_sync(0xffffffffu, walk, 0);
-        if (walk >= total_walks) break;
+        uint32_t local = 0;
+        if (lane == 0) local = atomicAdd(o.next_walk, 1u);
+        local = __shfl_sync(0xffffffffu, local, 0);
+        if (local >= total_walks) break;   // total_walks = walks of this rank
+        const uint32_t walk = local * o.part_size + o.part_rank;
         const uint32_t start = g.anchor_ids[walk / attempts], attempt = walk % attempts;
 
         uint32_t n_nodes = 1, nlog = 1, draws = 0;
@@ -275,10 +279,10 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
             if (nbw >> 31) { accepted = true; break; }
             if (len >= len_threshold) break;
         }
-        if (lane == 0) o.res_draws[walk] = draws;
+        if (lane == 0) o.res_draws[local] = draws;
         if (accepted) {
             const long long len = sum_all - g.delta[slots[n_nodes - 2]];
-            if (len >= 0) emit_path(o, walk, nodes, slots, n_nodes, len);
+            if (len >= 0) emit_path(o, local, nodes, slots, n_nodes, len);
         }
         clear_visited(bm, sc.words, vlog, nlog);
     }
@@ -305,10 +309,11 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
     uint32_t *vlog = sc.vlog + static_cast<uint64_t>(wslot) * sc.cap;
     unsigned long long examined = 0;
     for (;;) {
-        uint32_t walk = 0;
-        if (lane == 0) walk = atomicAdd(o.next_walk, 1u);
-        walk = __shfl_sync(0xffffffffu, walk, 0);
-        if (walk >= total_walks) break;
+        uint32_t local = 0;
+        if (lane == 0) local = atomicAdd(o.next_walk, 1u);
+        local = __shfl_sync(0xffffffffu, local, 0);
+        if (local >= total_walks) break;   // total_walks = walks of this rank
+        const uint32_t walk = local * o.part_size + o.part_rank;
         // anchor = last a with walk_base[a] <= walk
         uint32_t lo = 0, hi = g.anchors;
         while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (walk_base[mid] <= walk) lo = mid; else hi = mid; }
@@ -325,7 +330,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
         __syncwarp();
         bool reached = false;
         if (nbw0 >> 31) {
-            emit_path(o, walk, nodes, slots, 2, static_cast<int64_t>(g.node_len[start]));
+            emit_path(o, local, nodes, slots, 2, static_cast<int64_t>(g.node_len[start]));
         } else {
             int step = 0;
             uint32_t skip = 0;
@@ -378,10 +383,10 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
                 const long long len = static_cast<long long>(g.node_len[start]) + part;
-                if (len >= 0) emit_path(o, walk, nodes, slots, n_nodes, len);
+                if (len >= 0) emit_path(o, local, nodes, slots, n_nodes, len);
             }
         }
-        if (lane == 0) o.res_draws[walk] = 0;
+        if (lane == 0) o.res_draws[local] = 0;
         clear_visited(bm, sc.words, vlog, nlog);
     }
     if (lane == 0 && examined) atomicAdd(o.steps, examined);
@@ -433,11 +438,36 @@ WalkGraph make_walk_graph(Ctx &c, int metric) {
     return w;
 }
 
-// Runs one walk kernel over `total_walks` walks and appends the accepted paths to c.all.
+constexpr int WK_MAX_RANKS = 16;
+struct RankTable {
+    uint64_t walk_displ[WK_MAX_RANKS];   // where rank r's per-walk results start in the gathered arrays
+    uint64_t pool_displ[WK_MAX_RANKS];   // where rank r's path pool starts in the gathered pool
+};
+
+// Gathered per-walk results are rank-major (rank r ran walk ids r, r + size, ...): put them back in walk-id order.
+__global__ void walk_order_kernel(uint32_t total_walks, uint32_t size, RankTable t, const uint32_t *__restrict__ g_n, const uint64_t *__restrict__ g_off,
+                                  const int64_t *__restrict__ g_len, const uint32_t *__restrict__ g_draws, uint32_t *__restrict__ res_n,
+                                  uint64_t *__restrict__ res_off, int64_t *__restrict__ res_len, uint32_t *__restrict__ res_draws) {
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= total_walks) return;
+    const uint32_t r = w % size;
+    const uint64_t src = t.walk_displ[r] + w / size;
+    res_n[w] = g_n[src];
+    res_off[w] = g_off[src] + t.pool_displ[r];
+    res_len[w] = g_len[src];
+    res_draws[w] = g_draws[src];
+}
+
+// Runs one walk kernel over `total_walks` walks (this rank's share of them when a communicator is
+// attached) and appends the accepted paths of ALL ranks to c.all in walk-id order.
 template <typename LaunchFn>
 void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_stats *out, LaunchFn launch) {
     GraphTables &g = c.g;
     const uint64_t launches_before = c.launches.count;
+    const int ranks = xch_size(c), me = xch_rank(c);
+    HERA_REQUIRE(ranks <= WK_MAX_RANKS, 37, "more than 16 ranks are not supported");
+    auto share = [&](int r) { return static_cast<uint32_t>((static_cast<uint64_t>(total_walks) + ranks - 1 - r) / ranks); };
+    const uint32_t my_walks = share(me);
     cudaEvent_t ev0, ev1;
     HERA_CUDA(cudaEventCreate(&ev0));
     HERA_CUDA(cudaEventCreate(&ev1));
@@ -450,33 +480,36 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         const uint64_t per_warp = (3ull * cap + words) * sizeof(uint32_t);
         uint64_t warps = static_cast<uint64_t>(sms) * c.opt_walk_warps_per_sm;
         while (warps > WK_WARPS && warps * per_warp > (8ull << 30)) warps /= 2;
-        if (warps > total_walks) warps = (total_walks + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
+        if (warps > my_walks) warps = (static_cast<uint64_t>(my_walks) + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
+        if (warps == 0) warps = WK_WARPS;
         const unsigned blocks = static_cast<unsigned>((warps + WK_WARPS - 1) / WK_WARPS);
         warps = static_cast<uint64_t>(blocks) * WK_WARPS;
+        const uint64_t res_cap = std::max<uint32_t>(my_walks, 1);
 
         WalkRun r;
-        HERA_CUDA(cudaMallocAsync(&r.res_n, total_walks * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.res_draws, total_walks * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.res_off, total_walks * sizeof(uint64_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.res_len, total_walks * sizeof(int64_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.res_n, res_cap * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.res_draws, res_cap * sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.res_off, res_cap * sizeof(uint64_t), c.stream));
+        HERA_CUDA(cudaMallocAsync(&r.res_len, res_cap * sizeof(int64_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&r.d_ctr, 4 * sizeof(unsigned long long), c.stream));
         HERA_CUDA(cudaMallocAsync(&r.bitmap, warps * words * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&r.nodes, warps * cap * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&r.slots, warps * cap * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&r.vlog, warps * cap * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMemsetAsync(r.bitmap, 0, warps * words * sizeof(uint32_t), c.stream));
-        uint64_t pool_cap = std::max<uint64_t>(std::max<uint64_t>(1u << 16, c.walk_pool_hint), std::min<uint64_t>(static_cast<uint64_t>(total_walks) * 256, 1ull << 28));
+        uint64_t pool_cap = std::max<uint64_t>(std::max<uint64_t>(1u << 16, c.walk_pool_hint), std::min<uint64_t>(static_cast<uint64_t>(my_walks) * 256, 1ull << 28));
         unsigned long long h_ctr[4];
         for (;;) {
             HERA_CUDA(cudaMallocAsync(&r.pool_nodes, pool_cap * sizeof(uint32_t), c.stream));
             HERA_CUDA(cudaMallocAsync(&r.pool_slots, pool_cap * sizeof(uint32_t), c.stream));
             HERA_CUDA(cudaMemsetAsync(r.d_ctr, 0, 4 * sizeof(unsigned long long), c.stream));
-            HERA_CUDA(cudaMemsetAsync(r.res_n, 0, total_walks * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMemsetAsync(r.res_n, 0, res_cap * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMemsetAsync(r.res_draws, 0, res_cap * sizeof(uint32_t), c.stream));
             WalkScratch sc{r.bitmap, r.nodes, r.slots, r.vlog, words, cap};
             WalkOut wo{r.res_n, r.res_off, r.res_len, r.res_draws, r.pool_nodes, r.pool_slots, pool_cap, r.d_ctr, r.d_ctr + 1,
-                       reinterpret_cast<unsigned int *>(r.d_ctr + 2)};
+                       reinterpret_cast<unsigned int *>(r.d_ctr + 2), static_cast<uint32_t>(me), static_cast<uint32_t>(ranks)};
             HERA_CUDA(cudaEventRecord(ev0, c.stream));
-            launch(blocks, sc, wo);
+            if (my_walks) launch(blocks, my_walks, sc, wo);
             HERA_CUDA(cudaEventRecord(ev1, c.stream));
             HERA_CUDA(cudaMemcpyAsync(h_ctr, r.d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, c.stream));
             HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -488,7 +521,48 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         HERA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
         steps = h_ctr[1];
         c.walk_pool_hint = std::max<uint64_t>(c.walk_pool_hint, h_ctr[0] + h_ctr[0] / 8);
-        const uint64_t new_nodes = h_ctr[0];
+        uint64_t new_nodes = h_ctr[0];
+
+        // per-walk results in walk-id order + one pool holding every accepted path
+        uint32_t *res_n = r.res_n, *res_draws = r.res_draws, *pool_nodes = r.pool_nodes, *pool_slots = r.pool_slots;
+        uint64_t *res_off = r.res_off;
+        int64_t *res_len = r.res_len;
+        std::vector<void *> gathered;
+        if (ranks > 1) {
+            // exchange step: all-gather of the ranks' accepted paths
+            const uint64_t mine[2] = {h_ctr[0], h_ctr[1]};
+            std::vector<uint64_t> all(2 * static_cast<size_t>(ranks));
+            c.xch->all_gather_host(c, mine, 2, all.data());
+            RankTable t{};
+            std::vector<uint64_t> wcount(ranks), wdispl(ranks), pcount(ranks), pdispl(ranks);
+            uint64_t wtot = 0, ptot = 0;
+            steps = 0;
+            for (int k = 0; k < ranks; k++) {
+                wcount[k] = share(k); wdispl[k] = wtot; wtot += wcount[k];
+                pcount[k] = all[2 * k]; pdispl[k] = ptot; ptot += pcount[k];
+                steps += all[2 * k + 1];
+                t.walk_displ[k] = wdispl[k]; t.pool_displ[k] = pdispl[k];
+            }
+            uint32_t *g_n, *g_draws, *g_pn, *g_ps, *o_n, *o_draws;
+            uint64_t *g_off, *o_off;
+            int64_t *g_len, *o_len;
+            auto alloc = [&](auto **p, uint64_t n) {
+                HERA_CUDA(cudaMallocAsync(p, std::max<uint64_t>(n, 1) * sizeof(**p), c.stream));
+                gathered.push_back(*p);
+            };
+            alloc(&g_n, wtot); alloc(&g_draws, wtot); alloc(&g_off, wtot); alloc(&g_len, wtot); alloc(&g_pn, ptot); alloc(&g_ps, ptot);
+            alloc(&o_n, wtot); alloc(&o_draws, wtot); alloc(&o_off, wtot); alloc(&o_len, wtot);
+            c.xch->all_gatherv(c, r.res_n, g_n, wcount.data(), wdispl.data(), sizeof(uint32_t));
+            c.xch->all_gatherv(c, r.res_draws, g_draws, wcount.data(), wdispl.data(), sizeof(uint32_t));
+            c.xch->all_gatherv(c, r.res_off, g_off, wcount.data(), wdispl.data(), sizeof(uint64_t));
+            c.xch->all_gatherv(c, r.res_len, g_len, wcount.data(), wdispl.data(), sizeof(int64_t));
+            c.xch->all_gatherv(c, r.pool_nodes, g_pn, pcount.data(), pdispl.data(), sizeof(uint32_t));
+            c.xch->all_gatherv(c, r.pool_slots, g_ps, pcount.data(), pdispl.data(), sizeof(uint32_t));
+            HERA_LAUNCH(c, walk_order_kernel, div_up(total_walks, 256), 256, 0, total_walks, static_cast<uint32_t>(ranks), t, g_n, g_off, g_len, g_draws,
+                        o_n, o_off, o_len, o_draws);
+            res_n = o_n; res_draws = o_draws; res_off = o_off; res_len = o_len; pool_nodes = g_pn; pool_slots = g_ps;
+            new_nodes = ptot;
+        }
 
         // order by walk id and append to the path store
         uint8_t *flags = nullptr;
@@ -498,9 +572,9 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         HERA_CUDA(cudaMallocAsync(&acc_scan, total_walks * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&node_scan, total_walks * sizeof(uint64_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&d_found, sizeof(uint32_t), c.stream));
-        HERA_LAUNCH(c, flag_nonzero_kernel, div_up(total_walks, 256), 256, 0, total_walks, r.res_n, flags);
+        HERA_LAUNCH(c, flag_nonzero_kernel, div_up(total_walks, 256), 256, 0, total_walks, res_n, flags);
         exclusive_scan_u8_to_u32(c, flags, total_walks, acc_scan, d_found);
-        exclusive_scan_u32_to_u64(c, r.res_n, total_walks, node_scan, nullptr);
+        exclusive_scan_u32_to_u64(c, res_n, total_walks, node_scan, nullptr);
         uint32_t h_found = 0;
         HERA_CUDA(cudaMemcpyAsync(&h_found, d_found, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -512,17 +586,18 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         ps.slot.reserve(ps.nodes + new_nodes, true, ps.nodes > ps.paths ? ps.nodes - ps.paths : 0, c.stream);
         if (ps.paths == 0) HERA_CUDA(cudaMemsetAsync(ps.off.p, 0, sizeof(uint64_t), c.stream));
         if (found) {
-            HERA_LAUNCH(c, gather_paths_kernel, div_up(static_cast<uint64_t>(total_walks) * 32, WK_THREADS), WK_THREADS, 0, total_walks, r.res_n, r.res_off,
-                        r.res_len, acc_scan, node_scan, r.pool_nodes, r.pool_slots, ps.paths, ps.nodes, ps.off.p, ps.node.p, ps.slot.p, ps.len.p);
+            HERA_LAUNCH(c, gather_paths_kernel, div_up(static_cast<uint64_t>(total_walks) * 32, WK_THREADS), WK_THREADS, 0, total_walks, res_n, res_off,
+                        res_len, acc_scan, node_scan, pool_nodes, pool_slots, ps.paths, ps.nodes, ps.off.p, ps.node.p, ps.slot.p, ps.len.p);
         }
         ps.paths += found;
         ps.nodes += new_nodes;
         if (kind == 0) {
             const size_t before = c.mc_draws.size();
             c.mc_draws.resize(before + total_walks);
-            HERA_CUDA(cudaMemcpyAsync(c.mc_draws.data() + before, r.res_draws, total_walks * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaMemcpyAsync(c.mc_draws.data() + before, res_draws, total_walks * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
         }
         HERA_CUDA(cudaStreamSynchronize(c.stream));
+        for (void *p : gathered) HERA_CUDA(cudaFreeAsync(p, c.stream));
         for (void *p : {static_cast<void *>(flags), static_cast<void *>(acc_scan), static_cast<void *>(node_scan), static_cast<void *>(d_found),
                         static_cast<void *>(r.res_n), static_cast<void *>(r.res_draws), static_cast<void *>(r.res_off), static_cast<void *>(r.res_len),
                         static_cast<void *>(r.d_ctr), static_cast<void *>(r.bitmap), static_cast<void *>(r.nodes), static_cast<void *>(r.slots),
@@ -549,8 +624,8 @@ void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t s
     const uint64_t total = c.g.anchors * static_cast<uint64_t>(pp.rebuild_attempts > 0 ? pp.rebuild_attempts : 0);
     HERA_REQUIRE(total < (1ull << 32), 9, "too many Monte-Carlo walks for one call");
     WalkGraph wg = make_walk_graph(c, metric);
-    run_walks(c, static_cast<uint32_t>(total), 0, metric, out, [&](unsigned blocks, WalkScratch sc, WalkOut wo) {
-        HERA_LAUNCH(c, walk_mc_kernel, blocks, WK_THREADS, 0, wg, sc, wo, static_cast<uint32_t>(total), static_cast<uint32_t>(pp.rebuild_attempts),
+    run_walks(c, static_cast<uint32_t>(total), 0, metric, out, [&](unsigned blocks, uint32_t my_walks, WalkScratch sc, WalkOut wo) {
+        HERA_LAUNCH(c, walk_mc_kernel, blocks, WK_THREADS, 0, wg, sc, wo, my_walks, static_cast<uint32_t>(pp.rebuild_attempts),
                     pp.backtrack_attempts, static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
     });
 }
@@ -571,8 +646,8 @@ void walk_deterministic(Ctx &c, int metric, hera_walk_stats *out) {
         HERA_CUDA(cudaMemcpyAsync(&total, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
     }
-    run_walks(c, total, 1, metric, out, [&](unsigned blocks, WalkScratch sc, WalkOut wo) {
-        HERA_LAUNCH(c, walk_det_kernel, blocks, WK_THREADS, 0, wg, sc, wo, total, walk_base);
+    run_walks(c, total, 1, metric, out, [&](unsigned blocks, uint32_t my_walks, WalkScratch sc, WalkOut wo) {
+        HERA_LAUNCH(c, walk_det_kernel, blocks, WK_THREADS, 0, wg, sc, wo, my_walks, walk_base);
     });
     if (first_edges) {
         HERA_CUDA(cudaFreeAsync(first_edges, c.stream)); HERA_CUDA(cudaFreeAsync(walk_base, c.stream)); HERA_CUDA(cudaFreeAsync(d_total, c.stream));
