@@ -9,8 +9,10 @@ A step = one pass of the hot path over one synthetic dataset of BASELINE.json co
 Monte-Carlo and greedy walks (2 metrics each) -> unique -> anchor-pair groups and consensus.
 `value` is graph-build overlaps/s with the PAF text already resident in HBM; `paths_per_s` the walk
 rate; `e2e` the same step through the C ABI from pinned host buffers with the result read back.
-N > 1 (torchrun): every rank runs the same path on its own dataset replica (different generator
-seed), no data-path collective -> weak scaling; time = max over ranks.
+N > 1 (torchrun, one rank per GPU): the SHARDED path on ONE dataset N times the size (genome, contigs
+and repeat families scaled by N -> per-GPU work fixed, weak scaling): every rank tokenizes its byte
+range of the PAF files, kept overlaps are all-gathered over NCCL, every rank holds the full CSR, walks
+are dealt out by walk id and the accepted paths all-gathered; time = max over ranks.
 """
 import argparse
 import json
@@ -46,12 +48,20 @@ def ensure_tools():
     return ROOT / "tools" / "bin" / "gen_dataset"
 
 
-def make_dataset(seed):
-    d = DATA_ROOT / f"ecoli_seed{seed}"
+def gen_args(scale):
+    """configs[1] generator options with genome, contigs and repeat families multiplied by `scale`."""
+    a = list(WORKLOAD["gen"])
+    for key, base in (("--genome", 4600000), ("--contigs", 10), ("--families", 10)):
+        a[a.index(key) + 1] = str(base * scale)
+    return a
+
+
+def make_dataset(seed, scale=1):
+    d = DATA_ROOT / (f"ecoli_seed{seed}" if scale == 1 else f"ecoli_x{scale}_seed{seed}")
     if not (d / "done").exists():
         d.mkdir(parents=True, exist_ok=True)
         gen = ensure_tools()
-        out = subprocess.run([str(gen), "--out", str(d), "--seed", str(seed)] + WORKLOAD["gen"], check=True, capture_output=True, text=True).stdout
+        out = subprocess.run([str(gen), "--out", str(d), "--seed", str(seed)] + gen_args(scale), check=True, capture_output=True, text=True).stdout
         (d / "done").write_text(out)
     return d, json.loads((d / "done").read_text())
 
@@ -147,15 +157,19 @@ def run_reference_sample(ds, steps, warmup):
 
 
 def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
-    """One step through the C ABI.  rr / cr: (pointer, nbytes).  Returns stage times (ms, CUDA events on the
-    library's stream), counts and the kernel-launch delta."""
+    """One step through the C ABI.  rr / cr: (pointer, nbytes) of the whole file, or -- sharded run -- a Slice of it.
+    Returns stage times (ms, CUDA events on the library's stream), counts and the kernel-launch delta."""
     launches0 = h.launches
     h.graph_reset()
     h.paths_reset()
-    load = h.load_device_ptr if device_resident else h.load_host_ptr
+
+    def load(src, anchors):
+        if isinstance(src, Slice):
+            return h.load_shard_ptr(src.ptr(device_resident), device_resident, src.owned, src.avail, src.prev, src.at_eof, anchors)
+        return (h.load_device_ptr if device_resident else h.load_host_ptr)(src[0], src[1], anchors)
     h.timer_start()
-    r1 = load(rr[0], rr[1], False)
-    r2 = load(cr[0], cr[1], True)
+    r1 = load(rr, False)
+    r2 = load(cr, True)
     info = h.finalize(WORKLOAD["metrics"])
     t_graph = h.timer_stop()
     h.timer_start()
@@ -185,6 +199,27 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
             "rr_bytes": r1.bytes, "rr_kept": r1.kept}
 
 
+class Slice:
+    """This rank's byte range of a PAF file (hera_shard_range): pinned host copy + device copy."""
+
+    def __init__(self, path, rank, world, dev, capi, torch, np):
+        n = path.stat().st_size
+        b, e, a = capi.shard_range(n, rank, world)
+        self.owned, self.avail, self.at_eof, self.file_bytes = e - b, a - b, a == n, n
+        self.prev = -1
+        if b:
+            with open(path, "rb") as f:
+                f.seek(b - 1)
+                self.prev = f.read(1)[0]
+        self.host = torch.empty(max(self.avail, 1), dtype=torch.uint8, pin_memory=True)
+        if self.avail:
+            self.host.numpy()[:self.avail] = np.fromfile(path, dtype=np.uint8, count=self.avail, offset=b)
+        self.dev = self.host.to(dev)
+
+    def ptr(self, device_resident):
+        return self.dev.data_ptr() if device_resident else self.host.data_ptr()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -196,10 +231,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    config = {"workload": WORKLOAD["name"], "generator": "tools/gen_dataset " + " ".join(WORKLOAD["gen"]) + f" --seed {WORKLOAD['seed']}+rank",
+    config = {"workload": WORKLOAD["name"], "generator": "tools/gen_dataset " + " ".join(WORKLOAD["gen"]) + f" --seed {WORKLOAD['seed']}",
               "filter": "reference defaults (AVG)", "rb_att": WORKLOAD["rb_att"], "metrics": WORKLOAD["metrics"],
-              "parallelism": f"{world} independent dataset replicas, no collective" if world > 1 else "single GPU",
-              "l2": "PAF text (173 MB) is larger than L2 (126 MB); the roofline leg additionally writes 512 MB before the parse kernel"}
+              "parallelism": (f"{world} ranks, one dataset {world}x the size: PAF sharded by byte range, kept overlaps all-gathered (NCCL), CSR replicated, "
+                              f"walks dealt out by walk id, paths all-gathered (NCCL)") if world > 1 else "single GPU",
+              "l2": "PAF text (173 MB per GPU) is larger than L2 (126 MB); the roofline leg additionally writes 512 MB before the parse kernel"}
+    if world > 1:
+        config["generator"] = "tools/gen_dataset " + " ".join(gen_args(world)) + f" --seed {WORKLOAD['seed']}"
 
     if args.impl == "reference":
         if rank != 0:
@@ -227,18 +265,34 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
     dev = torch.device("cuda", local_rank)
-    ds, meta = make_dataset(WORKLOAD["seed"] + rank)
-
-    def pinned(path):
-        n = path.stat().st_size
-        t = torch.empty(max(n, 1), dtype=torch.uint8, pin_memory=True)
-        t.numpy()[:n] = np.fromfile(path, dtype=np.uint8)
-        return t, n
-    rr_h, rr_n = pinned(ds / "rr_overlaps.paf")
-    cr_h, cr_n = pinned(ds / "cr_overlaps.paf")
-    rr_d, cr_d = rr_h.to(dev), cr_h.to(dev)
-    torch.cuda.synchronize(dev)
+    torch.cuda.set_device(local_rank)
+    if rank == 0:
+        make_dataset(WORKLOAD["seed"], world)
+    if world > 1:
+        dist.barrier()
+    ds, meta = make_dataset(WORKLOAD["seed"], world)
     h = capi.Hera(local_rank)
+    if world > 1:
+        # the library's own NCCL communicator (collectives run on its stream); torch.distributed only hands out the id
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(capi.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        h.comm_init_nccl(rank, world, bytes(idt.cpu().numpy()))
+        rr_s = Slice(ds / "rr_overlaps.paf", rank, world, dev, capi, torch, np)
+        cr_s = Slice(ds / "cr_overlaps.paf", rank, world, dev, capi, torch, np)
+        rr_n, cr_n = rr_s.avail, cr_s.avail
+        rr_d, cr_d = rr_s.dev, cr_s.dev
+    else:
+        def pinned(path):
+            n = path.stat().st_size
+            t = torch.empty(max(n, 1), dtype=torch.uint8, pin_memory=True)
+            t.numpy()[:n] = np.fromfile(path, dtype=np.uint8)
+            return t, n
+        rr_h, rr_n = pinned(ds / "rr_overlaps.paf")
+        cr_h, cr_n = pinned(ds / "cr_overlaps.paf")
+        rr_d, cr_d = rr_h.to(dev), cr_h.to(dev)
+    torch.cuda.synchronize(dev)
     pp = capi.default_path_params(rb_att=WORKLOAD["rb_att"])
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
 
@@ -248,6 +302,11 @@ def main():
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    def sources(device_resident):
+        if world > 1:
+            return rr_s, cr_s
+        return ((rr_d.data_ptr(), rr_n), (cr_d.data_ptr(), cr_n)) if device_resident else ((rr_h.data_ptr(), rr_n), (cr_h.data_ptr(), cr_n))
+
     def timed(device_resident, read_back, steps):
         per = []
         barrier()
@@ -256,13 +315,13 @@ def main():
             if device_resident:
                 flush.zero_()            # L2 flush between timed iterations (outside the event-timed stages)
                 torch.cuda.synchronize(dev)
-            ptrs = ((rr_d.data_ptr(), rr_n), (cr_d.data_ptr(), cr_n)) if device_resident else ((rr_h.data_ptr(), rr_n), (cr_h.data_ptr(), cr_n))
-            per.append(hot_path_step(h, capi, pp, ptrs[0], ptrs[1], device_resident, read_back))
+            src = sources(device_resident)
+            per.append(hot_path_step(h, capi, pp, src[0], src[1], device_resident, read_back))
         barrier()
         return per, time.perf_counter() - t0
 
     for _ in range(max(3, args.warmup)):
-        hot_path_step(h, capi, pp, (rr_d.data_ptr(), rr_n), (cr_d.data_ptr(), cr_n), True, False)
+        hot_path_step(h, capi, pp, *sources(True), True, False)
     with ClockSampler(local_rank) as clocks:
         dev_steps, _ = timed(True, False, args.steps)
         e2e_steps, e2e_wall = timed(False, True, args.steps)
@@ -271,7 +330,8 @@ def main():
     parse_ms = []
     for _ in range(args.steps + 1):
         h.graph_reset()
-        parse_ms.append(h.load_device_ptr(rr_d.data_ptr(), rr_n, False).parse_ms)
+        leg = h.load_device_ptr(rr_d.data_ptr(), rr_n, False)   # not collective: this rank's rr text as a stand-alone file
+        parse_ms.append(leg.parse_ms)
     h.set_option("flush_l2", 0)
     parse_ms = statistics.mean(parse_ms[1:])
 
@@ -279,13 +339,14 @@ def main():
         return sum(s[key] for s in steps)
     sums = torch.tensor([agg(dev_steps, "graph_ms"), agg(dev_steps, "paths_ms"), agg(dev_steps, "groups_ms"), e2e_wall * 1e3,
                          agg(e2e_steps, "graph_ms")], dtype=torch.float64, device=dev)
-    counts = torch.tensor([agg(dev_steps, "records"), agg(dev_steps, "walks"), agg(e2e_steps, "records"), agg(dev_steps, "launches"),
-                           agg(dev_steps, "unique_paths")], dtype=torch.float64, device=dev)
+    # records / walks / paths reported by the collective calls are already global; launches and copied bytes are per rank
+    counts = torch.tensor([agg(dev_steps, "launches"), rr_n + cr_n, e2e_steps[-1]["d2h"]], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(sums, op=dist.ReduceOp.MAX)
         dist.all_reduce(counts, op=dist.ReduceOp.SUM)
     graph_ms, paths_ms, groups_ms, e2e_ms, e2e_graph_ms = sums.tolist()
-    records, walks, e2e_records, launches, uniq = counts.tolist()
+    launches, h2d_bytes, d2h_bytes = counts.tolist()
+    records, walks, e2e_records, uniq = agg(dev_steps, "records"), agg(dev_steps, "walks"), agg(e2e_steps, "records"), agg(dev_steps, "unique_paths")
     if rank == 0:
         s0 = dev_steps[-1]
         peaks = {}
@@ -294,20 +355,20 @@ def main():
         except OSError:
             pass
         peak = peaks.get("hbm_gbs", 6650.0)
-        algo_bytes = s0["rr_bytes"] + 73 * s0["rr_kept"]   # every PAF byte read once + 73 B written per kept overlap
+        algo_bytes = leg.bytes + 73 * leg.kept   # every PAF byte read once + 73 B written per kept overlap
         achieved = algo_bytes / (parse_ms * 1e-3) / 1e9
         line = {
             "metric": "overlaps/s graph build", "value": records / (graph_ms * 1e-3), "unit": "overlaps/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": (graph_ms + paths_ms + groups_ms) / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-            "paths_per_s": walks / (paths_ms * 1e-3), "unique_paths_per_step": uniq / args.steps / world,
+            "paths_per_s": walks / (paths_ms * 1e-3), "unique_paths_per_step": uniq / args.steps,
             "stages_ms_per_step": {k: statistics.mean(s[k] for s in dev_steps) for k in
                                    ("graph_ms", "parse_ms", "intern_ms", "csr_ms", "rank_ms", "paths_ms", "groups_ms")},
             "per_step": {"records": s0["records"], "kept_overlaps": s0["kept"], "nodes": s0["nodes"], "walks": s0["walks"],
                          "adjacency_entries_examined": s0["walk_entries"], "anchor_pairs": s0["pairs"]},
             "gpu_launches": int(launches),
-            "e2e": {"value": e2e_records / (e2e_graph_ms * 1e-3), "unit": "overlaps/s", "h2d_bytes_per_step": rr_n + cr_n,
-                    "d2h_bytes_per_step": e2e_steps[-1]["d2h"], "whole_step_ms": e2e_ms / args.steps,
+            "e2e": {"value": e2e_records / (e2e_graph_ms * 1e-3), "unit": "overlaps/s", "h2d_bytes_per_step": int(h2d_bytes),
+                    "d2h_bytes_per_step": int(d2h_bytes), "whole_step_ms": e2e_ms / args.steps,
                     "note": "graph build from pinned host buffers (H2D inside the timed region); whole_step_ms adds walks, groups and the D2H read of the result"},
             "roofline": {"bound": "hbm", "kernel": "paf_parse_kernel (rr text)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s", "algorithmic_bytes": algo_bytes,
