@@ -26,7 +26,8 @@ struct LocalHub {
     bool aborted = false;
     std::vector<const void *> ptrs;
     std::vector<std::vector<uint64_t>> vals;
-    explicit LocalHub(int nranks) : n(nranks), ptrs(nranks, nullptr), vals(nranks) {}
+    std::vector<int> devices;   // CUDA device of every rank (-1 until it attached)
+    explicit LocalHub(int nranks) : n(nranks), ptrs(nranks, nullptr), vals(nranks), devices(nranks, -1) {}
 
     void barrier() {
         std::unique_lock<std::mutex> lk(m);
@@ -60,8 +61,40 @@ namespace {
 
 struct LocalExchange final : Exchange {
     std::shared_ptr<LocalHub> hub;
+    bool peers_ready = false;
     LocalExchange(std::shared_ptr<LocalHub> h, int r) : hub(std::move(h)) { rank = r; size = hub->n; }
     const char *transport() const override { return "local"; }
+    // Ranks on other GPUs pull from my buffers with peer copies: open my memory pool to them and enable
+    // peer access where the hardware has it (NVLink / PCIe P2P); otherwise the driver stages through the host.
+    void prepare_peers(Ctx &c) {
+        if (peers_ready) return;
+        {
+            std::lock_guard<std::mutex> lk(hub->m);
+            hub->devices[rank] = c.device;
+        }
+        hub->barrier();
+        cudaMemPool_t pool = nullptr;
+        const bool have_pool = cudaDeviceGetDefaultMemPool(&pool, c.device) == cudaSuccess;
+        for (int r = 0; r < size; r++) {
+            const int d = hub->devices[r];
+            if (d < 0 || d == c.device) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, c.device, d) != cudaSuccess || !can) continue;
+            const cudaError_t e = cudaDeviceEnablePeerAccess(d, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); continue; }
+            cudaGetLastError();
+            if (have_pool) {
+                cudaMemAccessDesc desc{};
+                desc.location.type = cudaMemLocationTypeDevice;
+                desc.location.id = d;
+                desc.flags = cudaMemAccessFlagsProtReadWrite;
+                cudaMemPoolSetAccess(pool, &desc, 1);
+                cudaGetLastError();
+            }
+        }
+        hub->barrier();
+        peers_ready = true;
+    }
     void abort() override { hub->abort(); }
     void barrier(Ctx &c) override {
         HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -81,6 +114,7 @@ struct LocalExchange final : Exchange {
         hub->barrier();
     }
     void all_gatherv(Ctx &c, const void *send, void *recv, const uint64_t *counts, const uint64_t *displs, size_t elem) override {
+        prepare_peers(c);
         HERA_CUDA(cudaStreamSynchronize(c.stream));   // my contribution is complete
         {
             std::lock_guard<std::mutex> lk(hub->m);
@@ -92,7 +126,8 @@ struct LocalExchange final : Exchange {
             char *dst = static_cast<char *>(recv) + displs[r] * elem;
             const void *src = hub->ptrs[r];
             if (dst == src) continue;
-            HERA_CUDA(cudaMemcpyAsync(dst, src, counts[r] * elem, cudaMemcpyDefault, c.stream));
+            if (hub->devices[r] == c.device) HERA_CUDA(cudaMemcpyAsync(dst, src, counts[r] * elem, cudaMemcpyDeviceToDevice, c.stream));
+            else HERA_CUDA(cudaMemcpyPeerAsync(dst, c.device, src, hub->devices[r], counts[r] * elem, c.stream));
         }
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         hub->barrier();                               // nobody reuses a send buffer before every rank has pulled it
