@@ -67,11 +67,21 @@ __device__ __forceinline__ uint64_t hash_finish(uint64_t h) {
     h ^= h >> 33; h *= 0xff51afd7ed558ccdull; h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ull; h ^= h >> 33;
     return h ? h : 1;  // 0 is the empty marker of the interning table
 }
-// Name hash: two 32-bit multiplicative lanes (cheap per byte), mixed to 64 bits at the end.
+// Name hash: the name as little-endian 32-bit words (last one zero-padded) through two 32-bit
+// multiplicative lanes, length folded in, mixed to 64 bits at the end.  add() feeds bytes (serial
+// readers); the tile parser feeds whole words taken from shared memory (hash_name_window).
 struct NameHash {
-    uint32_t x = 0x811C9DC5u, y = 0x9747B28Cu;
-    __device__ __forceinline__ void add(uint32_t c) { x = (x ^ c) * 0x01000193u; y = (y ^ c) * 0x85EBCA6Bu; }
-    __device__ __forceinline__ uint64_t finish() const { return hash_finish((static_cast<uint64_t>(y) << 32) | x); }
+    uint32_t x = 0x811C9DC5u, y = 0x9747B28Cu, w = 0, nb = 0;
+    __device__ __forceinline__ void mix(uint32_t word) { x = (x ^ word) * 0x01000193u; y = (y ^ word) * 0x85EBCA6Bu; }
+    __device__ __forceinline__ void add(uint32_t c) {
+        w |= c << (8 * (nb & 3));
+        nb++;
+        if ((nb & 3) == 0) { mix(w); w = 0; }
+    }
+    __device__ __forceinline__ uint64_t finish() {
+        if (nb & 3) mix(w);
+        return hash_finish((static_cast<uint64_t>(y ^ nb) << 32) | x);
+    }
 };
 
 // fp32 filter, reference src/OverlapGraph.cpp:156-202 (name equality is checked by the caller).
@@ -286,54 +296,102 @@ __device__ int slow_path_record(const ParseArgs &a, uint64_t start, SerialRecord
     return whole ? 1 : 0;
 }
 
+// ---- field readers over the staged window -------------------------------------------------------
+// `mask` has one bit per byte of the window (1 = not white space), so a token is a run of ones;
+// text words are read whole and shifted into place -- no per-byte loops on the regular path.
+
+// First position >= p whose mask bit equals `one`; >= PF_WIN when the window has none.
+__device__ __forceinline__ uint32_t next_bit(const uint32_t *mask, uint32_t p, bool one) {
+    while (p < PF_WIN) {
+        const uint32_t w = p >> 5;
+        uint32_t win = __funnelshift_r(mask[w], mask[w + 1], p & 31u);
+        if (!one) win = ~win;
+        if (win) return p + __ffs(win) - 1;
+        p += 32;
+    }
+    return PF_WIN;
+}
+
+// Hash of the token [b, e): same function as NameHash fed byte by byte.
+__device__ __forceinline__ uint64_t hash_name_window(const uint8_t *s, uint32_t b, uint32_t e) {
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(s) + (b >> 2);   // s is 16-byte aligned
+    const uint32_t sh = (b & 3u) * 8u, len = e - b;
+    NameHash h;
+    uint32_t lo = wp[0];
+    uint32_t i = 0;
+    for (; i + 4 <= len; i += 4) {
+        const uint32_t hi = *++wp;
+        h.mix(__funnelshift_r(lo, hi, sh));
+        lo = hi;
+    }
+    if (len & 3u) h.mix(__funnelshift_r(lo, wp[1], sh) & ((1u << ((len & 3u) * 8u)) - 1u));
+    h.nb = len;
+    h.w = 0;
+    return hash_finish((static_cast<uint64_t>(h.y ^ h.nb) << 32) | h.x);
+}
+
+// Four ASCII digits (first character in the low byte, already XORed with '0') -> value.
+__device__ __forceinline__ uint32_t digits4(uint32_t d) {
+    const uint32_t t = ((d * 2561u) >> 8) & 0x00ff00ffu;        // b0*10+b1 | b2*10+b3
+    return ((t * 6553601u) >> 16) & 0xffffu;
+}
+
+// Integer token [b, e): [+-]?digits within int range.  Returns false when formatted extraction would
+// fail or stop early on it (the caller declares the record irregular).
+__device__ __forceinline__ bool int_token(const uint8_t *s, uint32_t b, uint32_t e, int &out) {
+    uint32_t c0 = s[b];
+    const bool neg = c0 == '-';
+    if (neg || c0 == '+') b++;
+    const uint32_t len = e - b;
+    if (len - 1u <= 7u) {   // 1..8 digits: the eight bytes that END at e, leading bytes masked off
+        const uint32_t q = e + 8u;                 // s - 16 is readable, so (e - 8) never underflows the buffer
+        const uint32_t *wp = reinterpret_cast<const uint32_t *>(s - 16) + (q >> 2);
+        const uint32_t sh = (q & 3u) * 8u;
+        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        uint32_t lo = __funnelshift_r(w0, w1, sh) ^ 0x30303030u;   // characters e-8 .. e-5
+        uint32_t hi = __funnelshift_r(w1, w2, sh) ^ 0x30303030u;   // characters e-4 .. e-1
+        const uint32_t keep_hi = len >= 4 ? 0xffffffffu : (0xffffffffu << ((4u - len) * 8u));
+        const uint32_t keep_lo = len <= 4 ? 0u : (len == 8 ? 0xffffffffu : (0xffffffffu << ((8u - len) * 8u)));
+        lo &= keep_lo;
+        hi &= keep_hi;
+        // every kept byte must be 0..9
+        if ((((lo + 0x76767676u) | lo) | ((hi + 0x76767676u) | hi)) & 0x80808080u) return false;
+        const uint32_t v = digits4(lo) * 10000u + digits4(hi);
+        out = neg ? -static_cast<int>(v) : static_cast<int>(v);
+        return true;
+    }
+    if (len == 0) return false;
+    unsigned long long acc = 0;   // long tokens (leading zeros, values near INT_MAX): plain loop
+    for (uint32_t i = b; i < e; i++) {
+        const uint32_t d = static_cast<uint32_t>(s[i]) - '0';
+        if (d > 9u) return false;
+        if (acc <= 4294967295ull) acc = acc * 10 + d;
+    }
+    if (acc > (neg ? 2147483648ull : 2147483647ull)) return false;
+    out = neg ? static_cast<int>(0u - static_cast<uint32_t>(acc)) : static_cast<int>(static_cast<uint32_t>(acc));
+    return true;
+}
+
 // One thread reads one record from the staged window.  Returns the keep flag.
-__device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, uint32_t p0, uint64_t tile_byte0, bool reaches_eof,
-                                          uint64_t rec_idx, StagedRecord &out) {
+__device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, const uint32_t *mask, uint32_t p0, uint64_t tile_byte0,
+                                          bool reaches_eof, uint64_t rec_idx, StagedRecord &out) {
     if (rec_idx >= a.rec_limit) return false;
     SerialRecord r;
-    uint32_t p = p0;
     int status = 1;  // 1 regular, 0 irregular, 2 window exhausted
-    auto read_name = [&](uint64_t &off, uint32_t &len, uint64_t &hash) {
-        NameHash h;
-        const uint32_t b = p;
-        uint32_t c;
-        while (p < PF_WIN && !dev_is_space(c = s[p])) { h.add(c); p++; }
-        if (p >= PF_WIN) status = 2;
-        off = tile_byte0 + b; len = p - b; hash = h.finish();
-    };
-    auto skip_space = [&]() {
-        while (p < PF_WIN && dev_is_space(s[p])) p++;
-        if (p >= PF_WIN) status = 2;
-    };
-    auto read_int = [&](int &v) {
-        uint32_t c = s[p];
-        bool neg = false;
-        if (c == '+' || c == '-') { neg = c == '-'; p++; c = p < PF_WIN ? s[p] : ' '; }
-        unsigned long long acc = 0;
-        uint32_t digits = 0, d;
-        while ((d = c - '0') <= 9u) {
-            if (acc <= 4294967295ull) acc = acc * 10 + d;
-            digits++; p++;
-            if (p >= PF_WIN) { status = 2; return; }
-            c = s[p];
-        }
-        if (!dev_is_space(c) || digits == 0 || acc > (neg ? 2147483648ull : 2147483647ull)) { status = 0; return; }
-        v = neg ? static_cast<int>(0u - static_cast<uint32_t>(acc)) : static_cast<int>(static_cast<uint32_t>(acc));
-    };
-    read_name(r.qoff, r.qnlen, r.qhash);
-    int *ints3[3] = {&r.qlen, &r.qs, &r.qe};
+    uint32_t b = p0, e;
+    int ints[9];
 #pragma unroll
-    for (int f = 0; f < 3 && status == 1; f++) { skip_space(); if (status == 1) read_int(*ints3[f]); }
-    if (status == 1) skip_space();
-    if (status == 1) {  // strand: exactly one character
-        r.strand = s[p++];
-        if (p >= PF_WIN) status = 2; else if (!dev_is_space(s[p])) status = 0;
+    for (int f = 0; f < 12; f++) {
+        if (status != 1) break;
+        if (f) b = next_bit(mask, e, true);          // token start
+        e = b < PF_WIN ? next_bit(mask, b, false) : PF_WIN;   // token end
+        if (e >= PF_WIN) { status = 2; break; }
+        if (f == 0) { r.qoff = tile_byte0 + b; r.qnlen = e - b; r.qhash = hash_name_window(s, b, e); }
+        else if (f == 5) { r.toff = tile_byte0 + b; r.tnlen = e - b; r.thash = hash_name_window(s, b, e); }
+        else if (f == 4) { r.strand = s[b]; if (e - b != 1) status = 0; }
+        else if (!int_token(s, b, e, ints[f < 4 ? f - 1 : f - 3])) status = 0;
     }
-    if (status == 1) skip_space();
-    if (status == 1) read_name(r.toff, r.tnlen, r.thash);
-    int *ints6[6] = {&r.tlen, &r.ts, &r.te, &r.matches, &r.block, &r.mapq};
-#pragma unroll
-    for (int f = 0; f < 6 && status == 1; f++) { skip_space(); if (status == 1) read_int(*ints6[f]); }
+    r.qlen = ints[0]; r.qs = ints[1]; r.qe = ints[2]; r.tlen = ints[3]; r.ts = ints[4]; r.te = ints[5]; r.matches = ints[6];
     if (status == 2) {
         if (reaches_eof) return false;  // trailing record with fewer than 12 tokens: not a record
         status = slow_path_record(a, tile_byte0 + p0, r);
@@ -358,8 +416,12 @@ __device__ __forceinline__ uint32_t nonspace4(uint32_t w) {
 }
 
 __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a) {
-    __shared__ __align__(16) uint8_t s_text[PF_WIN];
-    __shared__ uint16_t s_nonws[PF_CHUNKS + 1];
+    // text window with 16 spare bytes on both sides (the field readers load whole words around a token)
+    __shared__ __align__(16) uint8_t s_raw[PF_WIN + 32];
+    // non-space bit per byte: chunk ch at s_nonws[ch + 2] (so that 32-byte units are aligned words),
+    // bit 15 of s_nonws[1] = the byte before the tile; two zero words of padding behind the window
+    __shared__ __align__(8) uint16_t s_nonws[PF_CHUNKS + 2 + 4];
+    uint8_t *s_text = s_raw + 16;
     __shared__ uint16_t s_rec_off[PF_MAXREC];
     __shared__ uint32_t s_scan[33];
     __shared__ unsigned int s_tile;
@@ -377,12 +439,14 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
     for (int ch = tid; ch < PF_CHUNKS; ch += PF_THREADS) {
         const uint4 v = __ldg(src + ch);
         reinterpret_cast<uint4 *>(s_text)[ch] = v;
-        s_nonws[ch + 1] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
+        s_nonws[ch + 2] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
     }
     if (tid == 0) {
         uint32_t prev_nonws = a.prev_nonws ? 1u : 0u;  // does the byte before the tile belong to a token?
         if (tile_byte0 > 0) prev_nonws = dev_is_space(a.text[tile_byte0 - 1]) ? 0u : 1u;
-        s_nonws[0] = static_cast<uint16_t>(prev_nonws << 15);
+        s_nonws[1] = static_cast<uint16_t>(prev_nonws << 15);
+        for (int k = 0; k < 4; k++) s_nonws[PF_CHUNKS + 2 + k] = 0;
+        for (int k = 0; k < 4; k++) { reinterpret_cast<uint32_t *>(s_raw)[k] = 0x20202020u; reinterpret_cast<uint32_t *>(s_raw + 16 + PF_WIN)[k] = 0x20202020u; }
     }
     __syncthreads();
 
@@ -394,8 +458,8 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
         const int ch = tid * PF_CPT + k;
         uint32_t starts = 0;
         if (ch < PF_TILE / 16) {
-            const uint32_t cur = s_nonws[ch + 1];
-            starts = cur & ~((cur << 1) | ((s_nonws[ch] >> 15) & 1u)) & 0xffffu;
+            const uint32_t cur = s_nonws[ch + 2];
+            starts = cur & ~((cur << 1) | ((s_nonws[ch + 1] >> 15) & 1u)) & 0xffffu;
             const uint64_t b0 = tile_byte0 + static_cast<uint64_t>(ch) * 16;
             if (b0 + 16 > a.owned) starts = b0 >= a.owned ? 0u : (starts & ((1u << static_cast<uint32_t>(a.owned - b0)) - 1u));
         }
@@ -443,7 +507,7 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
         const uint32_t j = b0 + tid;
         StagedRecord r;
         bool keep = false;
-        if (j < nrec) keep = parse_one(a, s_text, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+        if (j < nrec) keep = parse_one(a, s_text, reinterpret_cast<const uint32_t *>(s_nonws) + 1, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
         uint32_t tot;
         const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
         if (b0 == 0) { mine = r; keep0 = keep; e0 = ex; tot0 = tot; }
@@ -464,7 +528,7 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
         const uint32_t j = b0 + tid;
         StagedRecord r;
         bool keep = false;
-        if (j < nrec) keep = parse_one(a, s_text, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+        if (j < nrec) keep = parse_one(a, s_text, reinterpret_cast<const uint32_t *>(s_nonws) + 1, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
         uint32_t tot;
         const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
         if (keep) store_record(a.kept, out0 + run + ex, r);
