@@ -84,6 +84,10 @@ struct NameHash {
     }
 };
 
+// x / 2.0f of the reference: the operand is an int converted to float (0 or |x| >= 1), so halving is exact
+// and x * 0.5f gives the same bits as the IEEE division.
+__device__ __forceinline__ float half_exact(float x) { return __fmul_rn(x, 0.5f); }
+
 // fp32 filter, reference src/OverlapGraph.cpp:156-202 (name equality is checked by the caller).
 __device__ __forceinline__ bool filter_fields(const FilterDev &f, int qlen, int qs, int qe, int tlen, int ts, int te) {
     const int q_ovl = static_cast<int>(static_cast<uint32_t>(qe) - static_cast<uint32_t>(qs));
@@ -100,7 +104,7 @@ __device__ __forceinline__ bool filter_fields(const FilterDev &f, int qlen, int 
         const float sh = __int2float_rn(static_cast<int>(static_cast<uint32_t>(q_ohg) + static_cast<uint32_t>(t_ohg)));
         const float st = __int2float_rn(static_cast<int>(static_cast<uint32_t>(qlen) + static_cast<uint32_t>(tlen)));
         if (f.mode == HERA_MODE_AVG) {
-            ovl = __fdiv_rn(so, 2.0f); ohg = __fdiv_rn(sh, 2.0f); tot = __fdiv_rn(st, 2.0f);
+            ovl = half_exact(so); ohg = half_exact(sh); tot = half_exact(st);
         } else if (f.mode == HERA_MODE_SUM) {
             ovl = so; ohg = sh; tot = st;
         } else {
@@ -117,10 +121,10 @@ __device__ __forceinline__ void score_fields(int qlen, int qs, int qe, int tlen,
     const int t_ovl = static_cast<int>(static_cast<uint32_t>(te) - static_cast<uint32_t>(ts));
     const int q_ohg = static_cast<int>(static_cast<uint32_t>(qlen) - static_cast<uint32_t>(qe));
     si = __fdiv_rn(__int2float_rn(matches), __int2float_rn(min(qlen, tlen)));
-    const float half_ovl = __fdiv_rn(__int2float_rn(static_cast<int>(static_cast<uint32_t>(q_ovl) + static_cast<uint32_t>(t_ovl))), 2.0f);
+    const float half_ovl = half_exact(__int2float_rn(static_cast<int>(static_cast<uint32_t>(q_ovl) + static_cast<uint32_t>(t_ovl))));
     os = __fmul_rn(half_ovl, si);
-    const float ext = __fdiv_rn(__int2float_rn(qs), 2.0f);
-    const float ohg = __fdiv_rn(__int2float_rn(static_cast<int>(static_cast<uint32_t>(q_ohg) + static_cast<uint32_t>(ts))), 2.0f);
+    const float ext = half_exact(__int2float_rn(qs));
+    const float ohg = half_exact(__int2float_rn(static_cast<int>(static_cast<uint32_t>(q_ohg) + static_cast<uint32_t>(ts))));
     es = fabsf(__fsub_rn(__fadd_rn(os, ext), ohg));
 }
 
@@ -381,10 +385,25 @@ __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, 
     uint32_t b = p0, e;
     int ints[9];
 #pragma unroll
+    uint32_t nb = 0;   // start of the next token
     for (int f = 0; f < 12; f++) {
         if (status != 1) break;
-        if (f) b = next_bit(mask, e, true);          // token start
-        e = b < PF_WIN ? next_bit(mask, b, false) : PF_WIN;   // token end
+        if (f) b = nb;
+        if (b >= PF_WIN) { status = 2; break; }
+        {   // one 32-bit window usually holds the end of this token and the start of the next
+            const uint32_t w = b >> 5;
+            const uint32_t win = __funnelshift_r(mask[w], mask[w + 1], b & 31u);
+            const uint32_t zeros = ~win;
+            if (zeros) {
+                const uint32_t eo = __ffs(zeros) - 1;
+                e = b + eo;
+                const uint32_t ones = win & (0xffffffffu << eo);
+                nb = ones ? b + __ffs(ones) - 1 : next_bit(mask, b + 32, true);
+            } else {
+                e = next_bit(mask, b + 32, false);
+                nb = next_bit(mask, e, true);
+            }
+        }
         if (e >= PF_WIN) { status = 2; break; }
         if (f == 0) { r.qoff = tile_byte0 + b; r.qnlen = e - b; r.qhash = hash_name_window(s, b, e); }
         else if (f == 5) { r.toff = tile_byte0 + b; r.tnlen = e - b; r.thash = hash_name_window(s, b, e); }
@@ -404,6 +423,16 @@ __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, 
     return make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), out);
 }
 
+// Position of the k-th (0-based) set bit of a 16-bit mask that has more than k bits set.
+__device__ __forceinline__ uint32_t select_bit16(uint32_t m, uint32_t k) {
+    uint32_t pos = 0, c;
+    c = __popc(m & 0xffu); if (k >= c) { k -= c; pos = 8; m >>= 8; }
+    c = __popc(m & 0xfu);  if (k >= c) { k -= c; pos += 4; m >>= 4; }
+    c = __popc(m & 0x3u);  if (k >= c) { k -= c; pos += 2; m >>= 2; }
+    c = m & 1u;            if (k >= c) pos += 1;
+    return pos;
+}
+
 // 4 bits: byte b of w is not white space (SWAR, no per-byte loop).
 __device__ __forceinline__ uint32_t nonspace4(uint32_t w) {
     const uint32_t low7 = w & 0x7f7f7f7fu;
@@ -415,7 +444,7 @@ __device__ __forceinline__ uint32_t nonspace4(uint32_t w) {
     return (((ns >> 7) * 0x00204081u) >> 21) & 0xfu;
 }
 
-__global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a) {
+__global__ void __launch_bounds__(PF_THREADS, 3) paf_parse_kernel(const ParseArgs a) {
     // text window with 16 spare bytes on both sides (the field readers load whole words around a token)
     __shared__ __align__(16) uint8_t s_raw[PF_WIN + 32];
     // non-space bit per byte: chunk ch at s_nonws[ch + 2] (so that 32-byte units are aligned words),
@@ -489,7 +518,7 @@ __global__ void __launch_bounds__(PF_THREADS) paf_parse_kernel(const ParseArgs a
             const uint32_t cnt = __popc(my_mask[k]);
             const uint32_t rem = static_cast<uint32_t>((16 - ((tok_base + o) & 15)) & 15);
             if (rem < cnt) {  // a 16-byte chunk holds at most 8 token starts, so at most one record start
-                const uint32_t bit = __fns(my_mask[k], 0, static_cast<int>(rem) + 1);
+                const uint32_t bit = select_bit16(my_mask[k], rem);
                 s_rec_off[(o + rem - first_rec_ord) >> 4] = static_cast<uint16_t>((tid * PF_CPT + k) * 16 + bit);
             }
             o += cnt;
