@@ -444,7 +444,7 @@ __device__ __forceinline__ uint32_t nonspace4(uint32_t w) {
     return (((ns >> 7) * 0x00204081u) >> 21) & 0xfu;
 }
 
-__global__ void __launch_bounds__(PF_THREADS, 3) paf_parse_kernel(const ParseArgs a) {
+__global__ void __launch_bounds__(PF_THREADS, 4) paf_parse_kernel(const ParseArgs a) {
     // text window with 16 spare bytes on both sides (the field readers load whole words around a token)
     __shared__ __align__(16) uint8_t s_raw[PF_WIN + 32];
     // non-space bit per byte: chunk ch at s_nonws[ch + 2] (so that 32-byte units are aligned words),
