@@ -80,6 +80,8 @@ struct GraphTables {
     DBuf<uint32_t> a_nbr;                    // neighbour id, bit 31 = neighbour is an anchor
     DBuf<float> a_es, a_os;
     DBuf<int32_t> a_delta;                   // q_start - t_start of the slot (src/Path.cpp:13)
+    DBuf<uint4> adj4;                        // the same four fields interleaved {nbr, es, os, delta}: one 128-bit load per entry in the roulette scan
+    DBuf<uint8_t> node_exact;                // bit m: the fp64 sum of metric m over any subset of the node's list is exact in any order
     DBuf<uint32_t> rank[4];                  // per metric; empty if not built
     bool rank_ready[4] = {false, false, false, false};
     DBuf<uint32_t> canon;
@@ -103,6 +105,7 @@ struct Ctx {
     cudaEvent_t timer0 = nullptr, timer1 = nullptr;
     int opt_flush_l2 = 0;
     int opt_walk_warps_per_sm = 32;
+    int opt_walk_smem_bitmap = 1;  // 0 = keep the walks' visited bitmaps in global memory whatever the graph size (tests)
     uint64_t walk_pool_hint = 0;   // largest path pool a walk call needed so far (avoids the overflow re-run)
     DBuf<uint8_t> l2_flush_buf;
     std::unique_ptr<Exchange> xch;   // null = single rank

@@ -161,10 +161,12 @@ __global__ void csr_offsets_kernel(uint64_t S, uint64_t N, const uint32_t *__res
     if (s == 0 || keys[s] != keys[s - 1]) off[keys[s]] = static_cast<uint32_t>(s);
 }
 
+__device__ __forceinline__ float metric_value(int metric, float es, float os);
+
 __global__ void csr_gather_kernel(uint64_t S, const uint32_t *__restrict__ pay, const uint32_t *__restrict__ e_q, const uint32_t *__restrict__ e_t,
                                   const uint32_t *__restrict__ qs, const uint32_t *__restrict__ ts, const float *__restrict__ es,
                                   const float *__restrict__ os, const uint8_t *__restrict__ node_anchor, uint32_t *__restrict__ a_nbr,
-                                  float *__restrict__ a_es, float *__restrict__ a_os, int32_t *__restrict__ a_delta) {
+                                  float *__restrict__ a_es, float *__restrict__ a_os, int32_t *__restrict__ a_delta, uint4 *__restrict__ adj4) {
     const uint64_t s = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (s >= S) return;
     const uint32_t p = pay[s], e = p >> 1, side = p & 1;
@@ -174,6 +176,46 @@ __global__ void csr_gather_kernel(uint64_t S, const uint32_t *__restrict__ pay, 
     a_os[s] = os[e];
     const int64_t d = side ? static_cast<int64_t>(ts[e]) - static_cast<int64_t>(qs[e]) : static_cast<int64_t>(qs[e]) - static_cast<int64_t>(ts[e]);
     a_delta[s] = static_cast<int32_t>(d);
+    adj4[s] = make_uint4(a_nbr[s], __float_as_uint(es[e]), __float_as_uint(os[e]), static_cast<uint32_t>(static_cast<int32_t>(d)));
+}
+
+// One warp per node.  The roulette of the Monte-Carlo walk needs the fp64 sum of the candidates'
+// metrics in list order (src/PathManager.cpp:63-66,107-113).  If every value of the node's list is a
+// non-negative finite fp32 number, hence an integer multiple of q = 2^(smallest exponent - 23), and the
+// sum of ALL of them stays below 2^53 * q, then every partial sum over every subset is an integer
+// multiple of q below 2^53 * q: exactly representable, so any summation order gives the sequential
+// result bit for bit.  Bit m of node_exact[x] records that for metric m.
+__global__ void __launch_bounds__(128) node_exact_kernel(uint32_t N, const uint32_t *__restrict__ off, const float *__restrict__ a_es,
+                                                         const float *__restrict__ a_os, uint8_t *__restrict__ node_exact) {
+    const uint32_t x = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (x >= N) return;
+    const uint32_t base = off[x], deg = off[x + 1] - base;
+    uint32_t flags = 0;
+    for (int m = 0; m < 4; m++) {
+        bool weird = false;
+        int min_exp = 1 << 20;
+        double part = 0.0;
+        for (uint32_t k = lane; k < deg; k += 32) {
+            const float v = metric_value(m, a_es[base + k], a_os[base + k]);
+            const uint32_t bits = __float_as_uint(v), ex = (bits >> 23) & 0xffu;
+            if ((bits >> 31) || ex == 0xffu) weird = true;
+            else if (bits != 0) min_exp = min(min_exp, static_cast<int>(ex ? ex : 1u) - 150);
+            part = __dadd_rn(part, static_cast<double>(v));
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            min_exp = min(min_exp, __shfl_xor_sync(0xffffffffu, min_exp, d));
+            part = __dadd_rn(part, __shfl_xor_sync(0xffffffffu, part, d));
+        }
+        weird = __any_sync(0xffffffffu, weird);
+        bool exact = !weird;
+        if (exact && part > 0.0) {
+            const int total_exp = static_cast<int>((__double_as_longlong(part) >> 52) & 0x7ff) - 1023;
+            exact = total_exp < min_exp + 53;
+        }
+        if (exact) flags |= 1u << m;
+    }
+    if (lane == 0) node_exact[x] = static_cast<uint8_t>(flags);
 }
 
 __global__ void anchor_list_kernel(uint64_t N, const uint8_t *__restrict__ node_anchor, const uint32_t *__restrict__ anchor_scan, uint32_t *__restrict__ anchor_ids) {
@@ -354,12 +396,13 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         HERA_CUDA(cudaMallocAsync(&keys_alt, occ * sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMallocAsync(&vals_alt, occ * sizeof(uint32_t), c.stream));
         g.adj_pay.reserve(occ); g.adj_off.reserve(N + 1);
-        g.a_nbr.reserve(occ); g.a_es.reserve(occ); g.a_os.reserve(occ); g.a_delta.reserve(occ); g.canon.reserve(occ);
+        g.a_nbr.reserve(occ); g.a_es.reserve(occ); g.a_os.reserve(occ); g.a_delta.reserve(occ); g.canon.reserve(occ); g.adj4.reserve(occ); g.node_exact.reserve(N);
         HERA_LAUNCH(c, csr_entries_kernel, div_up(occ, 256), 256, 0, E, g.e_q.p, g.e_t.p, keys32, g.adj_pay.p);
         radix_sort_pairs(c, keys32, g.adj_pay.p, keys_alt, vals_alt, occ, bits_for(N));
         HERA_LAUNCH(c, csr_offsets_kernel, div_up(occ + 1, 256), 256, 0, occ, N, keys32, g.adj_off.p);
         HERA_LAUNCH(c, csr_gather_kernel, div_up(occ, 256), 256, 0, occ, g.adj_pay.p, g.e_q.p, g.e_t.p, c.kept.qs.p, c.kept.ts.p, c.kept.es.p, c.kept.os.p,
-                    g.node_anchor.p, g.a_nbr.p, g.a_es.p, g.a_os.p, g.a_delta.p);
+                    g.node_anchor.p, g.a_nbr.p, g.a_es.p, g.a_os.p, g.a_delta.p, g.adj4.p);
+        HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.a_es.p, g.a_os.p, g.node_exact.p);
         HERA_CUDA(cudaFreeAsync(keys32, c.stream)); HERA_CUDA(cudaFreeAsync(keys_alt, c.stream)); HERA_CUDA(cudaFreeAsync(vals_alt, c.stream));
         HERA_CUDA(cudaEventRecord(ev[2], c.stream));
 

@@ -30,8 +30,12 @@ struct WalkGraph {
     const uint32_t *off, *nbr, *canon, *rank, *node_len, *anchor_ids;
     const float *metric;      // a_es or a_os
     const int32_t *delta;
+    const uint4 *adj4;        // {nbr, es, os, delta} per slot
+    const uint8_t *node_exact;
     uint32_t N, anchors;
     int sqrt_metric;
+    int use_os;               // which field of adj4 is the metric
+    uint32_t exact_bit;       // bit of node_exact for this metric
 };
 
 struct WalkScratch {
@@ -113,17 +117,34 @@ __device__ __forceinline__ void clear_visited(uint32_t *bm, uint32_t words, cons
     __syncwarp();
 }
 
+// Visited-set probe: the walk's bitmap lives in shared memory when the graph is small enough
+// (SMEM_BM), else in the warp's slab of global scratch.
+template <bool SMEM_BM>
+__device__ __forceinline__ bool bm_get(const uint32_t *s_bm, const uint32_t *g_bm, uint32_t i) {
+    if (SMEM_BM) return (s_bm[i >> 5] >> (i & 31)) & 1u;
+    return (g_bm[i >> 5] >> (i & 31)) & 1u;
+}
+
+template <bool SMEM_BM>
 __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkScratch sc, WalkOut o, uint32_t total_walks, uint32_t attempts,
                                                              int backtrack_attempts, long long len_threshold, uint64_t seed, uint32_t metric_id) {
-    __shared__ uint32_t s_cslot[WK_WARPS][WK_CACHE];
-    __shared__ float s_cval[WK_WARPS][WK_CACHE];
+    // dynamic shared memory: candidate cache (slot, value) per warp, then the per-warp visited bitmaps
+    extern __shared__ __align__(16) uint32_t wk_smem[];
     const uint32_t lane = lane_id(), wib = warp_id();
+    uint32_t *s_cslot = wk_smem + wib * WK_CACHE;
+    float *s_cval = reinterpret_cast<float *>(wk_smem + WK_WARPS * WK_CACHE) + wib * WK_CACHE;
+    uint32_t *s_bm = wk_smem + 2 * WK_WARPS * WK_CACHE + (SMEM_BM ? wib * sc.words : 0u);
     const uint32_t wslot = blockIdx.x * WK_WARPS + wib;
-    uint32_t *bm = sc.bitmap + static_cast<uint64_t>(wslot) * sc.words;
+    uint32_t *g_bm = sc.bitmap + (SMEM_BM ? 0ull : static_cast<uint64_t>(wslot) * sc.words);
+    uint32_t *bm = SMEM_BM ? s_bm : g_bm;
     uint32_t *nodes = sc.nodes + static_cast<uint64_t>(wslot) * sc.cap;
     uint32_t *slots = sc.slots + static_cast<uint64_t>(wslot) * sc.cap;
     uint32_t *vlog = sc.vlog + static_cast<uint64_t>(wslot) * sc.cap;
     unsigned long long examined = 0;
+    if (SMEM_BM) {
+        for (uint32_t i = lane; i < sc.words; i += 32) s_bm[i] = 0;
+        __syncwarp();
+    }
 
     for (;;) {
         uint32_t local = 0;
@@ -143,31 +164,28 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
 
         for (;;) {
             const uint32_t base = g.off[cur], deg = g.off[cur + 1] - base;
-            // ---- pass 1: forced anchor edge, candidate set, exactness bookkeeping (src/PathManager.cpp:53-67)
+            const bool order_free = (g.node_exact[cur] & g.exact_bit) != 0;
+            // ---- pass 1: forced anchor edge, candidate set (src/PathManager.cpp:53-67)
             int forced = -1;
             double part = 0.0;
             uint32_t ncand = 0;
-            int min_exp = 1 << 20;
-            bool weird = false;
             for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
                 const uint32_t k = c0 + lane;
                 const bool valid = k < deg;
-                const uint32_t nbw = valid ? g.nbr[base + k] : 0u;
-                const uint32_t nb = nbw & 0x7fffffffu;
-                const bool force = valid && (nbw >> 31) && nb != start;
+                uint4 a = make_uint4(0, 0, 0, 0);
+                if (valid) a = __ldg(g.adj4 + base + k);
+                const uint32_t nb = a.x & 0x7fffffffu;
+                const bool force = valid && (a.x >> 31) && nb != start;
                 const uint32_t fb = __ballot_sync(0xffffffffu, force);
                 if (fb) { forced = static_cast<int>(c0) + __ffs(fb) - 1; break; }
-                const bool cand = valid && !bit_get(bm, nb);
+                const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, nb);
                 const uint32_t cb = __ballot_sync(0xffffffffu, cand);
                 if (cand) {
-                    const float v = walk_metric(g, base + k);
-                    const uint32_t bits = __float_as_uint(v);
-                    const uint32_t ex = (bits >> 23) & 0xffu;
-                    if ((bits >> 31) || ex == 0xffu) weird = true;                 // negative, inf, nan
-                    else if (bits != 0) min_exp = min(min_exp, static_cast<int>(ex ? ex : 1u) - 150);  // exponent of the lowest mantissa bit
+                    float v = __uint_as_float(g.use_os ? a.z : a.y);
+                    if (g.sqrt_metric) v = __fsqrt_rn(v);
                     part = __dadd_rn(part, static_cast<double>(v));
                     const uint32_t idx = ncand + __popc(cb & ((1u << lane) - 1u));
-                    if (idx < WK_CACHE) { s_cslot[wib][idx] = k; s_cval[wib][idx] = v; }
+                    if (idx < WK_CACHE) { s_cslot[idx] = k; s_cval[idx] = v; }
                 }
                 ncand += __popc(cb);
             }
@@ -186,7 +204,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
                         const uint32_t bb = g.off[back], bd = g.off[back + 1] - bb;
                         for (uint32_t c0 = 0; c0 < bd && !open; c0 += 32) {
                             const uint32_t k = c0 + lane;
-                            const bool un = k < bd && !bit_get(bm, g.nbr[bb + k] & 0x7fffffffu);
+                            const bool un = k < bd && !bm_get<SMEM_BM>(s_bm, g_bm, g.nbr[bb + k] & 0x7fffffffu);
                             open = __any_sync(0xffffffffu, un);
                         }
                         examined += bd;
@@ -202,53 +220,51 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
                 __syncwarp();
                 const double u = mc_draw(seed, metric_id, start, attempt, draws);
                 draws++;
-                const uint32_t weird_any = __any_sync(0xffffffffu, weird);
+                if (order_free && ncand <= WK_CACHE) {
+                    // Every partial sum is exact in any order (node_exact): lane l sums candidates [l*K, (l+1)*K),
+                    // lane totals are scanned, and the lane whose range crosses u*sum walks it once more.
+                    const uint32_t K = ((ncand + 31) >> 5) | 1u;   // odd stride: no bank conflicts
+                    const uint32_t lo = min(lane * K, ncand), hi = min(lo + K, ncand);
+                    double mine = 0.0;
+                    for (uint32_t i = lo; i < hi; i++) mine = __dadd_rn(mine, static_cast<double>(s_cval[i]));
+                    double incl = mine;
 #pragma unroll
-                for (int d = 16; d > 0; d >>= 1) min_exp = min(min_exp, __shfl_xor_sync(0xffffffffu, min_exp, d));
-                double total = warp_sum(part);
-                // exact in any order?  total < 2^(min_exp + 53)
-                bool exact = !weird_any;
-                if (exact && total > 0.0) {
-                    const int total_exp = static_cast<int>((__double_as_longlong(total) >> 52) & 0x7ff) - 1023;
-                    exact = total_exp < min_exp + 53;
-                }
-                const bool cached = ncand <= WK_CACHE;
-                if (exact && cached) {
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const double up = __shfl_up_sync(0xffffffffu, incl, d);
+                        if (lane >= static_cast<uint32_t>(d)) incl = __dadd_rn(incl, up);
+                    }
+                    const double total = __shfl_sync(0xffffffffu, incl, 31);
                     const double target = __dmul_rn(u, total);
-                    double carry = 0.0;
-                    for (uint32_t c0 = 0; c0 < ncand && pick < 0; c0 += 32) {
-                        const uint32_t i = c0 + lane;
-                        double v = i < ncand ? static_cast<double>(s_cval[wib][i]) : 0.0;
-#pragma unroll
-                        for (int d = 1; d < 32; d <<= 1) {
-                            const double up = __shfl_up_sync(0xffffffffu, v, d);
-                            if (lane >= static_cast<uint32_t>(d)) v = __dadd_rn(v, up);
+                    const uint32_t hit = __ballot_sync(0xffffffffu, hi > lo && incl >= target);
+                    if (hit) {
+                        const uint32_t src = __ffs(hit) - 1;
+                        int found = -1;
+                        if (lane == src) {
+                            double run = __dsub_rn(incl, mine);   // exact: both are multiples of the node's quantum
+                            for (uint32_t i = lo; i < hi; i++) {
+                                run = __dadd_rn(run, static_cast<double>(s_cval[i]));
+                                if (run >= target) { found = static_cast<int>(s_cslot[i]); break; }
+                            }
                         }
-                        const double incl = __dadd_rn(carry, v);
-                        const uint32_t hit = __ballot_sync(0xffffffffu, i < ncand && incl >= target);
-                        if (hit) pick = static_cast<int>(s_cslot[wib][c0 + __ffs(hit) - 1]);
-                        carry = __shfl_sync(0xffffffffu, incl, 31);
+                        pick = __shfl_sync(0xffffffffu, found, src);
                     }
                 } else {
                     // list-order accumulation: every lane replays the same sequence of additions
-                    double seq = 0.0;
-                    if (!exact) {
-                        for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
-                            const uint32_t k = c0 + lane;
-                            const bool valid = k < deg;
-                            const bool cand = valid && !bit_get(bm, g.nbr[base + k] & 0x7fffffffu);
-                            const float v = cand ? walk_metric(g, base + k) : 0.0f;
-                            const uint32_t cb = __ballot_sync(0xffffffffu, cand);
-                            for (uint32_t m = cb; m; m &= m - 1) seq = __dadd_rn(seq, static_cast<double>(__shfl_sync(0xffffffffu, v, __ffs(m) - 1)));
-                        }
-                        total = seq;
+                    double total = 0.0;
+                    for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
+                        const uint32_t k = c0 + lane;
+                        const bool valid = k < deg;
+                        const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, g.nbr[base + k] & 0x7fffffffu);
+                        const float v = cand ? walk_metric(g, base + k) : 0.0f;
+                        const uint32_t cb = __ballot_sync(0xffffffffu, cand);
+                        for (uint32_t m = cb; m; m &= m - 1) total = __dadd_rn(total, static_cast<double>(__shfl_sync(0xffffffffu, v, __ffs(m) - 1)));
                     }
                     const double target = __dmul_rn(u, total);
-                    seq = 0.0;
+                    double seq = 0.0;
                     for (uint32_t c0 = 0; c0 < deg && pick < 0; c0 += 32) {
                         const uint32_t k = c0 + lane;
                         const bool valid = k < deg;
-                        const bool cand = valid && !bit_get(bm, g.nbr[base + k] & 0x7fffffffu);
+                        const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, g.nbr[base + k] & 0x7fffffffu);
                         const float v = cand ? walk_metric(g, base + k) : 0.0f;
                         const uint32_t cb = __ballot_sync(0xffffffffu, cand);
                         for (uint32_t m = cb; m; m &= m - 1) {
@@ -263,9 +279,10 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
             }
             // ---- take the edge (src/PathManager.cpp:117-142)
             const uint32_t slot = base + static_cast<uint32_t>(pick);
-            const uint32_t nbw = g.nbr[slot];
+            const uint4 taken = __ldg(g.adj4 + slot);
+            const uint32_t nbw = taken.x;
             cur = nbw & 0x7fffffffu;
-            const int32_t dl = g.delta[slot];
+            const int32_t dl = static_cast<int32_t>(taken.w);
             if (n_nodes >= sc.cap) break;  // cannot happen: a walk visits every node at most once
             if (lane == 0) {
                 nodes[n_nodes] = cur; slots[n_nodes - 1] = slot; vlog[nlog] = cur;
@@ -433,6 +450,9 @@ WalkGraph make_walk_graph(Ctx &c, int metric) {
     w.node_len = g.node_len.p; w.anchor_ids = g.anchor_ids.p;
     w.metric = (metric == HERA_EXTENSION_SCORE || metric == HERA_EXTENSION_SCORE_SQRT) ? g.a_es.p : g.a_os.p;
     w.delta = g.a_delta.p;
+    w.adj4 = g.adj4.p; w.node_exact = g.node_exact.p;
+    w.use_os = (metric == HERA_OVERLAP_SCORE || metric == HERA_OVERLAP_SCORE_SQRT) ? 1 : 0;
+    w.exact_bit = 1u << metric;
     w.N = static_cast<uint32_t>(g.N); w.anchors = static_cast<uint32_t>(g.anchors);
     w.sqrt_metric = (metric == HERA_EXTENSION_SCORE_SQRT || metric == HERA_OVERLAP_SCORE_SQRT) ? 1 : 0;
     return w;
@@ -625,8 +645,18 @@ void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t s
     HERA_REQUIRE(total < (1ull << 32), 9, "too many Monte-Carlo walks for one call");
     WalkGraph wg = make_walk_graph(c, metric);
     run_walks(c, static_cast<uint32_t>(total), 0, metric, out, [&](unsigned blocks, uint32_t my_walks, WalkScratch sc, WalkOut wo) {
-        HERA_LAUNCH(c, walk_mc_kernel, blocks, WK_THREADS, 0, wg, sc, wo, my_walks, static_cast<uint32_t>(pp.rebuild_attempts),
-                    pp.backtrack_attempts, static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
+        // visited bitmaps in shared memory while four of them fit beside the candidate cache (N <= 65536 nodes)
+        const bool smem_bm = c.opt_walk_smem_bitmap && sc.words <= 2048;
+        const size_t smem = (2ull * WK_WARPS * WK_CACHE + (smem_bm ? static_cast<size_t>(WK_WARPS) * sc.words : 0)) * sizeof(uint32_t);
+        if (smem_bm) {
+            walk_mc_kernel<true><<<blocks, WK_THREADS, smem, c.stream>>>(wg, sc, wo, my_walks, static_cast<uint32_t>(pp.rebuild_attempts), pp.backtrack_attempts,
+                                                                        static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
+        } else {
+            walk_mc_kernel<false><<<blocks, WK_THREADS, smem, c.stream>>>(wg, sc, wo, my_walks, static_cast<uint32_t>(pp.rebuild_attempts), pp.backtrack_attempts,
+                                                                         static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
+        }
+        c.launches.count++;
+        HERA_CUDA(cudaGetLastError());
     });
 }
 

@@ -98,3 +98,15 @@ def test_reader_edge_cases_gpu(oracle_bin, tmp_path):
     gpu = pipeline.run_hot_path(d, ["--mode", "max"], stages="graph")
     common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS, "both")
     assert gpu["node_anchor"].sum() == 0
+
+
+def test_walk_bitmap_in_global_memory(oracle_bin, datasets, tmp_path):
+    """Graphs above 65536 nodes keep the visited bitmaps of the Monte-Carlo walks in global memory; force that path."""
+    from telomeri_b200 import capi, pipeline
+    golden = common.load_golden("small_default")
+    ds = datasets[golden["dataset"]]
+    ora = common.run_dump(oracle_bin, ds, tmp_path / "o.bin", golden["options"], extra=["--rng", "philox", "--seed", "77"])
+    with capi.Hera(0) as h:
+        h.set_option("walk_smem_bitmap", 0)
+        gpu = pipeline.run_hot_path(ds, golden["options"], seed=77, hera=h)
+    common.assert_sections_equal(ora, gpu, PATH_SECTIONS + GROUP_SECTIONS, "global bitmap")
