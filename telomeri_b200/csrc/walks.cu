@@ -24,7 +24,8 @@ namespace hera {
 
 constexpr int WK_THREADS = 128;
 constexpr int WK_WARPS = WK_THREADS / 32;
-constexpr int WK_CACHE = 512;   // candidates cached in shared memory per warp between the two roulette passes
+constexpr int WK_MLP = 4;       // 32-entry chunks of the current node's list loaded per round trip
+constexpr int WK_CACHE = 1024;  // list entries (metric values) a warp keeps in shared memory between the two roulette passes
 
 struct WalkGraph {
     const uint32_t *off, *nbr, *canon, *rank, *node_len, *anchor_ids;
@@ -128,12 +129,11 @@ __device__ __forceinline__ bool bm_get(const uint32_t *s_bm, const uint32_t *g_b
 template <bool SMEM_BM>
 __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkScratch sc, WalkOut o, uint32_t total_walks, uint32_t attempts,
                                                              int backtrack_attempts, long long len_threshold, uint64_t seed, uint32_t metric_id) {
-    // dynamic shared memory: candidate cache (slot, value) per warp, then the per-warp visited bitmaps
+    // dynamic shared memory: per-warp value cache of the current node's list, then the per-warp visited bitmaps
     extern __shared__ __align__(16) uint32_t wk_smem[];
     const uint32_t lane = lane_id(), wib = warp_id();
-    uint32_t *s_cslot = wk_smem + wib * WK_CACHE;
-    float *s_cval = reinterpret_cast<float *>(wk_smem + WK_WARPS * WK_CACHE) + wib * WK_CACHE;
-    uint32_t *s_bm = wk_smem + 2 * WK_WARPS * WK_CACHE + (SMEM_BM ? wib * sc.words : 0u);
+    float *s_cval = reinterpret_cast<float *>(wk_smem) + wib * WK_CACHE;
+    uint32_t *s_bm = wk_smem + WK_WARPS * WK_CACHE + (SMEM_BM ? wib * sc.words : 0u);
     const uint32_t wslot = blockIdx.x * WK_WARPS + wib;
     uint32_t *g_bm = sc.bitmap + (SMEM_BM ? 0ull : static_cast<uint64_t>(wslot) * sc.words);
     uint32_t *bm = SMEM_BM ? s_bm : g_bm;
@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
         const uint32_t start = g.anchor_ids[walk / attempts], attempt = walk % attempts;
 
         uint32_t n_nodes = 1, nlog = 1, draws = 0;
+        double u_bank = 0.0;
         int backtracks = 0;
         long long sum_all = g.node_len[start];   // first node's length + every edge delta on the path
         uint32_t cur = start;
@@ -167,28 +168,43 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
             const bool order_free = (g.node_exact[cur] & g.exact_bit) != 0;
             // ---- pass 1: forced anchor edge, candidate set (src/PathManager.cpp:53-67)
             int forced = -1;
-            double part = 0.0;
-            uint32_t ncand = 0;
-            for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
-                const uint32_t k = c0 + lane;
-                const bool valid = k < deg;
-                uint4 a = make_uint4(0, 0, 0, 0);
-                if (valid) a = __ldg(g.adj4 + base + k);
-                const uint32_t nb = a.x & 0x7fffffffu;
-                const bool force = valid && (a.x >> 31) && nb != start;
-                const uint32_t fb = __ballot_sync(0xffffffffu, force);
-                if (fb) { forced = static_cast<int>(c0) + __ffs(fb) - 1; break; }
-                const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, nb);
-                const uint32_t cb = __ballot_sync(0xffffffffu, cand);
-                if (cand) {
-                    float v = __uint_as_float(g.use_os ? a.z : a.y);
-                    if (g.sqrt_metric) v = __fsqrt_rn(v);
-                    part = __dadd_rn(part, static_cast<double>(v));
-                    const uint32_t idx = ncand + __popc(cb & ((1u << lane) - 1u));
-                    if (idx < WK_CACHE) { s_cslot[idx] = k; s_cval[idx] = v; }
+            bool any_cand = false;
+            uint32_t forced_nbw = 0;
+            int32_t forced_dl = 0;
+            // four 32-entry chunks in flight per round trip: the step latency of a single walk is what
+            // bounds the kernel (the longest walk is its critical path), not the entries per second
+            for (uint32_t c0 = 0; c0 < deg && forced < 0; c0 += 32 * WK_MLP) {
+                uint4 a[WK_MLP];
+#pragma unroll
+                for (int j = 0; j < WK_MLP; j++) {
+                    const uint32_t k = c0 + 32 * j + lane;
+                    a[j] = k < deg ? __ldg(g.adj4 + base + k) : make_uint4(0, 0, 0, 0);
                 }
-                ncand += __popc(cb);
+#pragma unroll
+                for (int j = 0; j < WK_MLP; j++) {
+                    const uint32_t k = c0 + 32 * j + lane;
+                    if (c0 + 32 * j >= deg || forced >= 0) continue;   // warp-uniform
+                    const bool valid = k < deg;
+                    const uint32_t nb = a[j].x & 0x7fffffffu;
+                    const bool force = valid && (a[j].x >> 31) && nb != start;
+                    const uint32_t fb = __ballot_sync(0xffffffffu, force);
+                    if (fb) {
+                        const int src = __ffs(fb) - 1;
+                        forced = static_cast<int>(c0) + 32 * j + src;
+                        forced_nbw = __shfl_sync(0xffffffffu, a[j].x, src);
+                        forced_dl = static_cast<int32_t>(__shfl_sync(0xffffffffu, a[j].w, src));
+                        continue;
+                    }
+                    const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, nb);
+                    any_cand |= cand;
+                    // entry k keeps its place in the cache: its metric if it is a candidate, else -0.0f
+                    // (adding -0.0 to a sum changes nothing, and the sign bit tells the two apart)
+                    float v = __uint_as_float(g.use_os ? a[j].z : a[j].y);
+                    if (g.sqrt_metric) v = __fsqrt_rn(v);
+                    if (k < WK_CACHE) s_cval[k] = cand ? v : -0.0f;
+                }
             }
+            const uint32_t ncand = __any_sync(0xffffffffu, any_cand) ? 1u : 0u;   // only "none / some" matters below
             examined += deg;
             int pick = -1;
             if (forced >= 0) {
@@ -218,14 +234,17 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
             } else {
                 // ---- roulette (src/PathManager.cpp:102-115)
                 __syncwarp();
-                const double u = mc_draw(seed, metric_id, start, attempt, draws);
+                // draws come 32 at a time: lane l computes draw (draws & ~31) + l, one Philox call per lane per 32 steps
+                if ((draws & 31u) == 0) u_bank = mc_draw(seed, metric_id, start, attempt, draws + lane);
+                const double u = __shfl_sync(0xffffffffu, u_bank, draws & 31u);
                 draws++;
-                if (order_free && ncand <= WK_CACHE) {
-                    // Every partial sum is exact in any order (node_exact): lane l sums candidates [l*K, (l+1)*K),
+                if (order_free && deg <= WK_CACHE) {
+                    // Every partial sum is exact in any order (node_exact): lane l sums entries [l*K, (l+1)*K),
                     // lane totals are scanned, and the lane whose range crosses u*sum walks it once more.
-                    const uint32_t K = ((ncand + 31) >> 5) | 1u;   // odd stride: no bank conflicts
-                    const uint32_t lo = min(lane * K, ncand), hi = min(lo + K, ncand);
+                    const uint32_t K = ((deg + 31) >> 5) | 1u;   // odd stride: no bank conflicts
+                    const uint32_t lo = min(lane * K, deg), hi = min(lo + K, deg);
                     double mine = 0.0;
+#pragma unroll 4
                     for (uint32_t i = lo; i < hi; i++) mine = __dadd_rn(mine, static_cast<double>(s_cval[i]));
                     double incl = mine;
 #pragma unroll
@@ -235,19 +254,19 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
                     }
                     const double total = __shfl_sync(0xffffffffu, incl, 31);
                     const double target = __dmul_rn(u, total);
-                    const uint32_t hit = __ballot_sync(0xffffffffu, hi > lo && incl >= target);
-                    if (hit) {
-                        const uint32_t src = __ffs(hit) - 1;
-                        int found = -1;
-                        if (lane == src) {
-                            double run = __dsub_rn(incl, mine);   // exact: both are multiples of the node's quantum
-                            for (uint32_t i = lo; i < hi; i++) {
-                                run = __dadd_rn(run, static_cast<double>(s_cval[i]));
-                                if (run >= target) { found = static_cast<int>(s_cslot[i]); break; }
-                            }
+                    // first lane whose range holds a candidate at which the running sum reaches the target
+                    int found = -1;
+                    if (hi > lo && incl >= target) {
+                        double run = __dsub_rn(incl, mine);   // exact: both are multiples of the node's quantum
+                        for (uint32_t i = lo; i < hi; i++) {
+                            const float v = s_cval[i];
+                            if (__float_as_uint(v) >> 31) continue;   // not a candidate
+                            run = __dadd_rn(run, static_cast<double>(v));
+                            if (run >= target) { found = static_cast<int>(i); break; }
                         }
-                        pick = __shfl_sync(0xffffffffu, found, src);
                     }
+                    const uint32_t hit = __ballot_sync(0xffffffffu, found >= 0);
+                    if (hit) pick = __shfl_sync(0xffffffffu, found, __ffs(hit) - 1);
                 } else {
                     // list-order accumulation: every lane replays the same sequence of additions
                     double total = 0.0;
@@ -279,10 +298,14 @@ __global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkSc
             }
             // ---- take the edge (src/PathManager.cpp:117-142)
             const uint32_t slot = base + static_cast<uint32_t>(pick);
-            const uint4 taken = __ldg(g.adj4 + slot);
-            const uint32_t nbw = taken.x;
+            uint32_t nbw = forced_nbw;
+            int32_t dl = forced_dl;
+            if (forced < 0) {   // roulette pick: its entry left the registers, it is an L1/L2 hit
+                const uint4 taken = __ldg(g.adj4 + slot);
+                nbw = taken.x;
+                dl = static_cast<int32_t>(taken.w);
+            }
             cur = nbw & 0x7fffffffu;
-            const int32_t dl = static_cast<int32_t>(taken.w);
             if (n_nodes >= sc.cap) break;  // cannot happen: a walk visits every node at most once
             if (lane == 0) {
                 nodes[n_nodes] = cur; slots[n_nodes - 1] = slot; vlog[nlog] = cur;
@@ -647,7 +670,7 @@ void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t s
     run_walks(c, static_cast<uint32_t>(total), 0, metric, out, [&](unsigned blocks, uint32_t my_walks, WalkScratch sc, WalkOut wo) {
         // visited bitmaps in shared memory while four of them fit beside the candidate cache (N <= 65536 nodes)
         const bool smem_bm = c.opt_walk_smem_bitmap && sc.words <= 2048;
-        const size_t smem = (2ull * WK_WARPS * WK_CACHE + (smem_bm ? static_cast<size_t>(WK_WARPS) * sc.words : 0)) * sizeof(uint32_t);
+        const size_t smem = (1ull * WK_WARPS * WK_CACHE + (smem_bm ? static_cast<size_t>(WK_WARPS) * sc.words : 0)) * sizeof(uint32_t);
         if (smem_bm) {
             walk_mc_kernel<true><<<blocks, WK_THREADS, smem, c.stream>>>(wg, sc, wo, my_walks, static_cast<uint32_t>(pp.rebuild_attempts), pp.backtrack_attempts,
                                                                         static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
