@@ -173,16 +173,10 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
     info = h.finalize(WORKLOAD["metrics"])
     t_graph = h.timer_stop()
     h.timer_start()
-    walks = 0
-    steps = 0
-    for m in WORKLOAD["metrics"]:
-        s = h.monte_carlo(m, pp, 20261104)
-        walks += s.walks
-        steps += s.steps
-    for m in WORKLOAD["metrics"]:
-        s = h.deterministic(m)
-        walks += s.walks
-        steps += s.steps
+    # the four build calls of main() as one hera_paths_build call: their kernels share the GPU
+    stats = h.build_paths([("mc", m) for m in WORKLOAD["metrics"]] + [("det", m) for m in WORKLOAD["metrics"]], pp, 20261104)
+    walks = sum(s.walks for s in stats)
+    steps = sum(s.steps for s in stats)
     n_unique = h.unique()
     t_paths = h.timer_stop()
     h.timer_start()

@@ -197,6 +197,11 @@ int hera_graph_export(hera_ctx *ctx, hera_graph_view *out);
 int hera_paths_monte_carlo(hera_ctx *ctx, int metric, const hera_path_params *pp, uint64_t seed, hera_walk_stats *out);
 /* PathManager::buildDeterministic (src/PathManager.cpp:179-430). */
 int hera_paths_deterministic(hera_ctx *ctx, int metric, hera_walk_stats *out);
+/* The n build calls of main() (src/Main.cpp:237-243) as ONE call: kinds[i] = 0 buildMonteCarlo /
+ * 1 buildDeterministic with metrics[i].  The walk kernels of all calls run concurrently (one stream
+ * each), which hides the tail every walk kernel has; paths_ ends up exactly as the n separate calls in
+ * this order would leave it.  out (may be NULL) gets n entries.  n <= 8. */
+int hera_paths_build(hera_ctx *ctx, int n, const int *kinds, const int *metrics, const hera_path_params *pp, uint64_t seed, hera_walk_stats *out);
 /* PathManager::filterUnique (src/PathManager.cpp:432-438). */
 int hera_paths_unique(hera_ctx *ctx, uint64_t *n_unique);
 /* Forget all paths (a fresh PathManager). */

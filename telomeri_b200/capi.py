@@ -88,6 +88,7 @@ SIGNATURES = {
     "hera_graph_export": (C.c_int, [C.c_void_p, C.POINTER(GraphView)]),
     "hera_paths_monte_carlo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PathParams), C.c_uint64, C.POINTER(WalkStats)]),
     "hera_paths_deterministic": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(WalkStats)]),
+    "hera_paths_build": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(PathParams), C.c_uint64, C.POINTER(WalkStats)]),
     "hera_paths_unique": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "hera_paths_reset": (C.c_int, [C.c_void_p]),
     "hera_paths_export": (C.c_int, [C.c_void_p, C.POINTER(PathsView)]),
@@ -261,6 +262,15 @@ class Hera:
         s = WalkStats()
         self._check(self.lib.hera_paths_deterministic(self.h, METRIC[metric] if isinstance(metric, str) else metric, C.byref(s)))
         return s
+
+    def build_paths(self, calls, pp, seed=0):
+        """calls: [("mc" | "det", metric), ...] -- all walk kernels in flight together, paths appended in call order."""
+        n = len(calls)
+        kinds = (C.c_int * n)(*[0 if k == "mc" else 1 for k, _ in calls])
+        metrics = (C.c_int * n)(*[METRIC[m] if isinstance(m, str) else int(m) for _, m in calls])
+        stats = (WalkStats * n)()
+        self._check(self.lib.hera_paths_build(self.h, n, kinds, metrics, C.byref(pp), seed, stats))
+        return list(stats)
 
     def unique(self):
         n = C.c_uint64()

@@ -84,6 +84,7 @@ void hera_destroy(hera_ctx *ctx) {
     cudaSetDevice(ctx->c.device);
     cudaStreamSynchronize(ctx->c.stream);
     cudaStream_t s = ctx->c.stream;
+    for (cudaStream_t a : ctx->c.aux_streams) { cudaStreamSynchronize(a); cudaStreamDestroy(a); }
     delete ctx;
     cudaStreamDestroy(s);
 }
@@ -306,6 +307,13 @@ int hera_paths_monte_carlo(hera_ctx *ctx, int metric, const hera_path_params *pp
 int hera_paths_deterministic(hera_ctx *ctx, int metric, hera_walk_stats *out) {
     HERA_API_BEGIN(ctx)
     hera::walk_deterministic(c, metric, out);
+    HERA_API_END
+}
+
+int hera_paths_build(hera_ctx *ctx, int n, const int *kinds, const int *metrics, const hera_path_params *pp, uint64_t seed, hera_walk_stats *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(pp != nullptr && kinds != nullptr && metrics != nullptr, 101, "null argument");
+    hera::walk_build(c, n, kinds, metrics, *pp, seed, out);
     HERA_API_END
 }
 

@@ -106,7 +106,8 @@ struct Ctx {
     int opt_flush_l2 = 0;
     int opt_walk_warps_per_sm = 32;
     int opt_walk_smem_bitmap = 1;  // 0 = keep the walks' visited bitmaps in global memory whatever the graph size (tests)
-    uint64_t walk_pool_hint = 0;   // largest path pool a walk call needed so far (avoids the overflow re-run)
+    uint64_t walk_pool_hint[2][4] = {};   // per (kind, metric): largest path pool a walk call needed so far (avoids the overflow re-run)
+    std::vector<cudaStream_t> aux_streams;   // hera_paths_build: one stream per walk kernel in flight
     DBuf<uint8_t> l2_flush_buf;
     std::unique_ptr<Exchange> xch;   // null = single rank
 
@@ -165,6 +166,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out);
 void export_graph(Ctx &c, hera_graph_view *out);
 void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);
 void walk_deterministic(Ctx &c, int metric, hera_walk_stats *out);
+void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);
 void unique_paths(Ctx &c, uint64_t *n_unique);
 void export_paths(Ctx &c, hera_paths_view *out);
 void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out);

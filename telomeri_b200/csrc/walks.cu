@@ -501,70 +501,149 @@ __global__ void walk_order_kernel(uint32_t total_walks, uint32_t size, RankTable
     res_draws[w] = g_draws[src];
 }
 
-// Runs one walk kernel over `total_walks` walks (this rank's share of them when a communicator is
-// attached) and appends the accepted paths of ALL ranks to c.all in walk-id order.
-template <typename LaunchFn>
-void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_stats *out, LaunchFn launch) {
+// One walk call (Monte Carlo or greedy, one metric): scratch, the kernel launch on its own stream, and
+// -- once the kernel is done -- the gather of the accepted paths of ALL ranks into c.all in walk-id
+// order.  Several jobs may be in flight at once (hera_paths_build): their kernels share the GPU, which
+// hides the long tail every walk kernel has (its critical path is its longest walk).
+struct WalkJob {
+    int kind = 0, metric = 0;
+    uint32_t total_walks = 0, my_walks = 0;
+    hera_path_params pp{};
+    uint64_t seed = 0;
+    WalkGraph wg{};
+    WalkRun r;
+    uint32_t *first_edges = nullptr, *walk_base = nullptr;   // greedy walks: first edges per anchor, prefix
+    uint64_t pool_cap = 0, warps = 0;
+    uint32_t cap = 0, words = 0;
+    unsigned blocks = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    unsigned long long *h_ctr = nullptr;   // pinned: [0] pool used [1] entries examined [2] ticket
+    uint64_t launches = 0;
+};
+
+uint32_t walk_share(uint32_t total_walks, int ranks, int r) { return static_cast<uint32_t>((static_cast<uint64_t>(total_walks) + ranks - 1 - r) / ranks); }
+
+void job_launch_kernel(Ctx &c, WalkJob &j) {
+    WalkScratch sc{j.r.bitmap, j.r.nodes, j.r.slots, j.r.vlog, j.words, j.cap};
+    WalkOut wo{j.r.res_n, j.r.res_off, j.r.res_len, j.r.res_draws, j.r.pool_nodes, j.r.pool_slots, j.pool_cap, j.r.d_ctr, j.r.d_ctr + 1,
+               reinterpret_cast<unsigned int *>(j.r.d_ctr + 2), static_cast<uint32_t>(xch_rank(c)), static_cast<uint32_t>(xch_size(c))};
+    HERA_CUDA(cudaMemsetAsync(j.r.d_ctr, 0, 4 * sizeof(unsigned long long), j.stream));
+    HERA_CUDA(cudaMemsetAsync(j.r.res_n, 0, std::max<uint32_t>(j.my_walks, 1) * sizeof(uint32_t), j.stream));
+    HERA_CUDA(cudaMemsetAsync(j.r.res_draws, 0, std::max<uint32_t>(j.my_walks, 1) * sizeof(uint32_t), j.stream));
+    HERA_CUDA(cudaEventRecord(j.ev0, j.stream));
+    if (j.my_walks) {
+        if (j.kind == 0) {
+            // visited bitmaps in shared memory while four of them fit beside the value cache (N <= 65536 nodes)
+            const bool smem_bm = c.opt_walk_smem_bitmap && j.words <= 2048;
+            const size_t smem = (1ull * WK_WARPS * WK_CACHE + (smem_bm ? static_cast<size_t>(WK_WARPS) * j.words : 0)) * sizeof(uint32_t);
+            if (smem_bm) {
+                walk_mc_kernel<true><<<j.blocks, WK_THREADS, smem, j.stream>>>(j.wg, sc, wo, j.my_walks, static_cast<uint32_t>(j.pp.rebuild_attempts), j.pp.backtrack_attempts,
+                                                                               static_cast<long long>(j.pp.len_threshold), j.seed, static_cast<uint32_t>(j.metric));
+            } else {
+                walk_mc_kernel<false><<<j.blocks, WK_THREADS, smem, j.stream>>>(j.wg, sc, wo, j.my_walks, static_cast<uint32_t>(j.pp.rebuild_attempts), j.pp.backtrack_attempts,
+                                                                                static_cast<long long>(j.pp.len_threshold), j.seed, static_cast<uint32_t>(j.metric));
+            }
+        } else {
+            walk_det_kernel<<<j.blocks, WK_THREADS, 0, j.stream>>>(j.wg, sc, wo, j.my_walks, j.walk_base);
+        }
+        c.launches.count++;
+        j.launches++;
+        HERA_CUDA(cudaGetLastError());
+    }
+    HERA_CUDA(cudaEventRecord(j.ev1, j.stream));
+    HERA_CUDA(cudaMemcpyAsync(j.h_ctr, j.r.d_ctr, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, j.stream));
+}
+
+// Sizes the job, allocates its scratch (stream-ordered on the context's stream) and fills the walk table
+// of a greedy job.  warps_per_sm: this job's share of the resident walk warps.
+void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm) {
     GraphTables &g = c.g;
-    const uint64_t launches_before = c.launches.count;
+    HERA_REQUIRE(g.ready, 7, "walks: call hera_graph_finalize first");
+    HERA_REQUIRE(j.metric >= 0 && j.metric < 4, 8, "unknown metric");
     const int ranks = xch_size(c), me = xch_rank(c);
     HERA_REQUIRE(ranks <= WK_MAX_RANKS, 37, "more than 16 ranks are not supported");
-    auto share = [&](int r) { return static_cast<uint32_t>((static_cast<uint64_t>(total_walks) + ranks - 1 - r) / ranks); };
-    const uint32_t my_walks = share(me);
-    cudaEvent_t ev0, ev1;
-    HERA_CUDA(cudaEventCreate(&ev0));
-    HERA_CUDA(cudaEventCreate(&ev1));
+    j.wg = make_walk_graph(c, j.metric);
+    const uint64_t launches0 = c.launches.count;
+    if (j.kind == 0) {
+        const uint64_t total = g.anchors * static_cast<uint64_t>(j.pp.rebuild_attempts > 0 ? j.pp.rebuild_attempts : 0);
+        HERA_REQUIRE(total < (1ull << 32), 9, "too many Monte-Carlo walks for one call");
+        j.total_walks = static_cast<uint32_t>(total);
+    } else {
+        HERA_REQUIRE(g.E == 0 || g.rank_ready[j.metric], 10, "rank permutation for this metric was not built (metrics_mask of hera_graph_finalize)");
+        j.total_walks = 0;
+        if (g.anchors) {
+            uint32_t *d_total = nullptr;
+            HERA_CUDA(cudaMallocAsync(&j.first_edges, g.anchors * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMallocAsync(&j.walk_base, g.anchors * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMallocAsync(&d_total, sizeof(uint32_t), c.stream));
+            HERA_LAUNCH(c, det_count_kernel, div_up(g.anchors, 128), 128, 0, j.wg, j.first_edges);
+            exclusive_scan_u32(c, j.first_edges, g.anchors, j.walk_base, d_total);
+            HERA_CUDA(cudaMemcpyAsync(&j.total_walks, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            HERA_CUDA(cudaFreeAsync(d_total, c.stream));
+        }
+    }
+    j.my_walks = walk_share(j.total_walks, ranks, me);
+    HERA_CUDA(cudaEventCreate(&j.ev0));
+    HERA_CUDA(cudaEventCreate(&j.ev1));
+    HERA_CUDA(cudaMallocHost(&j.h_ctr, 4 * sizeof(unsigned long long)));
+    for (int k = 0; k < 4; k++) j.h_ctr[k] = 0;
+    if (j.total_walks == 0) { j.launches = c.launches.count - launches0; return; }
+    int sms = 148;
+    HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
+    j.cap = static_cast<uint32_t>(g.N + 1);
+    j.words = static_cast<uint32_t>((g.N + 31) / 32);
+    const uint64_t per_warp = (3ull * j.cap + j.words) * sizeof(uint32_t);
+    uint64_t warps = static_cast<uint64_t>(sms) * std::max(1, warps_per_sm);
+    while (warps > WK_WARPS && warps * per_warp > (8ull << 30)) warps /= 2;
+    if (warps > j.my_walks) warps = (static_cast<uint64_t>(j.my_walks) + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
+    if (warps == 0) warps = WK_WARPS;
+    j.blocks = static_cast<unsigned>((warps + WK_WARPS - 1) / WK_WARPS);
+    j.warps = static_cast<uint64_t>(j.blocks) * WK_WARPS;
+    const uint64_t res_cap = std::max<uint32_t>(j.my_walks, 1);
+    WalkRun &r = j.r;
+    HERA_CUDA(cudaMallocAsync(&r.res_n, res_cap * sizeof(uint32_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.res_draws, res_cap * sizeof(uint32_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.res_off, res_cap * sizeof(uint64_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.res_len, res_cap * sizeof(int64_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.d_ctr, 4 * sizeof(unsigned long long), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.bitmap, j.warps * j.words * sizeof(uint32_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.nodes, j.warps * j.cap * sizeof(uint32_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.slots, j.warps * j.cap * sizeof(uint32_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.vlog, j.warps * j.cap * sizeof(uint32_t), c.stream));
+    HERA_CUDA(cudaMemsetAsync(r.bitmap, 0, j.warps * j.words * sizeof(uint32_t), c.stream));
+    j.pool_cap = std::max<uint64_t>(std::max<uint64_t>(1u << 16, c.walk_pool_hint[j.kind][j.metric]), std::min<uint64_t>(static_cast<uint64_t>(j.my_walks) * 64, 1ull << 28));
+    HERA_CUDA(cudaMallocAsync(&r.pool_nodes, j.pool_cap * sizeof(uint32_t), c.stream));
+    HERA_CUDA(cudaMallocAsync(&r.pool_slots, j.pool_cap * sizeof(uint32_t), c.stream));
+    j.launches = c.launches.count - launches0;
+}
+
+// Waits for the job's kernel, re-runs it with a larger pool if the accepted paths did not fit (walks are
+// deterministic), exchanges results between ranks and appends the accepted paths to c.all.
+void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
+    const int ranks = xch_size(c);
+    const uint64_t launches0 = c.launches.count;
     uint64_t found = 0, steps = 0;
     float ms = 0;
+    const uint32_t total_walks = j.total_walks;
     if (total_walks > 0) {
-        int sms = 148;
-        HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
-        const uint32_t cap = static_cast<uint32_t>(g.N + 1), words = static_cast<uint32_t>((g.N + 31) / 32);
-        const uint64_t per_warp = (3ull * cap + words) * sizeof(uint32_t);
-        uint64_t warps = static_cast<uint64_t>(sms) * c.opt_walk_warps_per_sm;
-        while (warps > WK_WARPS && warps * per_warp > (8ull << 30)) warps /= 2;
-        if (warps > my_walks) warps = (static_cast<uint64_t>(my_walks) + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
-        if (warps == 0) warps = WK_WARPS;
-        const unsigned blocks = static_cast<unsigned>((warps + WK_WARPS - 1) / WK_WARPS);
-        warps = static_cast<uint64_t>(blocks) * WK_WARPS;
-        const uint64_t res_cap = std::max<uint32_t>(my_walks, 1);
-
-        WalkRun r;
-        HERA_CUDA(cudaMallocAsync(&r.res_n, res_cap * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.res_draws, res_cap * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.res_off, res_cap * sizeof(uint64_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.res_len, res_cap * sizeof(int64_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.d_ctr, 4 * sizeof(unsigned long long), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.bitmap, warps * words * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.nodes, warps * cap * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.slots, warps * cap * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&r.vlog, warps * cap * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMemsetAsync(r.bitmap, 0, warps * words * sizeof(uint32_t), c.stream));
-        uint64_t pool_cap = std::max<uint64_t>(std::max<uint64_t>(1u << 16, c.walk_pool_hint), std::min<uint64_t>(static_cast<uint64_t>(my_walks) * 256, 1ull << 28));
-        unsigned long long h_ctr[4];
+        WalkRun &r = j.r;
         for (;;) {
-            HERA_CUDA(cudaMallocAsync(&r.pool_nodes, pool_cap * sizeof(uint32_t), c.stream));
-            HERA_CUDA(cudaMallocAsync(&r.pool_slots, pool_cap * sizeof(uint32_t), c.stream));
-            HERA_CUDA(cudaMemsetAsync(r.d_ctr, 0, 4 * sizeof(unsigned long long), c.stream));
-            HERA_CUDA(cudaMemsetAsync(r.res_n, 0, res_cap * sizeof(uint32_t), c.stream));
-            HERA_CUDA(cudaMemsetAsync(r.res_draws, 0, res_cap * sizeof(uint32_t), c.stream));
-            WalkScratch sc{r.bitmap, r.nodes, r.slots, r.vlog, words, cap};
-            WalkOut wo{r.res_n, r.res_off, r.res_len, r.res_draws, r.pool_nodes, r.pool_slots, pool_cap, r.d_ctr, r.d_ctr + 1,
-                       reinterpret_cast<unsigned int *>(r.d_ctr + 2), static_cast<uint32_t>(me), static_cast<uint32_t>(ranks)};
-            HERA_CUDA(cudaEventRecord(ev0, c.stream));
-            if (my_walks) launch(blocks, my_walks, sc, wo);
-            HERA_CUDA(cudaEventRecord(ev1, c.stream));
-            HERA_CUDA(cudaMemcpyAsync(h_ctr, r.d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, c.stream));
-            HERA_CUDA(cudaStreamSynchronize(c.stream));
-            if (h_ctr[0] <= pool_cap) break;
-            HERA_CUDA(cudaFreeAsync(r.pool_nodes, c.stream));   // pool too small: walks are deterministic, run again with room
-            HERA_CUDA(cudaFreeAsync(r.pool_slots, c.stream));
-            pool_cap = h_ctr[0] + 1024;
+            HERA_CUDA(cudaStreamSynchronize(j.stream));
+            if (j.h_ctr[0] <= j.pool_cap) break;
+            HERA_CUDA(cudaFreeAsync(r.pool_nodes, j.stream));
+            HERA_CUDA(cudaFreeAsync(r.pool_slots, j.stream));
+            j.pool_cap = j.h_ctr[0] + 1024;
+            HERA_CUDA(cudaMallocAsync(&r.pool_nodes, j.pool_cap * sizeof(uint32_t), j.stream));
+            HERA_CUDA(cudaMallocAsync(&r.pool_slots, j.pool_cap * sizeof(uint32_t), j.stream));
+            job_launch_kernel(c, j);
         }
-        HERA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
-        steps = h_ctr[1];
-        c.walk_pool_hint = std::max<uint64_t>(c.walk_pool_hint, h_ctr[0] + h_ctr[0] / 8);
-        uint64_t new_nodes = h_ctr[0];
+        HERA_CUDA(cudaEventElapsedTime(&ms, j.ev0, j.ev1));
+        steps = j.h_ctr[1];
+        uint64_t &hint = c.walk_pool_hint[j.kind][j.metric];
+        hint = std::max<uint64_t>(hint, j.h_ctr[0] + j.h_ctr[0] / 8);
+        uint64_t new_nodes = j.h_ctr[0];
 
         // per-walk results in walk-id order + one pool holding every accepted path
         uint32_t *res_n = r.res_n, *res_draws = r.res_draws, *pool_nodes = r.pool_nodes, *pool_slots = r.pool_slots;
@@ -573,7 +652,7 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         std::vector<void *> gathered;
         if (ranks > 1) {
             // exchange step: all-gather of the ranks' accepted paths
-            const uint64_t mine[2] = {h_ctr[0], h_ctr[1]};
+            const uint64_t mine[2] = {j.h_ctr[0], j.h_ctr[1]};
             std::vector<uint64_t> all(2 * static_cast<size_t>(ranks));
             c.xch->all_gather_host(c, mine, 2, all.data());
             RankTable t{};
@@ -581,7 +660,7 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
             uint64_t wtot = 0, ptot = 0;
             steps = 0;
             for (int k = 0; k < ranks; k++) {
-                wcount[k] = share(k); wdispl[k] = wtot; wtot += wcount[k];
+                wcount[k] = walk_share(total_walks, ranks, k); wdispl[k] = wtot; wtot += wcount[k];
                 pcount[k] = all[2 * k]; pdispl[k] = ptot; ptot += pcount[k];
                 steps += all[2 * k + 1];
                 t.walk_displ[k] = wdispl[k]; t.pool_displ[k] = pdispl[k];
@@ -634,7 +713,7 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
         }
         ps.paths += found;
         ps.nodes += new_nodes;
-        if (kind == 0) {
+        if (j.kind == 0) {
             const size_t before = c.mc_draws.size();
             c.mc_draws.resize(before + total_walks);
             HERA_CUDA(cudaMemcpyAsync(c.mc_draws.data() + before, res_draws, total_walks * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
@@ -647,64 +726,69 @@ void run_walks(Ctx &c, uint32_t total_walks, int kind, int metric, hera_walk_sta
                         static_cast<void *>(r.vlog), static_cast<void *>(r.pool_nodes), static_cast<void *>(r.pool_slots)})
             HERA_CUDA(cudaFreeAsync(p, c.stream));
     }
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
+    if (j.first_edges) { HERA_CUDA(cudaFreeAsync(j.first_edges, c.stream)); HERA_CUDA(cudaFreeAsync(j.walk_base, c.stream)); }
+    cudaEventDestroy(j.ev0);
+    cudaEventDestroy(j.ev1);
+    cudaFreeHost(j.h_ctr);
+    j.h_ctr = nullptr;
     c.uniq_ready = false;
-    c.call_kind.push_back(static_cast<uint32_t>(kind));
-    c.call_metric.push_back(static_cast<uint32_t>(metric));
+    c.call_kind.push_back(static_cast<uint32_t>(j.kind));
+    c.call_metric.push_back(static_cast<uint32_t>(j.metric));
     c.call_found.push_back(found);
     if (out) {
         out->walks = total_walks; out->found = found; out->steps = steps; out->ms = ms;
-        out->launches = static_cast<uint32_t>(c.launches.count - launches_before);
+        out->launches = static_cast<uint32_t>(j.launches + (c.launches.count - launches0));
     }
 }
 
 }  // namespace
 
-void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out) {
-    HERA_REQUIRE(c.g.ready, 7, "hera_paths_monte_carlo: call hera_graph_finalize first");
-    HERA_REQUIRE(metric >= 0 && metric < 4, 8, "unknown metric");
-    const uint64_t total = c.g.anchors * static_cast<uint64_t>(pp.rebuild_attempts > 0 ? pp.rebuild_attempts : 0);
-    HERA_REQUIRE(total < (1ull << 32), 9, "too many Monte-Carlo walks for one call");
-    WalkGraph wg = make_walk_graph(c, metric);
-    run_walks(c, static_cast<uint32_t>(total), 0, metric, out, [&](unsigned blocks, uint32_t my_walks, WalkScratch sc, WalkOut wo) {
-        // visited bitmaps in shared memory while four of them fit beside the candidate cache (N <= 65536 nodes)
-        const bool smem_bm = c.opt_walk_smem_bitmap && sc.words <= 2048;
-        const size_t smem = (1ull * WK_WARPS * WK_CACHE + (smem_bm ? static_cast<size_t>(WK_WARPS) * sc.words : 0)) * sizeof(uint32_t);
-        if (smem_bm) {
-            walk_mc_kernel<true><<<blocks, WK_THREADS, smem, c.stream>>>(wg, sc, wo, my_walks, static_cast<uint32_t>(pp.rebuild_attempts), pp.backtrack_attempts,
-                                                                        static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
-        } else {
-            walk_mc_kernel<false><<<blocks, WK_THREADS, smem, c.stream>>>(wg, sc, wo, my_walks, static_cast<uint32_t>(pp.rebuild_attempts), pp.backtrack_attempts,
-                                                                         static_cast<long long>(pp.len_threshold), seed, static_cast<uint32_t>(metric));
+// kinds[i]: 0 = Monte Carlo, 1 = greedy.  All n kernels are in flight together (one stream each); the
+// accepted paths are appended in call order, exactly as n separate calls would leave them.
+void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out) {
+    HERA_REQUIRE(n >= 1 && n <= 8, 101, "hera_paths_build: between 1 and 8 calls");
+    std::vector<WalkJob> jobs(n);
+    // resident warps are shared out: greedy jobs have few walks and get a small share
+    int mc = 0, det = 0;
+    for (int i = 0; i < n; i++) (kinds[i] == 0 ? mc : det)++;
+    const int budget = c.opt_walk_warps_per_sm;
+    for (int i = 0; i < n; i++) {
+        WalkJob &j = jobs[i];
+        j.kind = kinds[i] ? 1 : 0; j.metric = metrics[i]; j.pp = pp; j.seed = seed;
+        const int share = n == 1 ? budget : (j.kind == 0 ? std::max(8, (budget - 4 * det) / std::max(1, mc)) : 4);
+        job_prepare(c, j, share);
+    }
+    if (n == 1) {
+        jobs[0].stream = c.stream;
+        if (jobs[0].total_walks) job_launch_kernel(c, jobs[0]);
+    } else {
+        while (c.aux_streams.size() < static_cast<size_t>(n)) {
+            cudaStream_t s;
+            HERA_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+            c.aux_streams.push_back(s);
         }
-        c.launches.count++;
-        HERA_CUDA(cudaGetLastError());
-    });
+        cudaEvent_t ready;
+        HERA_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+        HERA_CUDA(cudaEventRecord(ready, c.stream));   // scratch allocation and the graph itself are ordered on the context's stream
+        for (int i = 0; i < n; i++) {
+            jobs[i].stream = c.aux_streams[i];
+            HERA_CUDA(cudaStreamWaitEvent(jobs[i].stream, ready, 0));
+            if (jobs[i].total_walks) job_launch_kernel(c, jobs[i]);
+        }
+        cudaEventDestroy(ready);
+    }
+    for (int i = 0; i < n; i++) job_finish(c, jobs[i], out ? out + i : nullptr);
+}
+
+void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out) {
+    const int kind = 0;
+    walk_build(c, 1, &kind, &metric, pp, seed, out);
 }
 
 void walk_deterministic(Ctx &c, int metric, hera_walk_stats *out) {
-    HERA_REQUIRE(c.g.ready, 7, "hera_paths_deterministic: call hera_graph_finalize first");
-    HERA_REQUIRE(metric >= 0 && metric < 4, 8, "unknown metric");
-    HERA_REQUIRE(c.g.E == 0 || c.g.rank_ready[metric], 10, "rank permutation for this metric was not built (metrics_mask of hera_graph_finalize)");
-    WalkGraph wg = make_walk_graph(c, metric);
-    uint32_t total = 0;
-    uint32_t *first_edges = nullptr, *walk_base = nullptr, *d_total = nullptr;
-    if (c.g.anchors) {
-        HERA_CUDA(cudaMallocAsync(&first_edges, c.g.anchors * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&walk_base, c.g.anchors * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&d_total, sizeof(uint32_t), c.stream));
-        HERA_LAUNCH(c, det_count_kernel, div_up(c.g.anchors, 128), 128, 0, wg, first_edges);
-        exclusive_scan_u32(c, first_edges, c.g.anchors, walk_base, d_total);
-        HERA_CUDA(cudaMemcpyAsync(&total, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
-        HERA_CUDA(cudaStreamSynchronize(c.stream));
-    }
-    run_walks(c, total, 1, metric, out, [&](unsigned blocks, uint32_t my_walks, WalkScratch sc, WalkOut wo) {
-        HERA_LAUNCH(c, walk_det_kernel, blocks, WK_THREADS, 0, wg, sc, wo, my_walks, walk_base);
-    });
-    if (first_edges) {
-        HERA_CUDA(cudaFreeAsync(first_edges, c.stream)); HERA_CUDA(cudaFreeAsync(walk_base, c.stream)); HERA_CUDA(cudaFreeAsync(d_total, c.stream));
-    }
+    const int kind = 1;
+    hera_path_params pp{};
+    walk_build(c, 1, &kind, &metric, pp, 0, out);
 }
 
 }  // namespace hera

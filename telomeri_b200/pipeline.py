@@ -27,7 +27,7 @@ def parse_options(opts):
     return o
 
 
-def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None):
+def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, batched=False):
     o = parse_options(list(opts))
     ds_dir = Path(ds_dir)
     own = hera is None
@@ -45,11 +45,14 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None):
         if stages == "graph":
             return out
         pp = capi.default_path_params(o["rb_att"], o["bt_att"], o["len_thr"], o["w_size"], o["r_thr"])
-        stats = []
-        for m in o["metrics"]:
-            stats.append(h.monte_carlo(m, pp, seed))
-        for m in o["metrics"]:
-            stats.append(h.deterministic(m))
+        if batched:   # one call, all walk kernels in flight together (hera_paths_build)
+            stats = h.build_paths([("mc", m) for m in o["metrics"]] + [("det", m) for m in o["metrics"]], pp, seed)
+        else:         # the reference's call sequence (src/Main.cpp:237-243)
+            stats = []
+            for m in o["metrics"]:
+                stats.append(h.monte_carlo(m, pp, seed))
+            for m in o["metrics"]:
+                stats.append(h.deterministic(m))
         out["walk_stats"] = stats
         out.update(h.export_paths("p_"))
         h.unique()

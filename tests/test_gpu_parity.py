@@ -110,3 +110,14 @@ def test_walk_bitmap_in_global_memory(oracle_bin, datasets, tmp_path):
         h.set_option("walk_smem_bitmap", 0)
         gpu = pipeline.run_hot_path(ds, golden["options"], seed=77, hera=h)
     common.assert_sections_equal(ora, gpu, PATH_SECTIONS + GROUP_SECTIONS, "global bitmap")
+
+
+@pytest.mark.parametrize("case", ["small_default", "mixed_sqrt", "bundled_min"])
+def test_batched_build_equals_separate_calls(case, oracle_bin, datasets, tmp_path):
+    """hera_paths_build (all walk kernels in flight together) leaves paths_ exactly as the separate calls do."""
+    from telomeri_b200 import pipeline
+    golden = common.load_golden(case)
+    ds = datasets[golden["dataset"]]
+    ora = common.run_dump(oracle_bin, ds, tmp_path / "o.bin", golden["options"], extra=["--rng", "philox", "--seed", "31"])
+    gpu = pipeline.run_hot_path(ds, golden["options"], seed=31, batched=True)
+    common.assert_sections_equal(ora, gpu, PATH_SECTIONS + GROUP_SECTIONS, case + " batched")

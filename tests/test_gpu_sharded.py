@@ -18,10 +18,10 @@ def gang_devices(n):
     return [r % k for r in range(n)]
 
 
-def run_gang(ds, opts, seed, nranks, stages="all"):
+def run_gang(ds, opts, seed, nranks, stages="all", batched=False):
     from telomeri_b200 import capi, pipeline
     with capi.LocalGang(nranks, gang_devices(nranks)) as gang:
-        return gang.each(lambda r, h: pipeline.run_hot_path(ds, opts, seed=seed, stages=stages, hera=h))
+        return gang.each(lambda r, h: pipeline.run_hot_path(ds, opts, seed=seed, stages=stages, hera=h, batched=batched))
 
 
 @pytest.mark.parametrize("nranks", [2, 3])
@@ -31,7 +31,7 @@ def test_sharded_matches_oracle(case, nranks, oracle_bin, datasets, tmp_path):
     golden = common.load_golden(case)
     ds = datasets[golden["dataset"]]
     ora = common.run_dump(oracle_bin, ds, tmp_path / "o.bin", golden["options"], extra=["--rng", "philox", "--seed", "99"])
-    outs = run_gang(ds, golden["options"], 99, nranks)
+    outs = run_gang(ds, golden["options"], 99, nranks, batched=(nranks == 3))
     opts = pipeline.parse_options(golden["options"])
     ranks = [f"rank_{METRIC_ID[m]}" for m in opts["metrics"]]
     for r, gpu in enumerate(outs):
