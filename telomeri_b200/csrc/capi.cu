@@ -129,9 +129,17 @@ int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp) {
 
 static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard,
                         hera_load_result *out) {
-    std::unique_ptr<hera::LoadedText> t(new hera::LoadedText());
+    // text buffers are recycled across hera_graph_reset: no cudaMalloc / cudaFree in the steady state
+    std::unique_ptr<hera::LoadedText> t;
+    const uint64_t need = hera::padded_text_size(n);
+    size_t best = c.text_pool.size();
+    for (size_t i = 0; i < c.text_pool.size(); i++) {   // best fit
+        if (c.text_pool[i]->bytes.cap >= need && (best == c.text_pool.size() || c.text_pool[i]->bytes.cap < c.text_pool[best]->bytes.cap)) best = i;
+    }
+    if (best < c.text_pool.size()) { t = std::move(c.text_pool[best]); c.text_pool.erase(c.text_pool.begin() + best); }
+    if (!t) t.reset(new hera::LoadedText());
     t->n = n;
-    t->bytes.reserve(hera::padded_text_size(n));
+    t->bytes.reserve(need);
     cudaEvent_t e0, e1;
     HERA_CUDA(cudaEventCreate(&e0));
     HERA_CUDA(cudaEventCreate(&e1));
@@ -146,6 +154,7 @@ static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind
         hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, shard, &tmp);
     } catch (...) {
         cudaStreamSynchronize(c.stream);
+        c.text_pool.push_back(std::move(c.texts.back()));
         c.texts.pop_back();   // the failed load leaves no trace
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
@@ -276,7 +285,10 @@ int hera_comm_size(hera_ctx *ctx) { return ctx ? hera::xch_size(ctx->c) : 1; }
 int hera_graph_reset(hera_ctx *ctx) {
     HERA_API_BEGIN(ctx)
     HERA_CUDA(cudaStreamSynchronize(c.stream));
+    for (auto &t : c.texts) c.text_pool.push_back(std::move(t));
     c.texts.clear();
+    std::sort(c.text_pool.begin(), c.text_pool.end(), [](const auto &a, const auto &b) { return a->bytes.cap > b->bytes.cap; });
+    if (c.text_pool.size() > 4) c.text_pool.resize(4);   // keep the largest few
     c.own_rows.clear();
     c.kept.n = 0;
     c.g.ready = false;

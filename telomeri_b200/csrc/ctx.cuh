@@ -112,6 +112,7 @@ struct Ctx {
     std::unique_ptr<Exchange> xch;   // null = single rank
 
     std::vector<std::unique_ptr<LoadedText>> texts;
+    std::vector<std::unique_ptr<LoadedText>> text_pool;   // buffers of texts dropped by hera_graph_reset, reused by the next loads
     KeptTable kept;
     std::vector<RowRange> own_rows;   // per load: the kept rows this rank parsed itself (their name references point into ITS texts)
     GraphTables g;
