@@ -12,6 +12,8 @@
 // sorted list, the most frequent length is a block max-reduction, discardNotFrequent an ordered
 // block compaction, the int32-wrapping mean of calculateConsensusPath a block sum modulo 2^32,
 // valid_path_number a block count of node-sequence matches.
+#include <algorithm>
+
 #include "ctx.cuh"
 #include "introsort.cuh"
 #include "primitives.cuh"
@@ -30,6 +32,7 @@ struct GroupArgs {
     long long len_threshold;
     unsigned long long window_size;
     float ratio_threshold;
+    uint32_t smem_items;            // SortItem capacity of the CTA's dynamic shared memory
     // scratch, all indexed like ids
     uint32_t *freq, *w_tot, *w_lowc, *w_highc;
     unsigned long long *w_lowl, *w_highl, *borders;
@@ -43,10 +46,16 @@ struct GroupArgs {
     long long *pair_cons;
 };
 
-// Thread 0: cut the sorted list into groups (src/PathManager.cpp:515-581, 586-624).
-__device__ uint32_t split_groups(const GroupArgs &a, uint32_t b, uint32_t n) {
-    const uint32_t *ids = a.ids + b;
-    auto L = [&](uint32_t i) { return static_cast<unsigned long long>(a.len[ids[i]]); };
+// (length, path id) of one path while a pair's list is sorted in shared memory
+struct SortItem {
+    long long len;
+    uint32_t id, pad;
+};
+
+// Thread 0: cut the sorted list into groups (src/PathManager.cpp:515-581, 586-624).  L(i) = length of
+// the i-th path of the sorted list.
+template <typename LenFn>
+__device__ uint32_t split_groups(const GroupArgs &a, uint32_t b, uint32_t n, LenFn L) {
     uint32_t *gsize = a.grp_size0 + b;
     const unsigned long long min_len = L(0), max_len = L(n - 1);
     if (max_len - min_len < static_cast<unsigned long long>(a.len_threshold)) { gsize[0] = n; return 1; }
@@ -126,9 +135,24 @@ __global__ void __launch_bounds__(GP_THREADS) group_pairs_kernel(const GroupArgs
     const uint32_t k = blockIdx.x, tid = threadIdx.x;
     const uint32_t b = a.pair_off[k], n = a.pair_off[k + 1] - b;
     uint32_t *ids = a.ids + b;
-    if (tid == 0) {
+    // The sort is libstdc++'s introsort run by one thread (tie order!); its working set -- (length, id) per
+    // path -- is staged in shared memory when the pair fits, so that every compare and move is an LDS/STS.
+    extern __shared__ __align__(16) unsigned char gp_smem[];
+    SortItem *items = reinterpret_cast<SortItem *>(gp_smem);
+    const bool staged = n <= a.smem_items;
+    if (staged) {
+        for (uint32_t i = tid; i < n; i += GP_THREADS) { const uint32_t id = ids[i]; items[i] = SortItem{a.len[id], id, 0u}; }
+        __syncthreads();
+        if (tid == 0) {
+            libstdcxx_sort(items, static_cast<long>(n), [](const SortItem &x, const SortItem &y) { return x.len < y.len; });
+            s_ng = split_groups(a, b, n, [&](uint32_t i) { return static_cast<unsigned long long>(items[i].len); });
+            a.grp_count[k] = s_ng;
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < n; i += GP_THREADS) ids[i] = items[i].id;
+    } else if (tid == 0) {
         libstdcxx_sort(ids, static_cast<long>(n), [&](uint32_t x, uint32_t y) { return a.len[x] < a.len[y]; });
-        s_ng = split_groups(a, b, n);
+        s_ng = split_groups(a, b, n, [&](uint32_t i) { return static_cast<unsigned long long>(a.len[ids[i]]); });
         a.grp_count[k] = s_ng;
     }
     __syncthreads();
@@ -284,7 +308,10 @@ void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out) {
         a.grp_count = static_cast<uint32_t *>(alloc(K * 4)); a.grp_size0 = static_cast<uint32_t *>(alloc(P * 4)); a.grp_kept = static_cast<uint32_t *>(alloc(P * 4));
         a.grp_cons = static_cast<long long *>(alloc(P * 8)); a.grp_valid = static_cast<int *>(alloc(P * 4)); a.pig = static_cast<uint32_t *>(alloc(P * 4));
         a.pair_cons = static_cast<long long *>(alloc(K * 8));
-        HERA_LAUNCH(c, group_pairs_kernel, K, GP_THREADS, 0, a);
+        a.smem_items = std::min<uint32_t>(P, 10240);   // 16 B per path, up to 160 KB per CTA; larger pairs sort in global memory
+        const size_t smem = static_cast<size_t>(a.smem_items) * sizeof(SortItem);
+        HERA_CUDA(cudaFuncSetAttribute(group_pairs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        HERA_LAUNCH(c, group_pairs_kernel, K, GP_THREADS, smem, a);
         HERA_CUDA(cudaEventRecord(ev1, c.stream));
 
         // flatten on the host (marshalling only)
