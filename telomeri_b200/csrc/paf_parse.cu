@@ -5,18 +5,19 @@
 // as a whitespace-separated token stream, 16 tokens per record (12 typed + 4 skipped), so a
 // record boundary is "token index % 16 == 0", not a newline.
 //
-// One CTA owns one 8 KiB tile of text (plus a 512 B halo so the records that start in the tile
+// One CTA owns one 24 KiB tile of text (plus a 1 KiB halo so the records that start in the tile
 // can be finished).  Tiles are handed out by an atomic ticket so that a tile never waits for a
 // tile that has not started (chained scan with decoupled look-back):
 //   1. 128-bit coalesced loads stage tile+halo in shared memory; every thread classifies its
-//      16-byte chunks into a non-space bitmask; token starts = non-space after space.
-//   2. the tile's token count is published; a warp looks back over earlier tiles for the global
-//      index of the tile's first token (first chain).
-//   3. token starts are compacted to shared-memory offsets; every 16th global token opens a
-//      record.  A half-warp takes one record: lane k parses token k (names -> 64-bit hash,
-//      integers -> int32 with validity, strand char); warp shuffles hand the twelve fields to
-//      the half-warp leader, which runs the fp32 filter and scores in the reference's
-//      operation order (explicit round-to-nearest intrinsics, no FMA contraction).
+//      16-byte chunks into a non-space bitmask with SWAR arithmetic (one bit per byte).
+//   2. token starts = non-space after space; the tile's token count is published and a warp looks
+//      back over earlier tiles for the global index of the tile's first token (first chain).  A
+//      sharded load adds the tokens of the earlier ranks' byte ranges (ParseArgs::tok_base0).
+//   3. every 16th global token opens a record; its offset is found with popcount selection.  One
+//      thread takes one record: token boundaries come from the bitmask (funnel-shifted 32-bit
+//      windows, ffs), integer fields are converted eight digits at a time from whole words, names
+//      are hashed word-wise, then the fp32 filter and scores run in the reference's operation order
+//      (explicit round-to-nearest intrinsics, no FMA contraction).
 //   4. kept records are counted, the count goes through a second look-back chain, and the CTA
 //      writes its kept records at their final file-order position.
 // A record is "regular" when its nine integer tokens are [+-]?digits within int range and the
