@@ -184,7 +184,7 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
     t_groups = h.timer_stop()
     d2h = 0
     if read_back:  # the result a caller consumes: groups/consensus tables + the unique paths
-        paths = h.export_paths("u_")
+        paths = h.export_paths("u_", copy=False)   # views into the pinned mirrors the library copied the result to
         d2h = sum(v.nbytes for v in g.values() if hasattr(v, "nbytes")) + sum(v.nbytes for v in paths.values())
     return {"graph_ms": t_graph, "paths_ms": t_paths, "groups_ms": t_groups, "parse_ms": r1.parse_ms + r2.parse_ms,
             "parse_rr_ms": r1.parse_ms, "intern_ms": info.intern_ms, "csr_ms": info.csr_ms, "rank_ms": info.rank_ms,

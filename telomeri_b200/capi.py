@@ -119,10 +119,11 @@ class HeraError(RuntimeError):
         self.code = code
 
 
-def _arr(ptr, n, dtype):
+def _arr(ptr, n, dtype, copy=True):
+    """copy=False returns a view into the library's pinned mirror (valid until the next call that mutates that object)."""
     if n == 0 or not ptr:
         return np.zeros(0, dtype=dtype)
-    return np.ctypeslib.as_array(ptr, shape=(int(n),)).astype(dtype, copy=True)
+    return np.ctypeslib.as_array(ptr, shape=(int(n),)).astype(dtype, copy=copy)
 
 
 def default_filter(mode="avg", min_oll=0, min_olp=0.0, max_ohl=2 ** 64 - 1, max_ohp=1.0):
@@ -280,13 +281,13 @@ class Hera:
     def paths_reset(self):
         self._check(self.lib.hera_paths_reset(self.h))
 
-    def export_paths(self, prefix=""):
+    def export_paths(self, prefix="", copy=True):
         v = PathsView()
         self._check(self.lib.hera_paths_export(self.h, C.byref(v)))
         P = v.paths
         return {
-            prefix + "off": _arr(v.off, P + 1, np.uint64), prefix + "nodes": _arr(v.nodes, v.total_nodes, np.uint32),
-            prefix + "slots": _arr(v.slots, v.total_nodes - P, np.uint32), prefix + "len": _arr(v.len, P, np.int64),
+            prefix + "off": _arr(v.off, P + 1, np.uint64, copy), prefix + "nodes": _arr(v.nodes, v.total_nodes, np.uint32, copy),
+            prefix + "slots": _arr(v.slots, v.total_nodes - P, np.uint32, copy), prefix + "len": _arr(v.len, P, np.int64, copy),
             "call_kind": _arr(v.call_kind, v.calls, np.uint32), "call_metric": _arr(v.call_metric, v.calls, np.uint32),
             "call_found": _arr(v.call_found, v.calls, np.uint64), "mc_draws_per_walk": _arr(v.mc_draws_per_walk, v.mc_walks, np.uint32),
         }
