@@ -27,7 +27,8 @@ def parse_options(opts):
     return o
 
 
-def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, batched=False):
+def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, batched=False, exports=True):
+    """exports=False: make every (collective) call but copy no table back -- the other ranks of a gang at large sizes."""
     o = parse_options(list(opts))
     ds_dir = Path(ds_dir)
     own = hera is None
@@ -40,8 +41,9 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, bat
         out["load_ctr"] = np.array([r1.records, r2.records], dtype=np.uint64)
         out["load_cum_edges"] = np.array([r1.kept_total, r2.kept_total], dtype=np.uint64)
         h.finalize(o["metrics"])
-        out.update(h.export_graph())
-        out.update(slot_sections(out))
+        if exports:
+            out.update(h.export_graph())
+            out.update(slot_sections(out))
         if stages == "graph":
             return out
         pp = capi.default_path_params(o["rb_att"], o["bt_att"], o["len_thr"], o["w_size"], o["r_thr"])
@@ -54,10 +56,12 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, bat
             for m in o["metrics"]:
                 stats.append(h.deterministic(m))
         out["walk_stats"] = stats
-        out.update(h.export_paths("p_"))
+        if exports:
+            out.update(h.export_paths("p_"))
         h.unique()
-        u = h.export_paths("u_")
-        out.update({k: v for k, v in u.items() if k.startswith("u_")})
+        if exports:
+            u = h.export_paths("u_")
+            out.update({k: v for k, v in u.items() if k.startswith("u_")})
         if stages == "paths":
             return out
         out.update(h.groups(pp))

@@ -1,0 +1,67 @@
+#!/usr/bin/env python
+"""One BASELINE.json configuration end to end on the GPU box: generate the dataset, run the CPU oracle and the
+CUDA path (optionally as a local gang of N ranks) on it, compare every table bit for bit, print timings.
+  python tools/run_config.py dmel [--ranks N] [--rb-att K]
+Used for the configurations that are too large for the test-suite (configs[3])."""
+import argparse
+import json
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+CONFIGS = {
+    "yeast": ["--genome", "12000000", "--read-len", "20000", "--coverage", "60", "--contigs", "120", "--gap", "30000", "--families", "56", "--copies", "4", "--min-ovl", "1000", "--seed", "3"],
+    "dmel": ["--genome", "140000000", "--read-len", "20000", "--coverage", "60", "--contigs", "400", "--gap", "30000", "--families", "650", "--copies", "4", "--min-ovl", "1000", "--seed", "4"],
+}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("config")
+    ap.add_argument("--ranks", type=int, default=1)
+    ap.add_argument("--rb-att", type=int, default=10)
+    ap.add_argument("--out", default="/tmp/hera_cfg")
+    args = ap.parse_args()
+    import common
+    from telomeri_b200 import capi, pipeline
+    from test_gpu_parity import GRAPH_SECTIONS, GROUP_SECTIONS, PATH_SECTIONS
+    d = Path(args.out) / args.config
+    d.mkdir(parents=True, exist_ok=True)
+    common.build_generator()
+    common.build_oracle()
+    t0 = time.perf_counter()
+    meta = subprocess.run([str(common.GEN_BIN), "--out", str(d), "--no-fasta"] + CONFIGS[args.config], check=True, capture_output=True, text=True).stdout
+    t_gen = time.perf_counter() - t0
+    opts = ["--rb-att", str(args.rb_att)]
+    t0 = time.perf_counter()
+    ora = common.run_dump(common.ORACLE_BIN, d, d / "o.bin", opts, extra=["--rng", "philox", "--seed", "17"])
+    t_ora = time.perf_counter() - t0
+    (d / "o.bin").unlink()
+    t0 = time.perf_counter()
+    if args.ranks == 1:
+        gpu = pipeline.run_hot_path(d, opts, seed=17, batched=True)
+    else:
+        import torch
+        k = max(1, torch.cuda.device_count())
+        with capi.LocalGang(args.ranks, [r % k for r in range(args.ranks)]) as gang:
+            outs = gang.each(lambda r, h: pipeline.run_hot_path(d, opts, seed=17, hera=h, batched=True) if r == 0 else
+                             pipeline.run_hot_path(d, opts, seed=17, hera=h, batched=True, exports=False) and None)
+        gpu = outs[0]
+    t_gpu = time.perf_counter() - t0
+    names = GRAPH_SECTIONS + ["rank_0", "rank_1"] + PATH_SECTIONS + GROUP_SECTIONS
+    common.assert_sections_equal(ora, gpu, names, args.config)
+    st = gpu["walk_stats"]
+    print(json.dumps({"config": args.config, "ranks": args.ranks, "generator": json.loads(meta), "records": int(gpu["load_ctr"].sum()),
+                      "kept_overlaps": int(gpu["e_q"].size), "nodes": int(gpu["node_len"].size), "anchors": int(gpu["node_anchor"].sum()),
+                      "walks": int(sum(s.walks for s in st)), "paths": int(gpu["p_len"].size), "unique_paths": int(gpu["u_len"].size),
+                      "anchor_pairs": int(gpu["pair_a1"].size), "sections_compared": len(names), "bit_exact": True,
+                      "seconds": {"generate": round(t_gen, 1), "oracle_cpu": round(t_ora, 1), "cuda_path_incl_file_io_and_export": round(t_gpu, 1)}}))
+
+
+if __name__ == "__main__":
+    main()
