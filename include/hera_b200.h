@@ -127,7 +127,7 @@ uint64_t hera_kernel_launches(hera_ctx *ctx);    /* kernels launched by this con
 /* Measurement helpers (no reference counterpart; the reference only has Stopwatch, src/Stopwatch.cpp):
  * a CUDA-event pair on the context's own stream, and integer knobs.
  * Options: "flush_l2" (1 = write a buffer larger than L2 before every event-timed kernel region,
- * outside the timed region), "walk_warps_per_sm" (resident walk warps per SM, default 32), "walk_smem_bitmap" (0 = visited
+ * outside the timed region), "walk_warps_per_sm" (resident walk warps per SM shared by the walk kernels in flight, default 64), "walk_smem_bitmap" (0 = visited
  * bitmaps of the Monte-Carlo walks stay in global memory even when they would fit in shared memory). */
 int hera_timer_start(hera_ctx *ctx);
 int hera_timer_stop(hera_ctx *ctx, float *ms);   /* synchronises the stream */

@@ -115,6 +115,7 @@ int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
     const std::string k(key);
     if (k == "flush_l2") c.opt_flush_l2 = value != 0;
     else if (k == "walk_warps_per_sm") c.opt_walk_warps_per_sm = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(64, value)));
+    else if (k == "walk_variant") c.opt_walk_variant = static_cast<int>(value);
     else if (k == "walk_smem_bitmap") c.opt_walk_smem_bitmap = value != 0;
     else throw hera::Error{102, "unknown option: " + k};
     HERA_API_END

@@ -66,6 +66,7 @@ struct LoadedText {
 struct GraphTables {
     bool ready = false;
     uint64_t N = 0, anchors = 0, E = 0, S = 0;
+    uint32_t max_deg = 0;                    // longest adjacency list
     DBuf<uint32_t> e_q, e_t;                 // node ids per kept overlap
     DBuf<uint32_t> node_len;
     DBuf<uint8_t> node_anchor;
@@ -104,7 +105,8 @@ struct Ctx {
     // measurement helpers / knobs
     cudaEvent_t timer0 = nullptr, timer1 = nullptr;
     int opt_flush_l2 = 0;
-    int opt_walk_warps_per_sm = 32;
+    int opt_walk_warps_per_sm = 64;
+    int opt_walk_variant = 0;      // Monte-Carlo kernel variant (chunks in flight x resident CTAs), see walks.cu
     int opt_walk_smem_bitmap = 1;  // 0 = keep the walks' visited bitmaps in global memory whatever the graph size (tests)
     uint64_t walk_pool_hint[2][4] = {};   // per (kind, metric): largest path pool a walk call needed so far (avoids the overflow re-run)
     std::vector<cudaStream_t> aux_streams;   // hera_paths_build: one stream per walk kernel in flight

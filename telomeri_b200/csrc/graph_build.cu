@@ -186,10 +186,11 @@ __global__ void csr_gather_kernel(uint64_t S, const uint32_t *__restrict__ pay, 
 // multiple of q below 2^53 * q: exactly representable, so any summation order gives the sequential
 // result bit for bit.  Bit m of node_exact[x] records that for metric m.
 __global__ void __launch_bounds__(128) node_exact_kernel(uint32_t N, const uint32_t *__restrict__ off, const float *__restrict__ a_es,
-                                                         const float *__restrict__ a_os, uint8_t *__restrict__ node_exact) {
+                                                         const float *__restrict__ a_os, uint8_t *__restrict__ node_exact, uint32_t *__restrict__ max_deg) {
     const uint32_t x = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (x >= N) return;
     const uint32_t base = off[x], deg = off[x + 1] - base;
+    if (lane == 0) atomicMax(max_deg, deg);
     uint32_t flags = 0;
     for (int m = 0; m < 4; m++) {
         bool weird = false;
@@ -291,7 +292,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
     for (auto &e : ev) HERA_CUDA(cudaEventCreate(&e));
     HERA_CUDA(cudaEventRecord(ev[0], c.stream));
     g.ready = false;
-    g.E = E; g.S = occ; g.N = 0; g.anchors = 0;
+    g.E = E; g.S = occ; g.N = 0; g.anchors = 0; g.max_deg = 0;
     for (bool &r : g.rank_ready) r = false;
     float intern_ms = 0, csr_ms = 0, rank_ms = 0;
     if (E > 0) {
@@ -402,7 +403,13 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         HERA_LAUNCH(c, csr_offsets_kernel, div_up(occ + 1, 256), 256, 0, occ, N, keys32, g.adj_off.p);
         HERA_LAUNCH(c, csr_gather_kernel, div_up(occ, 256), 256, 0, occ, g.adj_pay.p, g.e_q.p, g.e_t.p, c.kept.qs.p, c.kept.ts.p, c.kept.es.p, c.kept.os.p,
                     g.node_anchor.p, g.a_nbr.p, g.a_es.p, g.a_os.p, g.a_delta.p, g.adj4.p);
-        HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.a_es.p, g.a_os.p, g.node_exact.p);
+        uint32_t *d_max_deg = nullptr;
+        HERA_CUDA(cudaMallocAsync(&d_max_deg, sizeof(uint32_t), c.stream));
+        HERA_CUDA(cudaMemsetAsync(d_max_deg, 0, sizeof(uint32_t), c.stream));
+        HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.a_es.p, g.a_os.p, g.node_exact.p, d_max_deg);
+        c.h_counters.reserve(16);
+        HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 15, d_max_deg, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));   // read after the final sync below
+        HERA_CUDA(cudaFreeAsync(d_max_deg, c.stream));
         HERA_CUDA(cudaFreeAsync(keys32, c.stream)); HERA_CUDA(cudaFreeAsync(keys_alt, c.stream)); HERA_CUDA(cudaFreeAsync(vals_alt, c.stream));
         HERA_CUDA(cudaEventRecord(ev[2], c.stream));
 
@@ -416,6 +423,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         }
         HERA_CUDA(cudaEventRecord(ev[3], c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
+        g.max_deg = static_cast<uint32_t>(c.h_counters.p[15] & 0xffffffffu);
         HERA_CUDA(cudaEventElapsedTime(&intern_ms, ev[0], ev[1]));
         HERA_CUDA(cudaEventElapsedTime(&csr_ms, ev[1], ev[2]));
         HERA_CUDA(cudaEventElapsedTime(&rank_ms, ev[2], ev[3]));

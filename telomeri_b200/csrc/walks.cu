@@ -24,8 +24,7 @@ namespace hera {
 
 constexpr int WK_THREADS = 128;
 constexpr int WK_WARPS = WK_THREADS / 32;
-constexpr int WK_MLP = 4;       // 32-entry chunks of the current node's list loaded per round trip
-constexpr int WK_CACHE = 1024;  // list entries (metric values) a warp keeps in shared memory between the two roulette passes
+constexpr int WK_CACHE_MAX = 1024;  // list entries (metric values) a warp can keep in shared memory between the two roulette passes
 
 struct WalkGraph {
     const uint32_t *off, *nbr, *canon, *rank, *node_len, *anchor_ids;
@@ -43,6 +42,7 @@ struct WalkScratch {
     uint32_t *bitmap;     // warps * words
     uint32_t *nodes, *slots, *vlog;   // warps * cap
     uint32_t words, cap;
+    uint32_t cache;       // entries of the per-warp value cache (multiple of 32, covers the longest list up to WK_CACHE_MAX)
 };
 
 struct WalkOut {
@@ -126,12 +126,13 @@ __device__ __forceinline__ bool bm_get(const uint32_t *s_bm, const uint32_t *g_b
     return (g_bm[i >> 5] >> (i & 31)) & 1u;
 }
 
-template <bool SMEM_BM>
-__global__ void __launch_bounds__(WK_THREADS) walk_mc_kernel(WalkGraph g, WalkScratch sc, WalkOut o, uint32_t total_walks, uint32_t attempts,
+template <bool SMEM_BM, int WK_MLP, int MIN_CTAS>
+__global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph g, WalkScratch sc, WalkOut o, uint32_t total_walks, uint32_t attempts,
                                                              int backtrack_attempts, long long len_threshold, uint64_t seed, uint32_t metric_id) {
     // dynamic shared memory: per-warp value cache of the current node's list, then the per-warp visited bitmaps
     extern __shared__ __align__(16) uint32_t wk_smem[];
     const uint32_t lane = lane_id(), wib = warp_id();
+    const uint32_t WK_CACHE = sc.cache;
     float *s_cval = reinterpret_cast<float *>(wk_smem) + wib * WK_CACHE;
     uint32_t *s_bm = wk_smem + WK_WARPS * WK_CACHE + (SMEM_BM ? wib * sc.words : 0u);
     const uint32_t wslot = blockIdx.x * WK_WARPS + wib;
@@ -525,7 +526,8 @@ struct WalkJob {
 uint32_t walk_share(uint32_t total_walks, int ranks, int r) { return static_cast<uint32_t>((static_cast<uint64_t>(total_walks) + ranks - 1 - r) / ranks); }
 
 void job_launch_kernel(Ctx &c, WalkJob &j) {
-    WalkScratch sc{j.r.bitmap, j.r.nodes, j.r.slots, j.r.vlog, j.words, j.cap};
+    const uint32_t cache = std::min<uint32_t>(WK_CACHE_MAX, std::max<uint32_t>(64, (c.g.max_deg + 31) / 32 * 32));
+    WalkScratch sc{j.r.bitmap, j.r.nodes, j.r.slots, j.r.vlog, j.words, j.cap, cache};
     WalkOut wo{j.r.res_n, j.r.res_off, j.r.res_len, j.r.res_draws, j.r.pool_nodes, j.r.pool_slots, j.pool_cap, j.r.d_ctr, j.r.d_ctr + 1,
                reinterpret_cast<unsigned int *>(j.r.d_ctr + 2), static_cast<uint32_t>(xch_rank(c)), static_cast<uint32_t>(xch_size(c))};
     HERA_CUDA(cudaMemsetAsync(j.r.d_ctr, 0, 4 * sizeof(unsigned long long), j.stream));
@@ -536,13 +538,20 @@ void job_launch_kernel(Ctx &c, WalkJob &j) {
         if (j.kind == 0) {
             // visited bitmaps in shared memory while four of them fit beside the value cache (N <= 65536 nodes)
             const bool smem_bm = c.opt_walk_smem_bitmap && j.words <= 2048;
-            const size_t smem = (1ull * WK_WARPS * WK_CACHE + (smem_bm ? static_cast<size_t>(WK_WARPS) * j.words : 0)) * sizeof(uint32_t);
+            const size_t smem = (1ull * WK_WARPS * cache + (smem_bm ? static_cast<size_t>(WK_WARPS) * j.words : 0)) * sizeof(uint32_t);
+            auto launch = [&](auto kernel) {
+                kernel<<<j.blocks, WK_THREADS, smem, j.stream>>>(j.wg, sc, wo, j.my_walks, static_cast<uint32_t>(j.pp.rebuild_attempts), j.pp.backtrack_attempts,
+                                                                static_cast<long long>(j.pp.len_threshold), j.seed, static_cast<uint32_t>(j.metric));
+            };
+            // variants: chunks in flight per round trip x resident CTAs (registers): 4 x 8 (<= 64 regs), 2 x 12 (<= 40), 1 x 16 (<= 32)
             if (smem_bm) {
-                walk_mc_kernel<true><<<j.blocks, WK_THREADS, smem, j.stream>>>(j.wg, sc, wo, j.my_walks, static_cast<uint32_t>(j.pp.rebuild_attempts), j.pp.backtrack_attempts,
-                                                                               static_cast<long long>(j.pp.len_threshold), j.seed, static_cast<uint32_t>(j.metric));
+                if (c.opt_walk_variant == 1) launch(walk_mc_kernel<true, 2, 12>);
+                else if (c.opt_walk_variant == 2) launch(walk_mc_kernel<true, 1, 16>);
+                else launch(walk_mc_kernel<true, 4, 8>);
             } else {
-                walk_mc_kernel<false><<<j.blocks, WK_THREADS, smem, j.stream>>>(j.wg, sc, wo, j.my_walks, static_cast<uint32_t>(j.pp.rebuild_attempts), j.pp.backtrack_attempts,
-                                                                                static_cast<long long>(j.pp.len_threshold), j.seed, static_cast<uint32_t>(j.metric));
+                if (c.opt_walk_variant == 1) launch(walk_mc_kernel<false, 2, 12>);
+                else if (c.opt_walk_variant == 2) launch(walk_mc_kernel<false, 1, 16>);
+                else launch(walk_mc_kernel<false, 4, 8>);
             }
         } else {
             walk_det_kernel<<<j.blocks, WK_THREADS, 0, j.stream>>>(j.wg, sc, wo, j.my_walks, j.walk_base);

@@ -21,6 +21,8 @@ h = capi.Hera(0)
 pp = capi.default_path_params(rb_att=bench.WORKLOAD["rb_att"])
 batched = "--separate" not in sys.argv
 for a in sys.argv[1:]:
+    if a.startswith("--variant="):
+        h.set_option("walk_variant", int(a.split("=")[1]))
     if a.startswith("--warps="):
         h.set_option("walk_warps_per_sm", int(a.split("=")[1]))
 for rep in range(5):
