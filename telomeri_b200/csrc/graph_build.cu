@@ -186,12 +186,15 @@ __global__ void csr_gather_kernel(uint64_t S, const uint32_t *__restrict__ pay, 
 // multiple of q below 2^53 * q: exactly representable, so any summation order gives the sequential
 // result bit for bit.  Bit m of node_exact[x] records that for metric m.
 __global__ void __launch_bounds__(128) node_exact_kernel(uint32_t N, const uint32_t *__restrict__ off, const float *__restrict__ a_es,
-                                                         const float *__restrict__ a_os, uint8_t *__restrict__ node_exact, uint32_t *__restrict__ max_deg) {
+                                                         const float *__restrict__ a_os, const uint32_t *__restrict__ a_nbr, uint8_t *__restrict__ node_exact, uint32_t *__restrict__ max_deg) {
     const uint32_t x = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (x >= N) return;
     const uint32_t base = off[x], deg = off[x + 1] - base;
     if (lane == 0) atomicMax(max_deg, deg);
     uint32_t flags = 0;
+    bool anchor_nbr = false;   // bit 4: some neighbour is an anchor (only then can a walk step be forced, src/PathManager.cpp:57-60)
+    for (uint32_t k = lane; k < deg; k += 32) anchor_nbr |= (a_nbr[base + k] >> 31) != 0;
+    if (__any_sync(0xffffffffu, anchor_nbr)) flags |= 16u;
     for (int m = 0; m < 4; m++) {
         bool weird = false;
         int min_exp = 1 << 20;
@@ -406,7 +409,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         uint32_t *d_max_deg = nullptr;
         HERA_CUDA(cudaMallocAsync(&d_max_deg, sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMemsetAsync(d_max_deg, 0, sizeof(uint32_t), c.stream));
-        HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.a_es.p, g.a_os.p, g.node_exact.p, d_max_deg);
+        HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.a_es.p, g.a_os.p, g.a_nbr.p, g.node_exact.p, d_max_deg);
         c.h_counters.reserve(16);
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 15, d_max_deg, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));   // read after the final sync below
         HERA_CUDA(cudaFreeAsync(d_max_deg, c.stream));

@@ -166,7 +166,9 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
 
         for (;;) {
             const uint32_t base = g.off[cur], deg = g.off[cur + 1] - base;
-            const bool order_free = (g.node_exact[cur] & g.exact_bit) != 0;
+            const uint32_t node_flags = g.node_exact[cur];
+            const bool order_free = (node_flags & g.exact_bit) != 0;
+            const bool may_force = (node_flags & 16u) != 0;   // the node has an anchor among its neighbours
             // ---- pass 1: forced anchor edge, candidate set (src/PathManager.cpp:53-67)
             int forced = -1;
             bool any_cand = false;
@@ -187,8 +189,8 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
                     if (c0 + 32 * j >= deg || forced >= 0) continue;   // warp-uniform
                     const bool valid = k < deg;
                     const uint32_t nb = a[j].x & 0x7fffffffu;
-                    const bool force = valid && (a[j].x >> 31) && nb != start;
-                    const uint32_t fb = __ballot_sync(0xffffffffu, force);
+                    const bool force = may_force && valid && (a[j].x >> 31) && nb != start;
+                    const uint32_t fb = may_force ? __ballot_sync(0xffffffffu, force) : 0u;
                     if (fb) {
                         const int src = __ffs(fb) - 1;
                         forced = static_cast<int>(c0) + 32 * j + src;
