@@ -220,6 +220,8 @@ struct NcclExchange final : Exchange {
         }
         HERA_NCCL(n.GroupEnd());
     }
+    void begin_batch() override { HERA_NCCL(nccl_api().GroupStart()); }
+    void end_batch() override { HERA_NCCL(nccl_api().GroupEnd()); }
     void barrier(Ctx &c) override {
         uint64_t one = 1;
         std::vector<uint64_t> all(size);

@@ -33,6 +33,10 @@ struct Exchange {
     // overlap any rank's receive window except its own (send == recv + displs[rank] * elem is allowed).
     // Stream-ordered on the context's stream.
     virtual void all_gatherv(Ctx &c, const void *send, void *recv, const uint64_t *counts, const uint64_t *displs, size_t elem) = 0;
+    // Several all_gatherv calls between begin_batch and end_batch may be issued as one operation (one NCCL
+    // group = one launch); their send and receive buffers must stay untouched until end_batch returns.
+    virtual void begin_batch() {}
+    virtual void end_batch() {}
     // Host barrier (after synchronising the context's stream).
     virtual void barrier(Ctx &c) = 0;
     // Called when this rank fails inside a collective call: wakes the ranks waiting for it.

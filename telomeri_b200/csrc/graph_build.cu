@@ -243,9 +243,9 @@ __device__ __forceinline__ float metric_value(int metric, float es, float os) {
 }
 
 __global__ void __launch_bounds__(RK_THREADS) rank_kernel(const uint32_t *__restrict__ off, const float *__restrict__ a_es, const float *__restrict__ a_os,
-                                                          int metric, uint32_t *__restrict__ rank) {
+                                                          int metric, uint32_t *__restrict__ rank, uint32_t node0) {
     __shared__ float sm[RK_SMEM];
-    const uint32_t x = blockIdx.x;
+    const uint32_t x = blockIdx.x + node0;
     const uint32_t base = off[x], deg = off[x + 1] - base;
     const bool staged = deg <= RK_SMEM;
     if (staged) {
@@ -264,9 +264,10 @@ __global__ void __launch_bounds__(RK_THREADS) rank_kernel(const uint32_t *__rest
     }
 }
 
-__global__ void __launch_bounds__(RK_THREADS) canon_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr, uint32_t *__restrict__ canon) {
+__global__ void __launch_bounds__(RK_THREADS) canon_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr, uint32_t *__restrict__ canon,
+                                                           uint32_t node0) {
     __shared__ uint32_t sm[RK_SMEM];
-    const uint32_t x = blockIdx.x;
+    const uint32_t x = blockIdx.x + node0;
     const uint32_t base = off[x], deg = off[x + 1] - base;
     const bool staged = deg <= RK_SMEM;
     if (staged) {
@@ -416,13 +417,28 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         HERA_CUDA(cudaFreeAsync(keys32, c.stream)); HERA_CUDA(cudaFreeAsync(keys_alt, c.stream)); HERA_CUDA(cudaFreeAsync(vals_alt, c.stream));
         HERA_CUDA(cudaEventRecord(ev[2], c.stream));
 
-        // ---- rank permutations + canonical slots
-        HERA_LAUNCH(c, canon_kernel, static_cast<unsigned>(N), RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.canon.p);
+        // ---- rank permutations + canonical slots: each rank does its share of the nodes, the slices are all-gathered
+        const int ranks = xch_size(c), me = xch_rank(c);
+        const uint64_t n_lo = N * me / ranks, n_hi = N * (me + 1) / ranks;
+        const unsigned my_nodes = static_cast<unsigned>(n_hi - n_lo);
+        if (my_nodes) HERA_LAUNCH(c, canon_kernel, my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.canon.p, static_cast<uint32_t>(n_lo));
         for (int m = 0; m < 4; m++) {
             if (!(metrics_mask & (1u << m))) continue;
             g.rank[m].reserve(occ);
-            HERA_LAUNCH(c, rank_kernel, static_cast<unsigned>(N), RK_THREADS, 0, g.adj_off.p, g.a_es.p, g.a_os.p, m, g.rank[m].p);
+            if (my_nodes) HERA_LAUNCH(c, rank_kernel, my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_es.p, g.a_os.p, m, g.rank[m].p, static_cast<uint32_t>(n_lo));
             g.rank_ready[m] = true;
+        }
+        if (ranks > 1) {
+            std::vector<uint32_t> cut(ranks + 1);
+            for (int r = 0; r <= ranks; r++) HERA_CUDA(cudaMemcpyAsync(&cut[r], g.adj_off.p + N * r / ranks, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            std::vector<uint64_t> counts(ranks), displs(ranks);
+            for (int r = 0; r < ranks; r++) { displs[r] = cut[r]; counts[r] = cut[r + 1] - cut[r]; }
+            c.xch->begin_batch();
+            c.xch->all_gatherv(c, g.canon.p + displs[me], g.canon.p, counts.data(), displs.data(), sizeof(uint32_t));
+            for (int m = 0; m < 4; m++)
+                if (g.rank_ready[m]) c.xch->all_gatherv(c, g.rank[m].p + displs[me], g.rank[m].p, counts.data(), displs.data(), sizeof(uint32_t));
+            c.xch->end_batch();
         }
         HERA_CUDA(cudaEventRecord(ev[3], c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));

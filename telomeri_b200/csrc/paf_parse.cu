@@ -627,12 +627,13 @@ uint64_t padded_text_size(uint64_t n) { return (n / PF_TILE + 2) * static_cast<u
 // Moves this rank's new kept rows [n0, n0 + counts[rank]) to their global place n0 + displs[rank] and
 // receives the other ranks' rows: one variable-size all-gather per column of the kept table.
 template <typename T>
-static void gather_column(Ctx &c, T *col, uint64_t n0, const uint64_t *counts, const uint64_t *displs, void *tmp) {
+static void gather_column(Ctx &c, T *col, uint64_t n0, const uint64_t *counts, const uint64_t *displs, char *&tmp) {
     const int r = xch_rank(c);
     const void *send = col + n0;
     if (displs[r] != 0 && counts[r]) {   // my rows move up: stage them so that no receive window overlaps the source
         HERA_CUDA(cudaMemcpyAsync(tmp, col + n0, counts[r] * sizeof(T), cudaMemcpyDeviceToDevice, c.stream));
         send = tmp;
+        tmp += (counts[r] * sizeof(T) + 255) / 256 * 256;   // every column gets its own staging area: the batch runs at end_batch
     }
     c.xch->all_gatherv(c, send, col + n0, counts, displs, sizeof(T));
 }
@@ -720,8 +721,10 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         c.kept.reserve(c.kept.n + total, c.stream, c.kept.n + counts[me]);
         KeptTable &k = c.kept;
         const uint64_t n0 = k.n;
-        void *tmp = nullptr;
-        HERA_CUDA(cudaMallocAsync(&tmp, std::max<uint64_t>(counts[me], 1) * sizeof(uint64_t), c.stream));
+        char *tmp0 = nullptr;
+        HERA_CUDA(cudaMallocAsync(&tmp0, std::max<uint64_t>(counts[me], 1) * 80 + 15 * 256, c.stream));   // 73 bytes per row + alignment
+        char *tmp = tmp0;
+        c.xch->begin_batch();
         gather_column(c, k.qs.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.qe.p, n0, counts.data(), displs.data(), tmp);
         gather_column(c, k.ts.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.te.p, n0, counts.data(), displs.data(), tmp);
         gather_column(c, k.qlen.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.tlen.p, n0, counts.data(), displs.data(), tmp);
@@ -731,7 +734,8 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         gather_column(c, k.flags.p, n0, counts.data(), displs.data(), tmp);
         gather_column(c, k.qhash.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.thash.p, n0, counts.data(), displs.data(), tmp);
         gather_column(c, k.qname.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.tname.p, n0, counts.data(), displs.data(), tmp);
-        HERA_CUDA(cudaFreeAsync(tmp, c.stream));
+        c.xch->end_batch();
+        HERA_CUDA(cudaFreeAsync(tmp0, c.stream));
         c.own_rows.push_back({n0 + displs[me], n0 + displs[me] + counts[me]});
         kept_new = total;
     } else if (hc.first_bad_rec < records) {
