@@ -213,6 +213,23 @@ int hera_paths_export(hera_ctx *ctx, hera_paths_view *out);
  * (src/PathManager.cpp:508-645, src/PathWindow.cpp, src/PathGroup.cpp, src/Main.cpp:277-342). */
 int hera_groups(hera_ctx *ctx, const hera_path_params *pp, hera_groups_view *out);
 
+/* The scaffold: chain of the anchor pairs' consensus paths (PathManager::constructConsensusPath,
+ * src/PathManager.cpp:664-767, as main() calls it at src/Main.cpp:344-353; min_path_num = 10 there) and
+ * Scaffolder (src/Scaffolder.cpp:12-147): reads / contigs FASTA (two lines per record; four for a path
+ * ending in 'q'), name lookup, substring / complement / reverse stitching.  The FASTA files are indexed
+ * and the sequence is assembled on the GPU.  `fasta` is the exact content of HERA_result.fasta.
+ * Needs hera_groups first.  Returns 40 ("No consensus found!") when no anchor pair qualifies. */
+typedef struct {
+    uint64_t nodes;                 /* scaffold path: nodes, and nodes - 1 slots */
+    const uint32_t *node, *slot;
+    uint64_t logged;                /* positions in node[] of the nodes Scaffolder::write prints ("a-b-c") */
+    const uint32_t *logged_index;
+    uint64_t fasta_bytes, sequence_length;
+    const char *fasta;
+    float ms;                       /* FASTA load + index + lookup + stitch, CUDA events */
+} hera_scaffold_view;
+int hera_scaffold(hera_ctx *ctx, const char *reads_fasta, const char *contigs_fasta, uint64_t min_path_num, hera_scaffold_view *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,6 +57,11 @@ class GroupsView(C.Structure):
                 ("grp_consensus", i64p), ("grp_valid", i32p), ("pair_consensus", i64p), ("ms", C.c_float)]
 
 
+class ScaffoldView(C.Structure):
+    _fields_ = [("nodes", C.c_uint64), ("node", u32p), ("slot", u32p), ("logged", C.c_uint64), ("logged_index", u32p),
+                ("fasta_bytes", C.c_uint64), ("sequence_length", C.c_uint64), ("fasta", C.POINTER(C.c_char)), ("ms", C.c_float)]
+
+
 class WalkStats(C.Structure):
     _fields_ = [("walks", C.c_uint64), ("found", C.c_uint64), ("steps", C.c_uint64), ("ms", C.c_float), ("launches", C.c_uint32)]
 
@@ -93,6 +98,7 @@ SIGNATURES = {
     "hera_paths_reset": (C.c_int, [C.c_void_p]),
     "hera_paths_export": (C.c_int, [C.c_void_p, C.POINTER(PathsView)]),
     "hera_groups": (C.c_int, [C.c_void_p, C.POINTER(PathParams), C.POINTER(GroupsView)]),
+    "hera_scaffold": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.c_uint64, C.POINTER(ScaffoldView)]),
 }
 
 _lib = None
@@ -291,6 +297,14 @@ class Hera:
             "call_kind": _arr(v.call_kind, v.calls, np.uint32), "call_metric": _arr(v.call_metric, v.calls, np.uint32),
             "call_found": _arr(v.call_found, v.calls, np.uint64), "mc_draws_per_walk": _arr(v.mc_draws_per_walk, v.mc_walks, np.uint32),
         }
+
+    def scaffold(self, reads_fasta, contigs_fasta, min_path_num=10):
+        """Chain of consensus paths + Scaffolder; returns the scaffold path and the bytes of HERA_result.fasta."""
+        v = ScaffoldView()
+        self._check(self.lib.hera_scaffold(self.h, str(reads_fasta).encode(), str(contigs_fasta).encode(), min_path_num, C.byref(v)))
+        return {"scaffold_nodes": _arr(v.node, v.nodes, np.uint32), "scaffold_slots": _arr(v.slot, v.nodes - 1, np.uint32),
+                "logged": _arr(v.logged_index, v.logged, np.uint32), "fasta": C.string_at(v.fasta, v.fasta_bytes),
+                "sequence_length": int(v.sequence_length), "ms": float(v.ms)}
 
     def groups(self, pp):
         v = GroupsView()

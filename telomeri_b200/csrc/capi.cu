@@ -342,6 +342,7 @@ int hera_paths_reset(hera_ctx *ctx) {
     c.all.paths = c.all.nodes = 0;
     c.uniq.paths = c.uniq.nodes = 0;
     c.uniq_ready = false;
+    c.groups_valid = false;
     c.call_kind.clear(); c.call_metric.clear(); c.call_found.clear(); c.mc_draws.clear();
     HERA_API_END
 }
@@ -356,7 +357,16 @@ int hera_paths_export(hera_ctx *ctx, hera_paths_view *out) {
 int hera_groups(hera_ctx *ctx, const hera_path_params *pp, hera_groups_view *out) {
     HERA_API_BEGIN(ctx)
     HERA_REQUIRE(pp != nullptr && out != nullptr, 101, "null argument");
+    c.groups_valid = false;
     hera::group_paths(c, *pp, out);
+    c.groups_valid = true;
+    HERA_API_END
+}
+
+int hera_scaffold(hera_ctx *ctx, const char *reads_fasta, const char *contigs_fasta, uint64_t min_path_num, hera_scaffold_view *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(out != nullptr, 101, "null output");
+    hera::build_scaffold(c, reads_fasta, contigs_fasta, min_path_num, out);
     HERA_API_END
 }
 

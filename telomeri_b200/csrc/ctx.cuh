@@ -149,6 +149,11 @@ struct Ctx {
         std::vector<int64_t> grp_consensus, pair_consensus;
         std::vector<int32_t> grp_valid;
     } grm;
+    bool groups_valid = false;   // grm describes the current paths
+    struct ScaffoldMirror {
+        std::vector<uint32_t> nodes, slots, logged;
+        HBuf<char> fasta;
+    } scm;
 };
 
 // ---- host-side helpers implemented in primitives.cu -----------------------------------------
@@ -173,5 +178,6 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
 void unique_paths(Ctx &c, uint64_t *n_unique);
 void export_paths(Ctx &c, hera_paths_view *out);
 void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out);
+void build_scaffold(Ctx &c, const char *reads_path, const char *contigs_path, uint64_t min_path_num, hera_scaffold_view *out);
 
 }  // namespace hera

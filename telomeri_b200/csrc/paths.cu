@@ -69,6 +69,7 @@ void unique_paths(Ctx &c, uint64_t *n_unique) {
         HERA_CUDA(cudaFreeAsync(node_scan, c.stream)); HERA_CUDA(cudaFreeAsync(d_np, c.stream)); HERA_CUDA(cudaFreeAsync(d_nn, c.stream));
     }
     c.uniq_ready = true;
+    c.groups_valid = false;
     if (n_unique) *n_unique = u.paths;
 }
 

@@ -745,6 +745,7 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
     cudaFreeHost(j.h_ctr);
     j.h_ctr = nullptr;
     c.uniq_ready = false;
+    c.groups_valid = false;
     c.call_kind.push_back(static_cast<uint32_t>(j.kind));
     c.call_metric.push_back(static_cast<uint32_t>(j.metric));
     c.call_found.push_back(found);

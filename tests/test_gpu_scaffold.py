@@ -1,0 +1,63 @@
+"""hera_scaffold (chain of consensus paths + Scaffolder on the GPU) against the oracle: same scaffold path
+and byte-identical HERA_result.fasta (reference src/PathManager.cpp:664-767, src/Scaffolder.cpp:12-147)."""
+from pathlib import Path
+
+import pytest
+
+import common
+
+pytestmark = pytest.mark.gpu
+
+
+def run_case(case, oracle_bin, datasets, tmp_path, seed, mutate=None):
+    from telomeri_b200 import capi, pipeline
+    golden = common.load_golden(case)
+    ds = datasets[golden["dataset"]]
+    if mutate:
+        ds = mutate(ds, tmp_path)
+    ora = common.run_dump(oracle_bin, ds, tmp_path / "o.bin", golden["options"], with_fasta=True, extra=["--rng", "philox", "--seed", str(seed)])
+    with capi.Hera(0) as h:
+        pipeline.run_hot_path(ds, golden["options"], seed=seed, hera=h, batched=True)
+        try:
+            sc = h.scaffold(ds / "reads.fasta", ds / "contigs.fasta")
+        except capi.HeraError as e:
+            sc = e
+    return ora, sc, Path(str(tmp_path / "o.bin") + ".fasta")
+
+
+@pytest.mark.parametrize("case", ["small_default", "small_windows", "mixed_default", "mixed_sqrt"])
+def test_scaffold_matches_oracle(case, oracle_bin, datasets, tmp_path):
+    ora, sc, fasta = run_case(case, oracle_bin, datasets, tmp_path, seed=5)
+    if case == "small_default":
+        assert int(ora["have_scaffold"][0]) == 1 and fasta.stat().st_size > 50000   # this case must exercise the stitching
+    if int(ora["have_scaffold"][0]):
+        assert not isinstance(sc, Exception), sc
+        assert sc["scaffold_nodes"].tolist() == ora["scaffold_nodes"].tolist()
+        assert sc["scaffold_slots"].tolist() == ora["scaffold_slots"].tolist()
+        assert sc["fasta"] == fasta.read_bytes()
+        assert sc["sequence_length"] == len(fasta.read_bytes().split(b"\n")[1])
+    else:
+        assert isinstance(sc, Exception) and sc.code == 40
+
+
+def test_no_consensus_is_reported(oracle_bin, datasets, tmp_path):
+    """bundled --filter-min: every group spans more than 100 000 -> main() prints "No consensus found!" (SURVEY 8(c))."""
+    ora, sc, _ = run_case("bundled_min", oracle_bin, {"bundled": common.bundled_dataset(tmp_path / "b")} | {}, tmp_path, seed=1,
+                          mutate=lambda ds, tmp: (ds / "reads.fasta").write_text(">none\nA\n") and (ds / "contigs.fasta").write_text(">none\nA\n") and ds)
+    assert int(ora["have_scaffold"][0]) == 0
+    assert isinstance(sc, Exception) and sc.code == 40
+
+
+def test_strand_and_crlf_variants(oracle_bin, datasets, tmp_path):
+    """Complemented pieces (relative strand '-') and a FASTA without the final newline give the same bytes as the oracle."""
+    def strip_newline(ds, tmp):
+        d = tmp / "ds"
+        d.mkdir()
+        for f in ("rr_overlaps.paf", "cr_overlaps.paf", "contigs.fasta"):
+            (d / f).write_bytes((ds / f).read_bytes())
+        (d / "reads.fasta").write_bytes((ds / "reads.fasta").read_bytes().rstrip(b"\n"))
+        return d
+    ora, sc, fasta = run_case("mixed_default", oracle_bin, datasets, tmp_path, seed=9, mutate=strip_newline)
+    if int(ora["have_scaffold"][0]):
+        assert not isinstance(sc, Exception), sc
+        assert sc["fasta"] == fasta.read_bytes()
