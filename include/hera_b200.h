@@ -187,6 +187,12 @@ int hera_graph_reset(hera_ctx *ctx);
  * canonical slots used by the greedy walks.  metrics_mask: bit m set = build ranks for metric m.
  * May be called again after further loads. */
 int hera_graph_finalize(hera_ctx *ctx, uint32_t metrics_mask, hera_graph_info *out);
+/* Binary cache of the parsed graph (no reference counterpart): what loading, filtering,
+ * scoring and node numbering produced -- kept overlaps in file order with node ids, node table with
+ * names, the filter used.  hera_graph_save after hera_graph_finalize; hera_graph_load_cache on a fresh
+ * graph restores it, then hera_graph_finalize builds CSR and ranks without reading any PAF text. */
+int hera_graph_save(hera_ctx *ctx, const char *path);
+int hera_graph_load_cache(hera_ctx *ctx, const char *path);
 /* nodes_ / edges_ / nodes_[i].edges as flat host arrays. */
 int hera_graph_export(hera_ctx *ctx, hera_graph_view *out);
 

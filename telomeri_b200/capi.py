@@ -91,6 +91,8 @@ SIGNATURES = {
     "hera_graph_reset": (C.c_int, [C.c_void_p]),
     "hera_graph_finalize": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(GraphInfo)]),
     "hera_graph_export": (C.c_int, [C.c_void_p, C.POINTER(GraphView)]),
+    "hera_graph_save": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "hera_graph_load_cache": (C.c_int, [C.c_void_p, C.c_char_p]),
     "hera_paths_monte_carlo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PathParams), C.c_uint64, C.POINTER(WalkStats)]),
     "hera_paths_deterministic": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(WalkStats)]),
     "hera_paths_build": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(PathParams), C.c_uint64, C.POINTER(WalkStats)]),
@@ -237,6 +239,12 @@ class Hera:
         info = GraphInfo()
         self._check(self.lib.hera_graph_finalize(self.h, mask, C.byref(info)))
         return info
+
+    def save_graph(self, path):
+        self._check(self.lib.hera_graph_save(self.h, str(path).encode()))
+
+    def load_graph_cache(self, path):
+        self._check(self.lib.hera_graph_load_cache(self.h, str(path).encode()))
 
     def export_graph(self):
         v = GraphView()

@@ -147,6 +147,7 @@ static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind
     HERA_CUDA(cudaEventRecord(e0, c.stream));
     if (n) HERA_CUDA(cudaMemcpyAsync(t->bytes.p, src, n, kind, c.stream));
     HERA_CUDA(cudaEventRecord(e1, c.stream));
+    HERA_REQUIRE(!c.cache_loaded, 54, "this graph was restored from a cache: hera_graph_reset before loading PAF text");
     const uint32_t file_id = static_cast<uint32_t>(c.texts.size());
     HERA_REQUIRE(file_id < 16, 5, "more than 16 loads per graph are not supported");
     c.texts.push_back(std::move(t));
@@ -291,6 +292,7 @@ int hera_graph_reset(hera_ctx *ctx) {
     std::sort(c.text_pool.begin(), c.text_pool.end(), [](const auto &a, const auto &b) { return a->bytes.cap > b->bytes.cap; });
     if (c.text_pool.size() > 4) c.text_pool.resize(4);   // keep the largest few
     c.own_rows.clear();
+    c.cache_loaded = false;
     c.kept.n = 0;
     c.g.ready = false;
     c.g.N = c.g.E = c.g.S = c.g.anchors = 0;
@@ -300,6 +302,20 @@ int hera_graph_reset(hera_ctx *ctx) {
 int hera_graph_finalize(hera_ctx *ctx, uint32_t metrics_mask, hera_graph_info *out) {
     HERA_API_BEGIN(ctx)
     hera::finalize_graph(c, metrics_mask, out);
+    HERA_API_END
+}
+
+int hera_graph_save(hera_ctx *ctx, const char *path) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(path != nullptr, 101, "null path");
+    hera::save_graph_cache(c, path);
+    HERA_API_END
+}
+
+int hera_graph_load_cache(hera_ctx *ctx, const char *path) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(path != nullptr, 101, "null path");
+    hera::load_graph_cache(c, path);
     HERA_API_END
 }
 

@@ -116,6 +116,7 @@ struct Ctx {
     std::vector<std::unique_ptr<LoadedText>> texts;
     std::vector<std::unique_ptr<LoadedText>> text_pool;   // buffers of texts dropped by hera_graph_reset, reused by the next loads
     KeptTable kept;
+    bool cache_loaded = false;        // kept overlaps + node table came from hera_graph_load_cache: finalize skips K3
     std::vector<RowRange> own_rows;   // per load: the kept rows this rank parsed itself (their name references point into ITS texts)
     GraphTables g;
 
@@ -172,6 +173,8 @@ void maybe_flush_l2(Ctx &c);
 void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out);
 void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out);
 void export_graph(Ctx &c, hera_graph_view *out);
+void save_graph_cache(Ctx &c, const char *path);
+void load_graph_cache(Ctx &c, const char *path);
 void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);
 void walk_deterministic(Ctx &c, int metric, hera_walk_stats *out);
 void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);

@@ -13,6 +13,8 @@
 // radix sort by owner keeps record order inside each node's list, which is the reference's
 // insertion order.  Rank permutations restate the per-step stable_sort of the greedy walk
 // (src/PathManager.cpp:289-296); canon[] its first-parallel-edge lookup (:340-347).
+#include <cstdio>
+#include <cstring>
 #include <vector>
 
 #include "ctx.cuh"
@@ -296,10 +298,13 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
     for (auto &e : ev) HERA_CUDA(cudaEventCreate(&e));
     HERA_CUDA(cudaEventRecord(ev[0], c.stream));
     g.ready = false;
-    g.E = E; g.S = occ; g.N = 0; g.anchors = 0; g.max_deg = 0;
+    g.E = E; g.S = occ; g.anchors = 0; g.max_deg = 0;
+    if (!c.cache_loaded) g.N = 0;
     for (bool &r : g.rank_ready) r = false;
     float intern_ms = 0, csr_ms = 0, rank_ms = 0;
     if (E > 0) {
+        uint64_t N = 0;
+        if (!c.cache_loaded) {
         // ---- K3
         uint32_t *occ_slot = nullptr, *first_scan = nullptr, *d_small = nullptr;
         uint8_t *first = nullptr;
@@ -326,7 +331,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             HERA_CUDA(cudaFreeAsync(minpos, c.stream));
             cap <<= 2;  // table too full: probe chains get long, rebuild four times larger
         }
-        const uint64_t N = h_small[0];
+        N = h_small[0];
         g.N = N;
         HERA_CUDA(cudaMallocAsync(&slot_id, cap * sizeof(uint32_t), c.stream));
         HERA_LAUNCH(c, intern_first_flags_kernel, div_up(occ, 256), 256, 0, occ, occ_slot, minpos, first);
@@ -393,6 +398,22 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         HERA_CUDA(cudaFreeAsync(keys, c.stream)); HERA_CUDA(cudaFreeAsync(minpos, c.stream)); HERA_CUDA(cudaFreeAsync(slot_id, c.stream));
         HERA_CUDA(cudaFreeAsync(occ_slot, c.stream)); HERA_CUDA(cudaFreeAsync(first_scan, c.stream)); HERA_CUDA(cudaFreeAsync(first, c.stream));
         HERA_CUDA(cudaFreeAsync(d_small, c.stream));
+        } else {
+            // node table, e_q / e_t restored from a cache file (hera_graph_load_cache): only the anchor list is derived
+            N = g.N;
+            uint32_t *anchor_scan = nullptr, *d_cnt = nullptr;
+            HERA_CUDA(cudaMallocAsync(&anchor_scan, N * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMallocAsync(&d_cnt, sizeof(uint32_t), c.stream));
+            exclusive_scan_u8_to_u32(c, g.node_anchor.p, N, anchor_scan, d_cnt);
+            uint32_t h_cnt = 0;
+            HERA_CUDA(cudaMemcpyAsync(&h_cnt, d_cnt, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            g.anchors = h_cnt;
+            g.anchor_ids.reserve(g.anchors + 1);
+            HERA_LAUNCH(c, anchor_list_kernel, div_up(N, 256), 256, 0, N, g.node_anchor.p, anchor_scan, g.anchor_ids.p);
+            HERA_CUDA(cudaFreeAsync(anchor_scan, c.stream));
+            HERA_CUDA(cudaFreeAsync(d_cnt, c.stream));
+        }
         HERA_CUDA(cudaEventRecord(ev[1], c.stream));
 
         // ---- K4
@@ -523,6 +544,88 @@ void export_graph(Ctx &c, hera_graph_view *out) {
     out->adj_off = m.adj_off.p; out->adj_rec = m.adj_rec.p; out->adj_side = m.adj_side.p; out->canon = m.canon.p;
     out->rank_es = g.rank_ready[0] ? m.rank[0].p : nullptr; out->rank_os = g.rank_ready[1] ? m.rank[1].p : nullptr;
     out->rank_es_sqrt = g.rank_ready[2] ? m.rank[2].p : nullptr; out->rank_os_sqrt = g.rank_ready[3] ? m.rank[3].p : nullptr;
+}
+
+}  // namespace hera
+
+// ---- binary cache of the parsed graph (the reference has no such format) -----------
+// Everything K1-K3 produce: kept overlaps in file order with their node ids, and the node table.  A later
+// run with other walk parameters restores it and goes straight to K4 (CSR, ranks) -- the PAF text (42 GB at
+// configs[4], bound by host->device copy) is not read again.
+namespace hera {
+
+namespace {
+constexpr char CACHE_MAGIC[8] = {'H', 'E', 'R', 'A', 'K', 'E', 'P', '1'};
+struct CacheHeader {
+    char magic[8];
+    uint64_t E, N, name_bytes;
+    hera_filter_params fp;
+};
+
+template <typename T>
+void put_array(Ctx &c, FILE *f, const T *dev, uint64_t n, std::vector<char> &buf) {
+    buf.resize(n * sizeof(T));
+    if (n) {
+        HERA_CUDA(cudaMemcpyAsync(buf.data(), dev, n * sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        HERA_REQUIRE(fwrite(buf.data(), sizeof(T), n, f) == n, 50, "cache: short write");
+    }
+}
+
+template <typename T>
+void get_array(Ctx &c, FILE *f, DBuf<T> &dev, uint64_t n, std::vector<char> &buf) {
+    dev.reserve(n + 1);
+    buf.resize(n * sizeof(T));
+    if (n) {
+        HERA_REQUIRE(fread(buf.data(), sizeof(T), n, f) == n, 51, "cache: file is truncated");
+        HERA_CUDA(cudaMemcpyAsync(dev.p, buf.data(), n * sizeof(T), cudaMemcpyHostToDevice, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+    }
+}
+}  // namespace
+
+void save_graph_cache(Ctx &c, const char *path) {
+    GraphTables &g = c.g;
+    HERA_REQUIRE(g.ready, 7, "hera_graph_save: call hera_graph_finalize first");
+    FILE *f = fopen(path, "wb");
+    if (!f) throw Error{1, std::string("Cannot write file: ") + path};
+    struct Closer { FILE *f; ~Closer() { fclose(f); } } closer{f};
+    CacheHeader h{};
+    std::memcpy(h.magic, CACHE_MAGIC, 8);
+    h.E = g.E; h.N = g.N; h.name_bytes = g.name_bytes; h.fp = c.fp;
+    HERA_REQUIRE(fwrite(&h, sizeof(h), 1, f) == 1, 50, "cache: short write");
+    std::vector<char> buf;
+    KeptTable &k = c.kept;
+    put_array(c, f, k.qs.p, g.E, buf); put_array(c, f, k.qe.p, g.E, buf); put_array(c, f, k.ts.p, g.E, buf); put_array(c, f, k.te.p, g.E, buf);
+    put_array(c, f, k.qlen.p, g.E, buf); put_array(c, f, k.tlen.p, g.E, buf); put_array(c, f, k.rec.p, g.E, buf);
+    put_array(c, f, k.os.p, g.E, buf); put_array(c, f, k.si.p, g.E, buf); put_array(c, f, k.es.p, g.E, buf); put_array(c, f, k.flags.p, g.E, buf);
+    put_array(c, f, g.e_q.p, g.E, buf); put_array(c, f, g.e_t.p, g.E, buf);
+    put_array(c, f, g.node_len.p, g.N, buf); put_array(c, f, g.node_anchor.p, g.N, buf);
+    put_array(c, f, g.node_name_off.p, g.N + 1, buf); put_array(c, f, g.node_names.p, g.name_bytes, buf);
+}
+
+void load_graph_cache(Ctx &c, const char *path) {
+    FILE *f = fopen(path, "rb");
+    if (!f) throw Error{1, std::string("Cannot open file: ") + path};
+    struct Closer { FILE *f; ~Closer() { fclose(f); } } closer{f};
+    CacheHeader h{};
+    HERA_REQUIRE(fread(&h, sizeof(h), 1, f) == 1 && std::memcmp(h.magic, CACHE_MAGIC, 8) == 0, 52, "not a hera_b200 graph cache");
+    HERA_REQUIRE(c.kept.n == 0 && c.texts.empty(), 53, "hera_graph_load_cache needs a fresh graph (hera_graph_reset)");
+    GraphTables &g = c.g;
+    std::vector<char> buf;
+    KeptTable &k = c.kept;
+    const uint64_t E = h.E, N = h.N;
+    get_array(c, f, k.qs, E, buf); get_array(c, f, k.qe, E, buf); get_array(c, f, k.ts, E, buf); get_array(c, f, k.te, E, buf);
+    get_array(c, f, k.qlen, E, buf); get_array(c, f, k.tlen, E, buf); get_array(c, f, k.rec, E, buf);
+    get_array(c, f, k.os, E, buf); get_array(c, f, k.si, E, buf); get_array(c, f, k.es, E, buf); get_array(c, f, k.flags, E, buf);
+    get_array(c, f, g.e_q, E, buf); get_array(c, f, g.e_t, E, buf);
+    get_array(c, f, g.node_len, N, buf); get_array(c, f, g.node_anchor, N, buf);
+    get_array(c, f, g.node_name_off, N + 1, buf); get_array(c, f, g.node_names, h.name_bytes, buf);
+    k.n = E;
+    g.N = N; g.name_bytes = h.name_bytes;
+    c.fp = h.fp;
+    c.cache_loaded = true;
+    g.ready = false;
 }
 
 }  // namespace hera
