@@ -79,6 +79,8 @@ public:
 
     // ---- not in the reference: access for the other host classes
     hera_ctx *device() const { return ctx_; }
+    /** the context of the live OverlapGraph (one per process in main()), for Scaffolder */
+    static hera_ctx *current_device();
     /** slot index (adj_off[owner] + k) -> pointer to nodes_[owner].edges[k] */
     const Edge *edge_of_slot(uint32_t slot) const;
     uint32_t slot_of_edge(const Edge *e) const;

@@ -13,6 +13,8 @@
 
 #include "hera_b200.h"
 
+namespace { hera_ctx *g_current = nullptr; }
+
 namespace {
 [[noreturn]] void die(hera_ctx *ctx, const char *what) {
     std::cerr << what << ": " << hera_last_error(ctx) << std::endl;
@@ -23,6 +25,7 @@ namespace {
 OverlapGraph::OverlapGraph() : filter_params_{AVG, 0, 0.0f, ULONG_MAX, 1.0f}, ctx_(nullptr) {
     const char *dev = std::getenv("HERA_DEVICE");
     ctx_ = hera_create(dev ? std::atoi(dev) : 0);
+    g_current = ctx_;
     if (!ctx_) {
         // no CPU fallback: without the CUDA device the graph cannot be built at all
         std::cerr << "hera_b200: " << hera_last_error(nullptr) << std::endl;
@@ -30,7 +33,12 @@ OverlapGraph::OverlapGraph() : filter_params_{AVG, 0, 0.0f, ULONG_MAX, 1.0f}, ct
     }
 }
 
-OverlapGraph::~OverlapGraph() { hera_destroy(ctx_); }
+hera_ctx *OverlapGraph::current_device() { return g_current; }
+
+OverlapGraph::~OverlapGraph() {
+    if (g_current == ctx_) g_current = nullptr;
+    hera_destroy(ctx_);
+}
 
 bool OverlapGraph::load(char *filepath, bool anchors) {
     hera_filter_params fp{static_cast<int32_t>(filter_params_.mode), filter_params_.min_overlap_length, filter_params_.min_overlap_percentage,

@@ -2,6 +2,7 @@
 // filter and grouping (group_pairs_kernel) run on the GPU; this file keeps the host-side paths_
 // vector and the pointer maps of the reference interface consistent with the device tables.
 #include <PathManager.hpp>
+#include <Scaffolder.hpp>
 
 #include <cstdlib>
 #include <iostream>
@@ -167,6 +168,7 @@ Path PathManager::constructConsensusPath(
         const std::map<std::pair<const OverlapGraph::Node *, const OverlapGraph::Node *>, std::vector<const Path *>> &between,
         std::map<std::pair<const OverlapGraph::Node *, const OverlapGraph::Node *>, const Path *> &consensus, ulong min_path_num) {
     using Key = std::pair<const OverlapGraph::Node *, const OverlapGraph::Node *>;
+    Scaffolder::min_path_num_ = min_path_num;   // Scaffolder::write hands the same threshold to hera_scaffold
     std::map<Key, std::pair<const Path *, ulong>> pool;
     std::vector<const OverlapGraph::Node *> anchors;
     ulong best = 0;

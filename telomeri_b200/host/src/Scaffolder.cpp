@@ -3,14 +3,33 @@
 // reversal on relative_strand, trimming when the next overlap starts before the previous one ends,
 // one global reverse at the end) are the reference's, restated.
 #include <Scaffolder.hpp>
+#include <OverlapGraph.hpp>
+
+#include "hera_b200.h"
 
 #include <algorithm>
 #include <cstring>
 #include <fstream>
 #include <iostream>
 #include <sstream>
+#include <stdexcept>
+
+unsigned long Scaffolder::min_path_num_ = 10;
 
 bool Scaffolder::load(const char *filename) {
+    files_.emplace_back(filename);
+    if (OverlapGraph::current_device()) {   // parsed on the GPU by write(); only check that it can be read
+        std::ifstream probe(filename);
+        if (!probe) {
+            std::cerr << "Cannot open file: " << filename << std::endl;
+            return false;
+        }
+        return true;
+    }
+    return load_host(filename);
+}
+
+bool Scaffolder::load_host(const char *filename) {
     const size_t n = std::strlen(filename);
     const bool fastq = n > 0 && filename[n - 1] == 'q';
     std::ifstream in(filename);
@@ -57,6 +76,29 @@ void Scaffolder::swapBases(std::string &str) {
 }
 
 bool Scaffolder::write(const char *filename) {
+    hera_ctx *ctx = OverlapGraph::current_device();
+    if (ctx && files_.size() == 2 && p_.nodes_.size() >= 2) {
+        hera_scaffold_view v{};
+        const int rc = hera_scaffold(ctx, files_[0].c_str(), files_[1].c_str(), min_path_num_, &v);
+        // the reference dies of std::out_of_range here (substr / vector::at): keep that observable behaviour
+        if (rc == 44 || rc == 45) throw std::out_of_range(hera_last_error(ctx));
+        bool same = rc == 0 && v.nodes == p_.nodes_.size();
+        for (uint64_t i = 0; same && i < v.nodes; i++) same = v.node[i] == p_.nodes_[i]->index;
+        if (rc != 0 || !same) {
+            std::cerr << "hera_scaffold: " << (rc ? hera_last_error(ctx) : "the library's chain of consensus paths differs from the given path") << std::endl;
+            return false;
+        }
+        std::ofstream out(filename, std::ios::binary);
+        if (!out) {
+            std::cerr << "Cannot write file: " << filename << std::endl;
+            return false;
+        }
+        for (uint64_t i = 0; i < v.logged; i++) std::cout << (i ? "-" : "") << p_.nodes_[v.logged_index[i]]->name;
+        std::cout << std::endl;
+        out.write(v.fasta, static_cast<std::streamsize>(v.fasta_bytes));
+        return true;
+    }
+    if (names_.empty()) for (const std::string &f : files_) if (!load_host(f.c_str())) return false;   // files were only probed by load()
     std::ofstream out(filename);
     if (!out) {
         std::cerr << "Cannot write file: " << filename << std::endl;
