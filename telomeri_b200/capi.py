@@ -7,7 +7,10 @@ from pathlib import Path
 import numpy as np
 
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libhera_b200.so"
+import os as _os
+
+# HERA_B200_LIB: a differently built copy of the same library (kernel tuning experiments)
+LIB_PATH = Path(_os.environ.get("HERA_B200_LIB") or PKG / "libhera_b200.so")
 
 MODE = {"min": 0, "max": 1, "avg": 2, "sum": 3}
 METRIC = {"es": 0, "os": 1, "es_sqrt": 2, "os_sqrt": 3}

@@ -31,12 +31,23 @@
 
 namespace hera {
 
-constexpr int PF_THREADS = 256;
-constexpr int PF_TILE = 24576;
+#ifndef PF_MIN_CTAS_D
+#define PF_MIN_CTAS_D 4
+#endif
+#ifndef PF_TILE_D
+#define PF_TILE_D 24576
+#endif
+#ifndef PF_THREADS_D
+#define PF_THREADS_D 256
+#endif
+constexpr int PF_THREADS = PF_THREADS_D;
+constexpr int PF_MIN_CTAS = PF_MIN_CTAS_D;
+constexpr int PF_TILE = PF_TILE_D;
 constexpr int PF_HALO = 1024;
 constexpr int PF_WIN = PF_TILE + PF_HALO;
 constexpr int PF_CHUNKS = PF_WIN / 16;
-constexpr int PF_CPT = (PF_TILE / 16 + PF_THREADS - 1) / PF_THREADS;   // tile chunks owned by one thread
+constexpr int PF_WPT = PF_TILE / 32 / PF_THREADS;   // 32-byte mask words owned by one thread
+static_assert(PF_WPT * 32 * PF_THREADS == PF_TILE, "tile = threads x whole mask words");
 constexpr int PF_MAXREC = PF_TILE / 32 + 2;   // a record is at least 16 tokens + 16 separators
 
 struct FilterDev {
@@ -286,7 +297,7 @@ struct ParseArgs {
 
 // Exact reader for a record that does not fit the shared-memory window (very long names).
 // Returns 1 = regular record in r, 0 = irregular (the tail kernel will deal with it).
-__device__ int slow_path_record(const ParseArgs &a, uint64_t start, SerialRecord &r) {
+__device__ __noinline__ int slow_path_record(const ParseArgs &a, uint64_t start, SerialRecord &r) {
     SerialCursor cur{a.text, a.n, start, true};
     if (!serial_read_record(cur, r)) return 0;
     // regular iff every typed token ended at white space
@@ -306,7 +317,7 @@ __device__ int slow_path_record(const ParseArgs &a, uint64_t start, SerialRecord
 // text words are read whole and shifted into place -- no per-byte loops on the regular path.
 
 // First position >= p whose mask bit equals `one`; >= PF_WIN when the window has none.
-__device__ __forceinline__ uint32_t next_bit(const uint32_t *mask, uint32_t p, bool one) {
+__device__ __noinline__ uint32_t next_bit(const uint32_t *mask, uint32_t p, bool one) {
     while (p < PF_WIN) {
         const uint32_t w = p >> 5;
         uint32_t win = __funnelshift_r(mask[w], mask[w + 1], p & 31u);
@@ -338,83 +349,105 @@ __device__ __forceinline__ uint64_t hash_name_window(const uint8_t *s, uint32_t 
 // Four ASCII digits (first character in the low byte, already XORed with '0') -> value.
 __device__ __forceinline__ uint32_t digits4(uint32_t d) {
     const uint32_t t = ((d * 2561u) >> 8) & 0x00ff00ffu;        // b0*10+b1 | b2*10+b3
-    return ((t * 6553601u) >> 16) & 0xffffu;
+    return (t * 6553601u) >> 16;                                // the product's upper half is (b0*10+b1)*100 + b2*10+b3
 }
 
-// Integer token [b, e): [+-]?digits within int range.  Returns false when formatted extraction would
-// fail or stop early on it (the caller declares the record irregular).
-__device__ __forceinline__ bool int_token(const uint8_t *s, uint32_t b, uint32_t e, int &out) {
-    uint32_t c0 = s[b];
+// Integer token [b, e), general form: [+-]?digits within int range.  Returns false when formatted extraction
+// would fail or stop early on it (the caller declares the record irregular).
+constexpr long long INT_TOKEN_BAD = 1ll << 40;
+// (result by value: an out-parameter of a non-inlined call would force the caller's fields into local memory)
+__device__ __noinline__ long long int_token_slow(const uint8_t *s, uint32_t b, uint32_t e) {
+    const uint32_t c0 = s[b];
     const bool neg = c0 == '-';
     if (neg || c0 == '+') b++;
-    const uint32_t len = e - b;
-    if (len - 1u <= 7u) {   // 1..8 digits: the eight bytes that END at e, leading bytes masked off
-        const uint32_t q = e + 8u;                 // s - 16 is readable, so (e - 8) never underflows the buffer
-        const uint32_t *wp = reinterpret_cast<const uint32_t *>(s - 16) + (q >> 2);
-        const uint32_t sh = (q & 3u) * 8u;
-        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
-        uint32_t lo = __funnelshift_r(w0, w1, sh) ^ 0x30303030u;   // characters e-8 .. e-5
-        uint32_t hi = __funnelshift_r(w1, w2, sh) ^ 0x30303030u;   // characters e-4 .. e-1
-        const uint32_t keep_hi = len >= 4 ? 0xffffffffu : (0xffffffffu << ((4u - len) * 8u));
-        const uint32_t keep_lo = len <= 4 ? 0u : (len == 8 ? 0xffffffffu : (0xffffffffu << ((8u - len) * 8u)));
-        lo &= keep_lo;
-        hi &= keep_hi;
-        // every kept byte must be 0..9
-        if ((((lo + 0x76767676u) | lo) | ((hi + 0x76767676u) | hi)) & 0x80808080u) return false;
-        const uint32_t v = digits4(lo) * 10000u + digits4(hi);
-        out = neg ? -static_cast<int>(v) : static_cast<int>(v);
-        return true;
-    }
-    if (len == 0) return false;
-    unsigned long long acc = 0;   // long tokens (leading zeros, values near INT_MAX): plain loop
+    if (e <= b) return INT_TOKEN_BAD;
+    unsigned long long acc = 0;
     for (uint32_t i = b; i < e; i++) {
         const uint32_t d = static_cast<uint32_t>(s[i]) - '0';
-        if (d > 9u) return false;
+        if (d > 9u) return INT_TOKEN_BAD;
         if (acc <= 4294967295ull) acc = acc * 10 + d;
     }
-    if (acc > (neg ? 2147483648ull : 2147483647ull)) return false;
-    out = neg ? static_cast<int>(0u - static_cast<uint32_t>(acc)) : static_cast<int>(static_cast<uint32_t>(acc));
+    if (acc > (neg ? 2147483648ull : 2147483647ull)) return INT_TOKEN_BAD;
+    return neg ? -static_cast<long long>(acc) : static_cast<long long>(acc);
+}
+
+// Integer token [b, e).  Fast path: one to eight digits, read as the eight bytes that END at e (three aligned
+// words, funnel-shifted), bytes before b cleared, all remaining bytes checked to be digits, then two
+// four-digit conversions.  Signs, longer tokens and anything that is not a digit go to int_token_slow.
+__device__ __forceinline__ bool int_token(const uint8_t *s, uint32_t b, uint32_t e, int &out) {
+    const uint32_t len = e - b;
+    const uint32_t q = e + 8u;                 // s - 16 is readable, so (e - 8) never underflows the buffer
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(s - 16) + (q >> 2);
+    const uint32_t sh = (q & 3u) * 8u;
+    const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+    const uint32_t drop = (8u - len) * 8u;     // bits of the eight-byte window that belong to earlier text
+    const uint32_t keep_lo = __funnelshift_lc(0u, 0xffffffffu, drop);                                      // drop >= 32: nothing kept
+    const uint32_t keep_hi = __funnelshift_lc(0u, 0xffffffffu, static_cast<uint32_t>(max(static_cast<int>(drop) - 32, 0)));
+    const uint32_t lo = (__funnelshift_r(w0, w1, sh) ^ 0x30303030u) & keep_lo;   // characters e-8 .. e-5
+    const uint32_t hi = (__funnelshift_r(w1, w2, sh) ^ 0x30303030u) & keep_hi;   // characters e-4 .. e-1
+    const uint32_t not_digit = (((lo + 0x76767676u) | lo) | ((hi + 0x76767676u) | hi)) & 0x80808080u;
+    if (len - 1u > 7u || not_digit) {
+        const long long v = int_token_slow(s, b, e);
+        out = static_cast<int>(v);
+        return v != INT_TOKEN_BAD;
+    }
+    out = static_cast<int>(digits4(lo) * 10000u + digits4(hi));
     return true;
 }
 
-// One thread reads one record from the staged window.  Returns the keep flag.
+// Span of the token that starts at b (a set mask bit, or PF_WIN when the window is used up): e = its end,
+// nb = start of the next token.  One 32-bit window of the mask usually holds both.  Everything stays <= PF_WIN
+// (the mask is zero behind the window), so a record that runs out of window just yields empty tokens.
+__device__ __forceinline__ void token_span(const uint32_t *mask, uint32_t b, uint32_t &e, uint32_t &nb) {
+    const uint32_t w = b >> 5;
+    const uint32_t win = __funnelshift_r(mask[w], mask[w + 1], b & 31u);
+    const uint32_t zeros = ~win;
+    if (zeros) {
+        const uint32_t eo = __ffs(zeros) - 1;
+        e = b + eo;
+        const uint32_t ones = win & (0xffffffffu << eo);
+        nb = ones ? b + __ffs(ones) - 1 : next_bit(mask, b + 32, true);
+    } else {
+        e = next_bit(mask, b + 32, false);
+        nb = next_bit(mask, e, true);
+    }
+}
+
+// One thread reads one record from the staged window: twelve tokens in straight-line code (fields stay in
+// registers).  A token that is not what formatted extraction expects makes the record irregular, unless the
+// window ran out first (then the exact reader decides).  Returns the keep flag.
 __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, const uint32_t *mask, uint32_t p0, uint64_t tile_byte0,
                                           bool reaches_eof, uint64_t rec_idx, StagedRecord &out) {
     if (rec_idx >= a.rec_limit) return false;
     SerialRecord r;
-    int status = 1;  // 1 regular, 0 irregular, 2 window exhausted
-    uint32_t b = p0, e;
-    int ints[9];
-#pragma unroll
-    uint32_t nb = 0;   // start of the next token
-    for (int f = 0; f < 12; f++) {
-        if (status != 1) break;
-        if (f) b = nb;
-        if (b >= PF_WIN) { status = 2; break; }
-        {   // one 32-bit window usually holds the end of this token and the start of the next
-            const uint32_t w = b >> 5;
-            const uint32_t win = __funnelshift_r(mask[w], mask[w + 1], b & 31u);
-            const uint32_t zeros = ~win;
-            if (zeros) {
-                const uint32_t eo = __ffs(zeros) - 1;
-                e = b + eo;
-                const uint32_t ones = win & (0xffffffffu << eo);
-                nb = ones ? b + __ffs(ones) - 1 : next_bit(mask, b + 32, true);
-            } else {
-                e = next_bit(mask, b + 32, false);
-                nb = next_bit(mask, e, true);
-            }
-        }
-        if (e >= PF_WIN) { status = 2; break; }
-        if (f == 0) { r.qoff = tile_byte0 + b; r.qnlen = e - b; r.qhash = hash_name_window(s, b, e); }
-        else if (f == 5) { r.toff = tile_byte0 + b; r.tnlen = e - b; r.thash = hash_name_window(s, b, e); }
-        else if (f == 4) { r.strand = s[b]; if (e - b != 1) status = 0; }
-        else if (!int_token(s, b, e, ints[f < 4 ? f - 1 : f - 3])) status = 0;
-    }
-    r.qlen = ints[0]; r.qs = ints[1]; r.qe = ints[2]; r.tlen = ints[3]; r.ts = ints[4]; r.te = ints[5]; r.matches = ints[6];
-    if (status == 2) {
+    uint32_t b = p0, e, nb;
+    bool bad = false;
+    auto int_field = [&](int &v) {
+        b = nb;
+        token_span(mask, b, e, nb);
+        const bool ok = int_token(s, b, e, v);
+        bad |= !ok && e < PF_WIN;
+    };
+    token_span(mask, b, e, nb);
+    const uint32_t qb = b, qe = e;
+    int_field(r.qlen); int_field(r.qs); int_field(r.qe);
+    b = nb;
+    token_span(mask, b, e, nb);
+    r.strand = s[b];
+    bad |= (e - b != 1u) && e < PF_WIN;
+    b = nb;
+    token_span(mask, b, e, nb);
+    const uint32_t tb = b, te = e;
+    int_field(r.tlen); int_field(r.ts); int_field(r.te); int_field(r.matches); int_field(r.block); int_field(r.mapq);
+    int status = bad ? 0 : (e >= PF_WIN ? 2 : 1);   // 1 regular, 0 irregular, 2 window exhausted
+    if (status == 1) {
+        r.qoff = tile_byte0 + qb; r.qnlen = qe - qb; r.qhash = hash_name_window(s, qb, qe);
+        r.toff = tile_byte0 + tb; r.tnlen = te - tb; r.thash = hash_name_window(s, tb, te);
+    } else if (status == 2) {
         if (reaches_eof) return false;  // trailing record with fewer than 12 tokens: not a record
-        status = slow_path_record(a, tile_byte0 + p0, r);
+        SerialRecord exact;   // (its address goes to a non-inlined call: keep it apart from r, which lives in registers)
+        status = slow_path_record(a, tile_byte0 + p0, exact);
+        r = exact;
     }
     if (status == 0) {
         atomicMin(&a.ctr->first_bad_rec, static_cast<unsigned long long>(rec_idx));
@@ -424,13 +457,14 @@ __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, 
     return make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), out);
 }
 
-// Position of the k-th (0-based) set bit of a 16-bit mask that has more than k bits set.
-__device__ __forceinline__ uint32_t select_bit16(uint32_t m, uint32_t k) {
+// Position of the k-th (0-based) set bit of a mask that has more than k bits set.
+__device__ __forceinline__ uint32_t select_bit32(uint32_t m, uint32_t k) {
     uint32_t pos = 0, c;
-    c = __popc(m & 0xffu); if (k >= c) { k -= c; pos = 8; m >>= 8; }
-    c = __popc(m & 0xfu);  if (k >= c) { k -= c; pos += 4; m >>= 4; }
-    c = __popc(m & 0x3u);  if (k >= c) { k -= c; pos += 2; m >>= 2; }
-    c = m & 1u;            if (k >= c) pos += 1;
+    c = __popc(m & 0xffffu); if (k >= c) { k -= c; pos = 16; m >>= 16; }
+    c = __popc(m & 0xffu);   if (k >= c) { k -= c; pos += 8; m >>= 8; }
+    c = __popc(m & 0xfu);    if (k >= c) { k -= c; pos += 4; m >>= 4; }
+    c = __popc(m & 0x3u);    if (k >= c) { k -= c; pos += 2; m >>= 2; }
+    c = m & 1u;              if (k >= c) pos += 1;
     return pos;
 }
 
@@ -445,7 +479,7 @@ __device__ __forceinline__ uint32_t nonspace4(uint32_t w) {
     return (((ns >> 7) * 0x00204081u) >> 21) & 0xfu;
 }
 
-__global__ void __launch_bounds__(PF_THREADS, 4) paf_parse_kernel(const ParseArgs a) {
+__global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(const ParseArgs a) {
     // text window with 16 spare bytes on both sides (the field readers load whole words around a token)
     __shared__ __align__(16) uint8_t s_raw[PF_WIN + 32];
     // non-space bit per byte: chunk ch at s_nonws[ch + 2] (so that 32-byte units are aligned words),
@@ -480,21 +514,27 @@ __global__ void __launch_bounds__(PF_THREADS, 4) paf_parse_kernel(const ParseArg
     }
     __syncthreads();
 
-    // 2. token starts of the chunks this thread owns (consecutive chunks, so thread order = text order)
-    uint32_t my_mask[PF_CPT];
+    // 2. token starts of the PF_WPT mask words (32 bytes each) this thread owns: consecutive, so thread order = text order
+    const uint32_t *mask = reinterpret_cast<const uint32_t *>(s_nonws) + 1;   // word i = bytes [32 i, 32 i + 32) of the window
+    uint32_t my_starts[PF_WPT];
     uint32_t my_tokens = 0;
+    {
+        uint32_t carry = mask[static_cast<int>(tid * PF_WPT) - 1] >> 31;   // is the byte before my stretch part of a token?
 #pragma unroll
-    for (int k = 0; k < PF_CPT; k++) {
-        const int ch = tid * PF_CPT + k;
-        uint32_t starts = 0;
-        if (ch < PF_TILE / 16) {
-            const uint32_t cur = s_nonws[ch + 2];
-            starts = cur & ~((cur << 1) | ((s_nonws[ch + 1] >> 15) & 1u)) & 0xffffu;
-            const uint64_t b0 = tile_byte0 + static_cast<uint64_t>(ch) * 16;
-            if (b0 + 16 > a.owned) starts = b0 >= a.owned ? 0u : (starts & ((1u << static_cast<uint32_t>(a.owned - b0)) - 1u));
+        for (int k = 0; k < PF_WPT; k++) {
+            const uint32_t m = mask[tid * PF_WPT + k];
+            my_starts[k] = m & ~((m << 1) | carry);
+            carry = m >> 31;
         }
-        my_mask[k] = starts;
-        my_tokens += __popc(starts);
+        if (tile_byte0 + PF_TILE > a.owned) {   // only the tile that holds the end of this rank's byte range
+#pragma unroll
+            for (int k = 0; k < PF_WPT; k++) {
+                const uint64_t b0 = tile_byte0 + static_cast<uint64_t>(tid * PF_WPT + k) * 32;
+                if (b0 + 32 > a.owned) my_starts[k] = b0 >= a.owned ? 0u : (my_starts[k] & ((1u << static_cast<uint32_t>(a.owned - b0)) - 1u));
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < PF_WPT; k++) my_tokens += __popc(my_starts[k]);
     }
     uint32_t tile_tokens;
     const uint32_t excl = block_exclusive_scan<uint32_t>(my_tokens, s_scan, &tile_tokens);
@@ -511,19 +551,15 @@ __global__ void __launch_bounds__(PF_THREADS, 4) paf_parse_kernel(const ParseArg
     const uint32_t nrec = tile_tokens > first_rec_ord ? (tile_tokens - first_rec_ord + 15) / 16 : 0;  // records starting in this tile
     const bool reaches_eof = a.at_eof && tile_byte0 + PF_WIN >= a.n;
 
-    // 3. every 16th token opens a record: note its offset
-    {
-        uint32_t o = excl;
+    // 3. every 16th token opens a record: note its offset (a stretch of 32 PF_WPT bytes rarely holds more than one)
+    for (uint32_t ord = static_cast<uint32_t>((16 - ((tok_base + excl) & 15)) & 15); ord < my_tokens; ord += 16) {
+        uint32_t r = ord, word = my_starts[0], k = 0;
 #pragma unroll
-        for (int k = 0; k < PF_CPT; k++) {
-            const uint32_t cnt = __popc(my_mask[k]);
-            const uint32_t rem = static_cast<uint32_t>((16 - ((tok_base + o) & 15)) & 15);
-            if (rem < cnt) {  // a 16-byte chunk holds at most 8 token starts, so at most one record start
-                const uint32_t bit = select_bit16(my_mask[k], rem);
-                s_rec_off[(o + rem - first_rec_ord) >> 4] = static_cast<uint16_t>((tid * PF_CPT + k) * 16 + bit);
-            }
-            o += cnt;
+        for (int j = 1; j < PF_WPT; j++) {
+            const uint32_t cnt = __popc(my_starts[j - 1]);
+            if (k == static_cast<uint32_t>(j - 1) && r >= cnt) { r -= cnt; word = my_starts[j]; k = j; }
         }
+        s_rec_off[(excl + ord - first_rec_ord) >> 4] = static_cast<uint16_t>((tid * PF_WPT + k) * 32 + select_bit32(word, r));
     }
     __syncthreads();
 
@@ -537,7 +573,7 @@ __global__ void __launch_bounds__(PF_THREADS, 4) paf_parse_kernel(const ParseArg
         const uint32_t j = b0 + tid;
         StagedRecord r;
         bool keep = false;
-        if (j < nrec) keep = parse_one(a, s_text, reinterpret_cast<const uint32_t *>(s_nonws) + 1, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+        if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
         uint32_t tot;
         const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
         if (b0 == 0) { mine = r; keep0 = keep; e0 = ex; tot0 = tot; }
@@ -558,7 +594,7 @@ __global__ void __launch_bounds__(PF_THREADS, 4) paf_parse_kernel(const ParseArg
         const uint32_t j = b0 + tid;
         StagedRecord r;
         bool keep = false;
-        if (j < nrec) keep = parse_one(a, s_text, reinterpret_cast<const uint32_t *>(s_nonws) + 1, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+        if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
         uint32_t tot;
         const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
         if (keep) store_record(a.kept, out0 + run + ex, r);
