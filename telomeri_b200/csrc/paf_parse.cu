@@ -32,13 +32,13 @@
 namespace hera {
 
 #ifndef PF_MIN_CTAS_D
-#define PF_MIN_CTAS_D 4
+#define PF_MIN_CTAS_D 3
 #endif
 #ifndef PF_TILE_D
-#define PF_TILE_D 24576
+#define PF_TILE_D 30720
 #endif
 #ifndef PF_THREADS_D
-#define PF_THREADS_D 256
+#define PF_THREADS_D 320
 #endif
 constexpr int PF_THREADS = PF_THREADS_D;
 constexpr int PF_MIN_CTAS = PF_MIN_CTAS_D;
@@ -247,15 +247,16 @@ __device__ __forceinline__ void st_state(unsigned long long *p, unsigned long lo
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// Called by warp 0.  Publishes this tile's aggregate, walks back over earlier tiles, publishes
-// the inclusive prefix and returns the exclusive prefix (same value in every lane).
-__device__ unsigned long long chain_exclusive(unsigned long long *state, unsigned int tile, unsigned long long aggregate) {
+// The chain is used in two steps so that a tile never has to wait: chain_publish makes the tile's aggregate
+// visible as soon as it is known; chain_resolve, called (by warp 0) after the CTA has done other work, walks
+// back over earlier tiles until it meets an inclusive prefix, publishes this tile's inclusive prefix and
+// returns the exclusive one (same value in every lane).
+__device__ __forceinline__ void chain_publish(unsigned long long *state, unsigned int tile, unsigned long long aggregate) {
+    st_state(&state[tile], (tile == 0 ? ST_INC : ST_AGG) | aggregate);
+}
+__device__ unsigned long long chain_resolve(unsigned long long *state, unsigned int tile, unsigned long long aggregate) {
     const uint32_t lane = lane_id();
-    if (tile == 0) {
-        if (lane == 0) st_state(&state[0], ST_INC | aggregate);
-        return 0;
-    }
-    if (lane == 0) st_state(&state[tile], ST_AGG | aggregate);
+    if (tile == 0) return 0;
     unsigned long long excl = 0;
     int look = static_cast<int>(tile) - 1;
     for (;;) {
@@ -479,126 +480,240 @@ __device__ __forceinline__ uint32_t nonspace4(uint32_t w) {
     return (((ns >> 7) * 0x00204081u) >> 21) & 0xfu;
 }
 
-__global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(const ParseArgs a) {
-    // text window with 16 spare bytes on both sides (the field readers load whole words around a token)
-    __shared__ __align__(16) uint8_t s_raw[PF_WIN + 32];
-    // non-space bit per byte: chunk ch at s_nonws[ch + 2] (so that 32-byte units are aligned words),
-    // bit 15 of s_nonws[1] = the byte before the tile; two zero words of padding behind the window
-    __shared__ __align__(8) uint16_t s_nonws[PF_CHUNKS + 2 + 4];
-    uint8_t *s_text = s_raw + 16;
-    __shared__ uint16_t s_rec_off[PF_MAXREC];
-    __shared__ uint32_t s_scan[33];
-    __shared__ unsigned int s_tile;
-    __shared__ unsigned long long s_tok_base, s_kept_base;
+// Shared memory of one staged tile: text window with 16 spare bytes on both sides (the field readers load whole
+// words around a token), then the non-space bit per byte: chunk ch at nonws[ch + 2] (so that 32-byte units are
+// aligned words), bit 15 of nonws[1] = the byte before the tile, two zero words of padding behind the window.
+constexpr int PF_RAW_BYTES = PF_WIN + 32;
+constexpr int PF_BUF_BYTES = (PF_RAW_BYTES + (PF_CHUNKS + 2 + 4) * 2 + 15) / 16 * 16;
+constexpr int PF_SMEM_BYTES = 2 * PF_BUF_BYTES;
+static_assert(PF_RAW_BYTES % 16 == 0, "mask words must stay aligned");
 
-    const uint32_t tid = threadIdx.x, lane = lane_id(), warp = warp_id();
-    if (tid == 0) s_tile = atomicAdd(&a.ctr->ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = s_tile;
+struct TileView {
+    uint8_t *raw;        // PF_RAW_BYTES
+    uint16_t *nonws;     // PF_CHUNKS + 6
+    __device__ __forceinline__ uint8_t *text() const { return raw + 16; }
+    __device__ __forceinline__ const uint32_t *mask() const { return reinterpret_cast<const uint32_t *>(nonws) + 1; }  // word i = bytes [32 i, 32 i + 32)
+};
+
+// Token starts of the PF_WPT mask words (32 bytes each) thread tid owns: consecutive, so thread order = text order.
+__device__ __forceinline__ uint32_t token_starts(const ParseArgs &a, const uint32_t *mask, uint64_t tile_byte0, uint32_t tid, uint32_t (&starts)[PF_WPT]) {
+    uint32_t carry = mask[static_cast<int>(tid * PF_WPT) - 1] >> 31;   // is the byte before my stretch part of a token?
+#pragma unroll
+    for (int k = 0; k < PF_WPT; k++) {
+        const uint32_t m = mask[tid * PF_WPT + k];
+        starts[k] = m & ~((m << 1) | carry);
+        carry = m >> 31;
+    }
+    if (tile_byte0 + PF_TILE > a.owned) {   // only the tile that holds the end of this rank's byte range
+#pragma unroll
+        for (int k = 0; k < PF_WPT; k++) {
+            const uint64_t b0 = tile_byte0 + static_cast<uint64_t>(tid * PF_WPT + k) * 32;
+            if (b0 + 32 > a.owned) starts[k] = b0 >= a.owned ? 0u : (starts[k] & ((1u << static_cast<uint32_t>(a.owned - b0)) - 1u));
+        }
+    }
+    uint32_t n = 0;
+#pragma unroll
+    for (int k = 0; k < PF_WPT; k++) n += __popc(starts[k]);
+    return n;
+}
+
+// Stage A of a tile, first half: asynchronous 16-byte copies of tile + halo into shared memory (the data is
+// looked at later, after the CTA has done other work).
+__device__ __forceinline__ void stage_issue(const ParseArgs &a, uint32_t tile, const TileView &tv) {
+    const uint8_t *src = a.text + static_cast<uint64_t>(tile) * PF_TILE;
+    const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(tv.text()));
+    for (int ch = threadIdx.x; ch < PF_CHUNKS; ch += PF_THREADS)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + ch * 16), "l"(src + static_cast<size_t>(ch) * 16) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// Second half: byte classification (every thread reads back the chunks it copied), token count; the count is
+// published to the first chain right away (nobody waits here).  Called by the whole CTA.
+__device__ __forceinline__ void stage_finish(const ParseArgs &a, uint32_t tile, const TileView &tv, uint16_t *s_excl, uint32_t *s_scan, uint32_t *s_tokens) {
+    const uint32_t tid = threadIdx.x;
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
-
-    // 1. stage tile + halo with 128-bit loads, classify bytes
-    const uint4 *src = reinterpret_cast<const uint4 *>(a.text + tile_byte0);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    const uint8_t *s_text = tv.text();
 #pragma unroll 2
     for (int ch = tid; ch < PF_CHUNKS; ch += PF_THREADS) {
-        const uint4 v = __ldg(src + ch);
-        reinterpret_cast<uint4 *>(s_text)[ch] = v;
-        s_nonws[ch + 2] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
+        const uint4 v = reinterpret_cast<const uint4 *>(s_text)[ch];
+        tv.nonws[ch + 2] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
     }
     if (tid == 0) {
         uint32_t prev_nonws = a.prev_nonws ? 1u : 0u;  // does the byte before the tile belong to a token?
         if (tile_byte0 > 0) prev_nonws = dev_is_space(a.text[tile_byte0 - 1]) ? 0u : 1u;
-        s_nonws[1] = static_cast<uint16_t>(prev_nonws << 15);
-        for (int k = 0; k < 4; k++) s_nonws[PF_CHUNKS + 2 + k] = 0;
-        for (int k = 0; k < 4; k++) { reinterpret_cast<uint32_t *>(s_raw)[k] = 0x20202020u; reinterpret_cast<uint32_t *>(s_raw + 16 + PF_WIN)[k] = 0x20202020u; }
+        tv.nonws[1] = static_cast<uint16_t>(prev_nonws << 15);
+        for (int k = 0; k < 4; k++) tv.nonws[PF_CHUNKS + 2 + k] = 0;
+        for (int k = 0; k < 4; k++) { reinterpret_cast<uint32_t *>(tv.raw)[k] = 0x20202020u; reinterpret_cast<uint32_t *>(tv.raw + 16 + PF_WIN)[k] = 0x20202020u; }
     }
     __syncthreads();
-
-    // 2. token starts of the PF_WPT mask words (32 bytes each) this thread owns: consecutive, so thread order = text order
-    const uint32_t *mask = reinterpret_cast<const uint32_t *>(s_nonws) + 1;   // word i = bytes [32 i, 32 i + 32) of the window
-    uint32_t my_starts[PF_WPT];
-    uint32_t my_tokens = 0;
-    {
-        uint32_t carry = mask[static_cast<int>(tid * PF_WPT) - 1] >> 31;   // is the byte before my stretch part of a token?
-#pragma unroll
-        for (int k = 0; k < PF_WPT; k++) {
-            const uint32_t m = mask[tid * PF_WPT + k];
-            my_starts[k] = m & ~((m << 1) | carry);
-            carry = m >> 31;
-        }
-        if (tile_byte0 + PF_TILE > a.owned) {   // only the tile that holds the end of this rank's byte range
-#pragma unroll
-            for (int k = 0; k < PF_WPT; k++) {
-                const uint64_t b0 = tile_byte0 + static_cast<uint64_t>(tid * PF_WPT + k) * 32;
-                if (b0 + 32 > a.owned) my_starts[k] = b0 >= a.owned ? 0u : (my_starts[k] & ((1u << static_cast<uint32_t>(a.owned - b0)) - 1u));
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < PF_WPT; k++) my_tokens += __popc(my_starts[k]);
-    }
+    uint32_t starts[PF_WPT];
+    const uint32_t my_tokens = token_starts(a, tv.mask(), tile_byte0, tid, starts);
     uint32_t tile_tokens;
     const uint32_t excl = block_exclusive_scan<uint32_t>(my_tokens, s_scan, &tile_tokens);
-    if (warp == 0) {  // first chain: global index of the tile's first token
-        const unsigned long long base = chain_exclusive(a.tok_state, tile, tile_tokens);
-        if (lane == 0) {
-            s_tok_base = base;
+    s_excl[tid] = static_cast<uint16_t>(excl);
+    if (tid == 0) {
+        *s_tokens = tile_tokens;
+        chain_publish(a.tok_state, tile, tile_tokens);
+    }
+}
+
+struct TileFrame {   // what the record stage needs to know about a staged tile (same in every thread)
+    unsigned long long tok_base;
+    uint32_t first_rec_ord, nrec;
+};
+
+// Stage B + C of a tile: look up chain 1 (global index of the tile's first token), then note the offset of every
+// record that starts in the tile (every 16th token).  Called by the whole CTA.
+__device__ __forceinline__ TileFrame frame_tile(const ParseArgs &a, uint32_t tile, const TileView &tv, const uint16_t *s_excl, uint32_t tile_tokens,
+                                                unsigned long long *s_base, uint16_t *s_rec_off) {
+    const uint32_t tid = threadIdx.x;
+    const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
+    if (warp_id() == 0) {
+        const unsigned long long base = chain_resolve(a.tok_state, tile, tile_tokens);
+        if (lane_id() == 0) {
+            *s_base = base;
             if (tile == a.tiles - 1) a.ctr->total_tokens = base + tile_tokens;
         }
     }
     __syncthreads();
-    const unsigned long long tok_base = a.tok_base0 + s_tok_base;
-    const uint32_t first_rec_ord = static_cast<uint32_t>((16 - (tok_base & 15)) & 15);
-    const uint32_t nrec = tile_tokens > first_rec_ord ? (tile_tokens - first_rec_ord + 15) / 16 : 0;  // records starting in this tile
-    const bool reaches_eof = a.at_eof && tile_byte0 + PF_WIN >= a.n;
-
-    // 3. every 16th token opens a record: note its offset (a stretch of 32 PF_WPT bytes rarely holds more than one)
-    for (uint32_t ord = static_cast<uint32_t>((16 - ((tok_base + excl) & 15)) & 15); ord < my_tokens; ord += 16) {
-        uint32_t r = ord, word = my_starts[0], k = 0;
+    TileFrame f;
+    f.tok_base = a.tok_base0 + *s_base;
+    f.first_rec_ord = static_cast<uint32_t>((16 - (f.tok_base & 15)) & 15);
+    f.nrec = tile_tokens > f.first_rec_ord ? (tile_tokens - f.first_rec_ord + 15) / 16 : 0;  // records starting in this tile
+    uint32_t starts[PF_WPT];
+    const uint32_t my_tokens = token_starts(a, tv.mask(), tile_byte0, tid, starts);
+    const uint32_t excl = s_excl[tid];
+    // a stretch of 32 PF_WPT bytes rarely holds more than one record start
+    for (uint32_t ord = static_cast<uint32_t>((16 - ((f.tok_base + excl) & 15)) & 15); ord < my_tokens; ord += 16) {
+        uint32_t r = ord, word = starts[0], k = 0;
 #pragma unroll
         for (int j = 1; j < PF_WPT; j++) {
-            const uint32_t cnt = __popc(my_starts[j - 1]);
-            if (k == static_cast<uint32_t>(j - 1) && r >= cnt) { r -= cnt; word = my_starts[j]; k = j; }
+            const uint32_t cnt = __popc(starts[j - 1]);
+            if (k == static_cast<uint32_t>(j - 1) && r >= cnt) { r -= cnt; word = starts[j]; k = j; }
         }
-        s_rec_off[(excl + ord - first_rec_ord) >> 4] = static_cast<uint16_t>((tid * PF_WPT + k) * 32 + select_bit32(word, r));
+        s_rec_off[(excl + ord - f.first_rec_ord) >> 4] = static_cast<uint16_t>((tid * PF_WPT + k) * 32 + select_bit32(word, r));
     }
     __syncthreads();
+    return f;
+}
 
-    // 4. one thread per record: parse, filter, score.  Tiles with more than PF_THREADS records (tiny records) take
-    //    further rounds; their records are parsed again after the chain instead of being kept in registers.
-    const uint64_t first_rec = (tok_base + first_rec_ord) >> 4;
-    StagedRecord mine;
-    bool keep0 = false;
-    uint32_t e0 = 0, tot0 = 0, tile_kept = 0;
-    for (uint32_t b0 = 0; b0 < nrec; b0 += PF_THREADS) {
-        const uint32_t j = b0 + tid;
-        StagedRecord r;
-        bool keep = false;
-        if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
-        uint32_t tot;
-        const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
-        if (b0 == 0) { mine = r; keep0 = keep; e0 = ex; tot0 = tot; }
-        tile_kept += tot;
+// Persistent CTAs; tiles are handed out by an atomic ticket (so a tile only ever depends on tiles that are
+// already running).  A CTA keeps two tiles staged and orders its work so that both chains are looked up long
+// after every earlier tile has published, and the copy of a new tile is in flight while other work is done:
+//     records of cur: parse, filter, score  ->  publish kept count (cur)
+//     ->  start the asynchronous copy of the tile after next into cur's buffer
+//     ->  chain 1 + record offsets of next
+//     ->  classify the new tile, publish its token count
+//     ->  chain 2 (cur), write cur's kept records  ->  cur = next
+__global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(const ParseArgs a) {
+    extern __shared__ __align__(16) uint8_t s_dyn[];
+    __shared__ uint16_t s_rec_off[PF_MAXREC];
+    __shared__ uint16_t s_excl[2][PF_THREADS];
+    __shared__ uint32_t s_scan[33];
+    __shared__ uint32_t s_tokens[2];
+    __shared__ unsigned int s_ticket;
+    __shared__ unsigned long long s_tok_base, s_kept_base;
+
+    const uint32_t tid = threadIdx.x, lane = lane_id(), warp = warp_id();
+    TileView tv[2];
+#pragma unroll
+    for (int p = 0; p < 2; p++) {
+        tv[p].raw = s_dyn + p * PF_BUF_BYTES;
+        tv[p].nonws = reinterpret_cast<uint16_t *>(s_dyn + p * PF_BUF_BYTES + PF_RAW_BYTES);
     }
-    if (warp == 0) {  // second chain: where the tile's kept overlaps go
-        const unsigned long long base = chain_exclusive(a.kept_state, tile, tile_kept);
-        if (lane == 0) {
-            s_kept_base = base;
-            if (tile == a.tiles - 1) a.ctr->kept = base + tile_kept;
-        }
-    }
+    auto take_ticket = [&]() -> uint32_t {
+        __syncthreads();
+        if (tid == 0) s_ticket = atomicAdd(&a.ctr->ticket, 1u);
+        __syncthreads();
+        return s_ticket;
+    };
+
+    uint32_t tile = take_ticket();
+    if (tile >= a.tiles) return;
+    stage_issue(a, tile, tv[0]);
+    uint32_t next = take_ticket();
+    if (next < a.tiles) stage_issue(a, next, tv[1]);
+    stage_finish(a, tile, tv[0], s_excl[0], s_scan, &s_tokens[0]);
+    if (next < a.tiles) stage_finish(a, next, tv[1], s_excl[1], s_scan, &s_tokens[1]);
     __syncthreads();
-    const uint64_t out0 = a.kept_base + s_kept_base;
-    if (keep0) store_record(a.kept, out0 + e0, mine);
-    uint32_t run = tot0;
-    for (uint32_t b0 = PF_THREADS; b0 < nrec; b0 += PF_THREADS) {
-        const uint32_t j = b0 + tid;
-        StagedRecord r;
-        bool keep = false;
-        if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
-        uint32_t tot;
-        const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
-        if (keep) store_record(a.kept, out0 + run + ex, r);
-        run += tot;
+    TileFrame f = frame_tile(a, tile, tv[0], s_excl[0], s_tokens[0], &s_tok_base, s_rec_off);
+    int p = 0;
+
+    while (tile < a.tiles) {
+        const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
+        const uint8_t *s_text = tv[p].text();
+        const uint32_t *mask = tv[p].mask();
+        const bool reaches_eof = a.at_eof && tile_byte0 + PF_WIN >= a.n;
+        const uint32_t nrec = f.nrec;
+
+        // one thread per record: parse, filter, score.  Tiles with more than PF_THREADS records (tiny records) take
+        // further rounds; their records are parsed again after the chain instead of being kept in registers.
+        const uint64_t first_rec = (f.tok_base + f.first_rec_ord) >> 4;
+        StagedRecord mine;
+        bool keep0 = false;
+        uint32_t e0 = 0, tot0 = 0, tile_kept = 0;
+        for (uint32_t b0 = 0; b0 < nrec; b0 += PF_THREADS) {
+            const uint32_t j = b0 + tid;
+            StagedRecord r;
+            bool keep = false;
+            if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+            uint32_t tot;
+            const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
+            if (b0 == 0) { mine = r; keep0 = keep; e0 = ex; tot0 = tot; }
+            tile_kept += tot;
+        }
+        if (tid == 0) chain_publish(a.kept_state, tile, tile_kept);
+
+        const bool rounds = nrec > PF_THREADS;
+        if (rounds) {   // rare: this tile still needs its text and record offsets, finish it before anything else
+            if (warp == 0) {
+                const unsigned long long base = chain_resolve(a.kept_state, tile, tile_kept);
+                if (lane == 0) {
+                    s_kept_base = base;
+                    if (tile == a.tiles - 1) a.ctr->kept = base + tile_kept;
+                }
+            }
+            __syncthreads();
+            const uint64_t out0 = a.kept_base + s_kept_base;
+            if (keep0) store_record(a.kept, out0 + e0, mine);
+            uint32_t run = tot0;
+            for (uint32_t b0 = PF_THREADS; b0 < nrec; b0 += PF_THREADS) {
+                const uint32_t j = b0 + tid;
+                StagedRecord r;
+                bool keep = false;
+                if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+                uint32_t tot;
+                const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
+                if (keep) store_record(a.kept, out0 + run + ex, r);
+                run += tot;
+            }
+        }
+
+        // cur's buffer is free: start copying the tile after next into it
+        const uint32_t after = take_ticket();
+        if (after < a.tiles) stage_issue(a, after, tv[p]);
+        // next tile: chain 1 was published an iteration ago
+        TileFrame fn{};
+        if (next < a.tiles) fn = frame_tile(a, next, tv[p ^ 1], s_excl[p ^ 1], s_tokens[p ^ 1], &s_tok_base, s_rec_off);
+        if (after < a.tiles) stage_finish(a, after, tv[p], s_excl[p], s_scan, &s_tokens[p]);
+
+        if (!rounds) {
+            if (warp == 0) {  // second chain: where the tile's kept overlaps go
+                const unsigned long long base = chain_resolve(a.kept_state, tile, tile_kept);
+                if (lane == 0) {
+                    s_kept_base = base;
+                    if (tile == a.tiles - 1) a.ctr->kept = base + tile_kept;
+                }
+            }
+            __syncthreads();
+            const uint64_t out0 = a.kept_base + s_kept_base;
+            if (keep0) store_record(a.kept, out0 + e0, mine);
+        }
+        tile = next;
+        next = after;
+        f = fn;
+        p ^= 1;
     }
 }
 
@@ -726,7 +841,10 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
 
     ParseArgs a{text.bytes.p, n, owned, tok_base0, sharded && shard->prev_nonws ? 1 : 0, (!sharded || shard->at_eof) ? 1 : 0,
                 tiles, file_id, anchors ? 1 : 0, rec_limit, c.kept.n, fd, kept_ptrs(c.kept), tok_state, kept_state, ctr};
-    HERA_LAUNCH(c, paf_parse_kernel, tiles, PF_THREADS, 0, a);
+    int sms = 148;
+    HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
+    HERA_CUDA(cudaFuncSetAttribute(paf_parse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM_BYTES));   // per device: cheap, idempotent
+    HERA_LAUNCH(c, paf_parse_kernel, std::min<uint32_t>(tiles, static_cast<uint32_t>(sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, a);
     HERA_CUDA(cudaEventRecord(ev1, c.stream));
 
     HERA_CUDA(cudaMemcpyAsync(c.h_counters.p, ctr, sizeof(ParseCounters), cudaMemcpyDeviceToHost, c.stream));
