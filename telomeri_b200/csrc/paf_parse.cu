@@ -5,21 +5,22 @@
 // as a whitespace-separated token stream, 16 tokens per record (12 typed + 4 skipped), so a
 // record boundary is "token index % 16 == 0", not a newline.
 //
-// One CTA owns one 24 KiB tile of text (plus a 1 KiB halo so the records that start in the tile
-// can be finished).  Tiles are handed out by an atomic ticket so that a tile never waits for a
-// tile that has not started (chained scan with decoupled look-back):
-//   1. 128-bit coalesced loads stage tile+halo in shared memory; every thread classifies its
-//      16-byte chunks into a non-space bitmask with SWAR arithmetic (one bit per byte).
-//   2. token starts = non-space after space; the tile's token count is published and a warp looks
-//      back over earlier tiles for the global index of the tile's first token (first chain).  A
-//      sharded load adds the tokens of the earlier ranks' byte ranges (ParseArgs::tok_base0).
+// Persistent CTAs (320 threads, 3 per SM) work on 30 KiB tiles of text (plus a 1 KiB halo so the records that
+// start in a tile can be finished).  Tiles are handed out by an atomic ticket so that a tile never waits for a
+// tile that has not started (chained scans with decoupled look-back); a CTA keeps two tiles staged in shared
+// memory and orders its work so that the chains are published early and looked up late:
+//   1. asynchronous 16-byte copies (cp.async) stage tile+halo in shared memory; every thread classifies the
+//      chunks it copied into a non-space bitmask with SWAR arithmetic (one bit per byte).
+//   2. token starts = non-space after space; the tile's token count is published to the first chain; the
+//      global index of the tile's first token is looked up an iteration later.  A sharded load adds the
+//      tokens of the earlier ranks' byte ranges (ParseArgs::tok_base0).
 //   3. every 16th global token opens a record; its offset is found with popcount selection.  One
 //      thread takes one record: token boundaries come from the bitmask (funnel-shifted 32-bit
 //      windows, ffs), integer fields are converted eight digits at a time from whole words, names
 //      are hashed word-wise, then the fp32 filter and scores run in the reference's operation order
 //      (explicit round-to-nearest intrinsics, no FMA contraction).
-//   4. kept records are counted, the count goes through a second look-back chain, and the CTA
-//      writes its kept records at their final file-order position.
+//   4. kept records are counted, the count is published to the second chain, the CTA stages its next tile,
+//      then looks the chain up and writes its kept records at their final file-order position.
 // A record is "regular" when its nine integer tokens are [+-]?digits within int range and the
 // strand token is one character.  The first irregular record (stream extraction would fail or
 // desynchronise there) ends the parallel part; a one-thread tail kernel continues from its byte
@@ -254,16 +255,22 @@ __device__ __forceinline__ void st_state(unsigned long long *p, unsigned long lo
 __device__ __forceinline__ void chain_publish(unsigned long long *state, unsigned int tile, unsigned long long aggregate) {
     st_state(&state[tile], (tile == 0 ? ST_INC : ST_AGG) | aggregate);
 }
-__device__ unsigned long long chain_resolve(unsigned long long *state, unsigned int tile, unsigned long long aggregate) {
+// First look-back window of a tile, loaded early (lane l: state of tile - 1 - l) so that the round trip to L2
+// overlaps with other work; chain_resolve re-reads whatever was still empty.
+__device__ __forceinline__ unsigned long long chain_probe(const unsigned long long *state, unsigned int tile) {
+    const int idx = static_cast<int>(tile) - 1 - static_cast<int>(lane_id());
+    return idx >= 0 ? ld_state(&state[idx]) : ST_INC;   // tiles before 0 behave like an inclusive prefix of 0
+}
+__device__ unsigned long long chain_resolve(unsigned long long *state, unsigned int tile, unsigned long long aggregate, unsigned long long probe) {
     const uint32_t lane = lane_id();
     if (tile == 0) return 0;
     unsigned long long excl = 0;
     int look = static_cast<int>(tile) - 1;
+    unsigned long long s = probe;
     for (;;) {
         const int idx = look - static_cast<int>(lane);
-        unsigned long long s = ST_INC;  // tiles before 0 behave like an inclusive prefix of 0
         if (idx >= 0) {
-            do { s = ld_state(&state[idx]); } while ((s & ST_MASK) == 0);
+            while ((s & ST_MASK) == 0) s = ld_state(&state[idx]);
         }
         const uint32_t inc_mask = __ballot_sync(0xffffffffu, (s & ST_MASK) == ST_INC);
         const uint32_t upto = inc_mask ? static_cast<uint32_t>(__ffs(inc_mask)) : 32u;  // lanes [0, upto) contribute
@@ -273,6 +280,8 @@ __device__ unsigned long long chain_resolve(unsigned long long *state, unsigned 
         excl += v;
         if (inc_mask) break;
         look -= 32;
+        const int nidx = look - static_cast<int>(lane);
+        s = nidx >= 0 ? ld_state(&state[nidx]) : ST_INC;
     }
     if (lane == 0) st_state(&state[tile], ST_INC | (excl + aggregate));
     return excl;
@@ -527,9 +536,9 @@ __device__ __forceinline__ void stage_issue(const ParseArgs &a, uint32_t tile, c
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
-// Second half: byte classification (every thread reads back the chunks it copied), token count; the count is
-// published to the first chain right away (nobody waits here).  Called by the whole CTA.
-__device__ __forceinline__ void stage_finish(const ParseArgs &a, uint32_t tile, const TileView &tv, uint16_t *s_excl, uint32_t *s_scan, uint32_t *s_tokens) {
+// Second half, part one: byte classification (every thread reads back the chunks it copied).  The mask may be
+// read by other threads after the next barrier.
+__device__ __forceinline__ void stage_classify(const ParseArgs &a, uint32_t tile, const TileView &tv) {
     const uint32_t tid = threadIdx.x;
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -546,16 +555,28 @@ __device__ __forceinline__ void stage_finish(const ParseArgs &a, uint32_t tile, 
         for (int k = 0; k < 4; k++) tv.nonws[PF_CHUNKS + 2 + k] = 0;
         for (int k = 0; k < 4; k++) { reinterpret_cast<uint32_t *>(tv.raw)[k] = 0x20202020u; reinterpret_cast<uint32_t *>(tv.raw + 16 + PF_WIN)[k] = 0x20202020u; }
     }
-    __syncthreads();
-    uint32_t starts[PF_WPT];
-    const uint32_t my_tokens = token_starts(a, tv.mask(), tile_byte0, tid, starts);
-    uint32_t tile_tokens;
-    const uint32_t excl = block_exclusive_scan<uint32_t>(my_tokens, s_scan, &tile_tokens);
-    s_excl[tid] = static_cast<uint16_t>(excl);
-    if (tid == 0) {
-        *s_tokens = tile_tokens;
-        chain_publish(a.tok_state, tile, tile_tokens);
+}
+
+// Block-wide exclusive scan with ONE barrier: every warp leaves its total in s_tot, every thread adds up the
+// totals of the warps before it.  The caller keeps a barrier between two scans that use the same s_tot.
+constexpr int PF_WARPS = PF_THREADS / 32;
+static_assert(PF_WARPS <= 32, "one lane per warp total");
+__device__ __forceinline__ uint32_t scan_part1(uint32_t v, uint32_t *s_tot) {   // returns the inclusive prefix inside the warp
+    const uint32_t lane = lane_id();
+    uint32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= static_cast<uint32_t>(d)) incl += up;
     }
+    if (lane == 31) s_tot[warp_id()] = incl;
+    return incl;
+}
+__device__ __forceinline__ uint32_t scan_part2(const uint32_t *s_tot, uint32_t *total) {   // after the barrier: sum of the warps before mine
+    const uint32_t lane = lane_id(), warp = warp_id();
+    const uint32_t t = lane < PF_WARPS ? s_tot[lane] : 0u;
+    *total = __reduce_add_sync(0xffffffffu, t);
+    return __reduce_add_sync(0xffffffffu, lane < warp ? t : 0u);
 }
 
 struct TileFrame {   // what the record stage needs to know about a staged tile (same in every thread)
@@ -563,22 +584,14 @@ struct TileFrame {   // what the record stage needs to know about a staged tile 
     uint32_t first_rec_ord, nrec;
 };
 
-// Stage B + C of a tile: look up chain 1 (global index of the tile's first token), then note the offset of every
-// record that starts in the tile (every 16th token).  Called by the whole CTA.
+// Stage C of a tile whose chain 1 has been resolved (base = tokens before the tile in this text): note the
+// offset of every record that starts in the tile (every 16th token).  s_rec_off is complete after the next barrier.
 __device__ __forceinline__ TileFrame frame_tile(const ParseArgs &a, uint32_t tile, const TileView &tv, const uint16_t *s_excl, uint32_t tile_tokens,
-                                                unsigned long long *s_base, uint16_t *s_rec_off) {
+                                                unsigned long long base, uint16_t *s_rec_off) {
     const uint32_t tid = threadIdx.x;
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
-    if (warp_id() == 0) {
-        const unsigned long long base = chain_resolve(a.tok_state, tile, tile_tokens);
-        if (lane_id() == 0) {
-            *s_base = base;
-            if (tile == a.tiles - 1) a.ctr->total_tokens = base + tile_tokens;
-        }
-    }
-    __syncthreads();
     TileFrame f;
-    f.tok_base = a.tok_base0 + *s_base;
+    f.tok_base = a.tok_base0 + base;
     f.first_rec_ord = static_cast<uint32_t>((16 - (f.tok_base & 15)) & 15);
     f.nrec = tile_tokens > f.first_rec_ord ? (tile_tokens - f.first_rec_ord + 15) / 16 : 0;  // records starting in this tile
     uint32_t starts[PF_WPT];
@@ -594,23 +607,22 @@ __device__ __forceinline__ TileFrame frame_tile(const ParseArgs &a, uint32_t til
         }
         s_rec_off[(excl + ord - f.first_rec_ord) >> 4] = static_cast<uint16_t>((tid * PF_WPT + k) * 32 + select_bit32(word, r));
     }
-    __syncthreads();
     return f;
 }
 
 // Persistent CTAs; tiles are handed out by an atomic ticket (so a tile only ever depends on tiles that are
 // already running).  A CTA keeps two tiles staged and orders its work so that both chains are looked up long
 // after every earlier tile has published, and the copy of a new tile is in flight while other work is done:
-//     records of cur: parse, filter, score  ->  publish kept count (cur)
-//     ->  start the asynchronous copy of the tile after next into cur's buffer
-//     ->  chain 1 + record offsets of next
-//     ->  classify the new tile, publish its token count
-//     ->  chain 2 (cur), write cur's kept records  ->  cur = next
+//     records of cur: parse, filter, score  ->  publish kept count (cur), take a ticket
+//     ->  start the asynchronous copy of the new tile into cur's buffer  ->  classify it, count its tokens
+//     ->  warp 0: publish the new tile's token count, resolve chain 1 of next and chain 2 of cur
+//     ->  record offsets of next, write cur's kept records  ->  cur = next
+// Six barriers per tile.
 __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(const ParseArgs a) {
     extern __shared__ __align__(16) uint8_t s_dyn[];
     __shared__ uint16_t s_rec_off[PF_MAXREC];
     __shared__ uint16_t s_excl[2][PF_THREADS];
-    __shared__ uint32_t s_scan[33];
+    __shared__ uint32_t s_tot_tok[PF_WARPS], s_tot_kept[PF_WARPS];
     __shared__ uint32_t s_tokens[2];
     __shared__ unsigned int s_ticket;
     __shared__ unsigned long long s_tok_base, s_kept_base;
@@ -622,22 +634,63 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
         tv[p].raw = s_dyn + p * PF_BUF_BYTES;
         tv[p].nonws = reinterpret_cast<uint16_t *>(s_dyn + p * PF_BUF_BYTES + PF_RAW_BYTES);
     }
-    auto take_ticket = [&]() -> uint32_t {
+    // Classifies the copied tile `t` in buffer q, counts its tokens and lets warp 0 publish the count; warp 0 also
+    // resolves chain 1 of tile `n` (-> s_tok_base) and chain 2 of tile `c` with aggregate kc (-> s_kept_base) while
+    // the other warps wait at the closing barrier.  Tiles >= a.tiles are skipped.
+    auto stage_and_service = [&](uint32_t t, int q, uint32_t n, uint32_t n_tokens, uint32_t c, uint32_t kc) {
+        uint32_t my_tokens = 0, incl = 0;
+        if (t < a.tiles) {
+            stage_classify(a, t, tv[q]);
+            __syncthreads();
+            uint32_t starts[PF_WPT];
+            my_tokens = token_starts(a, tv[q].mask(), static_cast<uint64_t>(t) * PF_TILE, tid, starts);
+            incl = scan_part1(my_tokens, s_tot_tok);
+        }
         __syncthreads();
-        if (tid == 0) s_ticket = atomicAdd(&a.ctr->ticket, 1u);
+        if (t < a.tiles) {
+            uint32_t total;
+            const uint32_t before = scan_part2(s_tot_tok, &total);
+            s_excl[q][tid] = static_cast<uint16_t>(before + incl - my_tokens);
+            if (tid == 0) { s_tokens[q] = total; chain_publish(a.tok_state, t, total); }
+        }
+        if (warp == 0) {
+            // both first look-back windows are requested before either is used (one round trip to L2, not two)
+            const unsigned long long probe_tok = n < a.tiles ? chain_probe(a.tok_state, n) : 0ull;
+            const unsigned long long probe_kept = c < a.tiles ? chain_probe(a.kept_state, c) : 0ull;
+            if (n < a.tiles) {
+                const unsigned long long base = chain_resolve(a.tok_state, n, n_tokens, probe_tok);
+                if (lane == 0) {
+                    s_tok_base = base;
+                    if (n == a.tiles - 1) a.ctr->total_tokens = base + n_tokens;
+                }
+            }
+            if (c < a.tiles) {
+                const unsigned long long base = chain_resolve(a.kept_state, c, kc, probe_kept);
+                if (lane == 0) {
+                    s_kept_base = base;
+                    if (c == a.tiles - 1) a.ctr->kept = base + kc;
+                }
+            }
+        }
         __syncthreads();
-        return s_ticket;
     };
 
-    uint32_t tile = take_ticket();
+    // Tickets are taken one at a time: tiles must reach the record stage in roughly ticket order everywhere, or a
+    // CTA's second tile (handled an iteration later) would hold up every CTA whose first tile comes after it.
+    if (tid == 0) s_ticket = atomicAdd(&a.ctr->ticket, 1u);
+    __syncthreads();
+    uint32_t tile = s_ticket;
     if (tile >= a.tiles) return;
     stage_issue(a, tile, tv[0]);
-    uint32_t next = take_ticket();
-    if (next < a.tiles) stage_issue(a, next, tv[1]);
-    stage_finish(a, tile, tv[0], s_excl[0], s_scan, &s_tokens[0]);
-    if (next < a.tiles) stage_finish(a, next, tv[1], s_excl[1], s_scan, &s_tokens[1]);
     __syncthreads();
-    TileFrame f = frame_tile(a, tile, tv[0], s_excl[0], s_tokens[0], &s_tok_base, s_rec_off);
+    if (tid == 0) s_ticket = atomicAdd(&a.ctr->ticket, 1u);
+    __syncthreads();
+    uint32_t next = s_ticket;
+    if (next < a.tiles) stage_issue(a, next, tv[1]);
+    stage_and_service(tile, 0, a.tiles, 0, a.tiles, 0);
+    stage_and_service(next, 1, tile, s_tokens[0], a.tiles, 0);
+    TileFrame f = frame_tile(a, tile, tv[0], s_excl[0], s_tokens[0], s_tok_base, s_rec_off);
+    __syncthreads();
     int p = 0;
 
     while (tile < a.tiles) {
@@ -646,6 +699,7 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
         const uint32_t *mask = tv[p].mask();
         const bool reaches_eof = a.at_eof && tile_byte0 + PF_WIN >= a.n;
         const uint32_t nrec = f.nrec;
+        const bool rounds = nrec > PF_THREADS;
 
         // one thread per record: parse, filter, score.  Tiles with more than PF_THREADS records (tiny records) take
         // further rounds; their records are parsed again after the chain instead of being kept in registers.
@@ -658,17 +712,23 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
             StagedRecord r;
             bool keep = false;
             if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+            const uint32_t votes = __ballot_sync(0xffffffffu, keep);
+            if (lane == 31) s_tot_kept[warp] = __popc(votes);
+            __syncthreads();
             uint32_t tot;
-            const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
+            const uint32_t ex = scan_part2(s_tot_kept, &tot) + __popc(votes & ((1u << lane) - 1u));
             if (b0 == 0) { mine = r; keep0 = keep; e0 = ex; tot0 = tot; }
             tile_kept += tot;
+            if (rounds) __syncthreads();   // s_tot_kept is written again right away
         }
-        if (tid == 0) chain_publish(a.kept_state, tile, tile_kept);
+        if (tid == 0) {
+            chain_publish(a.kept_state, tile, tile_kept);
+            s_ticket = atomicAdd(&a.ctr->ticket, 1u);
+        }
 
-        const bool rounds = nrec > PF_THREADS;
         if (rounds) {   // rare: this tile still needs its text and record offsets, finish it before anything else
             if (warp == 0) {
-                const unsigned long long base = chain_resolve(a.kept_state, tile, tile_kept);
+                const unsigned long long base = chain_resolve(a.kept_state, tile, tile_kept, chain_probe(a.kept_state, tile));
                 if (lane == 0) {
                     s_kept_base = base;
                     if (tile == a.tiles - 1) a.ctr->kept = base + tile_kept;
@@ -683,33 +743,25 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
                 StagedRecord r;
                 bool keep = false;
                 if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+                const uint32_t votes = __ballot_sync(0xffffffffu, keep);
+                if (lane == 31) s_tot_kept[warp] = __popc(votes);
+                __syncthreads();
                 uint32_t tot;
-                const uint32_t ex = block_exclusive_scan<uint32_t>(keep ? 1u : 0u, s_scan, &tot);
+                const uint32_t ex = scan_part2(s_tot_kept, &tot) + __popc(votes & ((1u << lane) - 1u));
                 if (keep) store_record(a.kept, out0 + run + ex, r);
                 run += tot;
+                __syncthreads();
             }
         }
 
-        // cur's buffer is free: start copying the tile after next into it
-        const uint32_t after = take_ticket();
+        __syncthreads();   // everybody is done with cur's text and record offsets; the ticket is visible
+        const uint32_t after = s_ticket;
         if (after < a.tiles) stage_issue(a, after, tv[p]);
-        // next tile: chain 1 was published an iteration ago
+        stage_and_service(after, p, next, s_tokens[p ^ 1], rounds ? a.tiles : tile, tile_kept);
         TileFrame fn{};
-        if (next < a.tiles) fn = frame_tile(a, next, tv[p ^ 1], s_excl[p ^ 1], s_tokens[p ^ 1], &s_tok_base, s_rec_off);
-        if (after < a.tiles) stage_finish(a, after, tv[p], s_excl[p], s_scan, &s_tokens[p]);
-
-        if (!rounds) {
-            if (warp == 0) {  // second chain: where the tile's kept overlaps go
-                const unsigned long long base = chain_resolve(a.kept_state, tile, tile_kept);
-                if (lane == 0) {
-                    s_kept_base = base;
-                    if (tile == a.tiles - 1) a.ctr->kept = base + tile_kept;
-                }
-            }
-            __syncthreads();
-            const uint64_t out0 = a.kept_base + s_kept_base;
-            if (keep0) store_record(a.kept, out0 + e0, mine);
-        }
+        if (next < a.tiles) fn = frame_tile(a, next, tv[p ^ 1], s_excl[p ^ 1], s_tokens[p ^ 1], s_tok_base, s_rec_off);
+        if (!rounds && keep0) store_record(a.kept, a.kept_base + s_kept_base + e0, mine);
+        __syncthreads();   // record offsets of next are complete
         tile = next;
         next = after;
         f = fn;
