@@ -229,11 +229,7 @@ __global__ void anchor_list_kernel(uint64_t N, const uint8_t *__restrict__ node_
     if (i < N && node_anchor[i]) anchor_ids[anchor_scan[i]] = static_cast<uint32_t>(i);
 }
 
-// One CTA per node.  rank by counting: position of slot i in the stable descending order =
-// #{j : m[j] > m[i]} + #{j < i : m[j] == m[i]}.  Values are staged in shared memory when the
-// list fits; longer lists are read through L1/L2.
 constexpr int RK_THREADS = 128;
-constexpr int RK_SMEM = 4096;
 
 __device__ __forceinline__ float metric_value(int metric, float es, float os) {
     switch (metric) {
@@ -244,45 +240,219 @@ __device__ __forceinline__ float metric_value(int metric, float es, float os) {
     }
 }
 
-__global__ void __launch_bounds__(RK_THREADS) rank_kernel(const uint32_t *__restrict__ off, const float *__restrict__ a_es, const float *__restrict__ a_os,
-                                                          int metric, uint32_t *__restrict__ rank, uint32_t node0) {
-    __shared__ float sm[RK_SMEM];
-    const uint32_t x = blockIdx.x + node0;
-    const uint32_t base = off[x], deg = off[x + 1] - base;
-    const bool staged = deg <= RK_SMEM;
-    if (staged) {
-        for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) sm[i] = metric_value(metric, a_es[base + i], a_os[base + i]);
-        __syncthreads();
-    }
+// K4b, one CTA per node: canonical slots and rank permutations of the node's list, staged in shared memory.
+//   canon[i] = first slot of the list with the same neighbour (shared-memory hash table: neighbour -> min index).
+//   rank[m]  = stable descending order by metric m, the order the reference recomputes at every greedy step
+//              (src/PathManager.cpp:289-296): a bitonic sort of 64-bit keys {orderable metric bits, ~index}; equal
+//              metrics keep list order because the index is part of the key (-0.0 is folded into +0.0 first, as
+//              `>` sees them).  A list with a NaN metric, or longer than CAP, is ranked by counting instead:
+//              position of slot i = #{j : m[j] > m[i]} + #{j < i : m[j] == m[i]}  (what `>` on NaN gives).
+// This kernel takes the lists longer than LOW entries (the short ones go to rank_small_kernel below).
+struct RankPtrs { uint32_t *p[4]; };
+
+__device__ __forceinline__ uint64_t rank_key(float v, uint32_t i, bool &nan) {
+    uint32_t bits = __float_as_uint(v);
+    if (v != v) nan = true;
+    if (bits == 0x80000000u) bits = 0;
+    const uint32_t u = (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u);
+    return (static_cast<uint64_t>(u) << 32) | (0xffffffffu - i);
+}
+
+__device__ void rank_by_counting(const float *__restrict__ a_es, const float *__restrict__ a_os, int metric, uint32_t base, uint32_t deg,
+                                 uint32_t *__restrict__ rank) {
     for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) {
-        const float mi = staged ? sm[i] : metric_value(metric, a_es[base + i], a_os[base + i]);
+        const float mi = metric_value(metric, a_es[base + i], a_os[base + i]);
         uint32_t r = 0;
-        if (staged) {
-            for (uint32_t j = 0; j < deg; j++) { const float mj = sm[j]; r += (mj > mi) || (mj == mi && j < i); }
-        } else {
-            for (uint32_t j = 0; j < deg; j++) { const float mj = metric_value(metric, a_es[base + j], a_os[base + j]); r += (mj > mi) || (mj == mi && j < i); }
-        }
+        for (uint32_t j = 0; j < deg; j++) { const float mj = metric_value(metric, a_es[base + j], a_os[base + j]); r += (mj > mi) || (mj == mi && j < i); }
         rank[base + r] = base + i;
     }
 }
 
-__global__ void __launch_bounds__(RK_THREADS) canon_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr, uint32_t *__restrict__ canon,
-                                                           uint32_t node0) {
-    __shared__ uint32_t sm[RK_SMEM];
-    const uint32_t x = blockIdx.x + node0;
+// Lists of up to RS_SMALL entries (almost all of them): canonical slots through the same kind of shared-memory
+// hash table, ranks by counting over 32-bit orderable keys read four at a time: position of slot i =
+// #{j : key[j] > key[i]}.  That is the stable order whenever the list holds no two equal keys, which is checked
+// with one sum (the positions of distinct keys add up to deg (deg - 1) / 2); in a list with equal keys the slots
+// that share a position add #{j < i : key[j] == key[i]}.  A list with a NaN is ranked with float compares.
+constexpr int RS_SMALL = 512;
+constexpr int RS_PER_THREAD = RS_SMALL / RK_THREADS;
+
+// cnt += (k > ki) as one compare and one predicated add
+__device__ __forceinline__ void count_greater(uint32_t &cnt, uint32_t k, uint32_t ki) {
+    asm("{\n\t.reg .pred p;\n\tsetp.gt.u32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(cnt) : "r"(k), "r"(ki));
+}
+
+__global__ void __launch_bounds__(RK_THREADS) rank_small_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr,
+                                                                const float *__restrict__ a_es, const float *__restrict__ a_os, uint32_t metrics_mask,
+                                                                RankPtrs rank, uint32_t *__restrict__ canon, uint32_t node0) {
+    __shared__ __align__(16) uint32_t s_words[RS_SMALL * 4];   // hash table (2 x 1024 words), then the keys
+    __shared__ uint32_t s_sum;
+    __shared__ int s_nan;
+    const uint32_t x = blockIdx.x + node0, tid = threadIdx.x;
     const uint32_t base = off[x], deg = off[x + 1] - base;
-    const bool staged = deg <= RK_SMEM;
-    if (staged) {
-        for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) sm[i] = a_nbr[base + i];
+    if (deg == 0 || deg > RS_SMALL) return;   // longer lists: rank_canon_kernel
+    uint32_t npad = 32;
+    while (npad < deg) npad <<= 1;
+
+    {   // canonical slots
+        const uint32_t T = 2 * npad, shift = 32 - (31 - __clz(T));
+        uint32_t *hkey = s_words, *hval = s_words + 2 * RS_SMALL;
+        for (uint32_t i = tid; i < T; i += RK_THREADS) { hkey[i] = 0xffffffffu; hval[i] = 0xffffffffu; }
         __syncthreads();
+        for (uint32_t i = tid; i < deg; i += RK_THREADS) {
+            const uint32_t nbr = a_nbr[base + i];
+            uint32_t h = (nbr * 2654435761u) >> shift;
+            for (;;) {
+                const uint32_t prev = atomicCAS(&hkey[h], 0xffffffffu, nbr);
+                if (prev == 0xffffffffu || prev == nbr) { atomicMin(&hval[h], i); break; }
+                h = (h + 1) & (T - 1);
+            }
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < deg; i += RK_THREADS) {
+            const uint32_t nbr = a_nbr[base + i];
+            uint32_t h = (nbr * 2654435761u) >> shift;
+            while (hkey[h] != nbr) h = (h + 1) & (T - 1);
+            canon[base + i] = base + hval[h];
+        }
     }
-    for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) {
-        const uint32_t ni = staged ? sm[i] : a_nbr[base + i];
-        uint32_t j = 0;
-        if (staged) { while (sm[j] != ni) j++; } else { while (a_nbr[base + j] != ni) j++; }
-        canon[base + i] = base + j;
+
+    uint32_t *key = s_words;
+    const uint32_t quads = (deg + 3) / 4;
+    for (int m = 0; m < 4; m++) {
+        if (!(metrics_mask & (1u << m))) continue;
+        __syncthreads();   // the table / the previous metric's keys are no longer read
+        if (tid == 0) { s_nan = 0; s_sum = 0; }
+        __syncthreads();
+        bool nan = false;
+        for (uint32_t i = tid; i < quads * 4; i += RK_THREADS)   // keys behind the list are 0: never greater than a real key
+            key[i] = i < deg ? static_cast<uint32_t>(rank_key(metric_value(m, a_es[base + i], a_os[base + i]), i, nan) >> 32) : 0u;
+        if (nan) s_nan = 1;
+        __syncthreads();
+        if (s_nan) { rank_by_counting(a_es, a_os, m, base, deg, rank.p[m]); continue; }
+        uint32_t r[RS_PER_THREAD], local = 0;
+#pragma unroll
+        for (int e = 0; e < RS_PER_THREAD; e++) {
+            const uint32_t i = tid + e * RK_THREADS;
+            r[e] = 0;
+            if (i < deg) {
+                const uint32_t ki = key[i];
+                uint32_t cnt = 0, cnt2 = 0;
+                for (uint32_t q = 0; q < quads; q++) {
+                    const uint4 k = reinterpret_cast<const uint4 *>(key)[q];
+                    count_greater(cnt, k.x, ki); count_greater(cnt2, k.y, ki); count_greater(cnt, k.z, ki); count_greater(cnt2, k.w, ki);
+                }
+                cnt += cnt2;
+                r[e] = cnt;
+                local += cnt;
+            }
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
+        if ((tid & 31u) == 0 && local) atomicAdd(&s_sum, local);
+        __syncthreads();
+        if (s_sum != deg * (deg - 1) / 2) {   // equal keys somewhere: they got the same position, list order decides between them
+            uint32_t *shared_pos = s_words + 2 * RS_SMALL;   // how many slots were given position p
+            for (uint32_t i = tid; i < deg; i += RK_THREADS) shared_pos[i] = 0;
+            __syncthreads();
+#pragma unroll
+            for (int e = 0; e < RS_PER_THREAD; e++)
+                if (tid + e * RK_THREADS < deg) atomicAdd(&shared_pos[r[e]], 1u);
+            __syncthreads();
+#pragma unroll
+            for (int e = 0; e < RS_PER_THREAD; e++) {
+                const uint32_t i = tid + e * RK_THREADS;
+                if (i < deg && shared_pos[r[e]] > 1) {
+                    const uint32_t ki = key[i];
+                    for (uint32_t j = 0; j < i; j++) r[e] += key[j] == ki;
+                }
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < RS_PER_THREAD; e++) {
+            const uint32_t i = tid + e * RK_THREADS;
+            if (i < deg) rank.p[m][base + r[e]] = base + i;
+        }
     }
 }
+
+template <int CAP, int LOW, bool LAST>
+__global__ void __launch_bounds__(RK_THREADS) rank_canon_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr,
+                                                                const float *__restrict__ a_es, const float *__restrict__ a_os, uint32_t metrics_mask,
+                                                                RankPtrs rank, uint32_t *__restrict__ canon, uint32_t node0) {
+    __shared__ __align__(8) uint32_t s_words[CAP * 4];   // hash table (2 CAP keys + 2 CAP values), then CAP sort keys of 64 bits
+    __shared__ int s_nan;
+    const uint32_t x = blockIdx.x + node0, tid = threadIdx.x;
+    const uint32_t base = off[x], deg = off[x + 1] - base;
+    if (deg <= LOW || deg == 0 || (!LAST && deg > CAP)) return;   // the other instance's node
+    const bool fits = deg <= CAP;
+    uint32_t npad = 32;
+    while (npad < deg) npad <<= 1;
+
+    // ---- canonical slots
+    if (fits) {
+        const uint32_t T = 2 * npad, shift = 32 - (31 - __clz(T));
+        uint32_t *hkey = s_words, *hval = s_words + 2 * CAP;
+        for (uint32_t i = tid; i < T; i += RK_THREADS) { hkey[i] = 0xffffffffu; hval[i] = 0xffffffffu; }
+        __syncthreads();
+        for (uint32_t i = tid; i < deg; i += RK_THREADS) {
+            const uint32_t nbr = a_nbr[base + i];
+            uint32_t h = (nbr * 2654435761u) >> shift;
+            for (;;) {
+                const uint32_t prev = atomicCAS(&hkey[h], 0xffffffffu, nbr);
+                if (prev == 0xffffffffu || prev == nbr) { atomicMin(&hval[h], i); break; }
+                h = (h + 1) & (T - 1);
+            }
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < deg; i += RK_THREADS) {
+            const uint32_t nbr = a_nbr[base + i];
+            uint32_t h = (nbr * 2654435761u) >> shift;
+            while (hkey[h] != nbr) h = (h + 1) & (T - 1);
+            canon[base + i] = base + hval[h];
+        }
+    } else {
+        for (uint32_t i = tid; i < deg; i += RK_THREADS) {
+            const uint32_t ni = a_nbr[base + i];
+            uint32_t j = 0;
+            while (a_nbr[base + j] != ni) j++;
+            canon[base + i] = base + j;
+        }
+    }
+
+    // ---- rank permutations
+    uint64_t *key = reinterpret_cast<uint64_t *>(s_words);
+    for (int m = 0; m < 4; m++) {
+        if (!(metrics_mask & (1u << m))) continue;
+        if (!fits) { rank_by_counting(a_es, a_os, m, base, deg, rank.p[m]); continue; }
+        __syncthreads();   // the table / the previous metric's keys are no longer read
+        if (tid == 0) s_nan = 0;
+        __syncthreads();
+        bool nan = false;
+        for (uint32_t i = tid; i < npad; i += RK_THREADS)
+            key[i] = i < deg ? rank_key(metric_value(m, a_es[base + i], a_os[base + i]), i, nan) : 0ull;
+        if (nan) s_nan = 1;
+        __syncthreads();
+        if (s_nan) { rank_by_counting(a_es, a_os, m, base, deg, rank.p[m]); continue; }
+        // Pair t of a step with distance j <= 32 lies in [64 (t / 32), 64 (t / 32) + 64): such steps only need the
+        // warp to agree, a step with a longer distance (and the step after it) needs the whole CTA.
+        bool wide = false;
+        for (uint32_t k = 2; k <= npad; k <<= 1) {
+            for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                if (j >= 64 || wide) __syncthreads(); else __syncwarp();
+                wide = j >= 64;
+                for (uint32_t t = tid; t < npad / 2; t += RK_THREADS) {
+                    const uint32_t idx = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                    const uint64_t ka = key[idx], kb = key[idx + j];
+                    const bool first_larger = (idx & k) == 0;   // descending blocks alternate with ascending ones; the last merge is descending
+                    if ((ka < kb) == first_larger) { key[idx] = kb; key[idx + j] = ka; }
+                }
+            }
+        }
+        __syncthreads();
+        for (uint32_t p = tid; p < deg; p += RK_THREADS) rank.p[m][base + p] = base + (0xffffffffu - static_cast<uint32_t>(key[p]));
+    }
+}
+
 
 static int bits_for(uint64_t n) {
     int b = 1;
@@ -304,6 +474,8 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
     float intern_ms = 0, csr_ms = 0, rank_ms = 0;
     if (E > 0) {
         uint64_t N = 0;
+        uint32_t *d_late = nullptr;          // results that are only looked at when the build is over
+        cudaEvent_t verify_done = nullptr;
         if (!c.cache_loaded) {
         // ---- K3
         uint32_t *occ_slot = nullptr, *first_scan = nullptr, *d_small = nullptr;
@@ -373,26 +545,38 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
                 HERA_CUDA(cudaFreeAsync(parts, c.stream));
             }
         }
-        for (int i = 0; i < own.n; i++) {
-            const uint64_t rows = own.end[i] - own.begin[i];
-            if (rows) HERA_LAUNCH(c, intern_verify_kernel, div_up(rows, 256), 256, 0, own, i, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p,
-                                  g.node_name_off.p, g.node_names.p, tp, d_small + 2);
+        // Every occurrence's bytes against its node's name: only reads, so it runs beside the CSR build on a side
+        // stream; the verdict is looked at together with the last results of this build.
+        HERA_CUDA(cudaMallocAsync(&d_late, 2 * sizeof(uint32_t), c.stream));   // [0] collision flag, [1] anchors
+        HERA_CUDA(cudaMemsetAsync(d_late, 0, 2 * sizeof(uint32_t), c.stream));
+        if (c.aux_streams.empty()) {
+            cudaStream_t st;
+            HERA_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            c.aux_streams.push_back(st);
+        }
+        {
+            cudaEvent_t names_ready;
+            HERA_CUDA(cudaEventCreateWithFlags(&names_ready, cudaEventDisableTiming));
+            HERA_CUDA(cudaEventRecord(names_ready, c.stream));
+            HERA_CUDA(cudaStreamWaitEvent(c.aux_streams[0], names_ready, 0));
+            cudaEventDestroy(names_ready);
+            for (int i = 0; i < own.n; i++) {
+                const uint64_t rows = own.end[i] - own.begin[i];
+                if (rows) {
+                    intern_verify_kernel<<<div_up(rows, 256), 256, 0, c.aux_streams[0]>>>(own, i, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p,
+                                                                                        g.node_name_off.p, g.node_names.p, tp, d_late);
+                    c.launches.count++;
+                    HERA_CUDA(cudaGetLastError());
+                }
+            }
+            HERA_CUDA(cudaEventCreateWithFlags(&verify_done, cudaEventDisableTiming));
+            HERA_CUDA(cudaEventRecord(verify_done, c.aux_streams[0]));
         }
         // anchors in node order
         uint32_t *anchor_scan = nullptr;
         HERA_CUDA(cudaMallocAsync(&anchor_scan, N * sizeof(uint32_t), c.stream));
-        exclusive_scan_u8_to_u32(c, g.node_anchor.p, N, anchor_scan, d_small + 3);
-        HERA_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, c.stream));
-        HERA_CUDA(cudaStreamSynchronize(c.stream));
-        uint64_t collided = h_small[2];
-        if (xch_size(c) > 1) {
-            std::vector<uint64_t> all(xch_size(c));
-            c.xch->all_gather_host(c, &collided, 1, all.data());
-            for (uint64_t v : all) collided |= v;
-        }
-        HERA_REQUIRE(!collided, 6, "64-bit name hash collision detected while interning node names");
-        g.anchors = h_small[3];
-        g.anchor_ids.reserve(g.anchors + 1);
+        exclusive_scan_u8_to_u32(c, g.node_anchor.p, N, anchor_scan, d_late + 1);
+        g.anchor_ids.reserve(N + 1);
         HERA_LAUNCH(c, anchor_list_kernel, div_up(N, 256), 256, 0, N, g.node_anchor.p, anchor_scan, g.anchor_ids.p);
         HERA_CUDA(cudaFreeAsync(anchor_scan, c.stream));
         HERA_CUDA(cudaFreeAsync(keys, c.stream)); HERA_CUDA(cudaFreeAsync(minpos, c.stream)); HERA_CUDA(cudaFreeAsync(slot_id, c.stream));
@@ -401,18 +585,14 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         } else {
             // node table, e_q / e_t restored from a cache file (hera_graph_load_cache): only the anchor list is derived
             N = g.N;
-            uint32_t *anchor_scan = nullptr, *d_cnt = nullptr;
+            uint32_t *anchor_scan = nullptr;
             HERA_CUDA(cudaMallocAsync(&anchor_scan, N * sizeof(uint32_t), c.stream));
-            HERA_CUDA(cudaMallocAsync(&d_cnt, sizeof(uint32_t), c.stream));
-            exclusive_scan_u8_to_u32(c, g.node_anchor.p, N, anchor_scan, d_cnt);
-            uint32_t h_cnt = 0;
-            HERA_CUDA(cudaMemcpyAsync(&h_cnt, d_cnt, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
-            HERA_CUDA(cudaStreamSynchronize(c.stream));
-            g.anchors = h_cnt;
-            g.anchor_ids.reserve(g.anchors + 1);
+            HERA_CUDA(cudaMallocAsync(&d_late, 2 * sizeof(uint32_t), c.stream));
+            HERA_CUDA(cudaMemsetAsync(d_late, 0, 2 * sizeof(uint32_t), c.stream));
+            exclusive_scan_u8_to_u32(c, g.node_anchor.p, N, anchor_scan, d_late + 1);
+            g.anchor_ids.reserve(N + 1);
             HERA_LAUNCH(c, anchor_list_kernel, div_up(N, 256), 256, 0, N, g.node_anchor.p, anchor_scan, g.anchor_ids.p);
             HERA_CUDA(cudaFreeAsync(anchor_scan, c.stream));
-            HERA_CUDA(cudaFreeAsync(d_cnt, c.stream));
         }
         HERA_CUDA(cudaEventRecord(ev[1], c.stream));
 
@@ -442,12 +622,16 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         const int ranks = xch_size(c), me = xch_rank(c);
         const uint64_t n_lo = N * me / ranks, n_hi = N * (me + 1) / ranks;
         const unsigned my_nodes = static_cast<unsigned>(n_hi - n_lo);
-        if (my_nodes) HERA_LAUNCH(c, canon_kernel, my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.canon.p, static_cast<uint32_t>(n_lo));
+        RankPtrs rp{};
         for (int m = 0; m < 4; m++) {
             if (!(metrics_mask & (1u << m))) continue;
             g.rank[m].reserve(occ);
-            if (my_nodes) HERA_LAUNCH(c, rank_kernel, my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_es.p, g.a_os.p, m, g.rank[m].p, static_cast<uint32_t>(n_lo));
+            rp.p[m] = g.rank[m].p;
             g.rank_ready[m] = true;
+        }
+        if (my_nodes) {
+            HERA_LAUNCH(c, rank_small_kernel, my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.a_es.p, g.a_os.p, metrics_mask, rp, g.canon.p, static_cast<uint32_t>(n_lo));
+            HERA_LAUNCH(c, (rank_canon_kernel<2048, 512, true>), my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.a_es.p, g.a_os.p, metrics_mask, rp, g.canon.p, static_cast<uint32_t>(n_lo));
         }
         if (ranks > 1) {
             std::vector<uint32_t> cut(ranks + 1);
@@ -462,8 +646,22 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             c.xch->end_batch();
         }
         HERA_CUDA(cudaEventRecord(ev[3], c.stream));
+        if (verify_done) {
+            HERA_CUDA(cudaStreamWaitEvent(c.stream, verify_done, 0));
+            cudaEventDestroy(verify_done);
+        }
+        HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 14, d_late, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaFreeAsync(d_late, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         g.max_deg = static_cast<uint32_t>(c.h_counters.p[15] & 0xffffffffu);
+        g.anchors = c.h_counters.p[14] >> 32;
+        uint64_t collided = c.h_counters.p[14] & 0xffffffffu;
+        if (xch_size(c) > 1) {
+            std::vector<uint64_t> all(xch_size(c));
+            c.xch->all_gather_host(c, &collided, 1, all.data());
+            for (uint64_t v : all) collided |= v;
+        }
+        HERA_REQUIRE(!collided, 6, "64-bit name hash collision detected while interning node names");
         HERA_CUDA(cudaEventElapsedTime(&intern_ms, ev[0], ev[1]));
         HERA_CUDA(cudaEventElapsedTime(&csr_ms, ev[1], ev[2]));
         HERA_CUDA(cudaEventElapsedTime(&rank_ms, ev[2], ev[3]));
