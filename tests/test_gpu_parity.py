@@ -121,3 +121,33 @@ def test_batched_build_equals_separate_calls(case, oracle_bin, datasets, tmp_pat
     ora = common.run_dump(oracle_bin, ds, tmp_path / "o.bin", golden["options"], extra=["--rng", "philox", "--seed", "31"])
     gpu = pipeline.run_hot_path(ds, golden["options"], seed=31, batched=True)
     common.assert_sections_equal(ora, gpu, PATH_SECTIONS + GROUP_SECTIONS, case + " batched")
+
+
+def test_rank_and_canon_of_long_lists(oracle_bin, tmp_path):
+    """K4b has three code paths by list length (<= 512: counting on 32-bit keys, <= 2048: bitonic sort in shared
+    memory, longer: counting from global memory); hubs of 40 / 700 / 2600 reads with many equal scores, parallel
+    edges (the same read twice) and all four metrics go through each of them."""
+    import random
+    from telomeri_b200 import pipeline
+    rng = random.Random(5)
+    lines = []
+    for hub, n in (("ctgA", 40), ("ctgB", 700), ("ctgC", 2600)):
+        for k in range(n):
+            name = f"{hub}r{rng.randrange(n * 3 // 4)}"          # repeats: parallel edges -> canon != slot
+            qs = rng.choice((10, 20, 30))
+            matches = rng.choice((900, 940, 960, 970))            # few distinct scores: long runs of ties
+            ts = rng.randrange(0, 3) * 100
+            lines.append(f"{name} 1000 {qs} 990 {rng.choice('+-')} {hub} 50000 {ts} {ts + 980} {matches} 980 0 tp:A:S cm:i:1 s1:i:1 dv:f:0.1\n")
+    d = tmp_path / "hubs"
+    d.mkdir()
+    (d / "rr_overlaps.paf").write_text("")
+    (d / "cr_overlaps.paf").write_text("".join(lines))
+    for metrics in ("es,os", "es_sqrt,os_sqrt"):
+        opts = ["--mode", "max", "--metrics", metrics]
+        ora = common.run_dump(oracle_bin, d, d / "o.bin", opts, extra=["--stage", "graph"])
+        gpu = pipeline.run_hot_path(d, opts, stages="graph")
+        ranks = [f"rank_{METRIC_ID[m]}" for m in metrics.split(",")]
+        deg = np.diff(ora["adj_off"].astype(np.int64))
+        assert deg.max() > 2048 and ((deg > 512) & (deg <= 2048)).any() and (ora["canon"] != np.arange(ora["canon"].size)).any()
+        common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + ranks, f"hubs {metrics}")
+
