@@ -187,7 +187,7 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
         paths = h.export_paths("u_", copy=False)   # views into the pinned mirrors the library copied the result to
         d2h = sum(v.nbytes for v in g.values() if hasattr(v, "nbytes")) + sum(v.nbytes for v in paths.values())
     return {"graph_ms": t_graph, "paths_ms": t_paths, "groups_ms": t_groups, "parse_ms": r1.parse_ms + r2.parse_ms,
-            "parse_rr_ms": r1.parse_ms, "intern_ms": info.intern_ms, "csr_ms": info.csr_ms, "rank_ms": info.rank_ms,
+            "exchange_ms": r1.exchange_ms + r2.exchange_ms, "parse_rr_ms": r1.parse_ms, "intern_ms": info.intern_ms, "csr_ms": info.csr_ms, "rank_ms": info.rank_ms,
             "records": r1.records + r2.records, "kept": r2.kept_total, "nodes": info.nodes, "walks": walks, "walk_entries": steps,
             "unique_paths": n_unique, "pairs": len(g["pair_a1"]), "launches": h.launches - launches0, "d2h": d2h,
             "rr_bytes": r1.bytes, "rr_kept": r1.kept}
@@ -357,7 +357,7 @@ def main():
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
             "paths_per_s": walks / (paths_ms * 1e-3), "unique_paths_per_step": uniq / args.steps,
             "stages_ms_per_step": {k: statistics.mean(s[k] for s in dev_steps) for k in
-                                   ("graph_ms", "parse_ms", "intern_ms", "csr_ms", "rank_ms", "paths_ms", "groups_ms")},
+                                   ("graph_ms", "parse_ms", "exchange_ms", "intern_ms", "csr_ms", "rank_ms", "paths_ms", "groups_ms")},
             "per_step": {"records": s0["records"], "kept_overlaps": s0["kept"], "nodes": s0["nodes"], "walks": s0["walks"],
                          "adjacency_entries_examined": s0["walk_entries"], "anchor_pairs": s0["pairs"]},
             "gpu_launches": int(launches),

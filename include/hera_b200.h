@@ -52,6 +52,7 @@ typedef struct {
     uint64_t bytes;
     float parse_ms;        /* device time of the tokenizer/filter/score kernels (CUDA events) */
     float h2d_ms;          /* host->device copy time, 0 for hera_graph_load_device */
+    float exchange_ms;     /* sharded loads: device time of the all-gather of the kept overlaps (0 otherwise) */
 } hera_load_result;
 
 typedef struct {

@@ -30,7 +30,7 @@ class PathParams(C.Structure):
 
 class LoadResult(C.Structure):
     _fields_ = [("records", C.c_uint64), ("kept", C.c_uint64), ("kept_total", C.c_uint64), ("bytes", C.c_uint64),
-                ("parse_ms", C.c_float), ("h2d_ms", C.c_float)]
+                ("parse_ms", C.c_float), ("h2d_ms", C.c_float), ("exchange_ms", C.c_float)]
 
 
 class GraphInfo(C.Structure):

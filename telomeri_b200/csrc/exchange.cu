@@ -113,6 +113,11 @@ struct LocalExchange final : Exchange {
         }
         hub->barrier();
     }
+    void all_gather_dev(Ctx &c, const uint64_t *d_in, uint64_t *d_out, size_t count) override {
+        std::vector<uint64_t> counts(size, count), displs(size);
+        for (int r = 0; r < size; r++) displs[r] = static_cast<uint64_t>(r) * count;
+        all_gatherv(c, d_in, d_out, counts.data(), displs.data(), sizeof(uint64_t));
+    }
     void all_gatherv(Ctx &c, const void *send, void *recv, const uint64_t *counts, const uint64_t *displs, size_t elem) override {
         prepare_peers(c);
         HERA_CUDA(cudaStreamSynchronize(c.stream));   // my contribution is complete
@@ -133,6 +138,98 @@ struct LocalExchange final : Exchange {
         hub->barrier();                               // nobody reuses a send buffer before every rank has pulled it
     }
 };
+
+}  // namespace
+
+// ---- gather_rows ------------------------------------------------------------------------------
+void Exchange::gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, uint64_t mine0, const uint64_t *counts, const uint64_t *displs) {
+    // my rows move up to their global place: stage them so that no receive window overlaps a source
+    const bool staged = mine0 != n0 + displs[rank] && counts[rank] != 0;
+    char *tmp0 = nullptr;
+    if (staged) {
+        size_t bytes = 0;
+        for (int k = 0; k < ncols; k++) bytes += (counts[rank] * cols[k].elem + 255) / 256 * 256;
+        HERA_CUDA(cudaMallocAsync(&tmp0, bytes, c.stream));
+    }
+    char *tmp = tmp0;
+    begin_batch();
+    for (int k = 0; k < ncols; k++) {
+        char *col = static_cast<char *>(cols[k].base) + n0 * cols[k].elem;
+        const void *send = static_cast<char *>(cols[k].base) + mine0 * cols[k].elem;
+        if (staged) {   // every column gets its own staging area: the batch runs at end_batch
+            HERA_CUDA(cudaMemcpyAsync(tmp, send, counts[rank] * cols[k].elem, cudaMemcpyDeviceToDevice, c.stream));
+            send = tmp;
+            tmp += (counts[rank] * cols[k].elem + 255) / 256 * 256;
+        }
+        all_gatherv(c, send, col, counts, displs, cols[k].elem);
+    }
+    end_batch();
+    if (tmp0) HERA_CUDA(cudaFreeAsync(tmp0, c.stream));
+}
+
+namespace {
+
+constexpr int GR_MAX_COLS = 16, GR_MAX_RANKS = 16;
+struct RowGatherArgs {
+    void *col[GR_MAX_COLS];
+    uint32_t elem[GR_MAX_COLS];
+    const char *window[GR_MAX_RANKS];   // every rank's packed rows (window[r] lives on GPU r)
+    uint64_t count[GR_MAX_RANKS], displ[GR_MAX_RANKS];
+    uint64_t n0, mine0;
+    int ncols, ranks, skip;   // skip: the rank whose rows are already in place (-1: none)
+};
+// Packed layout of a rank's rows inside its window: column after column, each starting on a 16-byte boundary.
+__host__ __device__ inline uint64_t window_col_offset(const uint32_t *elem, int k, uint64_t count) {
+    uint64_t off = 0;
+    for (int j = 0; j < k; j++) off += (count * elem[j] + 15) / 16 * 16;
+    return off;
+}
+
+// blockIdx.y = column.  Copies this rank's rows of the column into its window (4-byte words, the tail byte-wise).
+__global__ void __launch_bounds__(256) rows_pack_kernel(RowGatherArgs a, int me, char *window) {
+    const int k = blockIdx.y;
+    const uint64_t bytes = a.count[me] * a.elem[k];
+    const char *src = static_cast<const char *>(a.col[k]) + a.mine0 * a.elem[k];
+    char *dst = window + window_col_offset(a.elem, k, a.count[me]);
+    const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x, t = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (a.elem[k] % 4 == 0) {
+        for (uint64_t i = t; i < bytes / 4; i += stride) reinterpret_cast<uint32_t *>(dst)[i] = reinterpret_cast<const uint32_t *>(src)[i];
+    } else {
+        for (uint64_t i = t; i < bytes; i += stride) dst[i] = src[i];
+    }
+}
+
+// blockIdx.y = column, blockIdx.z = source rank.  Reads rank z's packed rows of the column out of ITS memory
+// (peer loads over NVLink; 16 bytes per load, the window side is aligned) and writes them to their global place
+// in this rank's column.
+__global__ void __launch_bounds__(256) rows_pull_kernel(RowGatherArgs a) {
+    const int k = blockIdx.y, r = blockIdx.z;
+    const uint64_t bytes = a.count[r] * a.elem[k];
+    if (!bytes || r == a.skip) return;
+    const char *src = a.window[r] + window_col_offset(a.elem, k, a.count[r]);
+    char *dst = static_cast<char *>(a.col[k]) + (a.n0 + a.displ[r]) * a.elem[k];
+    const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x, t = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint32_t e = a.elem[k];
+    if (e == 4) {
+        for (uint64_t i = t; i < (bytes + 15) / 16; i += stride) {
+            const uint4 v = reinterpret_cast<const uint4 *>(src)[i];
+            const uint64_t w = i * 4, words = bytes / 4;
+            uint32_t *d = reinterpret_cast<uint32_t *>(dst);
+            if (w + 4 <= words) { d[w] = v.x; d[w + 1] = v.y; d[w + 2] = v.z; d[w + 3] = v.w; }
+            else { if (w < words) d[w] = v.x; if (w + 1 < words) d[w + 1] = v.y; if (w + 2 < words) d[w + 2] = v.z; }
+        }
+    } else if (e == 8) {
+        for (uint64_t i = t; i < (bytes + 15) / 16; i += stride) {
+            const uint4 v = reinterpret_cast<const uint4 *>(src)[i];
+            const uint64_t w = i * 2, words = bytes / 8;
+            uint2 *d = reinterpret_cast<uint2 *>(dst);
+            d[w] = make_uint2(v.x, v.y);
+            if (w + 1 < words) d[w + 1] = make_uint2(v.z, v.w);
+        }
+    } else {
+        for (uint64_t i = t; i < bytes; i += stride) dst[i] = src[i];
+    }
+}
 
 // ---- NcclExchange -----------------------------------------------------------------------------
 struct NcclApi {
@@ -189,10 +286,13 @@ NcclApi &nccl_api() {
 
 struct NcclExchange final : Exchange {
     ncclComm_t comm = nullptr;
-    uint64_t *d_small = nullptr;   // staging of host gathers
-    size_t d_small_cap = 0;
+    uint64_t *d_small = nullptr, *h_small = nullptr;   // device / pinned staging of host gathers
+    size_t d_small_cap = 0, h_small_cap = 0;
     ~NcclExchange() override {
         if (d_small) cudaFree(d_small);
+        if (h_small) cudaFreeHost(h_small);
+        if (d_token) cudaFree(d_token);
+        close_windows();
         if (comm) nccl_api().CommDestroy(comm);
     }
     const char *transport() const override { return "nccl"; }
@@ -204,11 +304,98 @@ struct NcclExchange final : Exchange {
             HERA_CUDA(cudaMalloc(&d_small, need * 2 * sizeof(uint64_t)));
             d_small_cap = need * 2;
         }
+        if (need > h_small_cap) {
+            if (h_small) HERA_CUDA(cudaFreeHost(h_small));
+            HERA_CUDA(cudaHostAlloc(&h_small, need * 2 * sizeof(uint64_t), cudaHostAllocDefault));
+            h_small_cap = need * 2;
+        }
         uint64_t *d_in = d_small, *d_out = d_small + count;
-        HERA_CUDA(cudaMemcpyAsync(d_in, in, sizeof(uint64_t) * count, cudaMemcpyHostToDevice, c.stream));
+        std::memcpy(h_small, in, sizeof(uint64_t) * count);   // pinned staging: pageable copies would serialise with the stream
+        HERA_CUDA(cudaMemcpyAsync(d_in, h_small, sizeof(uint64_t) * count, cudaMemcpyHostToDevice, c.stream));
         HERA_NCCL(n.AllGather(d_in, d_out, static_cast<size_t>(count), ncclUint64, comm, c.stream));
-        HERA_CUDA(cudaMemcpyAsync(out, d_out, sizeof(uint64_t) * count * size, cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaMemcpyAsync(h_small + count, d_out, sizeof(uint64_t) * count * size, cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
+        std::memcpy(out, h_small + count, sizeof(uint64_t) * count * size);
+    }
+    void all_gather_dev(Ctx &c, const uint64_t *d_in, uint64_t *d_out, size_t count) override {
+        HERA_NCCL(nccl_api().AllGather(d_in, d_out, count, ncclUint64, comm, c.stream));
+    }
+
+    // ---- peer windows: one cudaMalloc'ed buffer per rank, mapped by every other rank through CUDA IPC ----
+    char *window = nullptr;
+    size_t window_cap = 0;
+    std::vector<char *> peer_window;   // [r] = rank r's window as seen from this process (mine for r == rank)
+    unsigned gather_seq = 0;
+    int ipc_state = 0;                 // 0 untested, 1 usable, -1 not available (fall back to NCCL broadcasts)
+    uint64_t *d_token = nullptr;       // two words for the stream-ordered rendezvous
+
+    void close_windows() {
+        for (int r = 0; r < static_cast<int>(peer_window.size()); r++)
+            if (r != rank && peer_window[r]) cudaIpcCloseMemHandle(peer_window[r]);
+        peer_window.clear();
+        if (window) cudaFree(window);
+        window = nullptr;
+        window_cap = 0;
+    }
+    // Every rank calls this with the same `need` (it is computed from the gathered counts).
+    bool ensure_windows(Ctx &c, size_t need) {
+        if (ipc_state < 0) return false;
+        if (ipc_state == 0 && (size > GR_MAX_RANKS || getenv("HERA_NO_PEER_WINDOWS"))) { ipc_state = -1; return false; }
+        if (need <= window_cap) return true;
+        HERA_CUDA(cudaStreamSynchronize(c.stream));   // nobody still reads the old windows: every pull is followed by a collective
+        barrier(c);
+        close_windows();
+        const size_t cap = (need + need / 2 + (1u << 20)) / 512 * 512;   // two halves, each a multiple of 256 bytes
+        uint64_t mine[9] = {0};
+        cudaIpcMemHandle_t h;
+        static_assert(sizeof(h) == 64, "IPC handle is 64 bytes");
+        bool ok = cudaMalloc(&window, cap) == cudaSuccess && cudaIpcGetMemHandle(&h, window) == cudaSuccess;
+        if (ok) { std::memcpy(mine, &h, 64); mine[8] = 1; } else cudaGetLastError();
+        std::vector<uint64_t> all(static_cast<size_t>(size) * 9);
+        all_gather_host(c, mine, 9, all.data());
+        for (int r = 0; r < size; r++) ok = ok && all[static_cast<size_t>(r) * 9 + 8] == 1;
+        peer_window.assign(size, nullptr);
+        for (int r = 0; ok && r < size; r++) {
+            if (r == rank) { peer_window[r] = window; continue; }
+            cudaIpcMemHandle_t hr;
+            std::memcpy(&hr, &all[static_cast<size_t>(r) * 9], 64);
+            void *p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+            peer_window[r] = static_cast<char *>(p);
+        }
+        // all ranks must take the same path
+        uint64_t vote = ok ? 1 : 0;
+        std::vector<uint64_t> votes(size);
+        all_gather_host(c, &vote, 1, votes.data());
+        for (uint64_t v : votes) ok = ok && v == 1;
+        if (!ok) { close_windows(); ipc_state = -1; return false; }
+        window_cap = cap;
+        ipc_state = 1;
+        if (!d_token) HERA_CUDA(cudaMalloc(&d_token, (1 + GR_MAX_RANKS) * sizeof(uint64_t)));
+        return true;
+    }
+
+    void gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, uint64_t mine0, const uint64_t *counts, const uint64_t *displs) override {
+        RowGatherArgs a{};
+        HERA_REQUIRE(ncols <= GR_MAX_COLS, 36, "gather_rows: too many columns");
+        uint64_t max_rows = 0;
+        for (int r = 0; r < size; r++) max_rows = std::max(max_rows, counts[r]);
+        for (int k = 0; k < ncols; k++) { a.col[k] = cols[k].base; a.elem[k] = cols[k].elem; }
+        const size_t need = window_col_offset(a.elem, ncols, max_rows) + 16;
+        if (!ensure_windows(c, 2 * ((need + 255) / 256 * 256))) { Exchange::gather_rows(c, cols, ncols, n0, mine0, counts, displs); return; }
+        // The windows have two halves used in turn: a half is written again two gathers later, and no rank gets past
+        // the rendezvous of the gather in between before every rank has finished pulling from it.
+        const size_t half = (gather_seq++ & 1u) ? window_cap / 2 : 0;
+        for (int r = 0; r < size; r++) { a.window[r] = peer_window[r] + half; a.count[r] = counts[r]; a.displ[r] = displs[r]; }
+        a.n0 = n0; a.mine0 = mine0; a.ncols = ncols; a.ranks = size;
+        a.skip = mine0 == n0 + displs[rank] ? rank : -1;
+        if (counts[rank]) rows_pack_kernel<<<dim3(148, ncols), 256, 0, c.stream>>>(a, rank, window + half);
+        // stream-ordered rendezvous: an NCCL all-gather of one word completes on a rank only after every rank's
+        // stream has passed its pack kernel
+        HERA_NCCL(nccl_api().AllGather(d_token, d_token + 1, 1, ncclUint64, comm, c.stream));
+        rows_pull_kernel<<<dim3(74, ncols, size), 256, 0, c.stream>>>(a);
+        c.launches.count += 2;
+        HERA_CUDA(cudaGetLastError());
     }
     void all_gatherv(Ctx &c, const void *send, void *recv, const uint64_t *counts, const uint64_t *displs, size_t elem) override {
         NcclApi &n = nccl_api();

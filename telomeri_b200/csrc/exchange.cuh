@@ -33,10 +33,20 @@ struct Exchange {
     // overlap any rank's receive window except its own (send == recv + displs[rank] * elem is allowed).
     // Stream-ordered on the context's stream.
     virtual void all_gatherv(Ctx &c, const void *send, void *recv, const uint64_t *counts, const uint64_t *displs, size_t elem) = 0;
+    // Equal-size all-gather of device memory: every rank contributes `count` 64-bit values at d_in and receives
+    // all of them at d_out (rank r's at d_out + r * count; d_in may be d_out + rank * count).  Stream-ordered,
+    // no host synchronisation on the NCCL transport.
+    virtual void all_gather_dev(Ctx &c, const uint64_t *d_in, uint64_t *d_out, size_t count) = 0;
     // Several all_gatherv calls between begin_batch and end_batch may be issued as one operation (one NCCL
     // group = one launch); their send and receive buffers must stay untouched until end_batch returns.
     virtual void begin_batch() {}
     virtual void end_batch() {}
+    // Rows [mine0, mine0 + counts[rank]) of every column (structure-of-arrays table) are this rank's; afterwards every
+    // rank holds every rank's rows, rank r's at n0 + displs[r] (mine0 is n0, or already n0 + displs[rank]).  The base implementation issues one all_gatherv per
+    // column in one batch; the NCCL transport pulls the rows straight out of the peers' memory over NVLink with
+    // its own kernel when the ranks can map each other's buffers.
+    struct Column { void *base; uint32_t elem; };
+    virtual void gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, uint64_t mine0, const uint64_t *counts, const uint64_t *displs);
     // Host barrier (after synchronising the context's stream).
     virtual void barrier(Ctx &c) = 0;
     // Called when this rank fails inside a collective call: wakes the ranks waiting for it.

@@ -224,6 +224,11 @@ __global__ void __launch_bounds__(128) node_exact_kernel(uint32_t N, const uint3
     if (lane == 0) node_exact[x] = static_cast<uint8_t>(flags);
 }
 
+// adj_off at the node-range boundaries of the ranks (N r / ranks), widened for the host
+__global__ void node_cut_kernel(const uint32_t *__restrict__ off, uint64_t N, int ranks, uint64_t *__restrict__ out) {
+    for (int r = threadIdx.x; r <= ranks; r += blockDim.x) out[r] = off[N * r / ranks];
+}
+
 __global__ void anchor_list_kernel(uint64_t N, const uint8_t *__restrict__ node_anchor, const uint32_t *__restrict__ anchor_scan, uint32_t *__restrict__ anchor_ids) {
     const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < N && node_anchor[i]) anchor_ids[anchor_scan[i]] = static_cast<uint32_t>(i);
@@ -612,7 +617,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         HERA_CUDA(cudaMallocAsync(&d_max_deg, sizeof(uint32_t), c.stream));
         HERA_CUDA(cudaMemsetAsync(d_max_deg, 0, sizeof(uint32_t), c.stream));
         HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.a_es.p, g.a_os.p, g.a_nbr.p, g.node_exact.p, d_max_deg);
-        c.h_counters.reserve(16);
+        c.h_counters.reserve(32 + xch_size(c));   // [14] late results, [15] max degree, [16..] slice boundaries of the ranks
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 15, d_max_deg, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));   // read after the final sync below
         HERA_CUDA(cudaFreeAsync(d_max_deg, c.stream));
         HERA_CUDA(cudaFreeAsync(keys32, c.stream)); HERA_CUDA(cudaFreeAsync(keys_alt, c.stream)); HERA_CUDA(cudaFreeAsync(vals_alt, c.stream));
@@ -620,6 +625,16 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
 
         // ---- rank permutations + canonical slots: each rank does its share of the nodes, the slices are all-gathered
         const int ranks = xch_size(c), me = xch_rank(c);
+        cudaEvent_t cuts_ready = nullptr;
+        if (ranks > 1) {   // slot ranges of the ranks' node ranges: read now, needed (on the host) once the rank kernels are queued
+            uint64_t *d_cut = nullptr;
+            HERA_CUDA(cudaMallocAsync(&d_cut, (ranks + 1) * sizeof(uint64_t), c.stream));
+            HERA_LAUNCH(c, node_cut_kernel, 1, 64, 0, g.adj_off.p, N, ranks, d_cut);
+            HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 16, d_cut, (ranks + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
+            HERA_CUDA(cudaFreeAsync(d_cut, c.stream));
+            HERA_CUDA(cudaEventCreateWithFlags(&cuts_ready, cudaEventDisableTiming));
+            HERA_CUDA(cudaEventRecord(cuts_ready, c.stream));
+        }
         const uint64_t n_lo = N * me / ranks, n_hi = N * (me + 1) / ranks;
         const unsigned my_nodes = static_cast<unsigned>(n_hi - n_lo);
         RankPtrs rp{};
@@ -634,16 +649,16 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             HERA_LAUNCH(c, (rank_canon_kernel<2048, 512, true>), my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.a_es.p, g.a_os.p, metrics_mask, rp, g.canon.p, static_cast<uint32_t>(n_lo));
         }
         if (ranks > 1) {
-            std::vector<uint32_t> cut(ranks + 1);
-            for (int r = 0; r <= ranks; r++) HERA_CUDA(cudaMemcpyAsync(&cut[r], g.adj_off.p + N * r / ranks, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
-            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            HERA_CUDA(cudaEventSynchronize(cuts_ready));   // the slice boundaries left the device before the rank kernels started
+            cudaEventDestroy(cuts_ready);
+            const uint64_t *cut = c.h_counters.p + 16;
             std::vector<uint64_t> counts(ranks), displs(ranks);
             for (int r = 0; r < ranks; r++) { displs[r] = cut[r]; counts[r] = cut[r + 1] - cut[r]; }
-            c.xch->begin_batch();
-            c.xch->all_gatherv(c, g.canon.p + displs[me], g.canon.p, counts.data(), displs.data(), sizeof(uint32_t));
+            Exchange::Column cols[5] = {{g.canon.p, 4}};
+            int ncols = 1;
             for (int m = 0; m < 4; m++)
-                if (g.rank_ready[m]) c.xch->all_gatherv(c, g.rank[m].p + displs[me], g.rank[m].p, counts.data(), displs.data(), sizeof(uint32_t));
-            c.xch->end_batch();
+                if (g.rank_ready[m]) cols[ncols++] = {g.rank[m].p, 4};
+            c.xch->gather_rows(c, cols, ncols, 0, displs[me], counts.data(), displs.data());
         }
         HERA_CUDA(cudaEventRecord(ev[3], c.stream));
         if (verify_done) {

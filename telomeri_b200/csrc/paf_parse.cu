@@ -292,6 +292,7 @@ struct ParseArgs {
     uint64_t n;                 // bytes of text available (whole file, or slice + look-ahead)
     uint64_t owned;             // tokens that start at a byte >= owned belong to the next rank (== n for a whole file)
     uint64_t tok_base0;         // global index of the first token that starts in this text (0 for a whole file)
+    const unsigned long long *tok_base0_dev;   // sharded load: the same number, computed on the device from all ranks' counts
     int prev_nonws;             // the byte before text[0] is part of a token
     int at_eof;                 // text[n] is the end of the file
     uint32_t tiles;
@@ -591,7 +592,7 @@ __device__ __forceinline__ TileFrame frame_tile(const ParseArgs &a, uint32_t til
     const uint32_t tid = threadIdx.x;
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
     TileFrame f;
-    f.tok_base = a.tok_base0 + base;
+    f.tok_base = (a.tok_base0_dev ? *a.tok_base0_dev : a.tok_base0) + base;
     f.first_rec_ord = static_cast<uint32_t>((16 - (f.tok_base & 15)) & 15);
     f.nrec = tile_tokens > f.first_rec_ord ? (tile_tokens - f.first_rec_ord + 15) / 16 : 0;  // records starting in this tile
     uint32_t starts[PF_WPT];
@@ -816,6 +817,15 @@ __global__ void __launch_bounds__(256) paf_count_tokens_kernel(const uint8_t *__
     if (lane_id() == 0 && mine) atomicAdd(out, mine);
 }
 
+// tokens before rank `me`'s slice and tokens of all slices, from the gathered per-rank counts
+__global__ void shard_prefix_kernel(const uint64_t *__restrict__ counts, int ranks, int me, unsigned long long *out) {
+    if (threadIdx.x) return;
+    unsigned long long before = 0, all = 0;
+    for (int r = 0; r < ranks; r++) { if (r < me) before += counts[r]; all += counts[r]; }
+    out[0] = before;
+    out[1] = all;
+}
+
 __global__ void pad_text_kernel(uint8_t *text, uint64_t n, uint64_t padded) {
     const uint64_t i = n + static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < padded) text[i] = '\n';
@@ -826,20 +836,6 @@ static KeptPtrs kept_ptrs(KeptTable &k) {
 }
 
 uint64_t padded_text_size(uint64_t n) { return (n / PF_TILE + 2) * static_cast<uint64_t>(PF_TILE); }
-
-// Moves this rank's new kept rows [n0, n0 + counts[rank]) to their global place n0 + displs[rank] and
-// receives the other ranks' rows: one variable-size all-gather per column of the kept table.
-template <typename T>
-static void gather_column(Ctx &c, T *col, uint64_t n0, const uint64_t *counts, const uint64_t *displs, char *&tmp) {
-    const int r = xch_rank(c);
-    const void *send = col + n0;
-    if (displs[r] != 0 && counts[r]) {   // my rows move up: stage them so that no receive window overlaps the source
-        HERA_CUDA(cudaMemcpyAsync(tmp, col + n0, counts[r] * sizeof(T), cudaMemcpyDeviceToDevice, c.stream));
-        send = tmp;
-        tmp += (counts[r] * sizeof(T) + 255) / 256 * 256;   // every column gets its own staging area: the batch runs at end_batch
-    }
-    c.xch->all_gatherv(c, send, col + n0, counts, displs, sizeof(T));
-}
 
 void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out) {
     const uint64_t n = text.n;
@@ -857,41 +853,42 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     const uint64_t max_new = owned / 24 + 2;
     c.kept.reserve(c.kept.n + max_new, c.stream);
 
-    c.counters.reserve(64 + 2ull * tiles);
+    // device block: [0, 8) ParseCounters, [12] cut, [13] my token count, [14] tokens before my slice, [15] tokens of all
+    // slices, [16, 16 + 2 tiles) chain states, then what the ranks tell each other: token counts, {kept, first bad} pairs
+    const uint64_t gather_at = 16 + 2ull * tiles;
+    c.counters.reserve(gather_at + 3ull * ranks + 8);
     ParseCounters *ctr = reinterpret_cast<ParseCounters *>(c.counters.p);
     unsigned long long *tok_state = reinterpret_cast<unsigned long long *>(c.counters.p + 16);
     unsigned long long *kept_state = tok_state + tiles;
-    HERA_CUDA(cudaMemsetAsync(c.counters.p, 0, (16 + 2ull * tiles) * sizeof(uint64_t), c.stream));
+    HERA_CUDA(cudaMemsetAsync(c.counters.p, 0, (gather_at + 3ull * ranks) * sizeof(uint64_t), c.stream));
     ParseCounters init{};
     init.first_bad_rec = ~0ull;
     init.first_bad_off = ~0ull;
     HERA_CUDA(cudaMemcpyAsync(ctr, &init, sizeof(init), cudaMemcpyHostToDevice, c.stream));
-    c.h_counters.reserve(16);
+    c.h_counters.reserve(16 + 3ull * ranks);
 
     FilterDev fd{c.fp.mode, static_cast<float>(c.fp.min_overlap_length), c.fp.min_overlap_percentage,
                  static_cast<float>(c.fp.max_overhang_length), c.fp.max_overhang_percentage};
     const uint64_t rec_limit = test_load_num > 0 ? static_cast<uint64_t>(test_load_num) + 1 : ~0ull;
 
-    cudaEvent_t ev0, ev1;
+    cudaEvent_t ev0, ev1, ev2;
     HERA_CUDA(cudaEventCreate(&ev0));
     HERA_CUDA(cudaEventCreate(&ev1));
+    HERA_CUDA(cudaEventCreate(&ev2));
     maybe_flush_l2(c);
     HERA_CUDA(cudaEventRecord(ev0, c.stream));
 
-    // sharded: where do my records start?  tokens before my slice = sum over the earlier ranks
-    uint64_t tok_base0 = 0, tokens_all = 0;
-    std::vector<uint64_t> gathered(static_cast<size_t>(ranks) * 2);
+    // sharded: where do my records start?  tokens before my slice = sum over the earlier ranks, exchanged and added
+    // up on the device (no host round trip before the parse kernel)
+    uint64_t *d_tok_all = c.counters.p + gather_at, *d_kb_all = d_tok_all + ranks;
     if (sharded) {
         unsigned long long *d_tok = reinterpret_cast<unsigned long long *>(c.counters.p + 13);
         if (owned) HERA_LAUNCH(c, paf_count_tokens_kernel, std::min<unsigned>(div_up(div_up(owned, 16), 256), 148 * 8), 256, 0, text.bytes.p, owned, shard->prev_nonws ? 1 : 0, d_tok);
-        HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 13, d_tok, sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
-        HERA_CUDA(cudaStreamSynchronize(c.stream));
-        const uint64_t mine = c.h_counters.p[13];
-        c.xch->all_gather_host(c, &mine, 1, gathered.data());
-        for (int r = 0; r < ranks; r++) { if (r < me) tok_base0 += gathered[r]; tokens_all += gathered[r]; }
+        c.xch->all_gather_dev(c, c.counters.p + 13, d_tok_all, 1);
+        HERA_LAUNCH(c, shard_prefix_kernel, 1, 32, 0, d_tok_all, ranks, me, reinterpret_cast<unsigned long long *>(c.counters.p + 14));
     }
 
-    ParseArgs a{text.bytes.p, n, owned, tok_base0, sharded && shard->prev_nonws ? 1 : 0, (!sharded || shard->at_eof) ? 1 : 0,
+    ParseArgs a{text.bytes.p, n, owned, 0, sharded ? reinterpret_cast<const unsigned long long *>(c.counters.p + 14) : nullptr, sharded && shard->prev_nonws ? 1 : 0, (!sharded || shard->at_eof) ? 1 : 0,
                 tiles, file_id, anchors ? 1 : 0, rec_limit, c.kept.n, fd, kept_ptrs(c.kept), tok_state, kept_state, ctr};
     int sms = 148;
     HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
@@ -899,18 +896,22 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     HERA_LAUNCH(c, paf_parse_kernel, std::min<uint32_t>(tiles, static_cast<uint32_t>(sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, a);
     HERA_CUDA(cudaEventRecord(ev1, c.stream));
 
+    if (sharded) {   // every rank learns every rank's kept count and whether anybody met an irregular record
+        c.xch->all_gather_dev(c, c.counters.p + 2, d_kb_all, 2);   // ParseCounters::kept, first_bad_rec
+        HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 16, d_tok_all, 3ull * ranks * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
+    }
     HERA_CUDA(cudaMemcpyAsync(c.h_counters.p, ctr, sizeof(ParseCounters), cudaMemcpyDeviceToHost, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
     ParseCounters hc = *reinterpret_cast<ParseCounters *>(c.h_counters.p);
+    uint64_t tokens_all = 0;
+    for (int r = 0; sharded && r < ranks; r++) tokens_all += c.h_counters.p[16 + r];
 
     const uint64_t T = sharded ? tokens_all : hc.total_tokens;
     uint64_t records = T / 16 + ((T % 16) >= 12 ? 1 : 0);
     if (records > rec_limit) records = rec_limit;
     uint64_t kept_new = hc.kept;
     if (sharded) {
-        // every rank learns every rank's kept count and whether anybody met an irregular record
-        const uint64_t mine[2] = {hc.kept, hc.first_bad_rec};
-        c.xch->all_gather_host(c, mine, 2, gathered.data());
+        const uint64_t *gathered = c.h_counters.p + 16 + ranks;
         std::vector<uint64_t> counts(ranks), displs(ranks);
         uint64_t total = 0, first_bad = ~0ull;
         for (int r = 0; r < ranks; r++) {
@@ -922,26 +923,17 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         if (first_bad < records) {
             cudaEventDestroy(ev0);
             cudaEventDestroy(ev1);
+            cudaEventDestroy(ev2);
             throw Error{20, "irregular PAF record " + std::to_string(first_bad) + ": formatted extraction leaves the 16-token grid there; load this file unsharded"};
         }
         c.kept.reserve(c.kept.n + total, c.stream, c.kept.n + counts[me]);
         KeptTable &k = c.kept;
         const uint64_t n0 = k.n;
-        char *tmp0 = nullptr;
-        HERA_CUDA(cudaMallocAsync(&tmp0, std::max<uint64_t>(counts[me], 1) * 80 + 15 * 256, c.stream));   // 73 bytes per row + alignment
-        char *tmp = tmp0;
-        c.xch->begin_batch();
-        gather_column(c, k.qs.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.qe.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.ts.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.te.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.qlen.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.tlen.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.rec.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.os.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.si.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.es.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.flags.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.qhash.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.thash.p, n0, counts.data(), displs.data(), tmp);
-        gather_column(c, k.qname.p, n0, counts.data(), displs.data(), tmp); gather_column(c, k.tname.p, n0, counts.data(), displs.data(), tmp);
-        c.xch->end_batch();
-        HERA_CUDA(cudaFreeAsync(tmp0, c.stream));
+        const Exchange::Column cols[15] = {{k.qs.p, 4}, {k.qe.p, 4}, {k.ts.p, 4}, {k.te.p, 4}, {k.qlen.p, 4}, {k.tlen.p, 4}, {k.rec.p, 4},
+                                           {k.os.p, 4}, {k.si.p, 4}, {k.es.p, 4}, {k.flags.p, 1},
+                                           {k.qhash.p, 8}, {k.thash.p, 8}, {k.qname.p, 8}, {k.tname.p, 8}};
+        c.xch->gather_rows(c, cols, 15, n0, n0, counts.data(), displs.data());
+        HERA_CUDA(cudaEventRecord(ev2, c.stream));
         c.own_rows.push_back({n0 + displs[me], n0 + displs[me] + counts[me]});
         kept_new = total;
     } else if (hc.first_bad_rec < records) {
@@ -969,9 +961,15 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         out->kept_total = c.kept.n;
         out->bytes = n;
         HERA_CUDA(cudaEventElapsedTime(&out->parse_ms, ev0, ev1));
+        out->exchange_ms = 0;
+        if (sharded) {
+            HERA_CUDA(cudaEventSynchronize(ev2));
+            HERA_CUDA(cudaEventElapsedTime(&out->exchange_ms, ev1, ev2));
+        }
     }
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
+    cudaEventDestroy(ev2);
 }
 
 }  // namespace hera
