@@ -39,7 +39,7 @@ def test_struct_layouts_match_header():
     from telomeri_b200 import capi
     assert ctypes.sizeof(capi.FilterParams) == 40
     assert ctypes.sizeof(capi.PathParams) == 32
-    assert ctypes.sizeof(capi.LoadResult) == 40
+    assert ctypes.sizeof(capi.LoadResult) == 48   # 4 x u64 + parse_ms, h2d_ms, exchange_ms + padding
     assert ctypes.sizeof(capi.GraphInfo) == 48
     assert ctypes.sizeof(capi.WalkStats) == 32
     assert ctypes.sizeof(capi.GraphView) == 24 + 22 * 8
