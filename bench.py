@@ -193,6 +193,15 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
             "rr_bytes": r1.bytes, "rr_kept": r1.kept}
 
 
+def parse_traffic():
+    """DRAM bytes of one paf_parse_kernel launch on the rr text from the committed `ncu --set full` capture (per launch, like `achieved`)."""
+    try:
+        t = json.loads((ROOT / "profiles" / "parse_kernel_traffic.json").read_text())
+        return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 class Slice:
     """This rank's byte range of a PAF file (hera_shard_range): pinned host copy + device copy."""
 
@@ -319,6 +328,9 @@ def main():
     with ClockSampler(local_rank) as clocks:
         dev_steps, _ = timed(True, False, args.steps)
         e2e_steps, e2e_wall = timed(False, True, args.steps)
+    # measured ceiling for the walks: dependent list gathers on the finalized graph of the last step, same resident warps
+    h.probe_list_gather(64, 64)
+    gather_gbs, gather_ms = h.probe_list_gather(64, 256)
     # roofline leg: the dominant streaming kernel (paf_parse_kernel on the rr text) timed alone by its own CUDA events, L2 flushed
     h.set_option("flush_l2", 1)
     parse_ms = []
@@ -366,9 +378,17 @@ def main():
                     "note": "graph build from pinned host buffers (H2D inside the timed region); whole_step_ms adds walks, groups and the D2H read of the result"},
             "roofline": {"bound": "hbm", "kernel": "paf_parse_kernel (rr text)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s", "algorithmic_bytes": algo_bytes,
-                         "kernel_ms": parse_ms, "traffic": None},
+                         "kernel_ms": parse_ms, "traffic": parse_traffic()},
+            # north_star: the pointer-chasing walks are reported against the measured random-gather ceiling
+            "roofline_walks": {"bound": "dependent list gather (L2/HBM latency)", "kernel": "walk_mc_kernel x2 + walk_det_kernel x2 in flight together",
+                               "achieved": s0["walk_entries"] * 16 / (statistics.mean(s["paths_ms"] for s in dev_steps) * 1e-3) / 1e9 / world,
+                               "peak": gather_gbs, "unit": "GB/s per GPU", "frac": None,
+                               "peak_source": f"hera_probe_list_gather(64 warps/SM, 256 hops) on this graph: {gather_ms:.3f} ms",
+                               "algorithmic_bytes": int(s0["walk_entries"]) * 16},
             "clocks": clocks.summary(),
         }
+        rw = line["roofline_walks"]
+        rw["frac"] = rw["achieved"] / rw["peak"] if rw["peak"] else None
         if world == 1 and not args.no_cpu_baseline:
             ref = run_reference_sample(ds, 1, 0)
             line["cpu_baseline"] = {"value": ref["overlaps_per_s"], "unit": "overlaps/s", "cores": 1, "kind": ref["kind"], "sample": ref["sample"],

@@ -133,6 +133,11 @@ uint64_t hera_kernel_launches(hera_ctx *ctx);    /* kernels launched by this con
 int hera_timer_start(hera_ctx *ctx);
 int hera_timer_stop(hera_ctx *ctx, float *ms);   /* synchronises the stream */
 int hera_set_option(hera_ctx *ctx, const char *key, int64_t value);
+/* Measured ceiling for the walks on the finalized graph: warps_per_sm resident warps per SM each make `hops`
+ * dependent hops, reading the whole adjacency list of the current node (16-byte entries) and moving on to a
+ * neighbour found there -- the memory behaviour of a walk step (src/PathManager.cpp:52-113) without roulette,
+ * visited set or random numbers.  Reports list bytes per second. */
+int hera_probe_list_gather(hera_ctx *ctx, uint32_t warps_per_sm, uint32_t hops, double *gbytes_per_s, float *ms);
 
 /* ---- sharded runs: one rank per GPU ---------------------------------------------
  * No reference counterpart (the reference is single-threaded, src/Main.cpp).  A communicator is

@@ -78,6 +78,7 @@ SIGNATURES = {
     "hera_timer_start": (C.c_int, [C.c_void_p]),
     "hera_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "hera_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
+    "hera_probe_list_gather": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
     "hera_graph_set_filter": (C.c_int, [C.c_void_p, C.POINTER(FilterParams)]),
     "hera_graph_load_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_bytes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
@@ -180,6 +181,12 @@ class Hera:
         ms = C.c_float()
         self._check(self.lib.hera_timer_stop(self.h, C.byref(ms)))
         return ms.value
+
+    def probe_list_gather(self, warps_per_sm=64, hops=256):
+        """Measured list-walking ceiling on the finalized graph: (GB/s of adjacency entries, ms)."""
+        gbs, ms = C.c_double(), C.c_float()
+        self._check(self.lib.hera_probe_list_gather(self.h, int(warps_per_sm), int(hops), C.byref(gbs), C.byref(ms)))
+        return gbs.value, ms.value
 
     def set_option(self, key, value):
         self._check(self.lib.hera_set_option(self.h, key.encode(), int(value)))

@@ -109,6 +109,12 @@ int hera_timer_stop(hera_ctx *ctx, float *ms) {
     HERA_API_END
 }
 
+int hera_probe_list_gather(hera_ctx *ctx, uint32_t warps_per_sm, uint32_t hops, double *gbytes_per_s, float *ms) {
+    HERA_API_BEGIN(ctx)
+    hera::probe_list_gather(c, warps_per_sm, hops, gbytes_per_s, ms);
+    HERA_API_END
+}
+
 int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
     HERA_API_BEGIN(ctx)
     HERA_REQUIRE(key != nullptr, 101, "null option name");

@@ -177,6 +177,7 @@ void save_graph_cache(Ctx &c, const char *path);
 void load_graph_cache(Ctx &c, const char *path);
 void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);
 void walk_deterministic(Ctx &c, int metric, hera_walk_stats *out);
+void probe_list_gather(Ctx &c, uint32_t warps_per_sm, uint32_t hops, double *gbytes_per_s, float *ms_out);
 void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out);
 void unique_paths(Ctx &c, uint64_t *n_unique);
 void export_paths(Ctx &c, hera_paths_view *out);

@@ -794,6 +794,60 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
     for (int i = 0; i < n; i++) job_finish(c, jobs[i], out ? out + i : nullptr);
 }
 
+// ---- measured ceiling for list walking (north_star: "the pointer-chasing walks are reported against the measured
+// random-gather roofline") -------------------------------------------------------------------------------------
+// The same memory behaviour as a walk step and nothing else: a warp reads the whole adjacency list of its current
+// node as 16-byte entries, then hops to a neighbour it found there (the next address depends on loaded data), with
+// the walk kernels' number of resident warps.  No roulette, no visited set, no random numbers.
+__global__ void __launch_bounds__(WK_THREADS) list_gather_probe_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t N,
+                                                                       uint32_t hops, unsigned long long *bytes_out, uint32_t *sink) {
+    const uint32_t lane = threadIdx.x & 31u, w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t x = (w * 2654435761u) % N, acc = 0;
+    unsigned long long bytes = 0;
+    for (uint32_t h = 0; h < hops; h++) {
+        const uint32_t base = off[x], deg = off[x + 1] - base;
+        const uint32_t pick = deg ? ((w + h) * 0x9E3779B1u >> 8) % deg : 0;
+        uint32_t cand = x;
+        for (uint32_t k = lane; k < deg; k += 32) {
+            const uint4 e = adj4[base + k];
+            acc ^= e.y + e.z;
+            if (k == pick) cand = e.x & 0x7fffffffu;
+        }
+        bytes += static_cast<unsigned long long>(deg) * 16;
+        x = deg ? __shfl_sync(0xffffffffu, cand, pick & 31u) : (x + 1) % N;
+    }
+    if (lane == 0) atomicAdd(bytes_out, bytes);
+    if (acc == 0x12345678u) *sink = acc;
+}
+
+void probe_list_gather(Ctx &c, uint32_t warps_per_sm, uint32_t hops, double *gbytes_per_s, float *ms_out) {
+    GraphTables &g = c.g;
+    HERA_REQUIRE(g.ready && g.N > 0, 102, "hera_probe_list_gather: finalize a graph first");
+    int sms = 148;
+    HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
+    const unsigned warps = static_cast<unsigned>(sms) * std::max(1u, std::min(64u, warps_per_sm));
+    unsigned long long *d_bytes = nullptr;
+    HERA_CUDA(cudaMallocAsync(&d_bytes, 2 * sizeof(unsigned long long), c.stream));
+    HERA_CUDA(cudaMemsetAsync(d_bytes, 0, 2 * sizeof(unsigned long long), c.stream));
+    cudaEvent_t e0, e1;
+    HERA_CUDA(cudaEventCreate(&e0));
+    HERA_CUDA(cudaEventCreate(&e1));
+    HERA_CUDA(cudaEventRecord(e0, c.stream));
+    HERA_LAUNCH(c, list_gather_probe_kernel, div_up(static_cast<uint64_t>(warps) * 32, WK_THREADS), WK_THREADS, 0, g.adj_off.p, g.adj4.p,
+                static_cast<uint32_t>(g.N), hops, d_bytes, reinterpret_cast<uint32_t *>(d_bytes + 1));
+    HERA_CUDA(cudaEventRecord(e1, c.stream));
+    unsigned long long h_bytes = 0;
+    HERA_CUDA(cudaMemcpyAsync(&h_bytes, d_bytes, sizeof(h_bytes), cudaMemcpyDeviceToHost, c.stream));
+    HERA_CUDA(cudaStreamSynchronize(c.stream));
+    float ms = 0;
+    HERA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    HERA_CUDA(cudaFreeAsync(d_bytes, c.stream));
+    if (gbytes_per_s) *gbytes_per_s = ms > 0 ? static_cast<double>(h_bytes) / (ms * 1e-3) / 1e9 : 0.0;
+    if (ms_out) *ms_out = ms;
+}
+
 void walk_monte_carlo(Ctx &c, int metric, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out) {
     const int kind = 0;
     walk_build(c, 1, &kind, &metric, pp, seed, out);
