@@ -167,11 +167,13 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
         if isinstance(src, Slice):
             return h.load_shard_ptr(src.ptr(device_resident), device_resident, src.owned, src.avail, src.prev, src.at_eof, anchors)
         return (h.load_device_ptr if device_resident else h.load_host_ptr)(src[0], src[1], anchors)
+    h.comm_barrier()   # sharded runs: a late host thread of another rank is not part of this rank's stage times
     h.timer_start()
     r1 = load(rr, False)
     r2 = load(cr, True)
     info = h.finalize(WORKLOAD["metrics"])
     t_graph = h.timer_stop()
+    h.comm_barrier()
     h.timer_start()
     # the four build calls of main() as one hera_paths_build call: their kernels share the GPU
     stats = h.build_paths([("mc", m) for m in WORKLOAD["metrics"]] + [("det", m) for m in WORKLOAD["metrics"]], pp, 20261104)
@@ -236,8 +238,10 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     config = {"workload": WORKLOAD["name"], "generator": "tools/gen_dataset " + " ".join(WORKLOAD["gen"]) + f" --seed {WORKLOAD['seed']}",
               "filter": "reference defaults (AVG)", "rb_att": WORKLOAD["rb_att"], "metrics": WORKLOAD["metrics"],
-              "parallelism": (f"{world} ranks, one dataset {world}x the size: PAF sharded by byte range, kept overlaps all-gathered (NCCL), CSR replicated, "
-                              f"walks dealt out by walk id, paths all-gathered (NCCL)") if world > 1 else "single GPU",
+              "parallelism": (f"{world} ranks, one dataset {world}x the size: PAF sharded by byte range, kept overlaps pulled from peer memory over NVLink "
+                              f"(NCCL rendezvous), CSR replicated, walks dealt out by walk id, paths all-gathered (NCCL); ranks are aligned by a barrier before the "
+                              f"graph stage and before the path stage of every step (stage times exclude the wait for a late host thread; e2e wall time does not)")
+                             if world > 1 else "single GPU",
               "l2": "PAF text (173 MB per GPU) is larger than L2 (126 MB); the roofline leg additionally writes 512 MB before the parse kernel"}
     if world > 1:
         config["generator"] = "tools/gen_dataset " + " ".join(gen_args(world)) + f" --seed {WORKLOAD['seed']}"

@@ -160,6 +160,10 @@ void hera_comm_local_destroy(hera_local_gang *gang);
 int hera_comm_attach_local(hera_ctx *ctx, hera_local_gang *gang, int rank);
 int hera_comm_rank(hera_ctx *ctx);   /* 0 without a communicator */
 int hera_comm_size(hera_ctx *ctx);   /* 1 without a communicator */
+/* Waits until every rank's stream is idle and every rank has made this call (no-op without a communicator).
+ * bench.py aligns the ranks with it before a step's timed stages, so that a stage time does not contain the
+ * wait for a rank whose host thread was late. */
+int hera_comm_barrier(hera_ctx *ctx);
 /* The slice of a `file_bytes` long PAF file rank `rank` of `nranks` must hand to hera_graph_load_shard:
  * it OWNS the tokens starting in [*begin, *end) and must also provide the bytes up to *avail_end
  * (so that a record that starts in the slice can be finished) and the byte before *begin. */

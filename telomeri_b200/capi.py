@@ -89,6 +89,7 @@ SIGNATURES = {
     "hera_comm_local_destroy": (None, [C.c_void_p]),
     "hera_comm_attach_local": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "hera_comm_rank": (C.c_int, [C.c_void_p]),
+    "hera_comm_barrier": (C.c_int, [C.c_void_p]),
     "hera_comm_size": (C.c_int, [C.c_void_p]),
     "hera_shard_range": (None, [C.c_uint64, C.c_int, C.c_int, u64p, u64p, u64p]),
     "hera_graph_load_shard": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
@@ -181,6 +182,9 @@ class Hera:
         ms = C.c_float()
         self._check(self.lib.hera_timer_stop(self.h, C.byref(ms)))
         return ms.value
+
+    def comm_barrier(self):
+        self._check(self.lib.hera_comm_barrier(self.h))
 
     def probe_list_gather(self, warps_per_sm=64, hops=256):
         """Measured list-walking ceiling on the finalized graph: (GB/s of adjacency entries, ms)."""

@@ -290,6 +290,13 @@ int hera_comm_attach_local(hera_ctx *ctx, hera_local_gang *gang, int rank) {
 int hera_comm_rank(hera_ctx *ctx) { return ctx ? hera::xch_rank(ctx->c) : 0; }
 int hera_comm_size(hera_ctx *ctx) { return ctx ? hera::xch_size(ctx->c) : 1; }
 
+int hera_comm_barrier(hera_ctx *ctx) {
+    HERA_API_BEGIN(ctx)
+    HERA_CUDA(cudaStreamSynchronize(c.stream));
+    if (c.xch) c.xch->barrier(c);
+    HERA_API_END
+}
+
 int hera_graph_reset(hera_ctx *ctx) {
     HERA_API_BEGIN(ctx)
     HERA_CUDA(cudaStreamSynchronize(c.stream));

@@ -26,6 +26,8 @@
 // desynchronise there) ends the parallel part; a one-thread tail kernel continues from its byte
 // offset with the exact character-stream rules of formatted extraction.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 #include "ctx.cuh"
 #include "primitives.cuh"
@@ -886,6 +888,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         if (owned) HERA_LAUNCH(c, paf_count_tokens_kernel, std::min<unsigned>(div_up(div_up(owned, 16), 256), 148 * 8), 256, 0, text.bytes.p, owned, shard->prev_nonws ? 1 : 0, d_tok);
         c.xch->all_gather_dev(c, c.counters.p + 13, d_tok_all, 1);
         HERA_LAUNCH(c, shard_prefix_kernel, 1, 32, 0, d_tok_all, ranks, me, reinterpret_cast<unsigned long long *>(c.counters.p + 14));
+        HERA_CUDA(cudaEventRecord(ev2, c.stream));   // (reused below: only read here when HERA_DEBUG_TIMING is set)
     }
 
     ParseArgs a{text.bytes.p, n, owned, 0, sharded ? reinterpret_cast<const unsigned long long *>(c.counters.p + 14) : nullptr, sharded && shard->prev_nonws ? 1 : 0, (!sharded || shard->at_eof) ? 1 : 0,
@@ -902,6 +905,12 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     }
     HERA_CUDA(cudaMemcpyAsync(c.h_counters.p, ctr, sizeof(ParseCounters), cudaMemcpyDeviceToHost, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
+    if (sharded && getenv("HERA_DEBUG_TIMING")) {
+        float pre = 0, krn = 0;
+        cudaEventElapsedTime(&pre, ev0, ev2);
+        cudaEventElapsedTime(&krn, ev2, ev1);
+        fprintf(stderr, "[hera rank %d] load: token exchange %.3f ms, parse kernel %.3f ms\n", me, pre, krn);
+    }
     ParseCounters hc = *reinterpret_cast<ParseCounters *>(c.h_counters.p);
     uint64_t tokens_all = 0;
     for (int r = 0; sharded && r < ranks; r++) tokens_all += c.h_counters.p[16 + r];
