@@ -179,6 +179,7 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
     stats = h.build_paths([("mc", m) for m in WORKLOAD["metrics"]] + [("det", m) for m in WORKLOAD["metrics"]], pp, 20261104)
     walks = sum(s.walks for s in stats)
     steps = sum(s.steps for s in stats)
+    found = sum(s.found for s in stats)
     n_unique = h.unique()
     t_paths = h.timer_stop()
     h.timer_start()
@@ -190,7 +191,7 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
         d2h = sum(v.nbytes for v in g.values() if hasattr(v, "nbytes")) + sum(v.nbytes for v in paths.values())
     return {"graph_ms": t_graph, "paths_ms": t_paths, "groups_ms": t_groups, "parse_ms": r1.parse_ms + r2.parse_ms,
             "exchange_ms": r1.exchange_ms + r2.exchange_ms, "parse_rr_ms": r1.parse_ms, "intern_ms": info.intern_ms, "csr_ms": info.csr_ms, "rank_ms": info.rank_ms,
-            "records": r1.records + r2.records, "kept": r2.kept_total, "nodes": info.nodes, "walks": walks, "walk_entries": steps,
+            "records": r1.records + r2.records, "kept": r2.kept_total, "nodes": info.nodes, "walks": walks, "walk_entries": steps, "found": found,
             "unique_paths": n_unique, "pairs": len(g["pair_a1"]), "launches": h.launches - launches0, "d2h": d2h,
             "rr_bytes": r1.bytes, "rr_kept": r1.kept}
 
@@ -371,7 +372,8 @@ def main():
             "metric": "overlaps/s graph build", "value": records / (graph_ms * 1e-3), "unit": "overlaps/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": (graph_ms + paths_ms + groups_ms) / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-            "paths_per_s": walks / (paths_ms * 1e-3), "unique_paths_per_step": uniq / args.steps,
+            "paths_per_s": walks / (paths_ms * 1e-3), "accepted_paths_per_s": agg(dev_steps, "found") / (paths_ms * 1e-3),
+            "unique_paths_per_step": uniq / args.steps,
             "stages_ms_per_step": {k: statistics.mean(s[k] for s in dev_steps) for k in
                                    ("graph_ms", "parse_ms", "exchange_ms", "intern_ms", "csr_ms", "rank_ms", "paths_ms", "groups_ms")},
             "per_step": {"records": s0["records"], "kept_overlaps": s0["kept"], "nodes": s0["nodes"], "walks": s0["walks"],
@@ -391,6 +393,15 @@ def main():
                                "algorithmic_bytes": int(s0["walk_entries"]) * 16},
             "clocks": clocks.summary(),
         }
+        # % of the HBM roofline for every streaming stage, from its algorithmic bytes (E kept overlaps,
+        # 2E slots, N nodes, P paths) and the stage's device time
+        E_, N_, M_ = s0["kept"], s0["nodes"], len(WORKLOAD["metrics"])
+        st = line["stages_ms_per_step"]
+        stage_bytes = {"K3 interning (intern_ms)": (2 * E_ * 10 + 2 * E_ * 4, st["intern_ms"]),
+                       "K4 CSR + K4b ranks (csr_ms + rank_ms)": (2 * E_ * 80 + (N_ + 1) * 4 + 2 * E_ * 4 * (M_ + 1), st["csr_ms"] + st["rank_ms"])}
+        line["roofline_stages"] = [{"stage": k, "algorithmic_bytes": int(b), "ms": ms, "achieved": b / (ms * 1e-3) / 1e9, "peak": peak,
+                                    "unit": "GB/s per GPU (replicated stages: every GPU handles all kept overlaps)", "frac": b / (ms * 1e-3) / 1e9 / peak}
+                                   for k, (b, ms) in stage_bytes.items()]
         rw = line["roofline_walks"]
         rw["frac"] = rw["achieved"] / rw["peak"] if rw["peak"] else None
         if world == 1 and not args.no_cpu_baseline:

@@ -549,6 +549,9 @@ void job_launch_kernel(Ctx &c, WalkJob &j) {
             if (smem_bm) {
                 if (c.opt_walk_variant == 1) launch(walk_mc_kernel<true, 2, 12>);
                 else if (c.opt_walk_variant == 2) launch(walk_mc_kernel<true, 1, 16>);
+                else if (c.opt_walk_variant == 3) launch(walk_mc_kernel<true, 5, 8>);
+                else if (c.opt_walk_variant == 4) launch(walk_mc_kernel<true, 6, 8>);
+                else if (c.opt_walk_variant == 5) launch(walk_mc_kernel<true, 3, 8>);
                 else launch(walk_mc_kernel<true, 4, 8>);
             } else {
                 if (c.opt_walk_variant == 1) launch(walk_mc_kernel<false, 2, 12>);
