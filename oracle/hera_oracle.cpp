@@ -81,7 +81,10 @@ struct Cursor {
 
 }  // namespace
 
-uint64_t read_records(const std::string &text, uint64_t stop_after, std::vector<PafRecord> &out) {
+// The read loop of src/OverlapGraph.cpp:105-148; `sink` sees every record in file order (so a caller can filter on
+// the fly instead of holding all records of a 42 GB file).
+template <typename Sink>
+static uint64_t read_records_each(const std::string &text, uint64_t stop_after, Sink sink) {
     Cursor c(text);
     uint64_t ctr = 0;
     std::string skip;
@@ -93,10 +96,14 @@ uint64_t read_records(const std::string &text, uint64_t stop_after, std::vector<
         if (!ok) break;
         for (int k = 0; k < 4; k++) c.word(skip);  // src/OverlapGraph.cpp:124-127
         ctr++;
-        out.push_back(std::move(r));
+        sink(std::move(r));
         if (stop_after > 0 && stop_after < ctr) break;  // test_load_num_, src/OverlapGraph.cpp:145-147
     }
     return ctr;
+}
+
+uint64_t read_records(const std::string &text, uint64_t stop_after, std::vector<PafRecord> &out) {
+    return read_records_each(text, stop_after, [&](PafRecord &&r) { out.push_back(std::move(r)); });
 }
 
 // src/OverlapGraph.cpp:156-202.  All comparisons are fp32; the integer thresholds are
@@ -155,21 +162,20 @@ static bool starts_with_ctg(const std::string &name) {  // include/Utils.hpp:17-
 }
 
 void GraphBuilder::load_text(const std::string &text, bool anchors) {
-    std::vector<PafRecord> recs;
-    uint64_t ctr = read_records(text, test_load_num_, recs);
-    for (PafRecord &r : recs) {
+    uint64_t ctr = read_records_each(text, test_load_num_, [&](PafRecord &&r) {
         if (filter_record(r, fp_)) kept_.push_back(Kept{std::move(r), anchors});
-    }
+    });
     ctr_.push_back(ctr);
     cum_.push_back(kept_.size());
 }
 
 bool GraphBuilder::load_file(const char *path, bool anchors) {
-    std::ifstream f(path, std::ios::binary);
+    std::ifstream f(path, std::ios::binary | std::ios::ate);
     if (!f) return false;
-    std::stringstream ss;
-    ss << f.rdbuf();
-    load_text(ss.str(), anchors);
+    std::string text(static_cast<size_t>(f.tellg()), '\0');   // one copy of the file, not two
+    f.seekg(0);
+    f.read(text.data(), static_cast<std::streamsize>(text.size()));
+    load_text(text, anchors);
     return true;
 }
 

@@ -134,9 +134,8 @@ int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp) {
     HERA_API_END
 }
 
-static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard,
-                        hera_load_result *out) {
-    // text buffers are recycled across hera_graph_reset: no cudaMalloc / cudaFree in the steady state
+// Text buffers are recycled across hera_graph_reset: no cudaMalloc / cudaFree in the steady state.
+static std::unique_ptr<hera::LoadedText> acquire_text(Ctx &c, uint64_t n) {
     std::unique_ptr<hera::LoadedText> t;
     const uint64_t need = hera::padded_text_size(n);
     size_t best = c.text_pool.size();
@@ -147,23 +146,46 @@ static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind
     if (!t) t.reset(new hera::LoadedText());
     t->n = n;
     t->bytes.reserve(need);
+    return t;
+}
+
+// Parses a text whose bytes are (being copied) on the device, in stream order.
+static void commit_text(Ctx &c, std::unique_ptr<hera::LoadedText> t, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard, hera_load_result *out) {
+    if (c.cache_loaded) {
+        cudaStreamSynchronize(c.stream);
+        c.text_pool.push_back(std::move(t));
+        throw hera::Error{54, "this graph was restored from a cache: hera_graph_reset before loading PAF text"};
+    }
+    const uint32_t file_id = static_cast<uint32_t>(c.texts.size());
+    if (file_id >= 16) {
+        cudaStreamSynchronize(c.stream);
+        c.text_pool.push_back(std::move(t));
+        throw hera::Error{5, "more than 16 loads per graph are not supported"};
+    }
+    c.texts.push_back(std::move(t));
+    try {
+        hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, shard, out);
+    } catch (...) {
+        cudaStreamSynchronize(c.stream);
+        c.text_pool.push_back(std::move(c.texts.back()));
+        c.texts.pop_back();   // the failed load leaves no trace
+        throw;
+    }
+}
+
+static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard,
+                        hera_load_result *out) {
+    std::unique_ptr<hera::LoadedText> t = acquire_text(c, n);
     cudaEvent_t e0, e1;
     HERA_CUDA(cudaEventCreate(&e0));
     HERA_CUDA(cudaEventCreate(&e1));
     HERA_CUDA(cudaEventRecord(e0, c.stream));
     if (n) HERA_CUDA(cudaMemcpyAsync(t->bytes.p, src, n, kind, c.stream));
     HERA_CUDA(cudaEventRecord(e1, c.stream));
-    HERA_REQUIRE(!c.cache_loaded, 54, "this graph was restored from a cache: hera_graph_reset before loading PAF text");
-    const uint32_t file_id = static_cast<uint32_t>(c.texts.size());
-    HERA_REQUIRE(file_id < 16, 5, "more than 16 loads per graph are not supported");
-    c.texts.push_back(std::move(t));
     hera_load_result tmp{};
     try {
-        hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, shard, &tmp);
+        commit_text(c, std::move(t), anchors, test_load_num, shard, &tmp);
     } catch (...) {
-        cudaStreamSynchronize(c.stream);
-        c.text_pool.push_back(std::move(c.texts.back()));
-        c.texts.pop_back();   // the failed load leaves no trace
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
         throw;
@@ -174,6 +196,46 @@ static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind
     cudaEventDestroy(e1);
     tmp.h2d_ms = kind == cudaMemcpyHostToDevice ? copy_ms : 0.0f;
     if (out) *out = tmp;
+}
+
+// File bytes [b, e) -> device buffer, through two pinned staging blocks used in turn: the read of block i + 1 from
+// the file overlaps the host-to-device copy of block i, and the host never holds more than two blocks of the file
+// (a 42 GB PAF file needs 128 MiB of pinned memory, not 42 GB).  Returns the milliseconds the copies took on the stream.
+static float stream_file_to_device(Ctx &c, std::ifstream &f, const char *path, uint64_t b, uint64_t e, uint8_t *dst) {
+    constexpr uint64_t BLOCK = 64ull << 20;
+    struct Staging {
+        char *p[2] = {nullptr, nullptr};
+        cudaEvent_t done[2] = {nullptr, nullptr}, e0 = nullptr, e1 = nullptr;
+        ~Staging() {
+            for (int i = 0; i < 2; i++) { if (p[i]) cudaFreeHost(p[i]); if (done[i]) cudaEventDestroy(done[i]); }
+            if (e0) cudaEventDestroy(e0);
+            if (e1) cudaEventDestroy(e1);
+        }
+    } st;
+    const uint64_t block = std::min<uint64_t>(BLOCK, std::max<uint64_t>(e - b, 1));
+    for (int i = 0; i < 2; i++) {
+        if (i == 0 || e - b > block) HERA_CUDA(cudaMallocHost(&st.p[i], block));
+        HERA_CUDA(cudaEventCreateWithFlags(&st.done[i], cudaEventDisableTiming));
+    }
+    HERA_CUDA(cudaEventCreate(&st.e0));
+    HERA_CUDA(cudaEventCreate(&st.e1));
+    f.clear();
+    f.seekg(static_cast<std::streamoff>(b));
+    HERA_CUDA(cudaEventRecord(st.e0, c.stream));
+    int k = 0;
+    for (uint64_t at = b; at < e; at += block, k ^= 1) {
+        const uint64_t len = std::min(block, e - at);
+        HERA_CUDA(cudaEventSynchronize(st.done[k]));   // the copy that last used this block has finished (no-op the first time)
+        f.read(st.p[k], static_cast<std::streamsize>(len));
+        HERA_REQUIRE(static_cast<uint64_t>(f.gcount()) == len, 1, std::string("short read on ") + path);
+        HERA_CUDA(cudaMemcpyAsync(dst + (at - b), st.p[k], len, cudaMemcpyHostToDevice, c.stream));
+        HERA_CUDA(cudaEventRecord(st.done[k], c.stream));
+    }
+    HERA_CUDA(cudaEventRecord(st.e1, c.stream));
+    HERA_CUDA(cudaEventSynchronize(st.e1));   // the staging blocks are freed on return
+    float ms = 0;
+    HERA_CUDA(cudaEventElapsedTime(&ms, st.e0, st.e1));
+    return ms;
 }
 
 int hera_graph_load_bytes(hera_ctx *ctx, const void *host_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out) {
@@ -220,35 +282,43 @@ int hera_graph_load_file(hera_ctx *ctx, const char *path, int anchors, uint32_t 
     std::ifstream f(path, std::ios::binary | std::ios::ate);
     if (!f) throw hera::Error{1, std::string("Cannot open file: ") + path};
     const uint64_t n = static_cast<uint64_t>(f.tellg());
-    hera::HBuf<char> staging;
-    auto read_range = [&](uint64_t b, uint64_t e) {
-        staging.reserve(e - b + 1);
-        f.clear();
-        f.seekg(static_cast<std::streamoff>(b));
-        if (e > b) f.read(staging.p, static_cast<std::streamsize>(e - b));
-        HERA_REQUIRE(static_cast<uint64_t>(f.gcount()) == e - b || e == b, 1, std::string("short read on ") + path);
+    auto load_range = [&](uint64_t b, uint64_t e, const hera::ShardSpec *sp) {
+        std::unique_ptr<hera::LoadedText> t = acquire_text(c, e - b);
+        float h2d_ms = 0;
+        try {
+            h2d_ms = stream_file_to_device(c, f, path, b, e, t->bytes.p);
+        } catch (...) {
+            cudaStreamSynchronize(c.stream);
+            c.text_pool.push_back(std::move(t));
+            throw;
+        }
+        hera_load_result tmp{};
+        commit_text(c, std::move(t), anchors, test_load_num, sp, &tmp);
+        tmp.h2d_ms = h2d_ms;
+        if (out) *out = tmp;
     };
     bool whole = hera::xch_size(c) == 1;
     if (!whole) {
         // every rank reads only its byte range (+ the byte before it and the look-ahead)
         uint64_t b, e, a;
         hera_shard_range(n, hera::xch_rank(c), hera::xch_size(c), &b, &e, &a);
-        const uint64_t from = b ? b - 1 : 0;
-        read_range(from, a);
-        const int prev = b ? static_cast<unsigned char>(staging.p[0]) : -1;
+        int prev = -1;
+        if (b) {
+            f.clear();
+            f.seekg(static_cast<std::streamoff>(b - 1));
+            prev = f.get();
+            HERA_REQUIRE(prev >= 0, 1, std::string("short read on ") + path);
+        }
         const bool prev_nonws = prev >= 0 && !(prev == ' ' || (prev >= 9 && prev <= 13));
         hera::ShardSpec sp{e - b, prev_nonws, a == n};
         try {
-            load_common(c, staging.p + (b - from), a - b, cudaMemcpyHostToDevice, anchors, test_load_num, &sp, out);
+            load_range(b, a, &sp);
         } catch (const hera::Error &err) {
             if (err.code != 20) throw;
             whole = true;   // an irregular record: all ranks fall back to the exact whole-file reader (same decision on every rank)
         }
     }
-    if (whole) {
-        read_range(0, n);
-        load_common(c, staging.p, n, cudaMemcpyHostToDevice, anchors, test_load_num, nullptr, out);
-    }
+    if (whole) load_range(0, n, nullptr);
     HERA_API_END
 }
 

@@ -851,8 +851,20 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     HERA_REQUIRE(owned <= n, 101, "shard: owned bytes exceed the bytes provided");
 
     const uint32_t tiles = static_cast<uint32_t>(owned / PF_TILE + 1);
-    // worst case every record is kept: records <= bytes / 24 (12 one-byte tokens + separators)
-    const uint64_t max_new = owned / 24 + 2;
+    // worst case every record is kept: records <= bytes / 24 (12 one-byte tokens + separators).  For a large text that
+    // bound would reserve far more rows than the file can hold records (42 GB of PAF -> 128 GB of rows), so the tokens
+    // are counted first (one more pass over the text) and the rows are reserved for tokens / 16 records.
+    uint64_t max_new = owned / 24 + 2;
+    if (max_new > (64ull << 20)) {
+        c.counters.reserve(16);
+        unsigned long long *d_tok = reinterpret_cast<unsigned long long *>(c.counters.p + 13);
+        HERA_CUDA(cudaMemsetAsync(d_tok, 0, sizeof(unsigned long long), c.stream));
+        HERA_LAUNCH(c, paf_count_tokens_kernel, 148 * 8, 256, 0, text.bytes.p, owned, sharded && shard->prev_nonws ? 1 : 0, d_tok);
+        c.h_counters.reserve(16);
+        HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 13, d_tok, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        max_new = std::min<uint64_t>(max_new, c.h_counters.p[13] / 16 + 2);
+    }
     c.kept.reserve(c.kept.n + max_new, c.stream);
 
     // device block: [0, 8) ParseCounters, [12] cut, [13] my token count, [14] tokens before my slice, [15] tokens of all

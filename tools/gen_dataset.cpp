@@ -13,7 +13,7 @@
 //
 // Usage: gen_dataset --out DIR [--genome N] [--read-len N] [--coverage X] [--contigs N]
 //          [--gap N] [--min-ovl N] [--families N] [--copies N] [--seed N] [--jitter N]
-//          [--minus-frac F] [--no-fasta] [--max-rr N]
+//          [--minus-frac F] [--no-fasta] [--max-rr N] [--dry-run]
 #include <algorithm>
 #include <cinttypes>
 #include <cstdint>
@@ -54,8 +54,11 @@ struct Out {
     ~Out() { flush(); if (f) std::fclose(f); }
 };
 
+static bool g_dry_run = false;   // --dry-run: count the records, write nothing (used to size a configuration)
+
 static void paf_record(Out &o, const char *qn, int64_t ql, int64_t qs, int64_t qe, char strand, const char *tn,
                        int64_t tl, int64_t ts, int64_t te, int64_t matches, int64_t block) {
+    if (g_dry_run) return;
     char line[512];
     int n = std::snprintf(line, sizeof line,
                           "%s\t%" PRId64 "\t%" PRId64 "\t%" PRId64 "\t%c\t%s\t%" PRId64 "\t%" PRId64 "\t%" PRId64
@@ -88,6 +91,7 @@ int main(int argc, char **argv) {
         else if (a == "--minus-frac") minus_frac = std::atof(val());
         else if (a == "--max-rr") max_rr = std::atoll(val());
         else if (a == "--no-fasta") fasta = false;
+        else if (a == "--dry-run") { g_dry_run = true; fasta = false; }
         else { std::fprintf(stderr, "unknown option %s\n", a.c_str()); return 2; }
     }
     if (out_dir.empty()) { std::fprintf(stderr, "--out DIR is required\n"); return 2; }

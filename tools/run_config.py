@@ -2,7 +2,8 @@
 """One BASELINE.json configuration end to end on the GPU box: generate the dataset, run the CPU oracle and the
 CUDA path (optionally as a local gang of N ranks) on it, compare every table bit for bit, print timings.
   python tools/run_config.py dmel [--ranks N] [--rb-att K]
-Used for the configurations that are too large for the test-suite (configs[3])."""
+  python tools/run_config.py chr1 --rb-att 1000
+Used for the configurations that are too large for the test-suite (configs[3], configs[4])."""
 import argparse
 import json
 import subprocess
@@ -16,6 +17,9 @@ sys.path.insert(0, str(ROOT / "tests"))
 
 CONFIGS = {
     "yeast": ["--genome", "12000000", "--read-len", "20000", "--coverage", "60", "--contigs", "120", "--gap", "30000", "--families", "56", "--copies", "4", "--min-ovl", "1000", "--seed", "3"],
+    # configs[4]: human-chr1 scale, high repeat (272 families x 30 copies of 5-20 kb: ~40 % of the records are
+    # repeat-induced), 30x 25 kb reads -> 402 M read-read records (42 GB of PAF); run with --rb-att 1000
+    "chr1": ["--genome", "248000000", "--read-len", "25000", "--coverage", "30", "--contigs", "120", "--gap", "30000", "--families", "272", "--copies", "30", "--min-ovl", "1000", "--seed", "5"],
     "dmel": ["--genome", "140000000", "--read-len", "20000", "--coverage", "60", "--contigs", "400", "--gap", "30000", "--families", "650", "--copies", "4", "--min-ovl", "1000", "--seed", "4"],
 }
 
@@ -32,16 +36,22 @@ def main():
     from test_gpu_parity import GRAPH_SECTIONS, GROUP_SECTIONS, PATH_SECTIONS
     d = Path(args.out) / args.config
     d.mkdir(parents=True, exist_ok=True)
+
+    def note(msg):
+        print(f"[run_config +{time.perf_counter() - t_start:.0f}s] {msg}", file=sys.stderr, flush=True)
+    t_start = time.perf_counter()
     common.build_generator()
     common.build_oracle()
     t0 = time.perf_counter()
     meta = subprocess.run([str(common.GEN_BIN), "--out", str(d), "--no-fasta"] + CONFIGS[args.config], check=True, capture_output=True, text=True).stdout
     t_gen = time.perf_counter() - t0
+    note(f"generated {meta.strip()}")
     opts = ["--rb-att", str(args.rb_att)]
     t0 = time.perf_counter()
     ora = common.run_dump(common.ORACLE_BIN, d, d / "o.bin", opts, extra=["--rng", "philox", "--seed", "17"])
     t_ora = time.perf_counter() - t0
     (d / "o.bin").unlink()
+    note(f"oracle done in {t_ora:.0f} s")
     t0 = time.perf_counter()
     if args.ranks == 1:
         gpu = pipeline.run_hot_path(d, opts, seed=17, batched=True)
@@ -53,6 +63,7 @@ def main():
                              pipeline.run_hot_path(d, opts, seed=17, hera=h, batched=True, exports=False) and None)
         gpu = outs[0]
     t_gpu = time.perf_counter() - t0
+    note(f"CUDA path done in {t_gpu:.0f} s; comparing")
     names = GRAPH_SECTIONS + ["rank_0", "rank_1"] + PATH_SECTIONS + GROUP_SECTIONS
     common.assert_sections_equal(ora, gpu, names, args.config)
     st = gpu["walk_stats"]
