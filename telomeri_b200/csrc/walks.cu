@@ -17,8 +17,6 @@
 #include <algorithm>
 #include <vector>
 
-#include <type_traits>
-
 #include "ctx.cuh"
 #include "primitives.cuh"
 
@@ -136,12 +134,7 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
     const uint32_t lane = lane_id(), wib = warp_id();
     const uint32_t WK_CACHE = sc.cache;
     float *s_cval = reinterpret_cast<float *>(wk_smem) + wib * WK_CACHE;
-    // neighbour ids of the same entries (the picked one is read back from here): 16 bits are enough when the bitmaps are
-    // in shared memory (N <= 65536); a roulette pick is never an anchor (an anchor other than the start is a forced edge,
-    // the start is visited), so the anchor bit need not be kept
-    using NbrT = typename std::conditional<SMEM_BM, uint16_t, uint32_t>::type;
-    NbrT *s_cnbr = reinterpret_cast<NbrT *>(wk_smem + WK_WARPS * WK_CACHE) + wib * WK_CACHE;
-    uint32_t *s_bm = wk_smem + WK_WARPS * WK_CACHE + WK_WARPS * WK_CACHE * sizeof(NbrT) / 4 + (SMEM_BM ? wib * sc.words : 0u);
+    uint32_t *s_bm = wk_smem + WK_WARPS * WK_CACHE + (SMEM_BM ? wib * sc.words : 0u);
     const uint32_t wslot = blockIdx.x * WK_WARPS + wib;
     uint32_t *g_bm = sc.bitmap + (SMEM_BM ? 0ull : static_cast<uint64_t>(wslot) * sc.words);
     uint32_t *bm = SMEM_BM ? s_bm : g_bm;
@@ -211,7 +204,7 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
                     // (adding -0.0 to a sum changes nothing, and the sign bit tells the two apart)
                     float v = __uint_as_float(g.use_os ? a[j].z : a[j].y);
                     if (g.sqrt_metric) v = __fsqrt_rn(v);
-                    if (k < WK_CACHE) { s_cval[k] = cand ? v : -0.0f; s_cnbr[k] = static_cast<NbrT>(nb); }
+                    if (k < WK_CACHE) s_cval[k] = cand ? v : -0.0f;
                 }
             }
             const uint32_t ncand = __any_sync(0xffffffffu, any_cand) ? 1u : 0u;   // only "none / some" matters below
@@ -310,18 +303,10 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
             const uint32_t slot = base + static_cast<uint32_t>(pick);
             uint32_t nbw = forced_nbw;
             int32_t dl = forced_dl;
-            if (forced < 0) {
-                // roulette pick: the neighbour comes from the shared-memory copy of the list, so the next step's loads do
-                // not wait for a round trip to L2; the delta is only needed one step later (the length tests below look at
-                // the path without its last edge), its load overlaps with the next step
-                if (static_cast<uint32_t>(pick) < WK_CACHE) {
-                    nbw = s_cnbr[pick];
-                    dl = __ldg(g.delta + slot);
-                } else {
-                    const uint4 taken = __ldg(g.adj4 + slot);
-                    nbw = taken.x;
-                    dl = static_cast<int32_t>(taken.w);
-                }
+            if (forced < 0) {   // roulette pick: its entry left the registers, it is an L1/L2 hit
+                const uint4 taken = __ldg(g.adj4 + slot);
+                nbw = taken.x;
+                dl = static_cast<int32_t>(taken.w);
             }
             cur = nbw & 0x7fffffffu;
             if (n_nodes >= sc.cap) break;  // cannot happen: a walk visits every node at most once
@@ -555,9 +540,8 @@ void job_launch_kernel(Ctx &c, WalkJob &j) {
         if (j.kind == 0) {
             // visited bitmaps in shared memory while four of them fit beside the value cache (N <= 65536 nodes)
             const bool smem_bm = c.opt_walk_smem_bitmap && j.words <= 2048;
-            const size_t smem = 1ull * WK_WARPS * cache * (smem_bm ? 6 : 8) + (smem_bm ? static_cast<size_t>(WK_WARPS) * j.words * sizeof(uint32_t) : 0);
+            const size_t smem = (1ull * WK_WARPS * cache + (smem_bm ? static_cast<size_t>(WK_WARPS) * j.words : 0)) * sizeof(uint32_t);
             auto launch = [&](auto kernel) {
-                if (smem > 48 * 1024) HERA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
                 kernel<<<j.blocks, WK_THREADS, smem, j.stream>>>(j.wg, sc, wo, j.my_walks, static_cast<uint32_t>(j.pp.rebuild_attempts), j.pp.backtrack_attempts,
                                                                 static_cast<long long>(j.pp.len_threshold), j.seed, static_cast<uint32_t>(j.metric));
             };
