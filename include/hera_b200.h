@@ -169,7 +169,8 @@ int hera_comm_barrier(hera_ctx *ctx);
  * (so that a record that starts in the slice can be finished) and the byte before *begin. */
 void hera_shard_range(uint64_t file_bytes, int rank, int nranks, uint64_t *begin, uint64_t *end, uint64_t *avail_end);
 /* OverlapGraph::load over a byte-range slice (collective).  text = bytes [begin, avail_end) of the
- * file in host (on_device = 0) or device memory; owned = end - begin, avail = avail_end - begin;
+ * file in host (on_device = 0) or device memory (1 = copied into the library's own buffer, 2 = parsed in
+ * place under the contract of hera_graph_load_device_view); owned = end - begin, avail = avail_end - begin;
  * prev_byte = the file byte before `begin`, or -1 at the start of the file; at_eof = avail_end is the
  * end of the file.  Results (records, kept, kept_total) are global.  Returns 20 (and changes nothing)
  * when some slice holds a record formatted extraction would fail on (non-numeric field, strand of
@@ -190,6 +191,12 @@ int hera_graph_load_bytes(hera_ctx *ctx, const void *host_text, uint64_t n, int 
 /* ... or already resident in device memory (n bytes at a cudaMalloc'ed address; the library
  * copies it device-to-device into its own padded buffer). */
 int hera_graph_load_device(hera_ctx *ctx, const void *device_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out);
+/* Same, parsed IN PLACE: no copy is made.  device_text must be 16-byte aligned and lie in a cudaMalloc'ed
+ * allocation (the 16-byte chunk that holds byte n-1 is read whole, nothing behind it); the caller keeps the
+ * buffer alive and unchanged until hera_graph_reset / hera_destroy -- node names are read from it by
+ * hera_graph_finalize and hera_graph_save.  What a caller whose overlapper already left its PAF output in
+ * device memory uses; results are identical to hera_graph_load_device. */
+int hera_graph_load_device_view(hera_ctx *ctx, const void *device_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out);
 /* Drops all loaded overlaps (a fresh OverlapGraph). */
 int hera_graph_reset(hera_ctx *ctx);
 /* Node numbering (OverlapGraph::nodeIndex + node creation, src/OverlapGraph.cpp:208-218,251-258),

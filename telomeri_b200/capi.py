@@ -83,6 +83,7 @@ SIGNATURES = {
     "hera_graph_load_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_bytes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
+    "hera_graph_load_device_view": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_nccl_unique_id": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64]),
     "hera_comm_init_nccl": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "hera_comm_local_create": (C.c_void_p, [C.c_int]),
@@ -217,6 +218,12 @@ class Hera:
     def load_device_ptr(self, ptr, n, anchors, test_load_num=0):
         r = LoadResult()
         self._check(self.lib.hera_graph_load_device(self.h, C.c_void_p(ptr), n, int(anchors), test_load_num, C.byref(r)))
+        return r
+
+    def load_device_view_ptr(self, ptr, n, anchors, test_load_num=0):
+        """hera_graph_load_device_view: parsed in place, the caller keeps the buffer alive until graph_reset / close."""
+        r = LoadResult()
+        self._check(self.lib.hera_graph_load_device_view(self.h, C.c_void_p(ptr), n, int(anchors), test_load_num, C.byref(r)))
         return r
 
     # ---- sharded runs (one rank per GPU) -------------------------------------------------------

@@ -1,6 +1,9 @@
 // extern "C" entry points of libhera_b200.so (declared in include/hera_b200.h).
 #include <algorithm>
 #include <cstring>
+#include <ctime>
+#include <cstdio>
+#include <cstdlib>
 #include <fstream>
 
 #include "ctx.cuh"
@@ -153,13 +156,13 @@ static std::unique_ptr<hera::LoadedText> acquire_text(Ctx &c, uint64_t n) {
 static void commit_text(Ctx &c, std::unique_ptr<hera::LoadedText> t, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard, hera_load_result *out) {
     if (c.cache_loaded) {
         cudaStreamSynchronize(c.stream);
-        c.text_pool.push_back(std::move(t));
+        if (!t->view) c.text_pool.push_back(std::move(t));
         throw hera::Error{54, "this graph was restored from a cache: hera_graph_reset before loading PAF text"};
     }
     const uint32_t file_id = static_cast<uint32_t>(c.texts.size());
     if (file_id >= 16) {
         cudaStreamSynchronize(c.stream);
-        c.text_pool.push_back(std::move(t));
+        if (!t->view) c.text_pool.push_back(std::move(t));
         throw hera::Error{5, "more than 16 loads per graph are not supported"};
     }
     c.texts.push_back(std::move(t));
@@ -167,7 +170,7 @@ static void commit_text(Ctx &c, std::unique_ptr<hera::LoadedText> t, int anchors
         hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, shard, out);
     } catch (...) {
         cudaStreamSynchronize(c.stream);
-        c.text_pool.push_back(std::move(c.texts.back()));
+        if (!c.texts.back()->view) c.text_pool.push_back(std::move(c.texts.back()));
         c.texts.pop_back();   // the failed load leaves no trace
         throw;
     }
@@ -252,6 +255,23 @@ int hera_graph_load_device(hera_ctx *ctx, const void *device_text, uint64_t n, i
     HERA_API_END
 }
 
+int hera_graph_load_device_view(hera_ctx *ctx, const void *device_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(device_text != nullptr || n == 0, 101, "null text");
+    HERA_REQUIRE((reinterpret_cast<uintptr_t>(device_text) & 15u) == 0, 101, "hera_graph_load_device_view: the text must start at a 16-byte aligned address");
+    if (n == 0) {   // nothing to look at: an empty text of our own keeps every later stage on its usual path
+        load_common(c, device_text, 0, cudaMemcpyDeviceToDevice, anchors, test_load_num, nullptr, out);
+    } else {
+        std::unique_ptr<hera::LoadedText> t(new hera::LoadedText());
+        t->n = n;
+        t->view = static_cast<const uint8_t *>(device_text);
+        hera_load_result tmp{};
+        commit_text(c, std::move(t), anchors, test_load_num, nullptr, &tmp);
+        if (out) *out = tmp;
+    }
+    HERA_API_END
+}
+
 void hera_shard_range(uint64_t file_bytes, int rank, int nranks, uint64_t *begin, uint64_t *end, uint64_t *avail_end) {
     const uint64_t look_ahead = 1ull << 20;   // a record that starts in the slice must end within this many bytes after it
     if (nranks < 1) nranks = 1;
@@ -272,7 +292,17 @@ int hera_graph_load_shard(hera_ctx *ctx, const void *text, int on_device, uint64
     HERA_REQUIRE(owned <= avail, 101, "shard: owned > avail");
     const bool prev_nonws = prev_byte >= 0 && !(prev_byte == ' ' || (prev_byte >= 9 && prev_byte <= 13));
     hera::ShardSpec sp{owned, prev_nonws, at_eof != 0};
-    load_common(c, text, avail, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, anchors, test_load_num, &sp, out);
+    if (on_device == 2 && avail > 0) {   // parsed in place, like hera_graph_load_device_view
+        HERA_REQUIRE((reinterpret_cast<uintptr_t>(text) & 15u) == 0, 101, "hera_graph_load_shard(on_device = 2): the slice must start at a 16-byte aligned address");
+        std::unique_ptr<hera::LoadedText> t(new hera::LoadedText());
+        t->n = avail;
+        t->view = static_cast<const uint8_t *>(text);
+        hera_load_result tmp{};
+        commit_text(c, std::move(t), anchors, test_load_num, &sp, &tmp);
+        if (out) *out = tmp;
+    } else {
+        load_common(c, text, avail, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, anchors, test_load_num, &sp, out);
+    }
     HERA_API_END
 }
 
@@ -364,13 +394,19 @@ int hera_comm_barrier(hera_ctx *ctx) {
     HERA_API_BEGIN(ctx)
     HERA_CUDA(cudaStreamSynchronize(c.stream));
     if (c.xch) c.xch->barrier(c);
+    if (c.xch && getenv("HERA_DEBUG_TIMING")) {
+        timespec ts;
+        clock_gettime(CLOCK_REALTIME, &ts);
+        fprintf(stderr, "[hera rank %d] barrier left at host clock %.3f\n", hera::xch_rank(c), static_cast<double>(ts.tv_sec % 1000) * 1e3 + static_cast<double>(ts.tv_nsec) * 1e-6);
+    }
     HERA_API_END
 }
 
 int hera_graph_reset(hera_ctx *ctx) {
     HERA_API_BEGIN(ctx)
     HERA_CUDA(cudaStreamSynchronize(c.stream));
-    for (auto &t : c.texts) c.text_pool.push_back(std::move(t));
+    for (auto &t : c.texts)
+        if (!t->view) c.text_pool.push_back(std::move(t));   // (a view was the caller's buffer: nothing to recycle)
     c.texts.clear();
     std::sort(c.text_pool.begin(), c.text_pool.end(), [](const auto &a, const auto &b) { return a->bytes.cap > b->bytes.cap; });
     if (c.text_pool.size() > 4) c.text_pool.resize(4);   // keep the largest few

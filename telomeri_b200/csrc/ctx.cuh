@@ -61,6 +61,8 @@ struct RowRange {
 struct LoadedText {
     DBuf<uint8_t> bytes;  // padded with '\n' up to a multiple of the tile size plus one tile
     uint64_t n = 0;
+    const uint8_t *view = nullptr;   // hera_graph_load_device_view: the caller's buffer, parsed in place (nothing readable behind byte n)
+    const uint8_t *data() const { return view ? view : bytes.p; }
 };
 
 struct GraphTables {

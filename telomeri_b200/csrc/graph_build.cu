@@ -522,7 +522,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         // completed by gathering every rank's part (names are short: N * ~10 bytes).
         TextPtrs tp{};
         HERA_REQUIRE(c.texts.size() <= 16 && c.own_rows.size() <= 16, 5, "more than 16 loads per graph are not supported");
-        for (size_t i = 0; i < c.texts.size(); i++) tp.p[i] = c.texts[i]->bytes.p;
+        for (size_t i = 0; i < c.texts.size(); i++) tp.p[i] = c.texts[i]->data();
         OwnRows own{};
         own.n = static_cast<int>(c.own_rows.size());
         for (int i = 0; i < own.n; i++) { own.begin[i] = c.own_rows[i].begin; own.end[i] = c.own_rows[i].end; }

@@ -28,6 +28,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <ctime>
 
 #include "ctx.cuh"
 #include "primitives.cuh"
@@ -290,7 +291,8 @@ __device__ unsigned long long chain_resolve(unsigned long long *state, unsigned 
 }
 
 struct ParseArgs {
-    const uint8_t *text;        // padded: readable up to tiles * PF_TILE + PF_HALO, bytes >= n are '\n'
+    const uint8_t *text;        // padded: readable up to tiles * PF_TILE + PF_HALO, bytes >= n are '\n' (unless `bare`)
+    int bare;                   // the text is a caller's buffer: nothing behind its last 16-byte chunk may be read, bytes >= n count as white space
     uint64_t n;                 // bytes of text available (whole file, or slice + look-ahead)
     uint64_t owned;             // tokens that start at a byte >= owned belong to the next rank (== n for a whole file)
     uint64_t tok_base0;         // global index of the first token that starts in this text (0 for a whole file)
@@ -532,10 +534,20 @@ __device__ __forceinline__ uint32_t token_starts(const ParseArgs &a, const uint3
 // Stage A of a tile, first half: asynchronous 16-byte copies of tile + halo into shared memory (the data is
 // looked at later, after the CTA has done other work).
 __device__ __forceinline__ void stage_issue(const ParseArgs &a, uint32_t tile, const TileView &tv) {
-    const uint8_t *src = a.text + static_cast<uint64_t>(tile) * PF_TILE;
+    const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
+    const uint8_t *src = a.text + tile_byte0;
     const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(tv.text()));
-    for (int ch = threadIdx.x; ch < PF_CHUNKS; ch += PF_THREADS)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + ch * 16), "l"(src + static_cast<size_t>(ch) * 16) : "memory");
+    if (a.bare && tile_byte0 + PF_WIN > a.n) {
+        // the window reaches behind the caller's buffer: chunks that start behind byte n are not read at all (zero filled)
+        for (int ch = threadIdx.x; ch < PF_CHUNKS; ch += PF_THREADS) {
+            const uint64_t off = tile_byte0 + static_cast<uint64_t>(ch) * 16;
+            const uint32_t take = off < a.n ? 16u : 0u;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + ch * 16), "l"(take ? src + static_cast<size_t>(ch) * 16 : a.text), "r"(take) : "memory");
+        }
+    } else {
+        for (int ch = threadIdx.x; ch < PF_CHUNKS; ch += PF_THREADS)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + ch * 16), "l"(src + static_cast<size_t>(ch) * 16) : "memory");
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
@@ -546,10 +558,21 @@ __device__ __forceinline__ void stage_classify(const ParseArgs &a, uint32_t tile
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     const uint8_t *s_text = tv.text();
+    if (a.bare && tile_byte0 + PF_WIN > a.n) {
+        // bytes at and behind n (whatever the last chunk of the caller's buffer holds there, zeros behind it) are white space
+        for (int ch = tid; ch < PF_CHUNKS; ch += PF_THREADS) {
+            const uint4 v = reinterpret_cast<const uint4 *>(s_text)[ch];
+            uint32_t m = nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12);
+            const uint64_t off = tile_byte0 + static_cast<uint64_t>(ch) * 16;
+            if (off + 16 > a.n) m = off >= a.n ? 0u : (m & ((1u << static_cast<uint32_t>(a.n - off)) - 1u));
+            tv.nonws[ch + 2] = static_cast<uint16_t>(m);
+        }
+    } else {
 #pragma unroll 2
-    for (int ch = tid; ch < PF_CHUNKS; ch += PF_THREADS) {
-        const uint4 v = reinterpret_cast<const uint4 *>(s_text)[ch];
-        tv.nonws[ch + 2] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
+        for (int ch = tid; ch < PF_CHUNKS; ch += PF_THREADS) {
+            const uint4 v = reinterpret_cast<const uint4 *>(s_text)[ch];
+            tv.nonws[ch + 2] = static_cast<uint16_t>(nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12));
+        }
     }
     if (tid == 0) {
         uint32_t prev_nonws = a.prev_nonws ? 1u : 0u;  // does the byte before the tile belong to a token?
@@ -839,11 +862,24 @@ static KeptPtrs kept_ptrs(KeptTable &k) {
 
 uint64_t padded_text_size(uint64_t n) { return (n / PF_TILE + 2) * static_cast<uint64_t>(PF_TILE); }
 
+static double host_now_ms() {   // wall clock shared by the ranks of one box (HERA_DEBUG_TIMING)
+    timespec ts;
+    clock_gettime(CLOCK_REALTIME, &ts);
+    return static_cast<double>(ts.tv_sec % 1000) * 1e3 + static_cast<double>(ts.tv_nsec) * 1e-6;
+}
+
 void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out) {
+    const bool debug_timing = getenv("HERA_DEBUG_TIMING") != nullptr;
+    const double t_entry = debug_timing ? host_now_ms() : 0.0;
+    double t_gather = 0.0, t_launched = 0.0;
     const uint64_t n = text.n;
     const uint64_t padded = padded_text_size(n);
-    HERA_REQUIRE(text.bytes.cap >= padded, 3, "internal: text buffer not padded");
-    HERA_LAUNCH(c, pad_text_kernel, div_up(padded - n, 256), 256, 0, text.bytes.p, n, padded);
+    const bool bare = text.view != nullptr;
+    const uint8_t *text_p = text.data();
+    if (!bare) {
+        HERA_REQUIRE(text.bytes.cap >= padded, 3, "internal: text buffer not padded");
+        HERA_LAUNCH(c, pad_text_kernel, div_up(padded - n, 256), 256, 0, text.bytes.p, n, padded);
+    }
     const bool sharded = shard != nullptr;
     const int ranks = xch_size(c), me = xch_rank(c);
     HERA_REQUIRE(!sharded || c.xch, 21, "hera_graph_load_shard needs a communicator (hera_comm_init_nccl / hera_comm_attach_local)");
@@ -859,7 +895,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         c.counters.reserve(16);
         unsigned long long *d_tok = reinterpret_cast<unsigned long long *>(c.counters.p + 13);
         HERA_CUDA(cudaMemsetAsync(d_tok, 0, sizeof(unsigned long long), c.stream));
-        HERA_LAUNCH(c, paf_count_tokens_kernel, 148 * 8, 256, 0, text.bytes.p, owned, sharded && shard->prev_nonws ? 1 : 0, d_tok);
+        HERA_LAUNCH(c, paf_count_tokens_kernel, 148 * 8, 256, 0, text_p, owned, sharded && shard->prev_nonws ? 1 : 0, d_tok);
         c.h_counters.reserve(16);
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 13, d_tok, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -897,13 +933,14 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     uint64_t *d_tok_all = c.counters.p + gather_at, *d_kb_all = d_tok_all + ranks;
     if (sharded) {
         unsigned long long *d_tok = reinterpret_cast<unsigned long long *>(c.counters.p + 13);
-        if (owned) HERA_LAUNCH(c, paf_count_tokens_kernel, std::min<unsigned>(div_up(div_up(owned, 16), 256), 148 * 8), 256, 0, text.bytes.p, owned, shard->prev_nonws ? 1 : 0, d_tok);
+        if (owned) HERA_LAUNCH(c, paf_count_tokens_kernel, std::min<unsigned>(div_up(div_up(owned, 16), 256), 148 * 8), 256, 0, text_p, owned, shard->prev_nonws ? 1 : 0, d_tok);
+        if (debug_timing) t_gather = host_now_ms();
         c.xch->all_gather_dev(c, c.counters.p + 13, d_tok_all, 1);
         HERA_LAUNCH(c, shard_prefix_kernel, 1, 32, 0, d_tok_all, ranks, me, reinterpret_cast<unsigned long long *>(c.counters.p + 14));
         HERA_CUDA(cudaEventRecord(ev2, c.stream));   // (reused below: only read here when HERA_DEBUG_TIMING is set)
     }
 
-    ParseArgs a{text.bytes.p, n, owned, 0, sharded ? reinterpret_cast<const unsigned long long *>(c.counters.p + 14) : nullptr, sharded && shard->prev_nonws ? 1 : 0, (!sharded || shard->at_eof) ? 1 : 0,
+    ParseArgs a{text_p, bare ? 1 : 0, n, owned, 0, sharded ? reinterpret_cast<const unsigned long long *>(c.counters.p + 14) : nullptr, sharded && shard->prev_nonws ? 1 : 0, (!sharded || shard->at_eof) ? 1 : 0,
                 tiles, file_id, anchors ? 1 : 0, rec_limit, c.kept.n, fd, kept_ptrs(c.kept), tok_state, kept_state, ctr};
     int sms = 148;
     HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
@@ -916,12 +953,14 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 16, d_tok_all, 3ull * ranks * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
     }
     HERA_CUDA(cudaMemcpyAsync(c.h_counters.p, ctr, sizeof(ParseCounters), cudaMemcpyDeviceToHost, c.stream));
+    if (debug_timing) t_launched = host_now_ms();
     HERA_CUDA(cudaStreamSynchronize(c.stream));
-    if (sharded && getenv("HERA_DEBUG_TIMING")) {
+    if (sharded && debug_timing) {
         float pre = 0, krn = 0;
         cudaEventElapsedTime(&pre, ev0, ev2);
         cudaEventElapsedTime(&krn, ev2, ev1);
-        fprintf(stderr, "[hera rank %d] load: token exchange %.3f ms, parse kernel %.3f ms\n", me, pre, krn);
+        fprintf(stderr, "[hera rank %d] load: token exchange %.3f ms, parse kernel %.3f ms; host clock: entry %.3f, all-gather queued +%.3f, all queued +%.3f, synchronised +%.3f\n",
+                me, pre, krn, t_entry, t_gather - t_entry, t_launched - t_entry, host_now_ms() - t_entry);
     }
     ParseCounters hc = *reinterpret_cast<ParseCounters *>(c.h_counters.p);
     uint64_t tokens_all = 0;
@@ -965,7 +1004,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 12, d_cut, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         kept_new = c.h_counters.p[12];
-        HERA_LAUNCH(c, paf_tail_kernel, 1, 1, 0, text.bytes.p, n, hc.first_bad_off, hc.first_bad_rec, rec_limit, file_id, anchors ? 1 : 0, fd,
+        HERA_LAUNCH(c, paf_tail_kernel, 1, 1, 0, text_p, n, hc.first_bad_off, hc.first_bad_rec, rec_limit, file_id, anchors ? 1 : 0, fd,
                     kept_ptrs(c.kept), c.kept.n + kept_new, c.kept.qs.cap, ctr);
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p, ctr, sizeof(ParseCounters), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));

@@ -27,8 +27,10 @@ def parse_options(opts):
     return o
 
 
-def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, batched=False, exports=True):
-    """exports=False: make every (collective) call but copy no table back -- the other ranks of a gang at large sizes."""
+def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, batched=False, exports=True, loader="file"):
+    """exports=False: make every (collective) call but copy no table back -- the other ranks of a gang at large sizes.
+    loader="device_view": the PAF files are put into device tensors of exactly their size and parsed in place
+    (hera_graph_load_device_view) instead of going through hera_graph_load_file."""
     o = parse_options(list(opts))
     ds_dir = Path(ds_dir)
     own = hera is None
@@ -36,17 +38,34 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, bat
     out = {}
     try:
         h.set_filter(capi.default_filter(o["mode"], o["min_oll"], o["min_olp"], o["max_ohl"], o["max_ohp"]))
-        r1 = h.load_file(ds_dir / "rr_overlaps.paf", False, o["test_load_num"])
-        r2 = h.load_file(ds_dir / "cr_overlaps.paf", True, o["test_load_num"])
+        if loader == "device_view":
+            import torch
+            held = []   # the library reads node names from these buffers until the graph is finalized / exported
+
+            def load(name, anchors):
+                data = np.fromfile(ds_dir / name, dtype=np.uint8)
+                t = torch.from_numpy(data).to(torch.device("cuda", device)) if data.size else torch.empty(0, dtype=torch.uint8, device=torch.device("cuda", device))
+                held.append(t)
+                return h.load_device_view_ptr(t.data_ptr() if data.size else 0, int(data.size), anchors, o["test_load_num"])
+            out["_held"] = held
+        else:
+            def load(name, anchors):
+                return h.load_file(ds_dir / name, anchors, o["test_load_num"])
+        r1 = load("rr_overlaps.paf", False)
+        r2 = load("cr_overlaps.paf", True)
         out["load_ctr"] = np.array([r1.records, r2.records], dtype=np.uint64)
         out["load_cum_edges"] = np.array([r1.kept_total, r2.kept_total], dtype=np.uint64)
-        h.finalize(o["metrics"])
+        info = h.finalize(o["metrics"])
+        # device times of the stages (CUDA events inside the library), for the full-size runs of tools/run_config.py
+        tm = out["timings_ms"] = {"parse": [r1.parse_ms, r2.parse_ms], "h2d": [r1.h2d_ms, r2.h2d_ms], "paf_bytes": [int(r1.bytes), int(r2.bytes)],
+                                  "intern": info.intern_ms, "csr": info.csr_ms, "ranks": info.rank_ms, "slots": int(info.slots)}
         if exports:
             out.update(h.export_graph())
             out.update(slot_sections(out))
         if stages == "graph":
             return out
         pp = capi.default_path_params(o["rb_att"], o["bt_att"], o["len_thr"], o["w_size"], o["r_thr"])
+        h.timer_start()
         if batched:   # one call, all walk kernels in flight together (hera_paths_build)
             stats = h.build_paths([("mc", m) for m in o["metrics"]] + [("det", m) for m in o["metrics"]], pp, seed)
         else:         # the reference's call sequence (src/Main.cpp:237-243)
@@ -55,7 +74,10 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, bat
                 stats.append(h.monte_carlo(m, pp, seed))
             for m in o["metrics"]:
                 stats.append(h.deterministic(m))
+        tm["walk_stage"] = h.timer_stop()
         out["walk_stats"] = stats
+        tm["walks"] = [round(st.ms, 3) for st in stats]
+        tm["walk_entries_examined"] = int(sum(st.steps for st in stats))
         if exports:
             out.update(h.export_paths("p_"))
         h.unique()
@@ -65,6 +87,7 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, bat
         if stages == "paths":
             return out
         out.update(h.groups(pp))
+        tm["groups"] = out["ms"]
         return out
     finally:
         if own:

@@ -100,6 +100,34 @@ def test_reader_edge_cases_gpu(oracle_bin, tmp_path):
     assert gpu["node_anchor"].sum() == 0
 
 
+def test_device_view_loads_match_oracle(oracle_bin, tmp_path):
+    """hera_graph_load_device_view parses the caller's device buffer in place: nothing behind byte n is readable, so
+    texts whose end falls on / next to a tile, halo or 16-byte chunk boundary (the tokenizer stages 30 KiB tiles + 1 KiB
+    halo in 16-byte chunks) must give the oracle's tables, as must the stream edge cases."""
+    from telomeri_b200 import pipeline
+    rec = "read%05d 9000 10 8990 + ctg1 50000 %d %d 8000 8980 0 tp:A:S cm:i:1 s1:i:1 dv:f:0.1\n"
+    body = "".join(rec % (i, i % 7, 8980 + i % 7) for i in range(1200))   # ~ 3.1 tiles
+    texts = {"whole": body, "no_newline": body.rstrip("\n"), "crlf": body[:5000].replace(" ", "\r\n"), "nonnumeric": body[:3000] + "x" + body[3000:],
+             "one": rec % (1, 0, 8980), "space": " \n"}
+    tile, halo = 30720, 1024
+    for cut in (tile - 17, tile - 1, tile, tile + 1, tile + 15, tile + 16, tile + halo - 1, tile + halo, tile + halo + 1, 2 * tile, 2 * tile + 5, 3 * tile - 16, 3 * tile):
+        texts[f"cut{cut}"] = body[:cut]
+    assert len(body) > 3 * tile
+    for name, text in texts.items():
+        d = tmp_path / name
+        d.mkdir()
+        (d / "rr_overlaps.paf").write_text("")
+        (d / "cr_overlaps.paf").write_text(text, newline="")
+        ora = common.run_dump(oracle_bin, d, d / "o.bin", ["--mode", "max"], extra=["--stage", "graph"])
+        gpu = pipeline.run_hot_path(d, ["--mode", "max"], stages="graph", loader="device_view")
+        common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS, name)
+    # a whole dataset through the views, walks and groups included
+    d = common.make_dataset("small", tmp_path / "small")
+    ora = common.run_dump(oracle_bin, d, d / "o.bin", [], extra=["--rng", "philox", "--seed", "5"])
+    gpu = pipeline.run_hot_path(d, [], seed=5, loader="device_view")
+    common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + PATH_SECTIONS + GROUP_SECTIONS, "small through views")
+
+
 def test_walk_bitmap_in_global_memory(oracle_bin, datasets, tmp_path):
     """Graphs above 65536 nodes keep the visited bitmaps of the Monte-Carlo walks in global memory; force that path."""
     from telomeri_b200 import capi, pipeline

@@ -84,8 +84,10 @@ def test_irregular_file_falls_back_to_the_whole_file_reader(oracle_bin, tmp_path
         assert gang.each(load) == [20, 20]
 
 
-def test_shard_from_device_memory(oracle_bin, datasets, tmp_path):
-    """hera_graph_load_shard with the slice already resident in HBM (what bench.py times)."""
+@pytest.mark.parametrize("on_device", [1, 2], ids=["copied", "in_place"])
+def test_shard_from_device_memory(on_device, oracle_bin, datasets, tmp_path):
+    """hera_graph_load_shard with the slice already resident in HBM: copied into the library's buffer (1) or parsed in
+    place (2, what bench.py times -- a slice ends in the middle of the file, the bytes behind it are not readable)."""
     import torch
     from telomeri_b200 import capi
     ds = datasets["small"]
@@ -103,7 +105,7 @@ def test_shard_from_device_memory(oracle_bin, datasets, tmp_path):
                 t = torch.from_numpy(data[b:a].copy()).to(f"cuda:{devs[r]}") if a > b else torch.zeros(1, dtype=torch.uint8, device=f"cuda:{devs[r]}")
                 torch.cuda.synchronize(devs[r])
                 keep.append(t)
-                res.append(h.load_shard_ptr(t.data_ptr(), True, e - b, a - b, int(data[b - 1]) if b else -1, a == data.size, anchors))
+                res.append(h.load_shard_ptr(t.data_ptr(), on_device, e - b, a - b, int(data[b - 1]) if b else -1, a == data.size, anchors))
             h.finalize(["es", "os"])
             g = h.export_graph()
             g["load_ctr"] = np.array([x.records for x in res], dtype=np.uint64)

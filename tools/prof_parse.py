@@ -21,8 +21,8 @@ h = capi.Hera(0)
 h.set_option("flush_l2", 1)
 for _ in range(reps):
     h.graph_reset()
-    r1 = h.load_device_ptr(rr.data_ptr(), rr.numel(), False)
-    r2 = h.load_device_ptr(cr.data_ptr(), cr.numel(), True)
+    r1 = h.load_device_view_ptr(rr.data_ptr(), rr.numel(), False)
+    r2 = h.load_device_view_ptr(cr.data_ptr(), cr.numel(), True)
     info = h.finalize(["es", "os"])
     print(f"parse {r1.parse_ms:.3f}+{r2.parse_ms:.3f} ms intern {info.intern_ms:.3f} csr {info.csr_ms:.3f} rank {info.rank_ms:.3f}")
 h.close()

@@ -33,8 +33,8 @@ for rep in range(5):
     out = []
     h.graph_reset(); h.paths_reset(); out.append(lap("reset"))
     h.timer_start()
-    h.load_device_ptr(rr.data_ptr(), rr.numel(), False); out.append(lap("load_rr"))
-    h.load_device_ptr(cr.data_ptr(), cr.numel(), True); out.append(lap("load_cr"))
+    h.load_device_view_ptr(rr.data_ptr(), rr.numel(), False); out.append(lap("load_rr"))
+    h.load_device_view_ptr(cr.data_ptr(), cr.numel(), True); out.append(lap("load_cr"))
     info = h.finalize(["es", "os"]); out.append(lap("finalize"))
     g_ms = h.timer_stop()
     if batched:

@@ -18,8 +18,8 @@ rr = torch.from_numpy(np.fromfile(ds / "rr_overlaps.paf", dtype=np.uint8)).to(de
 cr = torch.from_numpy(np.fromfile(ds / "cr_overlaps.paf", dtype=np.uint8)).to(dev)
 torch.cuda.synchronize()
 h = capi.Hera(0)
-h.load_device_ptr(rr.data_ptr(), rr.numel(), False)
-h.load_device_ptr(cr.data_ptr(), cr.numel(), True)
+h.load_device_view_ptr(rr.data_ptr(), rr.numel(), False)
+h.load_device_view_ptr(cr.data_ptr(), cr.numel(), True)
 h.finalize(["es", "os"])
 pp = capi.default_path_params(rb_att=bench.WORKLOAD["rb_att"])
 for w in settings:

@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--ranks", type=int, default=1)
     ap.add_argument("--rb-att", type=int, default=10)
     ap.add_argument("--out", default="/tmp/hera_cfg")
+    ap.add_argument("--no-oracle", action="store_true", help="time the CUDA path only (stage times), no comparison")
+    ap.add_argument("--no-exports", action="store_true", help="with --no-oracle: do not copy the tables back to the host")
     args = ap.parse_args()
     import common
     from telomeri_b200 import capi, pipeline
@@ -47,14 +49,16 @@ def main():
     t_gen = time.perf_counter() - t0
     note(f"generated {meta.strip()}")
     opts = ["--rb-att", str(args.rb_att)]
-    t0 = time.perf_counter()
-    ora = common.run_dump(common.ORACLE_BIN, d, d / "o.bin", opts, extra=["--rng", "philox", "--seed", "17"])
-    t_ora = time.perf_counter() - t0
-    (d / "o.bin").unlink()
-    note(f"oracle done in {t_ora:.0f} s")
+    ora, t_ora = None, 0.0
+    if not args.no_oracle:
+        t0 = time.perf_counter()
+        ora = common.run_dump(common.ORACLE_BIN, d, d / "o.bin", opts, extra=["--rng", "philox", "--seed", "17"])
+        t_ora = time.perf_counter() - t0
+        (d / "o.bin").unlink()
+        note(f"oracle done in {t_ora:.0f} s")
     t0 = time.perf_counter()
     if args.ranks == 1:
-        gpu = pipeline.run_hot_path(d, opts, seed=17, batched=True)
+        gpu = pipeline.run_hot_path(d, opts, seed=17, batched=True, exports=not (args.no_oracle and args.no_exports))
     else:
         import torch
         k = max(1, torch.cuda.device_count())
@@ -65,8 +69,20 @@ def main():
     t_gpu = time.perf_counter() - t0
     note(f"CUDA path done in {t_gpu:.0f} s; comparing")
     names = GRAPH_SECTIONS + ["rank_0", "rank_1"] + PATH_SECTIONS + GROUP_SECTIONS
-    common.assert_sections_equal(ora, gpu, names, args.config)
     st = gpu["walk_stats"]
+    if args.no_oracle:
+        tm = gpu["timings_ms"]
+        rec = int(gpu["load_ctr"].sum())
+        graph_ms = sum(tm["parse"]) + tm["intern"] + tm["csr"] + tm["ranks"]
+        print(json.dumps({"config": args.config, "ranks": args.ranks, "generator": json.loads(meta), "records": rec, "kept_overlaps": int(gpu["load_cum_edges"][-1]),
+                          "walks": int(sum(s.walks for s in st)), "accepted_paths": int(sum(s.found for s in st)), "stage_ms": tm,
+                          "graph_build_ms": round(graph_ms, 2), "overlaps_per_s_graph_build": round(rec / graph_ms * 1e3),
+                          "walks_per_s": round(sum(s.walks for s in st) / tm["walk_stage"] * 1e3),
+                          "parse_GBps": [round(b / ms / 1e6, 1) if ms else None for b, ms in zip(tm["paf_bytes"], tm["parse"])],
+                          "h2d_GBps_incl_file_read": [round(b / ms / 1e6, 1) if ms else None for b, ms in zip(tm["paf_bytes"], tm["h2d"])],
+                          "seconds": {"generate": round(t_gen, 1), "cuda_path_incl_file_io": round(t_gpu, 1)}}))
+        return
+    common.assert_sections_equal(ora, gpu, names, args.config)
     print(json.dumps({"config": args.config, "ranks": args.ranks, "generator": json.loads(meta), "records": int(gpu["load_ctr"].sum()),
                       "kept_overlaps": int(gpu["e_q"].size), "nodes": int(gpu["node_len"].size), "anchors": int(gpu["node_anchor"].sum()),
                       "walks": int(sum(s.walks for s in st)), "paths": int(gpu["p_len"].size), "unique_paths": int(gpu["u_len"].size),
