@@ -177,6 +177,7 @@ struct RowGatherArgs {
     uint64_t count[GR_MAX_RANKS], displ[GR_MAX_RANKS];
     uint64_t n0, mine0;
     int ncols, ranks, skip;   // skip: the rank whose rows are already in place (-1: none)
+    int me;                   // the pulling rank: sources are visited in the order me + 1, me + 2, ... (mod ranks)
 };
 // Packed layout of a rank's rows inside its window: column after column, each starting on a 16-byte boundary.
 __host__ __device__ inline uint64_t window_col_offset(const uint32_t *elem, int k, uint64_t count) {
@@ -199,11 +200,13 @@ __global__ void __launch_bounds__(256) rows_pack_kernel(RowGatherArgs a, int me,
     }
 }
 
-// blockIdx.y = column, blockIdx.z = source rank.  Reads rank z's packed rows of the column out of ITS memory
-// (peer loads over NVLink; 16 bytes per load, the window side is aligned) and writes them to their global place
-// in this rank's column.
+// blockIdx.y = column, blockIdx.z = source: rank (me + 1 + z) mod ranks.  Reads that rank's packed rows of the column
+// out of ITS memory (peer loads over NVLink; 16 bytes per load, the window side is aligned) and writes them to their
+// global place in this rank's column.  Blocks are scheduled in z order, so at any moment the ranks pull from
+// DIFFERENT sources (a ring schedule): with the same order everywhere all ranks would read from one GPU at a time and
+// share its NVLink egress.
 __global__ void __launch_bounds__(256) rows_pull_kernel(RowGatherArgs a) {
-    const int k = blockIdx.y, r = blockIdx.z;
+    const int k = blockIdx.y, r = (a.me + 1 + static_cast<int>(blockIdx.z)) % a.ranks;
     const uint64_t bytes = a.count[r] * a.elem[k];
     if (!bytes || r == a.skip) return;
     const char *src = a.window[r] + window_col_offset(a.elem, k, a.count[r]);
@@ -228,6 +231,51 @@ __global__ void __launch_bounds__(256) rows_pull_kernel(RowGatherArgs a) {
         }
     } else {
         for (uint64_t i = t; i < bytes; i += stride) dst[i] = src[i];
+    }
+}
+
+// ---- mailbox all-gather: a few 64-bit words per rank, exchanged by peer stores over NVLink ------------------------------
+// Every rank owns a small cudaMalloc'ed mailbox that all other ranks map through CUDA IPC.  For gather number `seq`,
+// rank r stores its words into slot [seq & 1][r] of EVERY rank's mailbox (its own included), fences, then stores seq
+// into the slot's tag with release semantics; it then polls the tags of its own mailbox until every rank's message of
+// this gather has arrived.  One launch of 32 threads, no NCCL kernel, no proxy thread: the latency is one NVLink
+// round trip.  Two parities are enough: a rank can only start gather seq + 1 after it has received everybody's seq
+// message, and nobody can start seq + 2 before this rank has sent seq + 1, i.e. before it is done reading parity seq & 1.
+constexpr int MB_MAX_RANKS = GR_MAX_RANKS, MB_MAX_WORDS = 7, MB_SLOT = 1 + MB_MAX_WORDS;   // slot = {tag, words}
+constexpr size_t MB_BYTES = 2ull * MB_MAX_RANKS * MB_SLOT * sizeof(unsigned long long);
+struct MailboxArgs {
+    unsigned long long *box[MB_MAX_RANKS];   // every rank's mailbox as mapped here (box[me] = mine)
+    const unsigned long long *in;
+    unsigned long long *out;
+    unsigned long long seq;
+    int me, ranks, count;
+};
+__global__ void __launch_bounds__(32) mailbox_all_gather_kernel(MailboxArgs a) {
+    const int r = static_cast<int>(threadIdx.x);
+    const int par = static_cast<int>(a.seq & 1ull);
+    if (r < a.ranks) {
+        unsigned long long *slot = a.box[r] + (static_cast<size_t>(par) * MB_MAX_RANKS + a.me) * MB_SLOT;
+        for (int i = 0; i < a.count; i++) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(slot + 1 + i), "l"(a.in[i]) : "memory");
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(slot), "l"(a.seq) : "memory");
+    }
+    if (r < a.ranks) {
+        const unsigned long long *slot = a.box[a.me] + (static_cast<size_t>(par) * MB_MAX_RANKS + r) * MB_SLOT;
+        unsigned long long tag, t0 = 0, spins = 0;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(tag) : "l"(slot) : "memory");
+            if (tag == a.seq) break;
+            if ((++spins & 0xfffull) == 0) {   // a rank that never arrives must not hang the GPU: give up after 30 s (the launch fails)
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (!t0) t0 = now;
+                else if (now - t0 > 30000000000ull) __trap();
+            }
+        }
+        for (int i = 0; i < a.count; i++) {
+            unsigned long long v;
+            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(slot + 1 + i) : "memory");
+            a.out[static_cast<size_t>(r) * a.count + i] = v;
+        }
     }
 }
 
@@ -292,6 +340,7 @@ struct NcclExchange final : Exchange {
         if (d_small) cudaFree(d_small);
         if (h_small) cudaFreeHost(h_small);
         if (d_token) cudaFree(d_token);
+        close_mailbox();
         close_windows();
         if (comm) nccl_api().CommDestroy(comm);
     }
@@ -312,13 +361,69 @@ struct NcclExchange final : Exchange {
         uint64_t *d_in = d_small, *d_out = d_small + count;
         std::memcpy(h_small, in, sizeof(uint64_t) * count);   // pinned staging: pageable copies would serialise with the stream
         HERA_CUDA(cudaMemcpyAsync(d_in, h_small, sizeof(uint64_t) * count, cudaMemcpyHostToDevice, c.stream));
-        HERA_NCCL(n.AllGather(d_in, d_out, static_cast<size_t>(count), ncclUint64, comm, c.stream));
+        if (mailbox_state > 0 && count <= MB_MAX_WORDS) all_gather_dev(c, d_in, d_out, static_cast<size_t>(count));   // peer stores, no NCCL kernel
+        else HERA_NCCL(n.AllGather(d_in, d_out, static_cast<size_t>(count), ncclUint64, comm, c.stream));
         HERA_CUDA(cudaMemcpyAsync(h_small + count, d_out, sizeof(uint64_t) * count * size, cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         std::memcpy(out, h_small + count, sizeof(uint64_t) * count * size);
     }
     void all_gather_dev(Ctx &c, const uint64_t *d_in, uint64_t *d_out, size_t count) override {
+        if (count <= static_cast<size_t>(MB_MAX_WORDS) && ensure_mailbox(c)) {
+            MailboxArgs a{};
+            for (int r = 0; r < size; r++) a.box[r] = peer_mailbox[r];
+            a.in = reinterpret_cast<const unsigned long long *>(d_in);
+            a.out = reinterpret_cast<unsigned long long *>(d_out);
+            a.seq = ++mailbox_seq;
+            a.me = rank; a.ranks = size; a.count = static_cast<int>(count);
+            mailbox_all_gather_kernel<<<1, 32, 0, c.stream>>>(a);
+            c.launches.count++;
+            HERA_CUDA(cudaGetLastError());
+            return;
+        }
         HERA_NCCL(nccl_api().AllGather(d_in, d_out, count, ncclUint64, comm, c.stream));
+    }
+
+    // ---- mailbox (see mailbox_all_gather_kernel): allocated and mapped once per communicator ----
+    unsigned long long *mailbox = nullptr;
+    std::vector<unsigned long long *> peer_mailbox;
+    unsigned long long mailbox_seq = 0;
+    int mailbox_state = 0;             // 0 untested, 1 usable, -1 not available (NCCL all-gathers instead)
+    void close_mailbox() {
+        for (int r = 0; r < static_cast<int>(peer_mailbox.size()); r++)
+            if (r != rank && peer_mailbox[r]) cudaIpcCloseMemHandle(peer_mailbox[r]);
+        peer_mailbox.clear();
+        if (mailbox) cudaFree(mailbox);
+        mailbox = nullptr;
+    }
+    // Collective the first time (every rank reaches its first all_gather_dev at the same point of the protocol).
+    bool ensure_mailbox(Ctx &c) {
+        if (mailbox_state) return mailbox_state > 0;
+        if (size > MB_MAX_RANKS || getenv("HERA_NO_PEER_WINDOWS") || getenv("HERA_NO_MAILBOX")) { mailbox_state = -1; return false; }
+        uint64_t mine[9] = {0};
+        cudaIpcMemHandle_t h;
+        // (the tags are zero before any rank can know the handle: the host gather below is the barrier)
+        bool ok = cudaMalloc(&mailbox, MB_BYTES) == cudaSuccess && cudaMemset(mailbox, 0, MB_BYTES) == cudaSuccess &&
+                  cudaDeviceSynchronize() == cudaSuccess && cudaIpcGetMemHandle(&h, mailbox) == cudaSuccess;
+        if (ok) { std::memcpy(mine, &h, 64); mine[8] = 1; } else cudaGetLastError();
+        std::vector<uint64_t> all(static_cast<size_t>(size) * 9);
+        all_gather_host(c, mine, 9, all.data());
+        for (int r = 0; r < size; r++) ok = ok && all[static_cast<size_t>(r) * 9 + 8] == 1;
+        peer_mailbox.assign(size, nullptr);
+        for (int r = 0; ok && r < size; r++) {
+            if (r == rank) { peer_mailbox[r] = mailbox; continue; }
+            cudaIpcMemHandle_t hr;
+            std::memcpy(&hr, &all[static_cast<size_t>(r) * 9], 64);
+            void *p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+            peer_mailbox[r] = static_cast<unsigned long long *>(p);
+        }
+        uint64_t vote = ok ? 1 : 0;   // all ranks must take the same path
+        std::vector<uint64_t> votes(size);
+        all_gather_host(c, &vote, 1, votes.data());
+        for (uint64_t v : votes) ok = ok && v == 1;
+        if (!ok) { close_mailbox(); mailbox_state = -1; return false; }
+        mailbox_state = 1;
+        return true;
     }
 
     // ---- peer windows: one cudaMalloc'ed buffer per rank, mapped by every other rank through CUDA IPC ----
@@ -389,10 +494,11 @@ struct NcclExchange final : Exchange {
         for (int r = 0; r < size; r++) { a.window[r] = peer_window[r] + half; a.count[r] = counts[r]; a.displ[r] = displs[r]; }
         a.n0 = n0; a.mine0 = mine0; a.ncols = ncols; a.ranks = size;
         a.skip = mine0 == n0 + displs[rank] ? rank : -1;
+        a.me = rank;
         if (counts[rank]) rows_pack_kernel<<<dim3(148, ncols), 256, 0, c.stream>>>(a, rank, window + half);
         // stream-ordered rendezvous: an NCCL all-gather of one word completes on a rank only after every rank's
         // stream has passed its pack kernel
-        HERA_NCCL(nccl_api().AllGather(d_token, d_token + 1, 1, ncclUint64, comm, c.stream));
+        all_gather_dev(c, d_token, d_token + 1, 1);
         rows_pull_kernel<<<dim3(74, ncols, size), 256, 0, c.stream>>>(a);
         c.launches.count += 2;
         HERA_CUDA(cudaGetLastError());

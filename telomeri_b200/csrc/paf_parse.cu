@@ -28,6 +28,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <ctime>
 
 #include "ctx.cuh"
@@ -872,6 +873,22 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     const bool debug_timing = getenv("HERA_DEBUG_TIMING") != nullptr;
     const double t_entry = debug_timing ? host_now_ms() : 0.0;
     double t_gather = 0.0, t_launched = 0.0;
+    // HERA_DEBUG_TIMING=2: synchronise after every phase and note the host clock (which phase does the host wait for?)
+    const bool debug_phases = debug_timing && std::atoi(getenv("HERA_DEBUG_TIMING")) >= 2;
+    std::string phase_log;
+    auto mark = [&](const char *name) {
+        if (!debug_phases) return;
+        cudaStreamSynchronize(c.stream);
+        char buf[64];
+        snprintf(buf, sizeof buf, " %s +%.3f", name, host_now_ms() - t_entry);
+        phase_log += buf;
+    };
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr;   // (debug) device time in front of and behind the timed region
+    if (debug_timing) {
+        cudaEventCreate(&ev_in);
+        cudaEventCreate(&ev_out);
+        cudaEventRecord(ev_in, c.stream);
+    }
     const uint64_t n = text.n;
     const uint64_t padded = padded_text_size(n);
     const bool bare = text.view != nullptr;
@@ -926,6 +943,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     HERA_CUDA(cudaEventCreate(&ev1));
     HERA_CUDA(cudaEventCreate(&ev2));
     maybe_flush_l2(c);
+    mark("setup");
     HERA_CUDA(cudaEventRecord(ev0, c.stream));
 
     // sharded: where do my records start?  tokens before my slice = sum over the earlier ranks, exchanged and added
@@ -934,8 +952,10 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     if (sharded) {
         unsigned long long *d_tok = reinterpret_cast<unsigned long long *>(c.counters.p + 13);
         if (owned) HERA_LAUNCH(c, paf_count_tokens_kernel, std::min<unsigned>(div_up(div_up(owned, 16), 256), 148 * 8), 256, 0, text_p, owned, shard->prev_nonws ? 1 : 0, d_tok);
+        mark("count");
         if (debug_timing) t_gather = host_now_ms();
         c.xch->all_gather_dev(c, c.counters.p + 13, d_tok_all, 1);
+        mark("gather1");
         HERA_LAUNCH(c, shard_prefix_kernel, 1, 32, 0, d_tok_all, ranks, me, reinterpret_cast<unsigned long long *>(c.counters.p + 14));
         HERA_CUDA(cudaEventRecord(ev2, c.stream));   // (reused below: only read here when HERA_DEBUG_TIMING is set)
     }
@@ -947,14 +967,25 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     HERA_CUDA(cudaFuncSetAttribute(paf_parse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM_BYTES));   // per device: cheap, idempotent
     HERA_LAUNCH(c, paf_parse_kernel, std::min<uint32_t>(tiles, static_cast<uint32_t>(sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, a);
     HERA_CUDA(cudaEventRecord(ev1, c.stream));
+    mark("parse");
 
     if (sharded) {   // every rank learns every rank's kept count and whether anybody met an irregular record
         c.xch->all_gather_dev(c, c.counters.p + 2, d_kb_all, 2);   // ParseCounters::kept, first_bad_rec
+        mark("gather2");
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 16, d_tok_all, 3ull * ranks * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
     }
     HERA_CUDA(cudaMemcpyAsync(c.h_counters.p, ctr, sizeof(ParseCounters), cudaMemcpyDeviceToHost, c.stream));
-    if (debug_timing) t_launched = host_now_ms();
+    if (debug_timing) { t_launched = host_now_ms(); cudaEventRecord(ev_out, c.stream); }
     HERA_CUDA(cudaStreamSynchronize(c.stream));
+    if (debug_timing) {
+        float lead = 0, trail = 0;
+        cudaEventElapsedTime(&lead, ev_in, ev0);
+        cudaEventElapsedTime(&trail, ev1, ev_out);
+        fprintf(stderr, "[hera rank %d] load: device time entry -> timed region %.3f ms, parse kernel -> last copy %.3f ms; host clock at phase ends:%s end +%.3f\n", me, lead, trail,
+                phase_log.c_str(), host_now_ms() - t_entry);
+        cudaEventDestroy(ev_in);
+        cudaEventDestroy(ev_out);
+    }
     if (sharded && debug_timing) {
         float pre = 0, krn = 0;
         cudaEventElapsedTime(&pre, ev0, ev2);
