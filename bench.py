@@ -86,6 +86,23 @@ def make_ref_sample(ds):
     return s, json.loads((s / "done").read_text())
 
 
+def bind_to_gpu_cpus(index):
+    """Best effort: run this process (and first-touch its pinned buffers) on the CPUs NVML reports as local to the GPU,
+    so that the e2e leg's host<->device copies do not cross a socket.  No-op where NVML or the affinity call is missing."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 class ClockSampler:
     """nvidia-smi clocks line of the profiling recipe, sampled while the timed region runs."""
 
@@ -275,6 +292,7 @@ def main():
         dist.barrier()
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(local_rank)
+    bind_to_gpu_cpus(local_rank)
     if rank == 0:
         make_dataset(WORKLOAD["seed"], world)
     if world > 1:

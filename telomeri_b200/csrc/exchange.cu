@@ -144,7 +144,9 @@ struct LocalExchange final : Exchange {
 // ---- gather_rows ------------------------------------------------------------------------------
 void Exchange::gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, uint64_t mine0, const uint64_t *counts, const uint64_t *displs) {
     // my rows move up to their global place: stage them so that no receive window overlaps a source
-    const bool staged = mine0 != n0 + displs[rank] && counts[rank] != 0;
+    bool any_inplace = false;
+    for (int k = 0; k < ncols; k++) any_inplace = any_inplace || cols[k].src == nullptr;
+    const bool staged = any_inplace && mine0 != n0 + displs[rank] && counts[rank] != 0;
     char *tmp0 = nullptr;
     if (staged) {
         size_t bytes = 0;
@@ -155,8 +157,8 @@ void Exchange::gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, u
     begin_batch();
     for (int k = 0; k < ncols; k++) {
         char *col = static_cast<char *>(cols[k].base) + n0 * cols[k].elem;
-        const void *send = static_cast<char *>(cols[k].base) + mine0 * cols[k].elem;
-        if (staged) {   // every column gets its own staging area: the batch runs at end_batch
+        const void *send = cols[k].src ? cols[k].src : static_cast<char *>(cols[k].base) + mine0 * cols[k].elem;
+        if (staged && !cols[k].src) {   // every column gets its own staging area: the batch runs at end_batch
             HERA_CUDA(cudaMemcpyAsync(tmp, send, counts[rank] * cols[k].elem, cudaMemcpyDeviceToDevice, c.stream));
             send = tmp;
             tmp += (counts[rank] * cols[k].elem + 255) / 256 * 256;
@@ -172,6 +174,7 @@ namespace {
 constexpr int GR_MAX_COLS = 16, GR_MAX_RANKS = 16;
 struct RowGatherArgs {
     void *col[GR_MAX_COLS];
+    const void *src[GR_MAX_COLS];       // this rank's rows of the column when they are not inside it (else null)
     uint32_t elem[GR_MAX_COLS];
     const char *window[GR_MAX_RANKS];   // every rank's packed rows (window[r] lives on GPU r)
     uint64_t count[GR_MAX_RANKS], displ[GR_MAX_RANKS];
@@ -190,7 +193,7 @@ __host__ __device__ inline uint64_t window_col_offset(const uint32_t *elem, int 
 __global__ void __launch_bounds__(256) rows_pack_kernel(RowGatherArgs a, int me, char *window) {
     const int k = blockIdx.y;
     const uint64_t bytes = a.count[me] * a.elem[k];
-    const char *src = static_cast<const char *>(a.col[k]) + a.mine0 * a.elem[k];
+    const char *src = a.src[k] ? static_cast<const char *>(a.src[k]) : static_cast<const char *>(a.col[k]) + a.mine0 * a.elem[k];
     char *dst = window + window_col_offset(a.elem, k, a.count[me]);
     const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x, t = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (a.elem[k] % 4 == 0) {
@@ -485,7 +488,8 @@ struct NcclExchange final : Exchange {
         HERA_REQUIRE(ncols <= GR_MAX_COLS, 36, "gather_rows: too many columns");
         uint64_t max_rows = 0;
         for (int r = 0; r < size; r++) max_rows = std::max(max_rows, counts[r]);
-        for (int k = 0; k < ncols; k++) { a.col[k] = cols[k].base; a.elem[k] = cols[k].elem; }
+        bool all_inplace = true;
+        for (int k = 0; k < ncols; k++) { a.col[k] = cols[k].base; a.elem[k] = cols[k].elem; a.src[k] = cols[k].src; all_inplace = all_inplace && !cols[k].src; }
         const size_t need = window_col_offset(a.elem, ncols, max_rows) + 16;
         if (!ensure_windows(c, 2 * ((need + 255) / 256 * 256))) { Exchange::gather_rows(c, cols, ncols, n0, mine0, counts, displs); return; }
         // The windows have two halves used in turn: a half is written again two gathers later, and no rank gets past
@@ -493,7 +497,7 @@ struct NcclExchange final : Exchange {
         const size_t half = (gather_seq++ & 1u) ? window_cap / 2 : 0;
         for (int r = 0; r < size; r++) { a.window[r] = peer_window[r] + half; a.count[r] = counts[r]; a.displ[r] = displs[r]; }
         a.n0 = n0; a.mine0 = mine0; a.ncols = ncols; a.ranks = size;
-        a.skip = mine0 == n0 + displs[rank] ? rank : -1;
+        a.skip = all_inplace && mine0 == n0 + displs[rank] ? rank : -1;
         a.me = rank;
         if (counts[rank]) rows_pack_kernel<<<dim3(148, ncols), 256, 0, c.stream>>>(a, rank, window + half);
         // stream-ordered rendezvous: an NCCL all-gather of one word completes on a rank only after every rank's

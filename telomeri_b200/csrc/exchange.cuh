@@ -45,7 +45,9 @@ struct Exchange {
     // rank holds every rank's rows, rank r's at n0 + displs[r] (mine0 is n0, or already n0 + displs[rank]).  The base implementation issues one all_gatherv per
     // column in one batch; the NCCL transport pulls the rows straight out of the peers' memory over NVLink with
     // its own kernel when the ranks can map each other's buffers.
-    struct Column { void *base; uint32_t elem; };
+    // A column may name a separate source for this rank's rows (src != nullptr: counts[rank] elements there, mine0 is ignored
+    // for it); the walk stage gathers per-walk results and path pools out of their scratch buffers that way.
+    struct Column { void *base; uint32_t elem; const void *src = nullptr; };
     virtual void gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, uint64_t mine0, const uint64_t *counts, const uint64_t *displs);
     // Host barrier (after synchronising the context's stream).
     virtual void barrier(Ctx &c) = 0;

@@ -688,14 +688,12 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
             };
             alloc(&g_n, wtot); alloc(&g_draws, wtot); alloc(&g_off, wtot); alloc(&g_len, wtot); alloc(&g_pn, ptot); alloc(&g_ps, ptot);
             alloc(&o_n, wtot); alloc(&o_draws, wtot); alloc(&o_off, wtot); alloc(&o_len, wtot);
-            c.xch->begin_batch();
-            c.xch->all_gatherv(c, r.res_n, g_n, wcount.data(), wdispl.data(), sizeof(uint32_t));
-            c.xch->all_gatherv(c, r.res_draws, g_draws, wcount.data(), wdispl.data(), sizeof(uint32_t));
-            c.xch->all_gatherv(c, r.res_off, g_off, wcount.data(), wdispl.data(), sizeof(uint64_t));
-            c.xch->all_gatherv(c, r.res_len, g_len, wcount.data(), wdispl.data(), sizeof(int64_t));
-            c.xch->all_gatherv(c, r.pool_nodes, g_pn, pcount.data(), pdispl.data(), sizeof(uint32_t));
-            c.xch->all_gatherv(c, r.pool_slots, g_ps, pcount.data(), pdispl.data(), sizeof(uint32_t));
-            c.xch->end_batch();
+            // two row gathers (per-walk results, path pools): over peer windows on the NCCL transport (pack, mailbox
+            // rendezvous, pull over NVLink), else one batch of all_gatherv calls
+            const Exchange::Column wcols[4] = {{g_n, 4, r.res_n}, {g_draws, 4, r.res_draws}, {g_off, 8, r.res_off}, {g_len, 8, r.res_len}};
+            const Exchange::Column pcols[2] = {{g_pn, 4, r.pool_nodes}, {g_ps, 4, r.pool_slots}};
+            c.xch->gather_rows(c, wcols, 4, 0, 0, wcount.data(), wdispl.data());
+            c.xch->gather_rows(c, pcols, 2, 0, 0, pcount.data(), pdispl.data());
             HERA_LAUNCH(c, walk_order_kernel, div_up(total_walks, 256), 256, 0, total_walks, static_cast<uint32_t>(ranks), t, g_n, g_off, g_len, g_draws,
                         o_n, o_off, o_len, o_draws);
             res_n = o_n; res_draws = o_draws; res_off = o_off; res_len = o_len; pool_nodes = g_pn; pool_slots = g_ps;
