@@ -132,6 +132,7 @@ struct Ctx {
     DBuf<uint8_t> scratch_a, scratch_b, scratch_c, scratch_d;
     DBuf<uint64_t> counters;     // small device counter block
     HBuf<uint64_t> h_counters;
+    HBuf<unsigned long long> walk_h_ctr;   // pinned result words of the walk jobs in flight (4 per job)
 
     // export mirrors (pinned)
     struct GraphMirror {

@@ -571,7 +571,7 @@ void job_launch_kernel(Ctx &c, WalkJob &j) {
 
 // Sizes the job, allocates its scratch (stream-ordered on the context's stream) and fills the walk table
 // of a greedy job.  warps_per_sm: this job's share of the resident walk warps.
-void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm) {
+void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm, int slot) {
     GraphTables &g = c.g;
     HERA_REQUIRE(g.ready, 7, "walks: call hera_graph_finalize first");
     HERA_REQUIRE(j.metric >= 0 && j.metric < 4, 8, "unknown metric");
@@ -601,7 +601,8 @@ void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm) {
     j.my_walks = walk_share(j.total_walks, ranks, me);
     HERA_CUDA(cudaEventCreate(&j.ev0));
     HERA_CUDA(cudaEventCreate(&j.ev1));
-    HERA_CUDA(cudaMallocHost(&j.h_ctr, 4 * sizeof(unsigned long long)));
+    c.walk_h_ctr.reserve(64);   // pinned once per context (cudaMallocHost / cudaFreeHost per job cost more than the small kernels around them)
+    j.h_ctr = c.walk_h_ctr.p + 4 * slot;
     for (int k = 0; k < 4; k++) j.h_ctr[k] = 0;
     if (j.total_walks == 0) { j.launches = c.launches.count - launches0; return; }
     int sms = 148;
@@ -743,7 +744,6 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
     if (j.first_edges) { HERA_CUDA(cudaFreeAsync(j.first_edges, c.stream)); HERA_CUDA(cudaFreeAsync(j.walk_base, c.stream)); }
     cudaEventDestroy(j.ev0);
     cudaEventDestroy(j.ev1);
-    cudaFreeHost(j.h_ctr);
     j.h_ctr = nullptr;
     c.uniq_ready = false;
     c.groups_valid = false;
@@ -771,7 +771,7 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
         WalkJob &j = jobs[i];
         j.kind = kinds[i] ? 1 : 0; j.metric = metrics[i]; j.pp = pp; j.seed = seed;
         const int share = n == 1 ? budget : (j.kind == 0 ? std::max(8, (budget - 4 * det) / std::max(1, mc)) : 4);
-        job_prepare(c, j, share);
+        job_prepare(c, j, share, i);
     }
     if (n == 1) {
         jobs[0].stream = c.stream;
