@@ -79,6 +79,7 @@ hera_ctx *hera_create(int device) {
         uint64_t threshold = UINT64_MAX;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
     }
+    if (const char *v = getenv("HERA_PARSE_VARIANT")) h->c.opt_parse_variant = std::atoi(v);   // tuning experiments: same as hera_set_option("parse_variant")
     return h;
 }
 
@@ -125,6 +126,7 @@ int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
     if (k == "flush_l2") c.opt_flush_l2 = value != 0;
     else if (k == "walk_warps_per_sm") c.opt_walk_warps_per_sm = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(64, value)));
     else if (k == "walk_variant") c.opt_walk_variant = static_cast<int>(value);
+    else if (k == "parse_variant") c.opt_parse_variant = static_cast<int>(value);
     else if (k == "walk_smem_bitmap") c.opt_walk_smem_bitmap = value != 0;
     else throw hera::Error{102, "unknown option: " + k};
     HERA_API_END

@@ -108,6 +108,7 @@ struct Ctx {
     cudaEvent_t timer0 = nullptr, timer1 = nullptr;
     int opt_flush_l2 = 0;
     int opt_walk_warps_per_sm = 64;
+    int opt_parse_variant = 0;     // 0 = CTA tiles (paf_parse_kernel), 1 = warp-autonomous sub-tiles (paf_parse_warp_kernel)
     int opt_walk_variant = 0;      // Monte-Carlo kernel variant (chunks in flight x resident CTAs), see walks.cu
     int opt_walk_smem_bitmap = 1;  // 0 = keep the walks' visited bitmaps in global memory whatever the graph size (tests)
     uint64_t walk_pool_hint[2][4] = {};   // per (kind, metric): largest path pool a walk call needed so far (avoids the overflow re-run)

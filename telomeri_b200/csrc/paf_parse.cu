@@ -291,6 +291,41 @@ __device__ unsigned long long chain_resolve(unsigned long long *state, unsigned 
     return excl;
 }
 
+// Look-back for chains with MANY short tiles (the warp-autonomous kernel: one tile per 3 KiB): K windows of 32
+// predecessors are requested together, so one round trip to L2 covers 32 K tiles.  With a single window the chain
+// could resolve at most 32 tiles per round trip, less than the rate at which the warps of the GPU finish tiles.
+template <int K>
+__device__ unsigned long long chain_resolve_wide(unsigned long long *state, unsigned int tile, unsigned long long aggregate) {
+    const uint32_t lane = lane_id();
+    if (tile == 0) return 0;
+    unsigned long long acc = 0;
+    int look = static_cast<int>(tile) - 1;
+    for (bool done = false; !done; look -= 32 * K) {
+        unsigned long long s[K];
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int idx = look - static_cast<int>(lane) - 32 * k;
+            s[k] = idx >= 0 ? ld_state(&state[idx]) : ST_INC;   // tiles before 0 behave like an inclusive prefix of 0
+        }
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            if (done) continue;   // warp-uniform
+            const int idx = look - static_cast<int>(lane) - 32 * k;
+            if (idx >= 0) {
+                while ((s[k] & ST_MASK) == 0) s[k] = ld_state(&state[idx]);
+            }
+            const uint32_t inc_mask = __ballot_sync(0xffffffffu, (s[k] & ST_MASK) == ST_INC);
+            const uint32_t upto = inc_mask ? static_cast<uint32_t>(__ffs(inc_mask)) : 32u;  // lanes [0, upto) contribute
+            if (lane < upto) acc += s[k] & ~ST_MASK;
+            done = inc_mask != 0;
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if (lane == 0) st_state(&state[tile], ST_INC | (acc + aggregate));
+    return acc;
+}
+
 struct ParseArgs {
     const uint8_t *text;        // padded: readable up to tiles * PF_TILE + PF_HALO, bytes >= n are '\n' (unless `bare`)
     int bare;                   // the text is a caller's buffer: nothing behind its last 16-byte chunk may be read, bytes >= n count as white space
@@ -333,15 +368,16 @@ __device__ __noinline__ int slow_path_record(const ParseArgs &a, uint64_t start,
 // text words are read whole and shifted into place -- no per-byte loops on the regular path.
 
 // First position >= p whose mask bit equals `one`; >= PF_WIN when the window has none.
+template <int WIN>
 __device__ __noinline__ uint32_t next_bit(const uint32_t *mask, uint32_t p, bool one) {
-    while (p < PF_WIN) {
+    while (p < static_cast<uint32_t>(WIN)) {
         const uint32_t w = p >> 5;
         uint32_t win = __funnelshift_r(mask[w], mask[w + 1], p & 31u);
         if (!one) win = ~win;
         if (win) return p + __ffs(win) - 1;
         p += 32;
     }
-    return PF_WIN;
+    return WIN;
 }
 
 // Hash of the token [b, e): same function as NameHash fed byte by byte.
@@ -414,6 +450,7 @@ __device__ __forceinline__ bool int_token(const uint8_t *s, uint32_t b, uint32_t
 // Span of the token that starts at b (a set mask bit, or PF_WIN when the window is used up): e = its end,
 // nb = start of the next token.  One 32-bit window of the mask usually holds both.  Everything stays <= PF_WIN
 // (the mask is zero behind the window), so a record that runs out of window just yields empty tokens.
+template <int WIN>
 __device__ __forceinline__ void token_span(const uint32_t *mask, uint32_t b, uint32_t &e, uint32_t &nb) {
     const uint32_t w = b >> 5;
     const uint32_t win = __funnelshift_r(mask[w], mask[w + 1], b & 31u);
@@ -422,16 +459,17 @@ __device__ __forceinline__ void token_span(const uint32_t *mask, uint32_t b, uin
         const uint32_t eo = __ffs(zeros) - 1;
         e = b + eo;
         const uint32_t ones = win & (0xffffffffu << eo);
-        nb = ones ? b + __ffs(ones) - 1 : next_bit(mask, b + 32, true);
+        nb = ones ? b + __ffs(ones) - 1 : next_bit<WIN>(mask, b + 32, true);
     } else {
-        e = next_bit(mask, b + 32, false);
-        nb = next_bit(mask, e, true);
+        e = next_bit<WIN>(mask, b + 32, false);
+        nb = next_bit<WIN>(mask, e, true);
     }
 }
 
 // One thread reads one record from the staged window: twelve tokens in straight-line code (fields stay in
 // registers).  A token that is not what formatted extraction expects makes the record irregular, unless the
 // window ran out first (then the exact reader decides).  Returns the keep flag.
+template <int WIN>
 __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, const uint32_t *mask, uint32_t p0, uint64_t tile_byte0,
                                           bool reaches_eof, uint64_t rec_idx, StagedRecord &out) {
     if (rec_idx >= a.rec_limit) return false;
@@ -440,22 +478,22 @@ __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, 
     bool bad = false;
     auto int_field = [&](int &v) {
         b = nb;
-        token_span(mask, b, e, nb);
+        token_span<WIN>(mask, b, e, nb);
         const bool ok = int_token(s, b, e, v);
-        bad |= !ok && e < PF_WIN;
+        bad |= !ok && e < static_cast<uint32_t>(WIN);
     };
-    token_span(mask, b, e, nb);
+    token_span<WIN>(mask, b, e, nb);
     const uint32_t qb = b, qe = e;
     int_field(r.qlen); int_field(r.qs); int_field(r.qe);
     b = nb;
-    token_span(mask, b, e, nb);
+    token_span<WIN>(mask, b, e, nb);
     r.strand = s[b];
-    bad |= (e - b != 1u) && e < PF_WIN;
+    bad |= (e - b != 1u) && e < static_cast<uint32_t>(WIN);
     b = nb;
-    token_span(mask, b, e, nb);
+    token_span<WIN>(mask, b, e, nb);
     const uint32_t tb = b, te = e;
     int_field(r.tlen); int_field(r.ts); int_field(r.te); int_field(r.matches); int_field(r.block); int_field(r.mapq);
-    int status = bad ? 0 : (e >= PF_WIN ? 2 : 1);   // 1 regular, 0 irregular, 2 window exhausted
+    int status = bad ? 0 : (e >= static_cast<uint32_t>(WIN) ? 2 : 1);   // 1 regular, 0 irregular, 2 window exhausted
     if (status == 1) {
         r.qoff = tile_byte0 + qb; r.qnlen = qe - qb; r.qhash = hash_name_window(s, qb, qe);
         r.toff = tile_byte0 + tb; r.tnlen = te - tb; r.thash = hash_name_window(s, tb, te);
@@ -738,7 +776,7 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
             const uint32_t j = b0 + tid;
             StagedRecord r;
             bool keep = false;
-            if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+            if (j < nrec) keep = parse_one<PF_WIN>(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
             const uint32_t votes = __ballot_sync(0xffffffffu, keep);
             if (lane == 31) s_tot_kept[warp] = __popc(votes);
             __syncthreads();
@@ -769,7 +807,7 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
                 const uint32_t j = b0 + tid;
                 StagedRecord r;
                 bool keep = false;
-                if (j < nrec) keep = parse_one(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+                if (j < nrec) keep = parse_one<PF_WIN>(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
                 const uint32_t votes = __ballot_sync(0xffffffffu, keep);
                 if (lane == 31) s_tot_kept[warp] = __popc(votes);
                 __syncthreads();
@@ -793,6 +831,154 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
         next = after;
         f = fn;
         p ^= 1;
+    }
+}
+
+// ---- warp-autonomous variant (hera_set_option "parse_variant" = 1) -----------------------------------------------------
+// Same algorithm, no CTA-wide barrier: every WARP takes its own 3 KiB sub-tile (+ 256 bytes of halo) by ticket, stages and
+// classifies it in its own slice of shared memory, publishes / resolves both chains itself and parses one record per
+// lane.  The CTA kernel above spends a third of its stall samples at barriers (warps of a CTA finish the record stage at
+// different times); here a warp that waits -- for its copy, for a predecessor in a chain -- only stalls itself, the other
+// warps of the SM keep the issue slots busy.  The chains have ten times more entries (one per sub-tile).  A record that
+// does not end inside the halo (names of several hundred bytes) goes to the exact one-thread reader.
+constexpr int WW_TILE = 3072, WW_HALO = 256, WW_WIN = WW_TILE + WW_HALO, WW_CHUNKS = WW_WIN / 16;
+constexpr int WW_WARPS = 8, WW_THREADS = WW_WARPS * 32, WW_MIN_CTAS = 4;
+constexpr int WW_WPL = WW_TILE / 32 / 32;                 // mask words (32 bytes each) per lane
+static_assert(WW_WPL * 32 * 32 == WW_TILE, "sub-tile = 32 lanes x whole mask words");
+constexpr int WW_MAXREC = WW_TILE / 32 + 2;
+constexpr int WW_RAW_BYTES = WW_WIN + 32;
+constexpr int WW_MASK_BYTES = ((WW_CHUNKS + 2 + 4) * 2 + 15) / 16 * 16;
+constexpr int WW_REC_BYTES = (WW_MAXREC * 2 + 15) / 16 * 16;
+constexpr int WW_BUF_BYTES = WW_RAW_BYTES + WW_MASK_BYTES + WW_REC_BYTES;
+static_assert(WW_RAW_BYTES % 16 == 0 && WW_BUF_BYTES % 16 == 0, "per-warp buffers stay 16-byte aligned");
+
+__global__ void __launch_bounds__(WW_THREADS, WW_MIN_CTAS) paf_parse_warp_kernel(const ParseArgs a) {
+    __shared__ __align__(16) uint8_t s_buf[WW_WARPS * WW_BUF_BYTES];
+    const uint32_t lane = lane_id(), warp = warp_id();
+    uint8_t *raw = s_buf + warp * WW_BUF_BYTES;
+    uint8_t *s_text = raw + 16;
+    uint16_t *nonws = reinterpret_cast<uint16_t *>(raw + WW_RAW_BYTES);
+    const uint32_t *mask = reinterpret_cast<const uint32_t *>(nonws) + 1;   // word i = bytes [32 i, 32 i + 32) of the sub-tile
+    uint16_t *s_rec_off = reinterpret_cast<uint16_t *>(raw + WW_RAW_BYTES + WW_MASK_BYTES);
+    const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(s_text));
+    const unsigned long long tok_base0 = a.tok_base0_dev ? *a.tok_base0_dev : a.tok_base0;
+
+    for (;;) {
+        uint32_t tile = 0;
+        if (lane == 0) tile = atomicAdd(&a.ctr->ticket, 1u);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= a.tiles) break;
+        const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * WW_TILE;
+        const bool tail = a.bare && tile_byte0 + WW_WIN > a.n;   // the window reaches behind the caller's buffer
+        __syncwarp();   // everybody is done with the previous sub-tile's buffers
+
+        // 1. stage text + halo
+        const uint8_t *src = a.text + tile_byte0;
+        for (int ch = lane; ch < WW_CHUNKS; ch += 32) {
+            const uint64_t off = tile_byte0 + static_cast<uint64_t>(ch) * 16;
+            const uint32_t take = (!tail || off < a.n) ? 16u : 0u;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + ch * 16), "l"(take ? src + static_cast<size_t>(ch) * 16 : a.text), "r"(take) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (lane == 0) {
+            uint32_t prev_nonws = a.prev_nonws ? 1u : 0u;  // does the byte before the sub-tile belong to a token?
+            if (tile_byte0 > 0) prev_nonws = dev_is_space(a.text[tile_byte0 - 1]) ? 0u : 1u;
+            nonws[1] = static_cast<uint16_t>(prev_nonws << 15);
+            for (int k = 0; k < 4; k++) nonws[WW_CHUNKS + 2 + k] = 0;
+            for (int k = 0; k < 4; k++) { reinterpret_cast<uint32_t *>(raw)[k] = 0x20202020u; reinterpret_cast<uint32_t *>(raw + 16 + WW_WIN)[k] = 0x20202020u; }
+        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        // 2. classify the chunks this lane copied
+        for (int ch = lane; ch < WW_CHUNKS; ch += 32) {
+            const uint4 v = reinterpret_cast<const uint4 *>(s_text)[ch];
+            uint32_t m = nonspace4(v.x) | (nonspace4(v.y) << 4) | (nonspace4(v.z) << 8) | (nonspace4(v.w) << 12);
+            if (tail) {
+                const uint64_t off = tile_byte0 + static_cast<uint64_t>(ch) * 16;
+                if (off + 16 > a.n) m = off >= a.n ? 0u : (m & ((1u << static_cast<uint32_t>(a.n - off)) - 1u));
+            }
+            nonws[ch + 2] = static_cast<uint16_t>(m);
+        }
+        __syncwarp();
+
+        // 3. token starts of this lane's mask words (consecutive: lane order = text order)
+        uint32_t starts[WW_WPL];
+        uint32_t carry = mask[static_cast<int>(lane * WW_WPL) - 1] >> 31;
+#pragma unroll
+        for (int k = 0; k < WW_WPL; k++) {
+            const uint32_t m = mask[lane * WW_WPL + k];
+            starts[k] = m & ~((m << 1) | carry);
+            carry = m >> 31;
+        }
+        if (tile_byte0 + WW_TILE > a.owned) {   // only the sub-tile that holds the end of this rank's byte range
+#pragma unroll
+            for (int k = 0; k < WW_WPL; k++) {
+                const uint64_t b0 = tile_byte0 + static_cast<uint64_t>(lane * WW_WPL + k) * 32;
+                if (b0 + 32 > a.owned) starts[k] = b0 >= a.owned ? 0u : (starts[k] & ((1u << static_cast<uint32_t>(a.owned - b0)) - 1u));
+            }
+        }
+        uint32_t my_tokens = 0;
+#pragma unroll
+        for (int k = 0; k < WW_WPL; k++) my_tokens += __popc(starts[k]);
+        uint32_t incl = my_tokens;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= static_cast<uint32_t>(d)) incl += up;
+        }
+        const uint32_t tile_tokens = __shfl_sync(0xffffffffu, incl, 31), excl = incl - my_tokens;
+
+        // 4. chain 1: tokens before this sub-tile
+        if (lane == 0) chain_publish(a.tok_state, tile, tile_tokens);
+        const unsigned long long tbase = chain_resolve_wide<16>(a.tok_state, tile, tile_tokens);
+        if (lane == 0 && tile == a.tiles - 1) a.ctr->total_tokens = tbase + tile_tokens;
+        const unsigned long long tok_base = tok_base0 + tbase;
+
+        // 5. offsets of the records that start here (every 16th token)
+        const uint32_t first_rec_ord = static_cast<uint32_t>((16 - (tok_base & 15)) & 15);
+        const uint32_t nrec = tile_tokens > first_rec_ord ? (tile_tokens - first_rec_ord + 15) / 16 : 0;
+        for (uint32_t ord = static_cast<uint32_t>((16 - ((tok_base + excl) & 15)) & 15); ord < my_tokens; ord += 16) {
+            uint32_t r = ord, word = starts[0], k = 0;
+#pragma unroll
+            for (int j = 1; j < WW_WPL; j++) {
+                const uint32_t cnt = __popc(starts[j - 1]);
+                if (k == static_cast<uint32_t>(j - 1) && r >= cnt) { r -= cnt; word = starts[j]; k = j; }
+            }
+            s_rec_off[(excl + ord - first_rec_ord) >> 4] = static_cast<uint16_t>((lane * WW_WPL + k) * 32 + select_bit32(word, r));
+        }
+        __syncwarp();
+
+        // 6. one lane per record: parse, filter, score (further rounds only for tiny records; those are parsed again below)
+        const bool reaches_eof = a.at_eof && tile_byte0 + WW_WIN >= a.n;
+        const uint64_t first_rec = (tok_base + first_rec_ord) >> 4;
+        StagedRecord mine;
+        bool keep0 = false;
+        uint32_t e0 = 0, tot0 = 0, tile_kept = 0;
+        for (uint32_t b0 = 0; b0 < nrec; b0 += 32) {
+            const uint32_t j = b0 + lane;
+            StagedRecord r;
+            bool keep = false;
+            if (j < nrec) keep = parse_one<WW_WIN>(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+            const uint32_t votes = __ballot_sync(0xffffffffu, keep);
+            if (b0 == 0) { mine = r; keep0 = keep; e0 = __popc(votes & ((1u << lane) - 1u)); tot0 = __popc(votes); }
+            tile_kept += __popc(votes);
+        }
+
+        // 7. chain 2: kept records before this sub-tile, then the rows go to their final place
+        if (lane == 0) chain_publish(a.kept_state, tile, tile_kept);
+        const unsigned long long kbase = chain_resolve_wide<16>(a.kept_state, tile, tile_kept);
+        if (lane == 0 && tile == a.tiles - 1) a.ctr->kept = kbase + tile_kept;
+        const uint64_t out0 = a.kept_base + kbase;
+        if (keep0) store_record(a.kept, out0 + e0, mine);
+        uint32_t run = tot0;
+        for (uint32_t b0 = 32; b0 < nrec; b0 += 32) {
+            const uint32_t j = b0 + lane;
+            StagedRecord r;
+            bool keep = false;
+            if (j < nrec) keep = parse_one<WW_WIN>(a, s_text, mask, s_rec_off[j], tile_byte0, reaches_eof, first_rec + j, r);
+            const uint32_t votes = __ballot_sync(0xffffffffu, keep);
+            if (keep) store_record(a.kept, out0 + run + __popc(votes & ((1u << lane) - 1u)), r);
+            run += __popc(votes);
+        }
     }
 }
 
@@ -903,7 +1089,8 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     const uint64_t owned = sharded ? shard->owned : n;
     HERA_REQUIRE(owned <= n, 101, "shard: owned bytes exceed the bytes provided");
 
-    const uint32_t tiles = static_cast<uint32_t>(owned / PF_TILE + 1);
+    const bool warp_variant = c.opt_parse_variant == 1;
+    const uint32_t tiles = static_cast<uint32_t>(owned / (warp_variant ? WW_TILE : PF_TILE) + 1);
     // worst case every record is kept: records <= bytes / 24 (12 one-byte tokens + separators).  For a large text that
     // bound would reserve far more rows than the file can hold records (42 GB of PAF -> 128 GB of rows), so the tokens
     // are counted first (one more pass over the text) and the rows are reserved for tokens / 16 records.
@@ -965,7 +1152,11 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     int sms = 148;
     HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
     HERA_CUDA(cudaFuncSetAttribute(paf_parse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM_BYTES));   // per device: cheap, idempotent
-    HERA_LAUNCH(c, paf_parse_kernel, std::min<uint32_t>(tiles, static_cast<uint32_t>(sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, a);
+    if (warp_variant) {
+        HERA_LAUNCH(c, paf_parse_warp_kernel, std::min<uint32_t>(div_up(tiles, WW_WARPS), static_cast<uint32_t>(sms) * WW_MIN_CTAS), WW_THREADS, 0, a);
+    } else {
+        HERA_LAUNCH(c, paf_parse_kernel, std::min<uint32_t>(tiles, static_cast<uint32_t>(sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, a);
+    }
     HERA_CUDA(cudaEventRecord(ev1, c.stream));
     mark("parse");
 
