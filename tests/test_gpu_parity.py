@@ -128,6 +128,16 @@ def test_device_view_loads_match_oracle(oracle_bin, tmp_path):
     common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + PATH_SECTIONS + GROUP_SECTIONS, "small through views")
 
 
+def test_warp_parse_variant_matches_oracle(oracle_bin, tmp_path, monkeypatch):
+    """paf_parse_warp_kernel (parse_variant = 1: one 3 KiB sub-tile per warp, no CTA barrier; opt-in, see DESIGN.md K1+K2)
+    must give the same tables as the default kernel: stream edge cases, in-place loads cut at every boundary, a dataset."""
+    monkeypatch.setenv("HERA_PARSE_VARIANT", "1")
+    for name, fn in (("edge", test_reader_edge_cases_gpu), ("view", test_device_view_loads_match_oracle)):
+        d = tmp_path / name
+        d.mkdir()
+        fn(oracle_bin, d)
+
+
 def test_walk_bitmap_in_global_memory(oracle_bin, datasets, tmp_path):
     """Graphs above 65536 nodes keep the visited bitmaps of the Monte-Carlo walks in global memory; force that path."""
     from telomeri_b200 import capi, pipeline
