@@ -26,4 +26,6 @@ def datasets(tmp_path_factory):
     dirs = {"bundled": common.bundled_dataset(root / "bundled")}
     for name in common.DATASETS:
         dirs[name] = common.make_dataset(name, root / name)
+    for name in common.STAR_DATASETS:
+        dirs[name] = common.make_star_dataset(name, root / name)
     return dirs

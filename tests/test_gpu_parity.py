@@ -36,6 +36,16 @@ def test_hot_path_matches_oracle(case, oracle_bin, datasets, tmp_path):
     common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + ranks, case + " graph")
     common.assert_sections_equal(ora, gpu, PATH_SECTIONS, case + " paths")
     common.assert_sections_equal(ora, gpu, GROUP_SECTIONS, case + " groups")
+    if case in common.WINDOW_CASES:     # the CUDA result itself shows the window / border / multi-group code ran
+        common.assert_enters_window_code(gpu, golden["options"], case + " (CUDA)")
+        common.assert_enters_window_code(ora, golden["options"], case + " (oracle)")
+    if case in common.WINDOW_CASES + common.WRAP_CASES and golden["known"]["call_found"][:len(opts["metrics"])] == [0] * len(opts["metrics"]):
+        # no Monte-Carlo path survives len_threshold here, so nothing depends on the RNG: every section, groups and
+        # consensus included, must equal the digests of the UNMODIFIED reference
+        for k in PATH_SECTIONS + GROUP_SECTIONS:
+            if k in golden["sections"] and k != "mc_draws_per_walk":
+                got = {"dtype": str(gpu[k].dtype), "n": int(gpu[k].size), "sha": common.section_digest(gpu[k])}
+                assert got == golden["sections"][k], f"{case}: {k} differs from the reference golden"
     # the graph part does not depend on the RNG: it must also equal the reference-generated golden digests
     for k in GRAPH_SECTIONS:
         if k in golden["sections"]:

@@ -25,12 +25,17 @@ def run_case(case, oracle_bin, datasets, tmp_path, seed, mutate=None):
     return ora, sc, Path(str(tmp_path / "o.bin") + ".fasta")
 
 
-@pytest.mark.parametrize("case", ["small_default", "small_windows", "mixed_default", "mixed_sqrt"])
+@pytest.mark.parametrize("case", ["small_default", "small_windows", "mixed_default", "mixed_sqrt", "small_win", "mixed_win13", "star_border", "star_tournament"])
 def test_scaffold_matches_oracle(case, oracle_bin, datasets, tmp_path):
     ora, sc, fasta = run_case(case, oracle_bin, datasets, tmp_path, seed=5)
     if case == "small_default":
         assert int(ora["have_scaffold"][0]) == 1 and fasta.stat().st_size > 50000   # this case must exercise the stitching
-    if int(ora["have_scaffold"][0]):
+    if case in common.WINDOW_CASES:
+        assert int(ora["have_scaffold"][0]) == 1   # the chain is built from consensus paths picked among several groups
+    if int(ora["have_scaffold"][0]) and not int(ora["fasta_ok"][0]):
+        # the reference's substring() throws std::out_of_range here (src/Scaffolder.cpp:110-113): reported, nothing written
+        assert isinstance(sc, Exception) and sc.code == 45
+    elif int(ora["have_scaffold"][0]):
         assert not isinstance(sc, Exception), sc
         assert sc["scaffold_nodes"].tolist() == ora["scaffold_nodes"].tolist()
         assert sc["scaffold_slots"].tolist() == ora["scaffold_slots"].tolist()

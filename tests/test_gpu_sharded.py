@@ -25,7 +25,7 @@ def run_gang(ds, opts, seed, nranks, stages="all", batched=False):
 
 
 @pytest.mark.parametrize("nranks", [2, 3])
-@pytest.mark.parametrize("case", ["small_default", "mixed_sqrt", "bundled_min", "small_windows"])
+@pytest.mark.parametrize("case", ["small_default", "mixed_sqrt", "bundled_min", "small_windows"] + common.WINDOW_CASES + common.WRAP_CASES)
 def test_sharded_matches_oracle(case, nranks, oracle_bin, datasets, tmp_path):
     from telomeri_b200 import pipeline
     golden = common.load_golden(case)
@@ -36,6 +36,8 @@ def test_sharded_matches_oracle(case, nranks, oracle_bin, datasets, tmp_path):
     ranks = [f"rank_{METRIC_ID[m]}" for m in opts["metrics"]]
     for r, gpu in enumerate(outs):
         common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + ranks + PATH_SECTIONS + GROUP_SECTIONS, f"{case} rank {r}/{nranks}")
+        if case in common.WINDOW_CASES:
+            common.assert_enters_window_code(gpu, golden["options"], f"{case} rank {r}/{nranks}")
 
 
 def test_more_ranks_than_work(oracle_bin, tmp_path):

@@ -26,9 +26,23 @@ CASES = [
     ("bundled_min_cut", "bundled", ["--mode", "min", "--test-load-num", "9000", "--rb-att", "300"], False),
     ("small_default", "small", [], True),
     ("small_windows", "small", ["--len-thr", "200000", "--w-size", "500", "--rb-att", "400"], True),
+    # cases that ENTER the window / border / multi-group code (reference src/PathManager.cpp:527-580, src/PathWindow.cpp,
+    # src/Main.cpp:306-332); "known" records windowed_pairs and groups > pairs, and the tests assert both
+    ("bundled_min_win42", "bundled", ["--mode", "min", "--len-thr", "500000", "--w-size", "10000", "--rb-att", "300"], False),
+    ("bundled_min_win7", "bundled", ["--mode", "min", "--len-thr", "1000000", "--w-size", "50000", "--rb-att", "300", "--r-thr", "0.5"], False),
+    ("mixed_win13", "mixed", ["--len-thr", "50000", "--w-size", "1000", "--rb-att", "300"], True),
+    ("small_win", "small", ["--len-thr", "500", "--w-size", "100", "--rb-att", "50"], True),
+    ("star_wrap_neg", "star_wrap_neg", ["--len-thr", "3000000000", "--rb-att", "1"], False),
+    ("star_wrap_pos", "star_wrap_pos", ["--len-thr", "3000000000", "--rb-att", "1"], False),
+    ("star_border", "star_border", ["--len-thr", "150", "--w-size", "100", "--rb-att", "5"], False),
+    ("star_tournament", "star_tournament", ["--len-thr", "150", "--w-size", "100", "--rb-att", "5"], False),
     ("mixed_default", "mixed", ["--rb-att", "500"], True),
     ("mixed_sqrt", "mixed", ["--rb-att", "300", "--metrics", "es_sqrt,os_sqrt", "--mode", "max", "--max-ohp", "0.9"], True),
 ]
+
+
+def len_thr(opts):
+    return int(opts[opts.index("--len-thr") + 1]) if "--len-thr" in opts else 4700000
 
 
 def main():
@@ -39,6 +53,8 @@ def main():
         dirs = {"bundled": common.bundled_dataset(tmp / "bundled")}
         for name in common.DATASETS:
             dirs[name] = common.make_dataset(name, tmp / name)
+        for name in common.STAR_DATASETS:
+            dirs[name] = common.make_star_dataset(name, tmp / name)
         for name, ds, opts, with_fasta in CASES:
             dump = common.run_dump(ref, dirs[ds], tmp / f"{name}.bin", opts, with_fasta)
             fixture = {
@@ -49,6 +65,9 @@ def main():
                     "nodes": int(dump["node_len"].size), "anchors": int(dump["node_anchor"].sum()),
                     "call_found": dump["call_found"].tolist(), "unique_paths": int(dump["u_len"].size),
                     "pairs": int(dump["pair_a1"].size), "groups": int(dump["grp_pair"].size),
+                    "windowed_pairs": common.windowed_pairs(dump, len_thr(opts)),
+                    "max_group_sum": max([int(dump["u_len"][dump["grp_pig"][int(a):int(b)]].sum())
+                                          for a, b in zip(dump["grp_pig_off"][:-1], dump["grp_pig_off"][1:])] or [0]),
                     "have_scaffold": int(dump["have_scaffold"][0]),
                     "graph_stats": text(dump["graph_stats"]), "path_stats": text(dump["path_stats"]),
                 },
