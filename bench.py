@@ -1,18 +1,24 @@
 #!/usr/bin/env python
 """Benchmark of the HERA repeat-resolution hot path (BASELINE.json metric: overlaps/s graph build +
-paths/s extension, % HBM roofline).
+paths/s extension, 1/2/4/8 B200, % HBM roofline).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A step = one pass of the hot path over one synthetic dataset of BASELINE.json configs[1]
-(E. coli scale): PAF text -> filtered overlaps -> node ids -> CSR + rank permutations ->
-Monte-Carlo and greedy walks (2 metrics each) -> unique -> anchor-pair groups and consensus.
-`value` is graph-build overlaps/s with the PAF text already resident in HBM; `paths_per_s` the walk
-rate; `e2e` the same step through the C ABI from pinned host buffers with the result read back.
-N > 1 (torchrun, one rank per GPU): the SHARDED path on ONE dataset N times the size (genome, contigs
-and repeat families scaled by N -> per-GPU work fixed, weak scaling): every rank tokenizes its byte
-range of the PAF files, kept overlaps are all-gathered over NCCL, every rank holds the full CSR, walks
-are dealt out by walk id and the accepted paths all-gathered; time = max over ranks.
+Workload: BASELINE.json configs[3] -- the largest configuration that fits one GPU and the one BASELINE
+lists for 1/2/4/8 GPUs: synthetic D. melanogaster-scale genome (140 Mbp, 60x 20 kb reads, 400 contigs,
+650 repeat families), 104 M read-read + 0.4 M contig-read PAF records = 10.6 GB of text, reference
+defaults (AVG filter, --rb-att 2000, metrics ES and OS).
+A step = one pass of the hot path over that dataset: PAF text -> filtered overlaps -> node ids -> CSR +
+rank permutations -> Monte-Carlo and greedy walks (2 metrics each) -> unique -> anchor-pair groups and
+consensus.  `value` is graph-build overlaps/s with the PAF text already resident in HBM; `paths_per_s` the
+walk rate; `e2e` the WHOLE step through the C ABI from pinned host buffers (H2D inside) with the result a
+caller consumes read back (rank 0 only when sharded).
+N > 1 (torchrun, one rank per GPU): the SAME dataset sharded N ways (strong scaling): every rank tokenizes its
+byte range of the PAF files, kept overlaps are exchanged over NVLink, walks are dealt out by walk id and the
+accepted paths all-gathered; time = max over ranks.  Every run hashes its final tables on the
+device (hera_digest), compares the ranks with each other and with tests/golden/bench_digests.json (digests of a
+single-GPU run that was compared with the oracle table by table) and reports `parity_checked`.
+A secondary line for configs[1] (E. coli scale, last round's headline) rides along at N = 1.
 """
 import argparse
 import json
@@ -28,16 +34,31 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-WORKLOAD = {
-    "name": "configs[1]: synthetic E. coli-scale 4.6 Mbp, 10 repeat families, 50x 15 kb reads",
-    "gen": ["--genome", "4600000", "--read-len", "15000", "--coverage", "50", "--contigs", "10", "--gap", "40000",
-            "--families", "10", "--copies", "3", "--min-ovl", "2000", "--no-fasta"],
-    "seed": 2,
-    "rb_att": 2000,          # reference default (src/Main.cpp:64)
-    "metrics": ["es", "os"],  # the two calls main() enables (src/Main.cpp:237-243)
+WORKLOADS = {
+    "dmel": {
+        "name": "configs[3]: synthetic D. melanogaster-scale 140 Mbp, 60x 20 kb reads (~100M overlaps)",
+        "gen": ["--genome", "140000000", "--read-len", "20000", "--coverage", "60", "--contigs", "400", "--gap", "30000",
+                "--families", "650", "--copies", "4", "--min-ovl", "1000", "--no-fasta"],
+        "seed": 4,
+        # bounded sample for the reference's own CPU implementation (its loader is O(records x nodes), SURVEY F4: the full
+        # file would take ~1e8 s): the genome's first ~0.8 Mbp = the reads of the first two contigs and their cr records
+        "ref_sample": {"rr_records": 300000, "cr_records": 2200},
+    },
+    "ecoli": {
+        "name": "configs[1]: synthetic E. coli-scale 4.6 Mbp, 10 repeat families, 50x 15 kb reads",
+        "gen": ["--genome", "4600000", "--read-len", "15000", "--coverage", "50", "--contigs", "10", "--gap", "40000",
+                "--families", "10", "--copies", "3", "--min-ovl", "2000", "--no-fasta"],
+        "seed": 2,
+        "ref_sample": {"rr_records": 400000, "cr_records": 1 << 30},
+    },
 }
-REF_SAMPLE = {"rr_records": 400000, "rb_att": 100}   # bounded sample timed on the host cores
+RB_ATT = 2000                 # reference default (src/Main.cpp:64), both arms
+METRICS = ["es", "os"]        # the two calls main() enables (src/Main.cpp:237-243)
+WALK_SEED = 20261104
+REF_BUDGET_S = 170            # the reference arm stops starting new runs of its sample after this many seconds
+HEADLINE = os.environ.get("HERA_BENCH_WORKLOAD", "dmel")
 DATA_ROOT = Path(os.environ.get("HERA_BENCH_DATA", "/tmp/hera_bench"))
+DIGEST_GOLDEN = ROOT / "tests" / "golden" / "bench_digests.json"
 QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -48,41 +69,51 @@ def ensure_tools():
     return ROOT / "tools" / "bin" / "gen_dataset"
 
 
-def gen_args(scale):
-    """configs[1] generator options with genome, contigs and repeat families multiplied by `scale`."""
-    a = list(WORKLOAD["gen"])
-    for key, base in (("--genome", 4600000), ("--contigs", 10), ("--families", 10)):
-        a[a.index(key) + 1] = str(base * scale)
-    return a
-
-
-def make_dataset(seed, scale=1):
-    d = DATA_ROOT / (f"ecoli_seed{seed}" if scale == 1 else f"ecoli_x{scale}_seed{seed}")
+def make_dataset(key):
+    w = WORKLOADS[key]
+    d = DATA_ROOT / f"{key}_seed{w['seed']}"
     if not (d / "done").exists():
         d.mkdir(parents=True, exist_ok=True)
         gen = ensure_tools()
-        out = subprocess.run([str(gen), "--out", str(d), "--seed", str(seed)] + gen_args(scale), check=True, capture_output=True, text=True).stdout
+        out = subprocess.run([str(gen), "--out", str(d), "--seed", str(w["seed"])] + w["gen"], check=True, capture_output=True, text=True).stdout
         (d / "done").write_text(out)
     return d, json.loads((d / "done").read_text())
 
 
-def make_ref_sample(ds):
-    """First REF_SAMPLE['rr_records'] lines of rr_overlaps.paf + the whole cr file."""
-    s = ds / "ref_sample"
+def make_ref_sample(key):
+    """First ref_sample['rr_records'] lines of rr_overlaps.paf + first ref_sample['cr_records'] lines of cr_overlaps.paf.
+    Generated directly (gen_dataset --max-rr) when the full dataset is not there yet, so the reference arm does not
+    have to write 10 GB for a 30 MB sample."""
+    w = WORKLOADS[key]
+    want = w["ref_sample"]
+    full = DATA_ROOT / f"{key}_seed{w['seed']}"
+    s = DATA_ROOT / f"{key}_seed{w['seed']}_refsample"
     if not (s / "done").exists():
-        s.mkdir(exist_ok=True)
-        n = 0
-        with open(ds / "rr_overlaps.paf", "rb") as fi, open(s / "rr_overlaps.paf", "wb") as fo:
-            for line in fi:
-                fo.write(line)
-                n += 1
-                if n >= REF_SAMPLE["rr_records"]:
-                    break
-        (s / "cr_overlaps.paf").write_bytes((ds / "cr_overlaps.paf").read_bytes())
+        s.mkdir(parents=True, exist_ok=True)
+        if (full / "done").exists():
+            src = full
+        else:
+            src = s / "gen"
+            src.mkdir(exist_ok=True)
+            subprocess.run([str(ensure_tools()), "--out", str(src), "--seed", str(w["seed"]), "--max-rr", str(want["rr_records"])] + w["gen"],
+                           check=True, capture_output=True, text=True)
+        counts = {}
+        for name, limit in (("rr_overlaps.paf", want["rr_records"]), ("cr_overlaps.paf", want["cr_records"])):
+            n = 0
+            with open(src / name, "rb") as fi, open(s / name, "wb") as fo:
+                for line in fi:
+                    if n >= limit:
+                        break
+                    fo.write(line)
+                    n += 1
+            counts[name] = n
         for f in ("reads.fasta", "contigs.fasta"):
             (s / f).write_text(">none\nA\n")
-        cr = sum(1 for _ in open(s / "cr_overlaps.paf", "rb"))
-        (s / "done").write_text(json.dumps({"rr_records": n, "cr_records": cr}))
+        if src != full:
+            for f in src.iterdir():
+                f.unlink()
+            src.rmdir()
+        (s / "done").write_text(json.dumps({"rr_records": counts["rr_overlaps.paf"], "cr_records": counts["cr_overlaps.paf"]}))
     return s, json.loads((s / "done").read_text())
 
 
@@ -139,65 +170,109 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def run_reference_sample(ds, steps, warmup):
+def ref_sample_text(key):
+    rs = WORKLOADS[key]["ref_sample"]
+    cr = "all" if rs["cr_records"] >= 1 << 30 else f"the first {rs['cr_records']}"
+    return (f"the reference CPU binary cannot finish this workload (its loader is O(records x nodes)); it is timed on a bounded sample: "
+            f"the first {rs['rr_records']} rr records + {cr} cr records of the same files, --rb-att {RB_ATT} (the workload's), 1 thread "
+            f"(the reference has no threads)")
+
+
+def run_reference_sample(key, steps, warmup):
     """Times the reference's own CPU implementation (oracle/_ref/Telomeri when it was built from
-    /root/reference, else the oracle port) on the bounded sample.  Returns per-step dicts."""
-    sample, meta = make_ref_sample(ds)
+    /root/reference, else the oracle port) on the bounded sample.  Returns per-step means."""
+    sample, meta = make_ref_sample(key)
     records = meta["rr_records"] + meta["cr_records"]
     ref_bin = ROOT / "oracle" / "_ref" / "Telomeri"
     kind = "reference" if ref_bin.exists() else "port"
     out = []
+    warmup = min(warmup, 1)   # a CPU binary: one run to fill the page cache is all the warm-up there is
+    t_begin = time.perf_counter()
     for i in range(warmup + steps):
+        if out and time.perf_counter() - t_begin > REF_BUDGET_S:
+            break             # bounded: the steps actually timed are reported
         if kind == "reference":
-            cmd = [str(ref_bin), "--rb-att", str(REF_SAMPLE["rb_att"]), str(sample / "rr_overlaps.paf"), str(sample / "cr_overlaps.paf"),
+            cmd = [str(ref_bin), "--rb-att", str(RB_ATT), str(sample / "rr_overlaps.paf"), str(sample / "cr_overlaps.paf"),
                    str(sample / "reads.fasta"), str(sample / "contigs.fasta"), str(sample / "out.fasta")]
             t0 = time.perf_counter()
             p = subprocess.run(cmd, capture_output=True, text=True)
             wall = time.perf_counter() - t0
             laps = [float(x) for x in re.findall(r"^Done \(([0-9.e+-]+)s\)", p.stdout, flags=re.M)]
             found = [int(x) for x in re.findall(r"^Found (\d+) paths\.", p.stdout, flags=re.M)]
+            anchors = [int(x) for x in re.findall(r"^-\s+anchor: (\d+)", p.stdout, flags=re.M)]
             load_s, paths_s = (laps + [wall, wall])[:2]
         else:
             ensure_tools()
-            cmd = [str(ROOT / "oracle" / "bin" / "hera_oracle"), "--rng", "mt19937", "--rb-att", str(REF_SAMPLE["rb_att"]), "--stage", "paths", "--timing",
+            cmd = [str(ROOT / "oracle" / "bin" / "hera_oracle"), "--rng", "mt19937", "--rb-att", str(RB_ATT), "--stage", "paths", "--timing",
                    str(sample / "rr_overlaps.paf"), str(sample / "cr_overlaps.paf"), str(sample / "o.bin")]
+            t0 = time.perf_counter()
             p = subprocess.run(cmd, capture_output=True, text=True, check=True)
+            wall = time.perf_counter() - t0
             t = json.loads(p.stdout.strip().splitlines()[-1])
-            load_s, paths_s, found = t["graph_s"], t["paths_s"], []
+            load_s, paths_s, found, anchors = t["graph_s"], t["paths_s"], [], []
         if i >= warmup:
-            out.append({"load_s": load_s, "paths_s": paths_s, "found": sum(found)})
+            out.append({"load_s": load_s, "paths_s": paths_s, "found": sum(found), "wall_s": wall, "anchors": anchors[0] if anchors else None})
     load = statistics.mean(s["load_s"] for s in out)
     paths = statistics.mean(s["paths_s"] for s in out)
-    return {"kind": kind, "records": records, "load_s": load, "paths_s": paths, "overlaps_per_s": records / load,
-            "sample": f"first {meta['rr_records']} rr records + all {meta['cr_records']} cr records of the workload, --rb-att {REF_SAMPLE['rb_att']}, "
-                      f"reference laps: load {load:.2f}s, walks {paths:.2f}s"}
+    wall = statistics.mean(s["wall_s"] for s in out)
+    n_anchor = out[-1]["anchors"]
+    mc_walks = len(METRICS) * RB_ATT * n_anchor if n_anchor else None
+    return {"kind": kind, "steps_timed": len(out), "records": records, "load_s": load, "paths_s": paths, "wall_s": wall, "overlaps_per_s": records / load,
+            "mc_walks": mc_walks, "paths_per_s": (mc_walks / paths) if (mc_walks and paths) else None,
+            "whole_step_overlaps_per_s": records / wall,
+            "sample": f"first {meta['rr_records']} rr + first {meta['cr_records']} cr records of the workload's files, --rb-att {RB_ATT}; "
+                      f"reference laps: load {load:.2f} s, walks {paths:.2f} s, whole run {wall:.2f} s"}
 
 
-def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
-    """One step through the C ABI.  rr / cr: (pointer, nbytes) of the whole file, or -- sharded run -- a Slice of it.
-    Returns stage times (ms, CUDA events on the library's stream), counts and the kernel-launch delta."""
+class Slice:
+    """This rank's byte range of a PAF file (hera_shard_range; the whole file at world size 1): pinned host copy + device copy."""
+
+    def __init__(self, path, rank, world, dev, capi, torch):
+        n = path.stat().st_size
+        b, e, a = capi.shard_range(n, rank, world) if world > 1 else (0, n, n)
+        self.owned, self.avail, self.at_eof, self.file_bytes, self.whole = e - b, a - b, a == n, n, world == 1
+        self.prev = -1
+        with open(path, "rb") as f:
+            if b:
+                f.seek(b - 1)
+                self.prev = f.read(1)[0]
+            self.host = torch.empty(max(self.avail, 1), dtype=torch.uint8, pin_memory=True)
+            if self.avail:
+                f.seek(b)
+                mv = memoryview(self.host.numpy())[:self.avail]
+                got = 0
+                while got < self.avail:
+                    k = f.readinto(mv[got:])
+                    if not k:
+                        raise IOError(f"short read on {path}")
+                    got += k
+        self.dev = self.host.to(dev)
+
+
+def hot_path_step(h, pp, rr, cr, device_resident, read_back):
+    """One step through the C ABI.  rr / cr: this rank's Slice of the file.  Returns stage times (ms, CUDA events on the
+    library's stream), counts and the kernel-launch delta."""
     launches0 = h.launches
     h.graph_reset()
     h.paths_reset()
 
     def load(src, anchors):
-        if isinstance(src, Slice):
-            return h.load_shard_ptr(src.ptr(device_resident), 2 if device_resident else 0, src.owned, src.avail, src.prev, src.at_eof, anchors)
+        if not src.whole:
+            return h.load_shard_ptr(src.dev.data_ptr() if device_resident else src.host.data_ptr(), 2 if device_resident else 0,
+                                    src.owned, src.avail, src.prev, src.at_eof, anchors)
         # resident text is parsed in place (hera_graph_load_device_view): the buffers live for the whole run
-        return (h.load_device_view_ptr if device_resident else h.load_host_ptr)(src[0], src[1], anchors)
+        return h.load_device_view_ptr(src.dev.data_ptr(), src.avail, anchors) if device_resident else h.load_host_ptr(src.host.data_ptr(), src.avail, anchors)
     h.comm_barrier()   # sharded runs: a late host thread of another rank is not part of this rank's stage times
+    t_wall0 = time.perf_counter()
     h.timer_start()
     r1 = load(rr, False)
     r2 = load(cr, True)
-    info = h.finalize(WORKLOAD["metrics"])
+    info = h.finalize(METRICS)
     t_graph = h.timer_stop()
     h.comm_barrier()
     h.timer_start()
     # the four build calls of main() as one hera_paths_build call: their kernels share the GPU
-    stats = h.build_paths([("mc", m) for m in WORKLOAD["metrics"]] + [("det", m) for m in WORKLOAD["metrics"]], pp, 20261104)
-    walks = sum(s.walks for s in stats)
-    steps = sum(s.steps for s in stats)
-    found = sum(s.found for s in stats)
+    stats = h.build_paths([("mc", m) for m in METRICS] + [("det", m) for m in METRICS], pp, WALK_SEED)
     n_unique = h.unique()
     t_paths = h.timer_stop()
     h.timer_start()
@@ -207,41 +282,127 @@ def hot_path_step(h, capi, pp, rr, cr, device_resident, read_back):
     if read_back:  # the result a caller consumes: groups/consensus tables + the unique paths
         paths = h.export_paths("u_", copy=False)   # views into the pinned mirrors the library copied the result to
         d2h = sum(v.nbytes for v in g.values() if hasattr(v, "nbytes")) + sum(v.nbytes for v in paths.values())
-    return {"graph_ms": t_graph, "paths_ms": t_paths, "groups_ms": t_groups, "parse_ms": r1.parse_ms + r2.parse_ms,
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    return {"graph_ms": t_graph, "paths_ms": t_paths, "groups_ms": t_groups, "parse_ms": r1.parse_ms + r2.parse_ms, "h2d_ms": r1.h2d_ms + r2.h2d_ms,
             "exchange_ms": r1.exchange_ms + r2.exchange_ms, "parse_rr_ms": r1.parse_ms, "intern_ms": info.intern_ms, "csr_ms": info.csr_ms, "rank_ms": info.rank_ms,
-            "records": r1.records + r2.records, "kept": r2.kept_total, "nodes": info.nodes, "walks": walks, "walk_entries": steps, "found": found,
-            "unique_paths": n_unique, "pairs": len(g["pair_a1"]), "launches": h.launches - launches0, "d2h": d2h,
+            "records": r1.records + r2.records, "kept": r2.kept_total, "nodes": info.nodes, "walks": sum(s.walks for s in stats),
+            "walk_entries": sum(s.steps for s in stats), "found": sum(s.found for s in stats), "walk_ms": [round(s.ms, 3) for s in stats],
+            "unique_paths": n_unique, "unique_nodes": 0, "pairs": len(g["pair_a1"]), "launches": h.launches - launches0, "d2h": d2h, "wall_ms": wall_ms,
             "rr_bytes": r1.bytes, "rr_kept": r1.kept}
 
 
 def parse_traffic():
-    """DRAM bytes of one paf_parse_kernel launch on the rr text from the committed `ncu --set full` capture (per launch, like `achieved`)."""
+    """DRAM bytes of one paf_parse_kernel launch from the committed `ncu --set full` capture, per PAF byte (the capture's text size is recorded with it)."""
     try:
-        t = json.loads((ROOT / "profiles" / "parse_kernel_traffic.json").read_text())
-        return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
-    except (OSError, KeyError, ValueError):
+        return json.loads((ROOT / "profiles" / "parse_kernel_traffic.json").read_text())
+    except (OSError, ValueError):
         return None
 
 
-class Slice:
-    """This rank's byte range of a PAF file (hera_shard_range): pinned host copy + device copy."""
+def measure(key, args, torch, dist, capi, h, rank, world, dev, local_rank, with_e2e=True, with_probe=True):
+    """All legs of one workload on the attached context.  Returns the dict of aggregated numbers (same on every rank)."""
+    ds, meta = make_dataset(key)
+    rr = Slice(ds / "rr_overlaps.paf", rank, world, dev, capi, torch)
+    cr = Slice(ds / "cr_overlaps.paf", rank, world, dev, capi, torch)
+    torch.cuda.synchronize(dev)
+    pp = capi.default_path_params(rb_att=RB_ATT)
 
-    def __init__(self, path, rank, world, dev, capi, torch, np):
-        n = path.stat().st_size
-        b, e, a = capi.shard_range(n, rank, world)
-        self.owned, self.avail, self.at_eof, self.file_bytes = e - b, a - b, a == n, n
-        self.prev = -1
-        if b:
-            with open(path, "rb") as f:
-                f.seek(b - 1)
-                self.prev = f.read(1)[0]
-        self.host = torch.empty(max(self.avail, 1), dtype=torch.uint8, pin_memory=True)
-        if self.avail:
-            self.host.numpy()[:self.avail] = np.fromfile(path, dtype=np.uint8, count=self.avail, offset=b)
-        self.dev = self.host.to(dev)
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
 
-    def ptr(self, device_resident):
-        return self.dev.data_ptr() if device_resident else self.host.data_ptr()
+    def timed(device_resident, read_back, steps):
+        per = []
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            per.append(hot_path_step(h, pp, rr, cr, device_resident, read_back))
+        barrier()
+        return per, time.perf_counter() - t0
+
+    warm = max(3, args.warmup)
+    for _ in range(warm):
+        hot_path_step(h, pp, rr, cr, True, False)
+    with ClockSampler(local_rank) as clocks:
+        dev_steps, _ = timed(True, False, args.steps)
+        digest = h.digest()     # tables of the last device-resident step
+        if with_e2e:
+            hot_path_step(h, pp, rr, cr, False, rank == 0)     # untimed: pinned-path buffers sized
+            e2e_steps, e2e_wall = timed(False, rank == 0, args.steps)
+        else:
+            e2e_steps, e2e_wall = dev_steps, 0.0
+    gather_gbs = gather_ms = None
+    if with_probe:   # measured ceiling for the walks: dependent list gathers on the finalized graph of the last step, same resident warps
+        h.probe_list_gather(64, 64)
+        gather_gbs, gather_ms = h.probe_list_gather(64, 256)
+    # roofline leg: the dominant streaming kernel (paf_parse_kernel on this rank's rr text) timed alone by its own CUDA events
+    h.set_option("flush_l2", 1)
+    parse_ms = []
+    for _ in range(min(args.steps, 5) + 1):
+        h.graph_reset()
+        leg = h.load_device_view_ptr(rr.dev.data_ptr(), rr.avail if world == 1 else rr.owned & ~15, False)   # not collective: a stand-alone text
+        parse_ms.append(leg.parse_ms)
+    h.set_option("flush_l2", 0)
+    h.graph_reset()
+    parse_ms = statistics.mean(parse_ms[1:])
+
+    def agg(steps, k):
+        return sum(s[k] for s in steps)
+    sums = torch.tensor([agg(dev_steps, k) for k in ("graph_ms", "paths_ms", "groups_ms", "parse_ms", "exchange_ms", "intern_ms", "csr_ms", "rank_ms")] +
+                        [e2e_wall * 1e3, agg(e2e_steps, "graph_ms"), agg(e2e_steps, "h2d_ms"), parse_ms], dtype=torch.float64, device=dev)
+    counts = torch.tensor([agg(dev_steps, "launches"), rr.avail + cr.avail, e2e_steps[-1]["d2h"]], dtype=torch.float64, device=dev)
+    dg = torch.tensor([v & 0x7fffffffffffffff for v in digest.values()], dtype=torch.int64, device=dev)
+    ranks_agree = True
+    if world > 1:
+        dist.all_reduce(sums, op=dist.ReduceOp.MAX)
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+        alld = [torch.empty_like(dg) for _ in range(world)]
+        dist.all_gather(alld, dg)
+        ranks_agree = all(bool(torch.equal(alld[0], d)) for d in alld)
+    s = sums.tolist()
+    stage = dict(zip(("graph_ms", "paths_ms", "groups_ms", "parse_ms", "exchange_ms", "intern_ms", "csr_ms", "rank_ms"), (v / args.steps for v in s[:8])))
+    golden = {}
+    try:
+        golden = json.loads(DIGEST_GOLDEN.read_text()).get(key, {})
+    except (OSError, ValueError):
+        pass
+    want = golden.get("digests")
+    matches = None if not want else all(int(want[k]) == v for k, v in digest.items())
+    s0 = dev_steps[-1]
+    res = {"key": key, "meta": meta, "stage": stage, "e2e_wall_ms": s[8] / args.steps, "e2e_graph_ms": s[9] / args.steps, "e2e_h2d_ms": s[10] / args.steps,
+           "parse_leg_ms": s[11], "parse_leg_bytes": int(leg.bytes), "parse_leg_kept": int(leg.kept),
+           "launches": counts[0].item(), "h2d_bytes": counts[1].item(), "d2h_bytes": counts[2].item(),
+           "records": s0["records"], "kept": s0["kept"], "nodes": s0["nodes"], "walks": s0["walks"], "walk_entries": s0["walk_entries"], "found": s0["found"],
+           "unique_paths": s0["unique_paths"], "pairs": s0["pairs"], "walk_ms": s0["walk_ms"], "gather_gbs": gather_gbs, "gather_ms": gather_ms,
+           "clocks": clocks.summary(), "digest": digest, "ranks_agree": ranks_agree, "golden_matches": matches, "golden_note": golden.get("verified"),
+           "bytes": rr.file_bytes + cr.file_bytes}
+    del rr, cr
+    torch.cuda.empty_cache()
+    return res
+
+
+def stage_rooflines(r, peak, world):
+    """every streaming stage against the HBM peak, from its algorithmic bytes (B PAF bytes, E kept
+    overlaps, 2E slots, N nodes, P unique paths) and the stage's device time (max over ranks); per GPU."""
+    E, N, M, B, P = r["kept"], r["nodes"], len(METRICS), r["bytes"], r["unique_paths"]
+    st = r["stage"]
+    rows = [("K1+K2 parse / filter / score (parse_ms)", B + 73 * E, st["parse_ms"], "every PAF byte read once + one 73-byte kept row written"),
+            ("K3 interning (intern_ms)", 2 * E * 10 + 2 * E * 4, st["intern_ms"], "names read once (~10 B), ids written"),
+            ("K4 CSR (csr_ms)", 2 * E * 80 + (N + 1) * 4, st["csr_ms"], "one pass in, one pass out of 40-byte directed entries, offsets"),
+            ("K4b ranks + canon (rank_ms)", 2 * E * 4 * (M + 1) + 2 * E * 8, st["rank_ms"], "metric + neighbour read per slot, one permutation per metric + canon written"),
+            ("K7+K8 unique + groups (groups_ms, unique inside paths_ms)", 16 * P, st["groups_ms"], "16 B per path read (int64 length + pair key)")]
+    out = []
+    for name, b, ms, what in rows:
+        gbs = b / world / (ms * 1e-3) / 1e9 if ms else None
+        out.append({"stage": name, "algorithmic_bytes_per_gpu": int(b / world), "ms": ms, "achieved": gbs, "peak": peak, "unit": "GB/s per GPU",
+                    "frac": gbs / peak if gbs else None, "bytes_model": what})
+    gb = sum(x[1] for x in rows[:4])
+    gbs = gb / world / (st["graph_ms"] * 1e-3) / 1e9
+    out.append({"stage": "whole graph build (graph_ms: parse x2 + exchange + K3 + K4 + K4b)", "algorithmic_bytes_per_gpu": int(gb / world), "ms": st["graph_ms"],
+                "achieved": gbs, "peak": peak, "unit": "GB/s per GPU", "frac": gbs / peak})
+    return out
 
 
 def main():
@@ -251,53 +412,54 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    config = {"workload": WORKLOAD["name"], "generator": "tools/gen_dataset " + " ".join(WORKLOAD["gen"]) + f" --seed {WORKLOAD['seed']}",
-              "filter": "reference defaults (AVG)", "rb_att": WORKLOAD["rb_att"], "metrics": WORKLOAD["metrics"],
-              "parallelism": (f"{world} ranks, one dataset {world}x the size: PAF sharded by byte range, kept overlaps pulled from peer memory over NVLink "
-                              f"(NCCL rendezvous), CSR replicated, walks dealt out by walk id, paths all-gathered (NCCL); ranks are aligned by a barrier before the "
+    W = WORKLOADS[HEADLINE]
+    config = {"workload": W["name"], "generator": "tools/gen_dataset " + " ".join(W["gen"]) + f" --seed {W['seed']}",
+              "filter": "reference defaults (AVG)", "rb_att": RB_ATT, "metrics": METRICS,
+              "reference_arm": ref_sample_text(HEADLINE),
+              "parallelism": (f"{world} ranks share ONE dataset (strong scaling): PAF sharded by byte range, kept overlaps exchanged over NVLink "
+                              f"(peer windows, NCCL rendezvous), walks dealt out by walk id, paths all-gathered; ranks are aligned by a barrier before the "
                               f"graph stage and before the path stage of every step (stage times exclude the wait for a late host thread; e2e wall time does not)")
                              if world > 1 else "single GPU",
-              "l2": "PAF text (173 MB per GPU) is larger than L2 (126 MB); the roofline leg additionally writes 512 MB before the parse kernel"}
-    if world > 1:
-        config["generator"] = "tools/gen_dataset " + " ".join(gen_args(world)) + f" --seed {WORKLOAD['seed']}"
+              "l2": "PAF text (10.6 GB) is far larger than L2 (126 MB): every step streams it from HBM; the roofline leg additionally writes 512 MB before the parse kernel"}
 
     if args.impl == "reference":
         if rank != 0:
             return
-        ds, meta = make_dataset(WORKLOAD["seed"])
-        ref = run_reference_sample(ds, args.steps, max(0, args.warmup))
+        ref = run_reference_sample(HEADLINE, args.steps, max(0, args.warmup))
         v = ref["overlaps_per_s"]
         print(json.dumps({
-            "impl": "reference", "metric": "overlaps/s graph build", "value": v, "unit": "overlaps/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * (ref["load_s"] + ref["paths_s"]), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": config,
-            "paths_per_s": None if not ref["paths_s"] else (len(WORKLOAD["metrics"]) * 10 * REF_SAMPLE["rb_att"]) / ref["paths_s"],
-            "cpu_baseline": {"value": v, "unit": "overlaps/s", "cores": 1, "kind": ref["kind"], "sample": ref["sample"]},
-            "e2e": {"value": v, "unit": "overlaps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+            "impl": "reference", "metric": "overlaps/s graph build", "value": v, "unit": "overlaps/s", "n_gpus": args.gpus, "steps": ref["steps_timed"],
+            "steps_requested": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * ref["wall_s"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config, "paths_per_s": ref["paths_per_s"],
+            "cpu_baseline": {"value": v, "unit": "overlaps/s", "cores": 1, "host_cores": os.cpu_count(), "kind": ref["kind"], "sample": ref["sample"]},
+            "e2e": {"value": ref["whole_step_overlaps_per_s"], "unit": "overlaps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                    "note": "whole reference run on the sample (load + walks + groups + consensus), records / wall time"}}))
         return
 
-    import numpy as np
     import torch
     from telomeri_b200 import build as b, capi
     if rank == 0:
         b.build_library()
+    dist = None
     if world > 1:
+        import datetime
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(minutes=30))
         dist.barrier()
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(local_rank)
     bind_to_gpu_cpus(local_rank)
     if rank == 0:
-        make_dataset(WORKLOAD["seed"], world)
+        make_dataset(HEADLINE)
     if world > 1:
         dist.barrier()
-    ds, meta = make_dataset(WORKLOAD["seed"], world)
     h = capi.Hera(local_rank)
     if world > 1:
         # the library's own NCCL communicator (collectives run on its stream); torch.distributed only hands out the id
@@ -306,127 +468,75 @@ def main():
             idt.copy_(torch.frombuffer(bytearray(capi.nccl_unique_id()), dtype=torch.uint8))
         dist.broadcast(idt, 0)
         h.comm_init_nccl(rank, world, bytes(idt.cpu().numpy()))
-        rr_s = Slice(ds / "rr_overlaps.paf", rank, world, dev, capi, torch, np)
-        cr_s = Slice(ds / "cr_overlaps.paf", rank, world, dev, capi, torch, np)
-        rr_n, cr_n = rr_s.avail, cr_s.avail
-        rr_d, cr_d = rr_s.dev, cr_s.dev
-    else:
-        def pinned(path):
-            n = path.stat().st_size
-            t = torch.empty(max(n, 1), dtype=torch.uint8, pin_memory=True)
-            t.numpy()[:n] = np.fromfile(path, dtype=np.uint8)
-            return t, n
-        rr_h, rr_n = pinned(ds / "rr_overlaps.paf")
-        cr_h, cr_n = pinned(ds / "cr_overlaps.paf")
-        rr_d, cr_d = rr_h.to(dev), cr_h.to(dev)
-    torch.cuda.synchronize(dev)
-    pp = capi.default_path_params(rb_att=WORKLOAD["rb_att"])
-    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
 
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize(dev)
+    r = measure(HEADLINE, args, torch, dist, capi, h, rank, world, dev, local_rank)
+    if not r["ranks_agree"]:
+        raise SystemExit("bench.py: the ranks ended with different tables (hera_digest differs)")
+    if r["golden_matches"] is False:
+        raise SystemExit(f"bench.py: the tables of this run differ from the oracle-verified digests in {DIGEST_GOLDEN}: {r['digest']}")
+    sec = None
+    if world == 1 and not args.no_secondary and HEADLINE != "ecoli":
+        sec = measure("ecoli", args, torch, dist, capi, h, rank, world, dev, local_rank, with_probe=False)
 
-    def sources(device_resident):
-        if world > 1:
-            return rr_s, cr_s
-        return ((rr_d.data_ptr(), rr_n), (cr_d.data_ptr(), cr_n)) if device_resident else ((rr_h.data_ptr(), rr_n), (cr_h.data_ptr(), cr_n))
-
-    def timed(device_resident, read_back, steps):
-        per = []
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(steps):
-            if device_resident:
-                flush.zero_()            # L2 flush between timed iterations (outside the event-timed stages)
-                torch.cuda.synchronize(dev)
-            src = sources(device_resident)
-            per.append(hot_path_step(h, capi, pp, src[0], src[1], device_resident, read_back))
-        barrier()
-        return per, time.perf_counter() - t0
-
-    for _ in range(max(3, args.warmup)):
-        hot_path_step(h, capi, pp, *sources(True), True, False)
-    with ClockSampler(local_rank) as clocks:
-        dev_steps, _ = timed(True, False, args.steps)
-        e2e_steps, e2e_wall = timed(False, True, args.steps)
-    # measured ceiling for the walks: dependent list gathers on the finalized graph of the last step, same resident warps
-    h.probe_list_gather(64, 64)
-    gather_gbs, gather_ms = h.probe_list_gather(64, 256)
-    # roofline leg: the dominant streaming kernel (paf_parse_kernel on the rr text) timed alone by its own CUDA events, L2 flushed
-    h.set_option("flush_l2", 1)
-    parse_ms = []
-    for _ in range(args.steps + 1):
-        h.graph_reset()
-        leg = h.load_device_view_ptr(rr_d.data_ptr(), rr_n, False)   # not collective: this rank's rr text as a stand-alone file
-        parse_ms.append(leg.parse_ms)
-    h.set_option("flush_l2", 0)
-    parse_ms = statistics.mean(parse_ms[1:])
-
-    def agg(steps, key):
-        return sum(s[key] for s in steps)
-    sums = torch.tensor([agg(dev_steps, "graph_ms"), agg(dev_steps, "paths_ms"), agg(dev_steps, "groups_ms"), e2e_wall * 1e3,
-                         agg(e2e_steps, "graph_ms")], dtype=torch.float64, device=dev)
-    # records / walks / paths reported by the collective calls are already global; launches and copied bytes are per rank
-    counts = torch.tensor([agg(dev_steps, "launches"), rr_n + cr_n, e2e_steps[-1]["d2h"]], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(sums, op=dist.ReduceOp.MAX)
-        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
-    graph_ms, paths_ms, groups_ms, e2e_ms, e2e_graph_ms = sums.tolist()
-    launches, h2d_bytes, d2h_bytes = counts.tolist()
-    records, walks, e2e_records, uniq = agg(dev_steps, "records"), agg(dev_steps, "walks"), agg(e2e_steps, "records"), agg(dev_steps, "unique_paths")
     if rank == 0:
-        s0 = dev_steps[-1]
         peaks = {}
         try:
             peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
         except OSError:
             pass
         peak = peaks.get("hbm_gbs", 6650.0)
-        algo_bytes = leg.bytes + 73 * leg.kept   # every PAF byte read once + 73 B written per kept overlap
-        achieved = algo_bytes / (parse_ms * 1e-3) / 1e9
+        st = r["stage"]
+        algo_bytes = r["parse_leg_bytes"] + 73 * r["parse_leg_kept"]   # every PAF byte read once + 73 B written per kept overlap
+        achieved = algo_bytes / (r["parse_leg_ms"] * 1e-3) / 1e9
+        tr = parse_traffic()
+        traffic = None
+        if tr and tr.get("text_bytes"):   # per launch like `achieved`: the capture's DRAM bytes per PAF byte x this launch's text
+            traffic = int((int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])) / int(tr["text_bytes"]) * r["parse_leg_bytes"])
+        step_ms = st["graph_ms"] + st["paths_ms"] + st["groups_ms"]
         line = {
-            "metric": "overlaps/s graph build", "value": records / (graph_ms * 1e-3), "unit": "overlaps/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": (graph_ms + paths_ms + groups_ms) / args.steps, "higher_is_better": True, "scaling": "weak",
+            "metric": "overlaps/s graph build", "value": r["records"] / (st["graph_ms"] * 1e-3), "unit": "overlaps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-            "paths_per_s": walks / (paths_ms * 1e-3), "accepted_paths_per_s": agg(dev_steps, "found") / (paths_ms * 1e-3),
-            "unique_paths_per_step": uniq / args.steps,
-            "stages_ms_per_step": {k: statistics.mean(s[k] for s in dev_steps) for k in
-                                   ("graph_ms", "parse_ms", "exchange_ms", "intern_ms", "csr_ms", "rank_ms", "paths_ms", "groups_ms")},
-            "per_step": {"records": s0["records"], "kept_overlaps": s0["kept"], "nodes": s0["nodes"], "walks": s0["walks"],
-                         "adjacency_entries_examined": s0["walk_entries"], "anchor_pairs": s0["pairs"]},
-            "gpu_launches": int(launches),
-            "e2e": {"value": e2e_records / (e2e_graph_ms * 1e-3), "unit": "overlaps/s", "h2d_bytes_per_step": int(h2d_bytes),
-                    "d2h_bytes_per_step": int(d2h_bytes), "whole_step_ms": e2e_ms / args.steps,
-                    "note": "graph build from pinned host buffers (H2D inside the timed region); whole_step_ms adds walks, groups and the D2H read of the result"},
-            "roofline": {"bound": "hbm", "kernel": "paf_parse_kernel (rr text)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s", "algorithmic_bytes": algo_bytes,
-                         "kernel_ms": parse_ms, "traffic": parse_traffic()},
-            # north_star: the pointer-chasing walks are reported against the measured random-gather ceiling
+            "paths_per_s": r["walks"] / (st["paths_ms"] * 1e-3), "accepted_paths_per_s": r["found"] / (st["paths_ms"] * 1e-3),
+            "unique_paths_per_step": r["unique_paths"],
+            "stages_ms_per_step": st,
+            "per_step": {"records": r["records"], "paf_bytes": r["bytes"], "kept_overlaps": r["kept"], "nodes": r["nodes"], "walks": r["walks"],
+                         "adjacency_entries_examined": r["walk_entries"], "anchor_pairs": r["pairs"], "walk_kernel_ms": r["walk_ms"]},
+            "gpu_launches": int(r["launches"]),
+            "e2e": {"value": r["records"] / (r["e2e_wall_ms"] * 1e-3), "unit": "overlaps/s", "h2d_bytes_per_step": int(r["h2d_bytes"]),
+                    "d2h_bytes_per_step": int(r["d2h_bytes"]), "whole_step_ms": r["e2e_wall_ms"], "graph_build_ms": r["e2e_graph_ms"], "h2d_ms": r["e2e_h2d_ms"],
+                    "note": "WHOLE step from pinned host buffers, wall clock: H2D of the PAF text + graph build + walks + unique + groups + D2H of the "
+                            "groups / consensus tables and the unique paths" + (" (read back on rank 0 only)" if world > 1 else "")},
+            "roofline": {"bound": "hbm", "kernel": "paf_parse_kernel (rr text" + (" of rank 0's byte range)" if world > 1 else ")"), "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "algorithmic_bytes": algo_bytes, "kernel_ms": r["parse_leg_ms"], "traffic": traffic},
+            "roofline_stages": stage_rooflines(r, peak, world),
+            # north_star: the pointer-chasing walks are reported against a measured ceiling: an L2-resident *streaming* probe of
+            # whole adjacency lists with dependent hops (not a random 32-byte-sector gather), 16-byte entries
             "roofline_walks": {"bound": "dependent list gather (L2/HBM latency)", "kernel": "walk_mc_kernel x2 + walk_det_kernel x2 in flight together",
-                               "achieved": s0["walk_entries"] * 16 / (statistics.mean(s["paths_ms"] for s in dev_steps) * 1e-3) / 1e9 / world,
-                               "peak": gather_gbs, "unit": "GB/s per GPU", "frac": None,
-                               "peak_source": f"hera_probe_list_gather(64 warps/SM, 256 hops) on this graph: {gather_ms:.3f} ms",
-                               "algorithmic_bytes": int(s0["walk_entries"]) * 16},
-            "clocks": clocks.summary(),
+                               "achieved": r["walk_entries"] * 16 / (st["paths_ms"] * 1e-3) / 1e9 / world,
+                               "peak": r["gather_gbs"], "unit": "GB/s per GPU", "frac": None,
+                               "peak_source": f"hera_probe_list_gather(64 warps/SM, 256 hops) on this graph: {r['gather_ms']:.3f} ms",
+                               "algorithmic_bytes": int(r["walk_entries"]) * 16,
+                               "algorithmic_bytes_survey_8d": int(r["walk_entries"]) * 8},
+            "parity_checked": {"ranks_agree": bool(r["ranks_agree"]), "matches_oracle_verified_digests": r["golden_matches"],
+                               "verified_by": r["golden_note"], "tables": list(r["digest"].keys())},
+            "clocks": r["clocks"],
         }
-        # % of the HBM roofline for every streaming stage, from its algorithmic bytes (E kept overlaps,
-        # 2E slots, N nodes, P paths) and the stage's device time
-        E_, N_, M_ = s0["kept"], s0["nodes"], len(WORKLOAD["metrics"])
-        st = line["stages_ms_per_step"]
-        stage_bytes = {"K3 interning (intern_ms)": (2 * E_ * 10 + 2 * E_ * 4, st["intern_ms"]),
-                       "K4 CSR + K4b ranks (csr_ms + rank_ms)": (2 * E_ * 80 + (N_ + 1) * 4 + 2 * E_ * 4 * (M_ + 1), st["csr_ms"] + st["rank_ms"])}
-        line["roofline_stages"] = [{"stage": k, "algorithmic_bytes": int(b), "ms": ms, "achieved": b / (ms * 1e-3) / 1e9, "peak": peak,
-                                    "unit": "GB/s per GPU (replicated stages: every GPU handles all kept overlaps)", "frac": b / (ms * 1e-3) / 1e9 / peak}
-                                   for k, (b, ms) in stage_bytes.items()]
         rw = line["roofline_walks"]
         rw["frac"] = rw["achieved"] / rw["peak"] if rw["peak"] else None
+        if sec:
+            ss = sec["stage"]
+            line["secondary"] = {"workload": WORKLOADS["ecoli"]["name"], "value": sec["records"] / (ss["graph_ms"] * 1e-3), "unit": "overlaps/s",
+                                 "paths_per_s": sec["walks"] / (ss["paths_ms"] * 1e-3), "stages_ms_per_step": ss,
+                                 "e2e_whole_step_ms": sec["e2e_wall_ms"], "e2e_value": sec["records"] / (sec["e2e_wall_ms"] * 1e-3),
+                                 "parse_kernel_frac": (sec["parse_leg_bytes"] + 73 * sec["parse_leg_kept"]) / (sec["parse_leg_ms"] * 1e-3) / 1e9 / peak,
+                                 "roofline_stages": stage_rooflines(sec, peak, 1),
+                                 "parity_checked": {"matches_oracle_verified_digests": sec["golden_matches"], "verified_by": sec["golden_note"]}}
         if world == 1 and not args.no_cpu_baseline:
-            ref = run_reference_sample(ds, 1, 0)
-            line["cpu_baseline"] = {"value": ref["overlaps_per_s"], "unit": "overlaps/s", "cores": 1, "kind": ref["kind"], "sample": ref["sample"],
-                                    "paths_per_s": (len(WORKLOAD["metrics"]) * 10 * REF_SAMPLE["rb_att"]) / ref["paths_s"] if ref["paths_s"] else None}
+            ref = run_reference_sample(HEADLINE, 1, 0)
+            line["cpu_baseline"] = {"value": ref["overlaps_per_s"], "unit": "overlaps/s", "cores": 1, "host_cores": os.cpu_count(), "kind": ref["kind"],
+                                    "sample": ref["sample"], "paths_per_s": ref["paths_per_s"], "whole_step_overlaps_per_s": ref["whole_step_overlaps_per_s"]}
         print(json.dumps(line))
     h.close()
     if world > 1:

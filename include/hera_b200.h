@@ -141,6 +141,19 @@ int hera_set_option(hera_ctx *ctx, const char *key, int64_t value);
  * visited set or random numbers.  Reports list bytes per second. */
 int hera_probe_list_gather(hera_ctx *ctx, uint32_t warps_per_sm, uint32_t hops, double *gbytes_per_s, float *ms);
 
+/* Parity evidence without moving the tables: 64-bit digests of the device-resident results, computed on the
+ * device (no reference counterpart).  digest(array) = sum over its 32-bit words w[i] of mix(i, w[i]) mod 2^64 with
+ *   x = (i + 1) * 0x9E3779B97F4A7C15 ^ (w[i] + 1) * 0xC2B2AE3D27D4EB4F;  x ^= x >> 32;  x *= 0xD6E8FEB86659FD93;  x ^= x >> 32
+ * (bytes of a uint8 array count as words; 64-bit elements as two words, low first).  out[] gets HERA_DIGEST_WORDS
+ * values in this order: node_len, node_anchor, e_q, e_t, adj_off, adj_rec*2+adj_side, walk view {neighbour | anchor
+ * bit 31, es, os, q_start - t_start} (4 words per slot), canon, rank_es, rank_os, rank_es_sqrt, rank_os_sqrt (0 when
+ * not built), then the paths hera_paths_export would return (unique ones after hera_paths_unique): off, nodes, slots,
+ * len, then the tables of the last hera_groups call: pair_a1, pair_a2, pair_sorted, grp_size0, grp_pig, grp_consensus,
+ * grp_valid, pair_consensus (0 before hera_groups).  bench.py compares the digests of all ranks with each other and
+ * with the digests of a run that was compared with the oracle table by table (tests/golden). */
+#define HERA_DIGEST_WORDS 24
+int hera_digest(hera_ctx *ctx, uint64_t *out);
+
 /* ---- sharded runs: one rank per GPU ---------------------------------------------
  * No reference counterpart (the reference is single-threaded, src/Main.cpp).  A communicator is
  * attached to a context once; afterwards hera_graph_load_file / hera_graph_load_shard,

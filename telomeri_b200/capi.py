@@ -79,6 +79,7 @@ SIGNATURES = {
     "hera_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "hera_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "hera_probe_list_gather": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
+    "hera_digest": (C.c_int, [C.c_void_p, u64p]),
     "hera_graph_set_filter": (C.c_int, [C.c_void_p, C.POINTER(FilterParams)]),
     "hera_graph_load_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_bytes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
@@ -108,6 +109,25 @@ SIGNATURES = {
     "hera_groups": (C.c_int, [C.c_void_p, C.POINTER(PathParams), C.POINTER(GroupsView)]),
     "hera_scaffold": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.c_uint64, C.POINTER(ScaffoldView)]),
 }
+
+DIGEST_NAMES = ["node_len", "node_anchor", "e_q", "e_t", "adj_off", "adj_pay", "walk_view", "canon", "rank_0", "rank_1", "rank_2", "rank_3",
+                "u_off", "u_nodes", "u_slots", "u_len", "pair_a1", "pair_a2", "pair_sorted", "grp_size0", "grp_pig", "grp_consensus", "grp_valid",
+                "pair_consensus"]
+DIGEST_WORDS = len(DIGEST_NAMES)
+
+
+def digest_words(a):
+    """numpy restatement of the digest of include/hera_b200.h (hera_digest) for one array."""
+    a = np.ascontiguousarray(a)
+    w = a.astype(np.uint64) if a.dtype.itemsize == 1 else a.view(np.uint32).astype(np.uint64)
+    i = np.arange(1, w.size + 1, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        x = (i * np.uint64(0x9E3779B97F4A7C15)) ^ ((w + np.uint64(1)) * np.uint64(0xC2B2AE3D27D4EB4F))
+        x ^= x >> np.uint64(32)
+        x *= np.uint64(0xD6E8FEB86659FD93)
+        x ^= x >> np.uint64(32)
+        return int(x.sum(dtype=np.uint64))
+
 
 _lib = None
 
@@ -195,6 +215,12 @@ class Hera:
 
     def set_option(self, key, value):
         self._check(self.lib.hera_set_option(self.h, key.encode(), int(value)))
+
+    def digest(self):
+        """hera_digest: {table name: 64-bit digest of the device-resident table}."""
+        out = (C.c_uint64 * DIGEST_WORDS)()
+        self._check(self.lib.hera_digest(self.h, out))
+        return dict(zip(DIGEST_NAMES, (int(v) for v in out)))
 
     def set_filter(self, fp):
         self._check(self.lib.hera_graph_set_filter(self.h, C.byref(fp)))

@@ -23,6 +23,76 @@ void maybe_flush_l2(Ctx &c) {
     HERA_CUDA(cudaGetLastError());
 }
 static std::string g_create_error;
+
+// ---- hera_digest --------------------------------------------------------------------------------
+__host__ __device__ inline unsigned long long digest_mix(unsigned long long i, unsigned long long w) {
+    unsigned long long x = ((i + 1) * 0x9E3779B97F4A7C15ull) ^ ((w + 1) * 0xC2B2AE3D27D4EB4Full);
+    x ^= x >> 32;
+    x *= 0xD6E8FEB86659FD93ull;
+    x ^= x >> 32;
+    return x;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) digest_kernel(const T *__restrict__ a, uint64_t n, unsigned long long *out) {
+    unsigned long long s = 0;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+        s += digest_mix(i, static_cast<unsigned long long>(a[i]));
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    if ((threadIdx.x & 31u) == 0 && s) atomicAdd(out, s);
+}
+
+template <typename T>
+static void digest_dev(Ctx &c, const T *a, uint64_t n, unsigned long long *out) {
+    if (!n) return;
+    const unsigned grid = std::min<uint64_t>(div_up(n, 256), 148 * 8);
+    HERA_LAUNCH(c, digest_kernel<T>, grid, 256, 0, a, n, out);
+}
+
+template <typename T>
+static uint64_t digest_host_words(const std::vector<T> &v) {
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(v.data());
+    const uint64_t n = v.size() * sizeof(T) / 4;
+    unsigned long long s = 0;
+    for (uint64_t i = 0; i < n; i++) s += digest_mix(i, w[i]);
+    return s;
+}
+
+static void digest_tables(Ctx &c, uint64_t *out) {
+    for (int i = 0; i < HERA_DIGEST_WORDS; i++) out[i] = 0;
+    unsigned long long *d = nullptr;
+    HERA_CUDA(cudaMallocAsync(&d, HERA_DIGEST_WORDS * sizeof(unsigned long long), c.stream));
+    HERA_CUDA(cudaMemsetAsync(d, 0, HERA_DIGEST_WORDS * sizeof(unsigned long long), c.stream));
+    const GraphTables &g = c.g;
+    if (g.ready && g.E) {
+        digest_dev(c, g.node_len.p, g.N, d + 0);
+        digest_dev(c, g.node_anchor.p, g.N, d + 1);
+        digest_dev(c, g.e_q.p, g.E, d + 2);
+        digest_dev(c, g.e_t.p, g.E, d + 3);
+        digest_dev(c, g.adj_off.p, g.N + 1, d + 4);
+        digest_dev(c, g.adj_pay.p, g.S, d + 5);
+        digest_dev(c, reinterpret_cast<const uint32_t *>(g.adj4.p), 4 * g.S, d + 6);
+        digest_dev(c, g.canon.p, g.S, d + 7);
+        for (int m = 0; m < 4; m++) if (g.rank_ready[m]) digest_dev(c, g.rank[m].p, g.S, d + 8 + m);
+    }
+    const PathStore &ps = c.uniq_ready ? c.uniq : c.all;
+    if (ps.paths) {
+        digest_dev(c, reinterpret_cast<const uint32_t *>(ps.off.p), 2 * (ps.paths + 1), d + 12);
+        digest_dev(c, ps.node.p, ps.nodes, d + 13);
+        digest_dev(c, ps.slot.p, ps.nodes - ps.paths, d + 14);
+        digest_dev(c, reinterpret_cast<const uint32_t *>(ps.len.p), 2 * ps.paths, d + 15);
+    }
+    HERA_CUDA(cudaMemcpyAsync(out, d, HERA_DIGEST_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+    HERA_CUDA(cudaStreamSynchronize(c.stream));
+    HERA_CUDA(cudaFreeAsync(d, c.stream));
+    if (c.groups_valid) {   // the group tables are marshalled on the host by hera_groups
+        const auto &m = c.grm;
+        out[16] = digest_host_words(m.pair_a1); out[17] = digest_host_words(m.pair_a2); out[18] = digest_host_words(m.pair_sorted);
+        out[19] = digest_host_words(m.grp_size0); out[20] = digest_host_words(m.grp_pig); out[21] = digest_host_words(m.grp_consensus);
+        out[22] = digest_host_words(m.grp_valid); out[23] = digest_host_words(m.pair_consensus);
+    }
+}
 }  // namespace hera
 
 struct hera_ctx {
@@ -129,6 +199,13 @@ int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
     else if (k == "parse_variant") c.opt_parse_variant = static_cast<int>(value);
     else if (k == "walk_smem_bitmap") c.opt_walk_smem_bitmap = value != 0;
     else throw hera::Error{102, "unknown option: " + k};
+    HERA_API_END
+}
+
+int hera_digest(hera_ctx *ctx, uint64_t *out) {
+    HERA_API_BEGIN(ctx)
+    HERA_REQUIRE(out != nullptr, 101, "null output");
+    hera::digest_tables(c, out);
     HERA_API_END
 }
 

@@ -55,6 +55,29 @@ def test_hot_path_matches_oracle(case, oracle_bin, datasets, tmp_path):
     assert gpu["call_found"].tolist()[len(opts["metrics"]):] == golden["known"]["call_found"][len(opts["metrics"]):]
 
 
+@pytest.mark.parametrize("case", ["mixed_default", "bundled_min_win42"])
+def test_device_digests_match_the_exported_tables(case, datasets):
+    """hera_digest (what bench.py compares across ranks and with tests/golden/bench_digests.json) hashes exactly the
+    tables the parity tests compare with the oracle: restated with numpy over the exported arrays."""
+    from telomeri_b200 import capi, pipeline
+    golden = common.load_golden(case)
+    with capi.Hera(0) as h:
+        out = pipeline.run_hot_path(datasets[golden["dataset"]], golden["options"], seed=3, hera=h, batched=True)
+        dg = h.digest()
+    nbr = out["a_q"] | (out["node_anchor"][out["a_q"]].astype(np.uint32) << np.uint32(31))
+    delta = (out["a_qs"].astype(np.int64) - out["a_ts"].astype(np.int64)).astype(np.int32).view(np.uint32)
+    walk_view = np.stack([nbr, out["a_es"].view(np.uint32), out["a_os"].view(np.uint32), delta], axis=1).reshape(-1)
+    expect = {"node_len": out["node_len"], "node_anchor": out["node_anchor"], "e_q": out["e_q"], "e_t": out["e_t"],
+              "adj_off": out["adj_off"].astype(np.uint32), "adj_pay": out["adj_rec"] * np.uint32(2) + out["adj_side"], "walk_view": walk_view,
+              "canon": out["canon"], "rank_0": out["rank_0"], "rank_1": out["rank_1"],
+              "u_off": out["u_off"], "u_nodes": out["u_nodes"], "u_slots": out["u_slots"], "u_len": out["u_len"]}
+    for k in ("pair_a1", "pair_a2", "pair_sorted", "grp_size0", "grp_pig", "grp_consensus", "grp_valid", "pair_consensus"):
+        expect[k] = out[k]
+    for k, arr in expect.items():
+        assert dg[k] == capi.digest_words(arr), k
+    assert dg["rank_2"] == 0 and dg["rank_3"] == 0 and dg["u_len"] != 0 and dg["grp_pig"] != 0
+
+
 def test_seed_changes_monte_carlo_only(oracle_bin, datasets, tmp_path):
     from telomeri_b200 import pipeline
     golden = common.load_golden("mixed_default")
