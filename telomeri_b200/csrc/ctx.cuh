@@ -110,8 +110,11 @@ struct Ctx {
     int opt_walk_warps_per_sm = 64;
     int opt_parse_variant = 0;     // 0 = CTA tiles (paf_parse_kernel), 1 = warp-autonomous sub-tiles (paf_parse_warp_kernel)
     int opt_walk_variant = 0;      // Monte-Carlo kernel variant (chunks in flight x resident CTAs), see walks.cu
+    int opt_walk_cap_small = 16384;  // nodes a walk may visit before its job is re-run with scratch for N nodes (tests lower it)
     int opt_walk_smem_bitmap = 1;  // 0 = keep the walks' visited bitmaps in global memory whatever the graph size (tests)
     uint64_t walk_pool_hint[2][4] = {};   // per (kind, metric): largest path pool a walk call needed so far (avoids the overflow re-run)
+    uint64_t walk_work_hint[2][4] = {};   // per (kind, metric): adjacency entries the last call examined (shares of the resident warps)
+    int walk_full_cap[2][4] = {};         // per (kind, metric): a walk outgrew the small per-warp scratch once, size it for N nodes
     std::vector<cudaStream_t> aux_streams;   // hera_paths_build: one stream per walk kernel in flight
     DBuf<uint8_t> l2_flush_buf;
     std::unique_ptr<Exchange> xch;   // null = single rank

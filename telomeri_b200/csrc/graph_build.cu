@@ -273,26 +273,39 @@ __device__ void rank_by_counting(const float *__restrict__ a_es, const float *__
     }
 }
 
-// Lists of up to RS_SMALL entries (almost all of them): canonical slots through the same kind of shared-memory
-// hash table, ranks by counting over 32-bit orderable keys read four at a time: position of slot i =
-// #{j : key[j] > key[i]}.  That is the stable order whenever the list holds no two equal keys, which is checked
-// with one sum (the positions of distinct keys add up to deg (deg - 1) / 2); in a list with equal keys the slots
-// that share a position add #{j < i : key[j] == key[i]}.  A list with a NaN is ranked with float compares.
+// Lists of up to RS_SMALL entries (almost all of them): one WARP per node, no CTA barrier.  Canonical slots through the
+// same kind of shared-memory hash table.  Ranks: position of slot i in the stable descending order =
+// #{j : K[j] > K[i]} with the 64-bit key K = {orderable metric bits, ~index} (all keys of a list are distinct, equal
+// metrics keep list order).  Counting every pair costs deg^2 compares (the reference's configs have lists of 300+
+// entries); instead 32 sampled keys, sorted in registers, split the list into 33 buckets: b(i) = #{splitters > K[i]}.
+// Every key of a lower bucket is greater than every key of a higher one, so
+//     position(i) = #{keys in buckets below b(i)} + #{K[j] in bucket b(i) : K[j] > K[i]}
+// and only the ~deg/32 keys of the own bucket are compared.  Skewed samples only cost time, never correctness.
+// A list with a NaN is ranked with float compares (what `>` does with a NaN is not an order).
 constexpr int RS_SMALL = 512;
-constexpr int RS_PER_THREAD = RS_SMALL / RK_THREADS;
+constexpr int RB_WARPS = 4, RB_THREADS = RB_WARPS * 32;
 
-// cnt += (k > ki) as one compare and one predicated add
-__device__ __forceinline__ void count_greater(uint32_t &cnt, uint32_t k, uint32_t ki) {
-    asm("{\n\t.reg .pred p;\n\tsetp.gt.u32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(cnt) : "r"(k), "r"(ki));
+__device__ void rank_by_counting_warp(const float *__restrict__ a_es, const float *__restrict__ a_os, int metric, uint32_t base, uint32_t deg,
+                                      uint32_t *__restrict__ rank) {
+    for (uint32_t i = threadIdx.x & 31u; i < deg; i += 32) {
+        const float mi = metric_value(metric, a_es[base + i], a_os[base + i]);
+        uint32_t r = 0;
+        for (uint32_t j = 0; j < deg; j++) { const float mj = metric_value(metric, a_es[base + j], a_os[base + j]); r += (mj > mi) || (mj == mi && j < i); }
+        rank[base + r] = base + i;
+    }
 }
 
-__global__ void __launch_bounds__(RK_THREADS) rank_small_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr,
+__global__ void __launch_bounds__(RB_THREADS) rank_small_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ a_nbr,
                                                                 const float *__restrict__ a_es, const float *__restrict__ a_os, uint32_t metrics_mask,
-                                                                RankPtrs rank, uint32_t *__restrict__ canon, uint32_t node0) {
-    __shared__ __align__(16) uint32_t s_words[RS_SMALL * 4];   // hash table (2 x 1024 words), then the keys
-    __shared__ uint32_t s_sum;
-    __shared__ int s_nan;
-    const uint32_t x = blockIdx.x + node0, tid = threadIdx.x;
+                                                                RankPtrs rank, uint32_t *__restrict__ canon, uint32_t node0, uint32_t nodes) {
+    __shared__ __align__(16) unsigned long long s_key[RB_WARPS][RS_SMALL];   // K[i]; first the canon hash table (keys)
+    __shared__ __align__(16) unsigned long long s_bkt[RB_WARPS][RS_SMALL];   // keys in bucket order; first the canon hash table (values)
+    __shared__ unsigned long long s_split[RB_WARPS][32];
+    __shared__ uint32_t s_cnt[RB_WARPS][36];
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t xi = blockIdx.x * RB_WARPS + w;
+    if (xi >= nodes) return;
+    const uint32_t x = node0 + xi;
     const uint32_t base = off[x], deg = off[x + 1] - base;
     if (deg == 0 || deg > RS_SMALL) return;   // longer lists: rank_canon_kernel
     uint32_t npad = 32;
@@ -300,10 +313,10 @@ __global__ void __launch_bounds__(RK_THREADS) rank_small_kernel(const uint32_t *
 
     {   // canonical slots
         const uint32_t T = 2 * npad, shift = 32 - (31 - __clz(T));
-        uint32_t *hkey = s_words, *hval = s_words + 2 * RS_SMALL;
-        for (uint32_t i = tid; i < T; i += RK_THREADS) { hkey[i] = 0xffffffffu; hval[i] = 0xffffffffu; }
-        __syncthreads();
-        for (uint32_t i = tid; i < deg; i += RK_THREADS) {
+        uint32_t *hkey = reinterpret_cast<uint32_t *>(s_key[w]), *hval = reinterpret_cast<uint32_t *>(s_bkt[w]);
+        for (uint32_t i = lane; i < T; i += 32) { hkey[i] = 0xffffffffu; hval[i] = 0xffffffffu; }
+        __syncwarp();
+        for (uint32_t i = lane; i < deg; i += 32) {
             const uint32_t nbr = a_nbr[base + i];
             uint32_t h = (nbr * 2654435761u) >> shift;
             for (;;) {
@@ -312,8 +325,8 @@ __global__ void __launch_bounds__(RK_THREADS) rank_small_kernel(const uint32_t *
                 h = (h + 1) & (T - 1);
             }
         }
-        __syncthreads();
-        for (uint32_t i = tid; i < deg; i += RK_THREADS) {
+        __syncwarp();
+        for (uint32_t i = lane; i < deg; i += 32) {
             const uint32_t nbr = a_nbr[base + i];
             uint32_t h = (nbr * 2654435761u) >> shift;
             while (hkey[h] != nbr) h = (h + 1) & (T - 1);
@@ -321,62 +334,99 @@ __global__ void __launch_bounds__(RK_THREADS) rank_small_kernel(const uint32_t *
         }
     }
 
-    uint32_t *key = s_words;
-    const uint32_t quads = (deg + 3) / 4;
+    unsigned long long *key = s_key[w], *bkt = s_bkt[w], *split = s_split[w];
+    uint32_t *cnt = s_cnt[w];
     for (int m = 0; m < 4; m++) {
         if (!(metrics_mask & (1u << m))) continue;
-        __syncthreads();   // the table / the previous metric's keys are no longer read
-        if (tid == 0) { s_nan = 0; s_sum = 0; }
-        __syncthreads();
+        __syncwarp();   // the table / the previous metric's arrays are no longer read
         bool nan = false;
-        for (uint32_t i = tid; i < quads * 4; i += RK_THREADS)   // keys behind the list are 0: never greater than a real key
-            key[i] = i < deg ? static_cast<uint32_t>(rank_key(metric_value(m, a_es[base + i], a_os[base + i]), i, nan) >> 32) : 0u;
-        if (nan) s_nan = 1;
-        __syncthreads();
-        if (s_nan) { rank_by_counting(a_es, a_os, m, base, deg, rank.p[m]); continue; }
-        uint32_t r[RS_PER_THREAD], local = 0;
+        for (uint32_t i = lane; i < deg; i += 32) key[i] = rank_key(metric_value(m, a_es[base + i], a_os[base + i]), i, nan);
+        if (lane < 34) cnt[lane] = 0;
+        if (lane < 2) cnt[32 + lane] = 0;
+        __syncwarp();
+        if (__any_sync(0xffffffffu, nan)) { rank_by_counting_warp(a_es, a_os, m, base, deg, rank.p[m]); continue; }
+        uint32_t *out = reinterpret_cast<uint32_t *>(bkt);   // positions are staged here once the buckets have been read
+        if (deg <= 64) {   // short list: compare with everything
+            uint32_t r[2];
 #pragma unroll
-        for (int e = 0; e < RS_PER_THREAD; e++) {
-            const uint32_t i = tid + e * RK_THREADS;
-            r[e] = 0;
-            if (i < deg) {
-                const uint32_t ki = key[i];
-                uint32_t cnt = 0, cnt2 = 0;
-                for (uint32_t q = 0; q < quads; q++) {
-                    const uint4 k = reinterpret_cast<const uint4 *>(key)[q];
-                    count_greater(cnt, k.x, ki); count_greater(cnt2, k.y, ki); count_greater(cnt, k.z, ki); count_greater(cnt2, k.w, ki);
-                }
-                cnt += cnt2;
-                r[e] = cnt;
-                local += cnt;
-            }
-        }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
-        if ((tid & 31u) == 0 && local) atomicAdd(&s_sum, local);
-        __syncthreads();
-        if (s_sum != deg * (deg - 1) / 2) {   // equal keys somewhere: they got the same position, list order decides between them
-            uint32_t *shared_pos = s_words + 2 * RS_SMALL;   // how many slots were given position p
-            for (uint32_t i = tid; i < deg; i += RK_THREADS) shared_pos[i] = 0;
-            __syncthreads();
-#pragma unroll
-            for (int e = 0; e < RS_PER_THREAD; e++)
-                if (tid + e * RK_THREADS < deg) atomicAdd(&shared_pos[r[e]], 1u);
-            __syncthreads();
-#pragma unroll
-            for (int e = 0; e < RS_PER_THREAD; e++) {
-                const uint32_t i = tid + e * RK_THREADS;
-                if (i < deg && shared_pos[r[e]] > 1) {
-                    const uint32_t ki = key[i];
-                    for (uint32_t j = 0; j < i; j++) r[e] += key[j] == ki;
+            for (int e = 0; e < 2; e++) {
+                const uint32_t i = lane + 32 * e;
+                r[e] = 0;
+                if (i < deg) {
+                    const unsigned long long ki = key[i];
+                    for (uint32_t j = 0; j < deg; j++) r[e] += key[j] > ki;
                 }
             }
-        }
+            __syncwarp();
 #pragma unroll
-        for (int e = 0; e < RS_PER_THREAD; e++) {
-            const uint32_t i = tid + e * RK_THREADS;
-            if (i < deg) rank.p[m][base + r[e]] = base + i;
+            for (int e = 0; e < 2; e++) if (lane + 32 * e < deg) out[r[e]] = lane + 32 * e;
+        } else {
+            // 32 samples at equal distances, sorted descending in registers (bitonic network over the lanes)
+            unsigned long long sp = key[static_cast<uint32_t>((static_cast<uint64_t>(lane) * deg) >> 5)];
+#pragma unroll
+            for (uint32_t k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                    const unsigned long long other = __shfl_xor_sync(0xffffffffu, sp, j);
+                    const bool lower_lane = (lane & j) == 0, desc = (lane & k) == 0;
+                    const bool take_max = lower_lane == desc;
+                    sp = take_max ? (sp > other ? sp : other) : (sp < other ? sp : other);
+                }
+            }
+            split[lane] = sp;
+            __syncwarp();
+            // bucket of every key, place inside the bucket in arrival order
+            constexpr int PER = RS_SMALL / 32;
+            uint32_t bk[PER], at[PER];
+#pragma unroll
+            for (int e = 0; e < PER; e++) {
+                const uint32_t i = lane + 32 * e;
+                bk[e] = 0; at[e] = 0;
+                if (i < deg) {
+                    const unsigned long long ki = key[i];
+                    uint32_t lo = 0, hi = 32;
+#pragma unroll
+                    for (int it = 0; it < 5; it++) { const uint32_t mid = (lo + hi) >> 1; if (split[mid] > ki) lo = mid + 1; else hi = mid; }
+                    if (lo < 32 && split[lo] > ki) lo++;
+                    bk[e] = lo;
+                    at[e] = atomicAdd(&cnt[lo], 1u);
+                }
+            }
+            __syncwarp();
+            // exclusive scan of the 33 bucket sizes
+            const uint32_t c0 = cnt[lane], c32 = cnt[32];
+            uint32_t incl = c0;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= static_cast<uint32_t>(d)) incl += up; }
+            __syncwarp();
+            cnt[lane] = incl - c0;
+            if (lane == 31) { cnt[32] = incl; cnt[33] = incl + c32; }
+            __syncwarp();
+#pragma unroll
+            for (int e = 0; e < PER; e++) {
+                const uint32_t i = lane + 32 * e;
+                if (i < deg) bkt[cnt[bk[e]] + at[e]] = key[i];
+            }
+            __syncwarp();
+            uint32_t r[PER];
+#pragma unroll
+            for (int e = 0; e < PER; e++) {
+                const uint32_t i = lane + 32 * e;
+                r[e] = 0;
+                if (i < deg) {
+                    const unsigned long long ki = key[i];
+                    const uint32_t b0 = cnt[bk[e]], b1 = cnt[bk[e] + 1];
+                    uint32_t g = b0;
+                    for (uint32_t j = b0; j < b1; j++) g += bkt[j] > ki;
+                    r[e] = g;
+                }
+            }
+            __syncwarp();   // the buckets have been read: their memory takes the positions
+#pragma unroll
+            for (int e = 0; e < PER; e++) if (lane + 32 * e < deg) out[r[e]] = lane + 32 * e;
         }
+        __syncwarp();
+        for (uint32_t p = lane; p < deg; p += 32) rank.p[m][base + p] = base + out[p];
     }
 }
 
@@ -645,7 +695,8 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             g.rank_ready[m] = true;
         }
         if (my_nodes) {
-            HERA_LAUNCH(c, rank_small_kernel, my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.a_es.p, g.a_os.p, metrics_mask, rp, g.canon.p, static_cast<uint32_t>(n_lo));
+            HERA_LAUNCH(c, rank_small_kernel, div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.a_es.p, g.a_os.p, metrics_mask, rp, g.canon.p,
+                        static_cast<uint32_t>(n_lo), my_nodes);
             HERA_LAUNCH(c, (rank_canon_kernel<2048, 512, true>), my_nodes, RK_THREADS, 0, g.adj_off.p, g.a_nbr.p, g.a_es.p, g.a_os.p, metrics_mask, rp, g.canon.p, static_cast<uint32_t>(n_lo));
         }
         if (ranks > 1) {

@@ -57,6 +57,7 @@ struct WalkOut {
     unsigned long long *pool_used;    // also keeps counting past the capacity
     unsigned long long *steps;        // adjacency entries examined
     unsigned int *next_walk;
+    unsigned int *overflow;           // set when a walk outgrew the per-warp scratch (cap): the job is run again with room for N nodes
     // walks are dealt out by id: this rank runs walk ids part_rank, part_rank + part_size, ... ; results are indexed by the local ordinal
     uint32_t part_rank, part_size;
 };
@@ -309,7 +310,7 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
                 dl = static_cast<int32_t>(taken.w);
             }
             cur = nbw & 0x7fffffffu;
-            if (n_nodes >= sc.cap) break;  // cannot happen: a walk visits every node at most once
+            if (nlog >= sc.cap) { if (lane == 0) *o.overflow = 1u; break; }   // scratch sized for typical walks: the host re-runs the job with cap = N + 1
             if (lane == 0) {
                 nodes[n_nodes] = cur; slots[n_nodes - 1] = slot; vlog[nlog] = cur;
                 bm[cur >> 5] |= 1u << (cur & 31);
@@ -405,7 +406,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
                 }
                 const uint32_t nbw = g.nbr[chosen];
                 const uint32_t next = nbw & 0x7fffffffu;
-                if (n_nodes >= sc.cap) break;
+                if (nlog >= sc.cap) { if (lane == 0) *o.overflow = 1u; break; }
                 if (lane == 0) {
                     slots[n_nodes - 1] = g.canon[chosen];
                     bm[cur >> 5] |= 1u << (cur & 31);
@@ -518,10 +519,11 @@ struct WalkJob {
     uint32_t *first_edges = nullptr, *walk_base = nullptr;   // greedy walks: first edges per anchor, prefix
     uint64_t pool_cap = 0, warps = 0;
     uint32_t cap = 0, words = 0;
+    int warps_per_sm = 1;
     unsigned blocks = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    unsigned long long *h_ctr = nullptr;   // pinned: [0] pool used [1] entries examined [2] ticket
+    unsigned long long *h_ctr = nullptr;   // pinned: [0] pool used [1] entries examined [2] ticket [3] scratch overflow
     uint64_t launches = 0;
 };
 
@@ -531,7 +533,8 @@ void job_launch_kernel(Ctx &c, WalkJob &j) {
     const uint32_t cache = std::min<uint32_t>(WK_CACHE_MAX, std::max<uint32_t>(64, (c.g.max_deg + 31) / 32 * 32));
     WalkScratch sc{j.r.bitmap, j.r.nodes, j.r.slots, j.r.vlog, j.words, j.cap, cache};
     WalkOut wo{j.r.res_n, j.r.res_off, j.r.res_len, j.r.res_draws, j.r.pool_nodes, j.r.pool_slots, j.pool_cap, j.r.d_ctr, j.r.d_ctr + 1,
-               reinterpret_cast<unsigned int *>(j.r.d_ctr + 2), static_cast<uint32_t>(xch_rank(c)), static_cast<uint32_t>(xch_size(c))};
+               reinterpret_cast<unsigned int *>(j.r.d_ctr + 2), reinterpret_cast<unsigned int *>(j.r.d_ctr + 3),
+               static_cast<uint32_t>(xch_rank(c)), static_cast<uint32_t>(xch_size(c))};
     HERA_CUDA(cudaMemsetAsync(j.r.d_ctr, 0, 4 * sizeof(unsigned long long), j.stream));
     HERA_CUDA(cudaMemsetAsync(j.r.res_n, 0, std::max<uint32_t>(j.my_walks, 1) * sizeof(uint32_t), j.stream));
     HERA_CUDA(cudaMemsetAsync(j.r.res_draws, 0, std::max<uint32_t>(j.my_walks, 1) * sizeof(uint32_t), j.stream));
@@ -567,6 +570,28 @@ void job_launch_kernel(Ctx &c, WalkJob &j) {
     }
     HERA_CUDA(cudaEventRecord(j.ev1, j.stream));
     HERA_CUDA(cudaMemcpyAsync(j.h_ctr, j.r.d_ctr, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, j.stream));
+}
+
+
+// Per-warp scratch of a job: visited bitmap + node / slot / visited logs for `cap` nodes.
+void job_alloc_scratch(Ctx &c, WalkJob &j, bool full, cudaStream_t stream) {
+    GraphTables &g = c.g;
+    int sms = 148;
+    HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
+    j.cap = static_cast<uint32_t>(full ? g.N + 1 : std::min<uint64_t>(g.N + 1, static_cast<uint64_t>(std::max(2, c.opt_walk_cap_small))));
+    const uint64_t per_warp = (3ull * j.cap + j.words) * sizeof(uint32_t);
+    uint64_t warps = static_cast<uint64_t>(sms) * std::max(1, j.warps_per_sm);
+    while (warps > WK_WARPS && warps * per_warp > (8ull << 30)) warps /= 2;
+    if (warps > j.my_walks) warps = (static_cast<uint64_t>(j.my_walks) + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
+    if (warps == 0) warps = WK_WARPS;
+    j.blocks = static_cast<unsigned>((warps + WK_WARPS - 1) / WK_WARPS);
+    j.warps = static_cast<uint64_t>(j.blocks) * WK_WARPS;
+    WalkRun &r = j.r;
+    HERA_CUDA(cudaMallocAsync(&r.bitmap, j.warps * j.words * sizeof(uint32_t), stream));
+    HERA_CUDA(cudaMallocAsync(&r.nodes, j.warps * j.cap * sizeof(uint32_t), stream));
+    HERA_CUDA(cudaMallocAsync(&r.slots, j.warps * j.cap * sizeof(uint32_t), stream));
+    HERA_CUDA(cudaMallocAsync(&r.vlog, j.warps * j.cap * sizeof(uint32_t), stream));
+    HERA_CUDA(cudaMemsetAsync(r.bitmap, 0, j.warps * j.words * sizeof(uint32_t), stream));
 }
 
 // Sizes the job, allocates its scratch (stream-ordered on the context's stream) and fills the walk table
@@ -605,17 +630,13 @@ void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm, int slot) {
     j.h_ctr = c.walk_h_ctr.p + 4 * slot;
     for (int k = 0; k < 4; k++) j.h_ctr[k] = 0;
     if (j.total_walks == 0) { j.launches = c.launches.count - launches0; return; }
-    int sms = 148;
-    HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
-    j.cap = static_cast<uint32_t>(g.N + 1);
+    // A walk may visit every node once, but a typical one visits a few hundred: the per-warp scratch (node / slot /
+    // visited logs) is sized for opt_walk_cap_small (16384) nodes so that a large graph does not cost resident warps (N = 420 k
+    // nodes would mean 5 MB per warp); a walk that outgrows it raises WalkOut::overflow and the job is run again
+    // with room for N nodes (remembered per kind and metric).
     j.words = static_cast<uint32_t>((g.N + 31) / 32);
-    const uint64_t per_warp = (3ull * j.cap + j.words) * sizeof(uint32_t);
-    uint64_t warps = static_cast<uint64_t>(sms) * std::max(1, warps_per_sm);
-    while (warps > WK_WARPS && warps * per_warp > (8ull << 30)) warps /= 2;
-    if (warps > j.my_walks) warps = (static_cast<uint64_t>(j.my_walks) + WK_WARPS - 1) / WK_WARPS * WK_WARPS;
-    if (warps == 0) warps = WK_WARPS;
-    j.blocks = static_cast<unsigned>((warps + WK_WARPS - 1) / WK_WARPS);
-    j.warps = static_cast<uint64_t>(j.blocks) * WK_WARPS;
+    j.warps_per_sm = warps_per_sm;
+    job_alloc_scratch(c, j, c.walk_full_cap[j.kind][j.metric] != 0, c.stream);
     const uint64_t res_cap = std::max<uint32_t>(j.my_walks, 1);
     WalkRun &r = j.r;
     HERA_CUDA(cudaMallocAsync(&r.res_n, res_cap * sizeof(uint32_t), c.stream));
@@ -623,11 +644,6 @@ void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm, int slot) {
     HERA_CUDA(cudaMallocAsync(&r.res_off, res_cap * sizeof(uint64_t), c.stream));
     HERA_CUDA(cudaMallocAsync(&r.res_len, res_cap * sizeof(int64_t), c.stream));
     HERA_CUDA(cudaMallocAsync(&r.d_ctr, 4 * sizeof(unsigned long long), c.stream));
-    HERA_CUDA(cudaMallocAsync(&r.bitmap, j.warps * j.words * sizeof(uint32_t), c.stream));
-    HERA_CUDA(cudaMallocAsync(&r.nodes, j.warps * j.cap * sizeof(uint32_t), c.stream));
-    HERA_CUDA(cudaMallocAsync(&r.slots, j.warps * j.cap * sizeof(uint32_t), c.stream));
-    HERA_CUDA(cudaMallocAsync(&r.vlog, j.warps * j.cap * sizeof(uint32_t), c.stream));
-    HERA_CUDA(cudaMemsetAsync(r.bitmap, 0, j.warps * j.words * sizeof(uint32_t), c.stream));
     j.pool_cap = std::max<uint64_t>(std::max<uint64_t>(1u << 16, c.walk_pool_hint[j.kind][j.metric]), std::min<uint64_t>(static_cast<uint64_t>(j.my_walks) * 64, 1ull << 28));
     HERA_CUDA(cudaMallocAsync(&r.pool_nodes, j.pool_cap * sizeof(uint32_t), c.stream));
     HERA_CUDA(cudaMallocAsync(&r.pool_slots, j.pool_cap * sizeof(uint32_t), c.stream));
@@ -646,14 +662,25 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
         WalkRun &r = j.r;
         for (;;) {
             HERA_CUDA(cudaStreamSynchronize(j.stream));
-            if (j.h_ctr[0] <= j.pool_cap) break;
-            HERA_CUDA(cudaFreeAsync(r.pool_nodes, j.stream));
-            HERA_CUDA(cudaFreeAsync(r.pool_slots, j.stream));
-            j.pool_cap = j.h_ctr[0] + 1024;
-            HERA_CUDA(cudaMallocAsync(&r.pool_nodes, j.pool_cap * sizeof(uint32_t), j.stream));
-            HERA_CUDA(cudaMallocAsync(&r.pool_slots, j.pool_cap * sizeof(uint32_t), j.stream));
+            const bool scratch_overflow = j.h_ctr[3] != 0;
+            if (j.h_ctr[0] <= j.pool_cap && !scratch_overflow) break;
+            if (scratch_overflow) {   // some walk visited more nodes than the small scratch holds: again with room for every node
+                HERA_REQUIRE(j.cap < c.g.N + 1, 38, "internal: walk scratch overflow at full capacity");
+                c.walk_full_cap[j.kind][j.metric] = 1;
+                for (void *q : {static_cast<void *>(r.bitmap), static_cast<void *>(r.nodes), static_cast<void *>(r.slots), static_cast<void *>(r.vlog)})
+                    HERA_CUDA(cudaFreeAsync(q, j.stream));
+                job_alloc_scratch(c, j, true, j.stream);
+            }
+            if (j.h_ctr[0] > j.pool_cap) {
+                HERA_CUDA(cudaFreeAsync(r.pool_nodes, j.stream));
+                HERA_CUDA(cudaFreeAsync(r.pool_slots, j.stream));
+                j.pool_cap = j.h_ctr[0] + 1024;
+                HERA_CUDA(cudaMallocAsync(&r.pool_nodes, j.pool_cap * sizeof(uint32_t), j.stream));
+                HERA_CUDA(cudaMallocAsync(&r.pool_slots, j.pool_cap * sizeof(uint32_t), j.stream));
+            }
             job_launch_kernel(c, j);
         }
+        c.walk_work_hint[j.kind][j.metric] = j.h_ctr[1];
         HERA_CUDA(cudaEventElapsedTime(&ms, j.ev0, j.ev1));
         steps = j.h_ctr[1];
         uint64_t &hint = c.walk_pool_hint[j.kind][j.metric];
@@ -767,10 +794,21 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
     int mc = 0, det = 0;
     for (int i = 0; i < n; i++) (kinds[i] == 0 ? mc : det)++;
     const int budget = c.opt_walk_warps_per_sm;
+    // Shares of the resident warps: in proportion to the adjacency entries the same call examined last time on this
+    // context (the kernels run side by side and the stage ends with the slowest one); equal Monte-Carlo shares and 4
+    // warps per greedy call when nothing is known yet.
+    double known = 0;
+    bool all_known = n > 1;
+    for (int i = 0; i < n; i++) {
+        const uint64_t w = c.walk_work_hint[kinds[i] ? 1 : 0][metrics[i] & 3];
+        all_known = all_known && w > 0;
+        known += static_cast<double>(w);
+    }
     for (int i = 0; i < n; i++) {
         WalkJob &j = jobs[i];
         j.kind = kinds[i] ? 1 : 0; j.metric = metrics[i]; j.pp = pp; j.seed = seed;
-        const int share = n == 1 ? budget : (j.kind == 0 ? std::max(8, (budget - 4 * det) / std::max(1, mc)) : 4);
+        int share = n == 1 ? budget : (j.kind == 0 ? std::max(8, (budget - 4 * det) / std::max(1, mc)) : 4);
+        if (all_known) share = std::max(4, static_cast<int>(budget * static_cast<double>(c.walk_work_hint[j.kind][j.metric & 3]) / known + 0.5) / 4 * 4);
         job_prepare(c, j, share, i);
     }
     if (n == 1) {

@@ -183,6 +183,24 @@ def test_walk_bitmap_in_global_memory(oracle_bin, datasets, tmp_path):
     common.assert_sections_equal(ora, gpu, PATH_SECTIONS + GROUP_SECTIONS, "global bitmap")
 
 
+@pytest.mark.parametrize("batched", [False, True])
+def test_walk_scratch_overflow_is_rerun_with_full_capacity(batched, oracle_bin, datasets, tmp_path):
+    """The per-warp walk scratch holds 16384 nodes by default; a walk that visits more makes the call run again with room
+    for every node.  Forced here with a capacity of 8 nodes: most walks overflow, the paths must still be the oracle's;
+    the second run of the same context goes straight to the full capacity (and the adaptive warp shares are in use)."""
+    from telomeri_b200 import capi, pipeline
+    golden = common.load_golden("small_default")
+    ds = datasets[golden["dataset"]]
+    ora = common.run_dump(oracle_bin, ds, tmp_path / "o.bin", golden["options"], extra=["--rng", "philox", "--seed", "78"])
+    with capi.Hera(0) as h:
+        h.set_option("walk_cap_small", 8)
+        for _ in range(2):
+            h.graph_reset()
+            h.paths_reset()
+            gpu = pipeline.run_hot_path(ds, golden["options"], seed=78, hera=h, batched=batched)
+            common.assert_sections_equal(ora, gpu, PATH_SECTIONS + GROUP_SECTIONS, "small walk scratch")
+
+
 @pytest.mark.parametrize("case", ["small_default", "mixed_sqrt", "bundled_min"])
 def test_batched_build_equals_separate_calls(case, oracle_bin, datasets, tmp_path):
     """hera_paths_build (all walk kernels in flight together) leaves paths_ exactly as the separate calls do."""
