@@ -128,7 +128,7 @@ uint64_t hera_kernel_launches(hera_ctx *ctx);    /* kernels launched by this con
 /* Measurement helpers (no reference counterpart; the reference only has Stopwatch, src/Stopwatch.cpp):
  * a CUDA-event pair on the context's own stream, and integer knobs.
  * Options: "flush_l2" (1 = write a buffer larger than L2 before every event-timed kernel region,
- * outside the timed region), "walk_warps_per_sm" (resident walk warps per SM shared by the walk kernels in flight, default 64), "walk_smem_bitmap" (0 = visited
+ * outside the timed region), "walk_warps_per_sm" (resident walk warps per SM shared by the walk kernels in flight, default 32), "walk_smem_bitmap" (0 = visited
  * bitmaps of the Monte-Carlo walks stay in global memory even when they would fit in shared memory),
  * "walk_variant" (chunks in flight x resident CTAs of the Monte-Carlo kernel, tuning), "walk_cap_small" (nodes a walk may
  * visit before its call is repeated with per-warp scratch for every node of the graph, default 16384), "parse_variant" (0 = the
@@ -160,9 +160,11 @@ int hera_digest(hera_ctx *ctx, uint64_t *out);
  * attached to a context once; afterwards hera_graph_load_file / hera_graph_load_shard,
  * hera_graph_finalize, hera_paths_monte_carlo and hera_paths_deterministic are COLLECTIVE: every
  * rank must call them with the same arguments.  The PAF text is parsed by byte range (each rank
- * tokenizes, filters and scores its slice), kept overlaps are all-gathered in file order, walks are
- * dealt out by walk id and the accepted paths all-gathered in the reference's path order, so every
- * rank ends up with the same graph and the same paths_, bit for bit what one GPU produces.
+ * tokenizes, filters and scores its slice), node ids and adjacency lists are built from every rank's own
+ * overlaps (the distinct names of the ranks are merged; every rank writes its part of each node's list
+ * straight into every rank's tables over NVLink), walks are dealt out by walk id and the accepted paths
+ * all-gathered in the reference's path order, so every rank ends up with the same graph and the same
+ * paths_, bit for bit what one GPU produces.
  *   NCCL transport: one process per GPU.  Rank 0 calls hera_nccl_unique_id, the launcher hands the
  *   128 bytes to every rank (torch.distributed broadcast, MPI_Bcast, a file), each rank calls
  *   hera_comm_init_nccl.  libnccl.so.2 is loaded on demand.
@@ -226,8 +228,12 @@ int hera_graph_finalize(hera_ctx *ctx, uint32_t metrics_mask, hera_graph_info *o
  * graph restores it, then hera_graph_finalize builds CSR and ranks without reading any PAF text. */
 int hera_graph_save(hera_ctx *ctx, const char *path);
 int hera_graph_load_cache(hera_ctx *ctx, const char *path);
-/* nodes_ / edges_ / nodes_[i].edges as flat host arrays. */
+/* nodes_ / edges_ / nodes_[i].edges as flat host arrays.  On a sharded context COLLECTIVE the first time after a
+ * hera_graph_finalize: the kept overlaps stay on the rank that parsed them until somebody needs the whole edges_
+ * table (this call, hera_graph_save, hera_scaffold, hera_digest), then every rank gathers them.  A rank that makes
+ * none of these calls while another rank does must call hera_graph_gather_rows instead. */
 int hera_graph_export(hera_ctx *ctx, hera_graph_view *out);
+int hera_graph_gather_rows(hera_ctx *ctx);
 
 /* ---- PathManager ------------------------------------------------------------------------- */
 /* PathManager::buildMonteCarlo (src/PathManager.cpp:12-177).  Draws come from Philox4x32-10 with

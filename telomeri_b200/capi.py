@@ -98,6 +98,7 @@ SIGNATURES = {
     "hera_graph_reset": (C.c_int, [C.c_void_p]),
     "hera_graph_finalize": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(GraphInfo)]),
     "hera_graph_export": (C.c_int, [C.c_void_p, C.POINTER(GraphView)]),
+    "hera_graph_gather_rows": (C.c_int, [C.c_void_p]),
     "hera_graph_save": (C.c_int, [C.c_void_p, C.c_char_p]),
     "hera_graph_load_cache": (C.c_int, [C.c_void_p, C.c_char_p]),
     "hera_paths_monte_carlo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PathParams), C.c_uint64, C.POINTER(WalkStats)]),
@@ -286,6 +287,10 @@ class Hera:
         info = GraphInfo()
         self._check(self.lib.hera_graph_finalize(self.h, mask, C.byref(info)))
         return info
+
+    def gather_rows(self):
+        """Sharded contexts: the collective part of export_graph / save_graph / scaffold / digest, for ranks that skip those calls."""
+        self._check(self.lib.hera_graph_gather_rows(self.h))
 
     def save_graph(self, path):
         self._check(self.lib.hera_graph_save(self.h, str(path).encode()))

@@ -66,10 +66,11 @@ static void digest_tables(Ctx &c, uint64_t *out) {
     HERA_CUDA(cudaMemsetAsync(d, 0, HERA_DIGEST_WORDS * sizeof(unsigned long long), c.stream));
     const GraphTables &g = c.g;
     if (g.ready && g.E) {
+        const RowView rows = rows_view(c);   // (collective on a sharded context)
         digest_dev(c, g.node_len.p, g.N, d + 0);
         digest_dev(c, g.node_anchor.p, g.N, d + 1);
-        digest_dev(c, g.e_q.p, g.E, d + 2);
-        digest_dev(c, g.e_t.p, g.E, d + 3);
+        digest_dev(c, rows.e_q, g.E, d + 2);
+        digest_dev(c, rows.e_t, g.E, d + 3);
         digest_dev(c, g.adj_off.p, g.N + 1, d + 4);
         digest_dev(c, g.adj_pay.p, g.S, d + 5);
         digest_dev(c, reinterpret_cast<const uint32_t *>(g.adj4.p), 4 * g.S, d + 6);
@@ -198,6 +199,7 @@ int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
     else if (k == "walk_variant") c.opt_walk_variant = static_cast<int>(value);
     else if (k == "parse_variant") c.opt_parse_variant = static_cast<int>(value);
     else if (k == "walk_smem_bitmap") c.opt_walk_smem_bitmap = value != 0;
+    else if (k == "walk_hints_reset") { for (auto &a : c.walk_work_hint) for (uint64_t &w : a) w = 0; }
     else if (k == "walk_cap_small") { c.opt_walk_cap_small = static_cast<int>(std::max<int64_t>(2, value)); for (auto &a : c.walk_full_cap) for (int &f : a) f = 0; }
     else throw hera::Error{102, "unknown option: " + k};
     HERA_API_END
@@ -491,6 +493,9 @@ int hera_graph_reset(hera_ctx *ctx) {
     std::sort(c.text_pool.begin(), c.text_pool.end(), [](const auto &a, const auto &b) { return a->bytes.cap > b->bytes.cap; });
     if (c.text_pool.size() > 4) c.text_pool.resize(4);   // keep the largest few
     c.own_rows.clear();
+    c.load_shapes.clear();
+    c.rows_total = 0;
+    c.gathered.valid = false;
     c.cache_loaded = false;
     c.kept.n = 0;
     c.g.ready = false;
@@ -501,6 +506,12 @@ int hera_graph_reset(hera_ctx *ctx) {
 int hera_graph_finalize(hera_ctx *ctx, uint32_t metrics_mask, hera_graph_info *out) {
     HERA_API_BEGIN(ctx)
     hera::finalize_graph(c, metrics_mask, out);
+    HERA_API_END
+}
+
+int hera_graph_gather_rows(hera_ctx *ctx) {
+    HERA_API_BEGIN(ctx)
+    (void)hera::rows_view(c);
     HERA_API_END
 }
 

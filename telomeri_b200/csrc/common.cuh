@@ -36,17 +36,26 @@ template <typename T>
 struct DBuf {
     T *p = nullptr;
     size_t cap = 0;
+    bool borrowed = false;   // p belongs to somebody else (a buffer the exchange shares between the ranks)
     ~DBuf() { release(); }
     DBuf() = default;
     DBuf(const DBuf &) = delete;
     DBuf &operator=(const DBuf &) = delete;
     void release() {
-        if (p) cudaFree(p);
+        if (p && !borrowed) cudaFree(p);
         p = nullptr;
         cap = 0;
+        borrowed = false;
+    }
+    void borrow(T *ptr, size_t n) {
+        release();
+        p = ptr;
+        cap = n;
+        borrowed = true;
     }
     void reserve(size_t n, bool keep = false, size_t keep_n = 0, cudaStream_t s = 0) {
         if (n <= cap) return;
+        if (borrowed) throw ::hera::Error{2, "internal: a borrowed buffer cannot grow"};
         size_t ncap = n + n / 4 + 64;
         T *np = nullptr;
         HERA_CUDA(cudaMalloc(&np, ncap * sizeof(T)));

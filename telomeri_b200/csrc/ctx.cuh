@@ -58,6 +58,37 @@ struct RowRange {
     uint64_t begin, end;
 };
 
+// Kept overlaps stay on the rank that parsed them.  One load contributes one piece: the local rows
+// [local0, local0 + count) of this rank's table are the rows [global0, global0 + count) of the file-order table the
+// reference calls edges_ (rr loads first, ranks in byte-range order inside a load).  A single rank has local == global.
+constexpr int MAX_LOADS = 16;
+struct RowPieces {
+    int n = 0;
+    uint64_t local0[MAX_LOADS], global0[MAX_LOADS], count[MAX_LOADS];
+    __host__ __device__ uint64_t global_of(uint64_t l) const {
+        for (int i = n - 1; i > 0; i--) if (l >= local0[i]) return global0[i] + (l - local0[i]);
+        return global0[0] + l;
+    }
+    __host__ __device__ bool local_of(uint64_t g, uint64_t *l) const {
+        for (int i = 0; i < n; i++) if (g >= global0[i] && g < global0[i] + count[i]) { *l = local0[i] + (g - global0[i]); return true; }
+        return false;
+    }
+};
+
+// What the ranks told each other about one load: kept rows per rank (global order = rank order inside the load).
+struct LoadShape {
+    uint64_t global0 = 0, total = 0;
+    std::vector<uint64_t> counts, displs;
+};
+
+// Read-only view of the file-order table of kept overlaps with their node ids (what export, cache and scaffold read).
+struct RowView {
+    uint64_t n = 0;
+    const uint32_t *qs, *qe, *ts, *te, *qlen, *tlen, *rec, *e_q, *e_t;
+    const float *os, *si, *es;
+    const uint8_t *flags;
+};
+
 struct LoadedText {
     DBuf<uint8_t> bytes;  // padded with '\n' up to a multiple of the tile size plus one tile
     uint64_t n = 0;
@@ -69,21 +100,18 @@ struct GraphTables {
     bool ready = false;
     uint64_t N = 0, anchors = 0, E = 0, S = 0;
     uint32_t max_deg = 0;                    // longest adjacency list
-    DBuf<uint32_t> e_q, e_t;                 // node ids per kept overlap
+    DBuf<uint32_t> e_q, e_t;                 // node ids per LOCAL kept overlap
     DBuf<uint32_t> node_len;
     DBuf<uint8_t> node_anchor;
-    DBuf<uint64_t> node_name;                // packed name reference of the first appearance (valid on the rank that parsed that row)
-    DBuf<uint32_t> node_row;                 // kept row that created the node
+    DBuf<uint32_t> node_pos;                 // first appearance of the node's name: 2 * global kept row + side (the row lives on one rank)
     DBuf<uint64_t> node_name_off;            // N + 1, into node_names
     DBuf<char> node_names;                   // every node's name, node order (complete on every rank)
     uint64_t name_bytes = 0;
     DBuf<uint32_t> adj_off;                  // N + 1
     DBuf<uint32_t> adj_pay;                  // slot -> 2 * kept + side
-    // walk-facing structure of arrays
-    DBuf<uint32_t> a_nbr;                    // neighbour id, bit 31 = neighbour is an anchor
-    DBuf<float> a_es, a_os;
-    DBuf<int32_t> a_delta;                   // q_start - t_start of the slot (src/Path.cpp:13)
-    DBuf<uint4> adj4;                        // the same four fields interleaved {nbr, es, os, delta}: one 128-bit load per entry in the roulette scan
+    // walk-facing view of a slot: {neighbour id | bit 31 = neighbour is an anchor, es, os, q_start - t_start (src/Path.cpp:13)},
+    // one 128-bit load per entry.  Sharded runs: every rank writes its entries into every rank's array (peer memory).
+    DBuf<uint4> adj4;
     DBuf<uint8_t> node_exact;                // bit m: the fp64 sum of metric m over any subset of the node's list is exact in any order
     DBuf<uint32_t> rank[4];                  // per metric; empty if not built
     bool rank_ready[4] = {false, false, false, false};
@@ -107,13 +135,13 @@ struct Ctx {
     // measurement helpers / knobs
     cudaEvent_t timer0 = nullptr, timer1 = nullptr;
     int opt_flush_l2 = 0;
-    int opt_walk_warps_per_sm = 64;
+    int opt_walk_warps_per_sm = 32;   // resident walk warps per SM shared by the walk kernels in flight (8 CTAs of 4 warps at <= 64 registers)
     int opt_parse_variant = 0;     // 0 = CTA tiles (paf_parse_kernel), 1 = warp-autonomous sub-tiles (paf_parse_warp_kernel)
     int opt_walk_variant = 0;      // Monte-Carlo kernel variant (chunks in flight x resident CTAs), see walks.cu
     int opt_walk_cap_small = 16384;  // nodes a walk may visit before its job is re-run with scratch for N nodes (tests lower it)
     int opt_walk_smem_bitmap = 1;  // 0 = keep the walks' visited bitmaps in global memory whatever the graph size (tests)
     uint64_t walk_pool_hint[2][4] = {};   // per (kind, metric): largest path pool a walk call needed so far (avoids the overflow re-run)
-    uint64_t walk_work_hint[2][4] = {};   // per (kind, metric): adjacency entries the last call examined (shares of the resident warps)
+    uint64_t walk_work_hint[2][4] = {};   // per (kind, metric): warp-microseconds the last call took (shares of the resident warps)
     int walk_full_cap[2][4] = {};         // per (kind, metric): a walk outgrew the small per-warp scratch once, size it for N nodes
     std::vector<cudaStream_t> aux_streams;   // hera_paths_build: one stream per walk kernel in flight
     DBuf<uint8_t> l2_flush_buf;
@@ -121,9 +149,17 @@ struct Ctx {
 
     std::vector<std::unique_ptr<LoadedText>> texts;
     std::vector<std::unique_ptr<LoadedText>> text_pool;   // buffers of texts dropped by hera_graph_reset, reused by the next loads
-    KeptTable kept;
+    KeptTable kept;                   // LOCAL rows: the kept overlaps this rank parsed itself (all of them on a single rank)
     bool cache_loaded = false;        // kept overlaps + node table came from hera_graph_load_cache: finalize skips K3
-    std::vector<RowRange> own_rows;   // per load: the kept rows this rank parsed itself (their name references point into ITS texts)
+    std::vector<RowRange> own_rows;   // per load: the GLOBAL rows this rank parsed itself
+    std::vector<LoadShape> load_shapes;   // per load: every rank's kept count
+    uint64_t rows_total = 0;          // kept overlaps of all ranks (== kept.n on a single rank)
+    struct GatheredRows {             // sharded runs, built on demand by rows_view(): the complete file-order table on this rank
+        bool valid = false;
+        DBuf<uint32_t> qs, qe, ts, te, qlen, tlen, rec, e_q, e_t;
+        DBuf<float> os, si, es;
+        DBuf<uint8_t> flags;
+    } gathered;
     GraphTables g;
 
     PathStore all, uniq;
@@ -179,6 +215,8 @@ void maybe_flush_l2(Ctx &c);
 // ---- stages ------------------------------------------------------------------------------
 void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out);
 void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out);
+RowPieces row_pieces(const Ctx &c);
+RowView rows_view(Ctx &c);   // COLLECTIVE on a sharded context the first time after a finalize (all-gather of the rows)
 void export_graph(Ctx &c, hera_graph_view *out);
 void save_graph_cache(Ctx &c, const char *path);
 void load_graph_cache(Ctx &c, const char *path);

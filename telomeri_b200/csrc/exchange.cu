@@ -100,6 +100,39 @@ struct LocalExchange final : Exchange {
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         hub->barrier();
     }
+    // One process: a rank's cudaMalloc'ed buffer is addressable by the others as it is (same device, or peer access).
+    struct Shared { void *p = nullptr; size_t cap = 0; };
+    std::vector<Shared> shared;
+    ~LocalExchange() override { for (Shared &b : shared) if (b.p) cudaFree(b.p); }
+    bool shared_buffers(Ctx &c, int key, size_t bytes, void **ptrs) override {
+        prepare_peers(c);
+        if (static_cast<size_t>(key) >= shared.size()) shared.resize(key + 1);
+        Shared &b = shared[key];
+        HERA_CUDA(cudaStreamSynchronize(c.stream));
+        hub->barrier();                       // nobody still writes into the buffer that may be replaced
+        if (bytes > b.cap) {
+            if (b.p) HERA_CUDA(cudaFree(b.p));
+            b.cap = bytes + bytes / 4 + 256;
+            HERA_CUDA(cudaMalloc(&b.p, b.cap));
+        }
+        {
+            std::lock_guard<std::mutex> lk(hub->m);
+            hub->ptrs[rank] = b.p;
+        }
+        hub->barrier();
+        bool ok = true;
+        for (int r = 0; r < size; r++) {
+            ptrs[r] = const_cast<void *>(hub->ptrs[r]);
+            if (hub->devices[r] != c.device) {
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, c.device, hub->devices[r]) != cudaSuccess || !can) ok = false;
+            }
+        }
+        hub->barrier();                       // everybody has read the table before it is reused
+        HERA_REQUIRE(ok, 39, "local gang: the ranks' devices cannot address each other's memory (peer access is needed)");
+        return true;
+    }
+    void all_reduce_sum_u32(Ctx &, uint32_t *, size_t) override { throw Error{39, "local gang: all_reduce is not needed (buffers are shared)"}; }
     void all_gather_host(Ctx &c, const uint64_t *in, int count, uint64_t *out) override {
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         {
@@ -290,6 +323,7 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
@@ -319,6 +353,7 @@ NcclApi &nccl_api() {
         api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
         api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
         api.Broadcast = reinterpret_cast<decltype(api.Broadcast)>(sym("ncclBroadcast"));
+        api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
         api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
         api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
         api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
@@ -339,13 +374,92 @@ struct NcclExchange final : Exchange {
     ncclComm_t comm = nullptr;
     uint64_t *d_small = nullptr, *h_small = nullptr;   // device / pinned staging of host gathers
     size_t d_small_cap = 0, h_small_cap = 0;
+    // Teardown in three steps (an exported allocation must not be freed while a peer still has it mapped): every rank
+    // closes the handles it imported, the ranks meet, then each frees what it exported.  hera_destroy is collective on a
+    // sharded context; a communicator that was aborted (a rank failed) skips the rendezvous.
+    bool aborted = false;
+    void abort() override { aborted = true; }
     ~NcclExchange() override {
+        unmap_mailbox();
+        unmap_windows();
+        for (SharedBuf &b : shared) unmap_shared(b);
+        if (comm && !aborted) {
+            uint64_t one = 1, *d = nullptr;
+            // a plain NCCL all-gather as the rendezvous (the mailbox is already unmapped)
+            if (cudaMalloc(&d, (1 + size) * sizeof(uint64_t)) == cudaSuccess) {
+                cudaMemcpy(d, &one, sizeof(one), cudaMemcpyHostToDevice);
+                if (nccl_api().AllGather(d, d + 1, 1, ncclUint64, comm, nullptr) == ncclSuccess) cudaStreamSynchronize(nullptr);
+                cudaFree(d);
+            }
+        }
+        if (mailbox) cudaFree(mailbox);
+        if (window) cudaFree(window);
+        for (SharedBuf &b : shared) if (b.mine) cudaFree(b.mine);
         if (d_small) cudaFree(d_small);
         if (h_small) cudaFreeHost(h_small);
         if (d_token) cudaFree(d_token);
-        close_mailbox();
-        close_windows();
         if (comm) nccl_api().CommDestroy(comm);
+        cudaGetLastError();
+    }
+
+    // ---- shared buffers: one cudaMalloc'ed buffer per rank and key, mapped by every other rank through CUDA IPC ----
+    struct SharedBuf {
+        void *mine = nullptr;
+        size_t cap = 0;
+        std::vector<void *> peer;   // [r] = rank r's buffer as mapped here (mine for r == rank); empty = not mapped
+    };
+    std::vector<SharedBuf> shared;
+    void unmap_shared(SharedBuf &b) {
+        for (int r = 0; r < static_cast<int>(b.peer.size()); r++)
+            if (r != rank && b.peer[r]) cudaIpcCloseMemHandle(b.peer[r]);
+        b.peer.clear();
+    }
+    bool shared_buffers(Ctx &c, int key, size_t bytes, void **ptrs) override {
+        if (static_cast<size_t>(key) >= shared.size()) shared.resize(key + 1);
+        SharedBuf &b = shared[key];
+        const bool ipc = !(size > GR_MAX_RANKS || getenv("HERA_NO_PEER_WINDOWS"));
+        // every rank asks for the same size and the buffers grow the same way, so this decision is the same everywhere
+        if (bytes > b.cap || (ipc && b.peer.empty() && ipc_shared_state >= 0)) {
+            HERA_CUDA(cudaStreamSynchronize(c.stream));
+            unmap_shared(b);
+            barrier(c);                         // every rank has closed its mappings of the buffers that are replaced
+            if (bytes > b.cap) {
+                if (b.mine) HERA_CUDA(cudaFree(b.mine));
+                b.mine = nullptr;
+                b.cap = (bytes + bytes / 4 + 4096) / 512 * 512;
+                HERA_CUDA(cudaMalloc(&b.mine, b.cap));
+            }
+            if (ipc && ipc_shared_state >= 0) {
+                uint64_t mine[9] = {0};
+                cudaIpcMemHandle_t h;
+                bool ok = cudaIpcGetMemHandle(&h, b.mine) == cudaSuccess;
+                if (ok) { std::memcpy(mine, &h, 64); mine[8] = 1; } else cudaGetLastError();
+                std::vector<uint64_t> all(static_cast<size_t>(size) * 9);
+                all_gather_host(c, mine, 9, all.data());
+                for (int r = 0; r < size; r++) ok = ok && all[static_cast<size_t>(r) * 9 + 8] == 1;
+                b.peer.assign(size, nullptr);
+                for (int r = 0; ok && r < size; r++) {
+                    if (r == rank) { b.peer[r] = b.mine; continue; }
+                    cudaIpcMemHandle_t hr;
+                    std::memcpy(&hr, &all[static_cast<size_t>(r) * 9], 64);
+                    void *q = nullptr;
+                    if (cudaIpcOpenMemHandle(&q, hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+                    b.peer[r] = q;
+                }
+                uint64_t vote = ok ? 1 : 0;   // all ranks must take the same path
+                std::vector<uint64_t> votes(size);
+                all_gather_host(c, &vote, 1, votes.data());
+                for (uint64_t v : votes) ok = ok && v == 1;
+                if (!ok) { unmap_shared(b); ipc_shared_state = -1; }
+            }
+        }
+        const bool mapped = !b.peer.empty();
+        for (int r = 0; r < size; r++) ptrs[r] = mapped ? b.peer[r] : (r == rank ? b.mine : nullptr);
+        return mapped;
+    }
+    int ipc_shared_state = 0;   // -1: mapping each other's buffers failed once, do not try again
+    void all_reduce_sum_u32(Ctx &c, uint32_t *buf, size_t count) override {
+        HERA_NCCL(nccl_api().AllReduce(buf, buf, count, ncclUint32, ncclSum, comm, c.stream));
     }
     const char *transport() const override { return "nccl"; }
     void all_gather_host(Ctx &c, const uint64_t *in, int count, uint64_t *out) override {
@@ -391,10 +505,13 @@ struct NcclExchange final : Exchange {
     std::vector<unsigned long long *> peer_mailbox;
     unsigned long long mailbox_seq = 0;
     int mailbox_state = 0;             // 0 untested, 1 usable, -1 not available (NCCL all-gathers instead)
-    void close_mailbox() {
+    void unmap_mailbox() {
         for (int r = 0; r < static_cast<int>(peer_mailbox.size()); r++)
             if (r != rank && peer_mailbox[r]) cudaIpcCloseMemHandle(peer_mailbox[r]);
         peer_mailbox.clear();
+    }
+    void close_mailbox() {   // (only on the failure path of ensure_mailbox: no rank uses a mailbox that not every rank could map)
+        unmap_mailbox();
         if (mailbox) cudaFree(mailbox);
         mailbox = nullptr;
     }
@@ -437,22 +554,26 @@ struct NcclExchange final : Exchange {
     int ipc_state = 0;                 // 0 untested, 1 usable, -1 not available (fall back to NCCL broadcasts)
     uint64_t *d_token = nullptr;       // two words for the stream-ordered rendezvous
 
-    void close_windows() {
+    void unmap_windows() {
         for (int r = 0; r < static_cast<int>(peer_window.size()); r++)
             if (r != rank && peer_window[r]) cudaIpcCloseMemHandle(peer_window[r]);
         peer_window.clear();
+    }
+    void free_window() {
         if (window) cudaFree(window);
         window = nullptr;
         window_cap = 0;
     }
+    void close_windows() { unmap_windows(); free_window(); }
     // Every rank calls this with the same `need` (it is computed from the gathered counts).
     bool ensure_windows(Ctx &c, size_t need) {
         if (ipc_state < 0) return false;
         if (ipc_state == 0 && (size > GR_MAX_RANKS || getenv("HERA_NO_PEER_WINDOWS"))) { ipc_state = -1; return false; }
         if (need <= window_cap) return true;
         HERA_CUDA(cudaStreamSynchronize(c.stream));   // nobody still reads the old windows: every pull is followed by a collective
-        barrier(c);
-        close_windows();
+        unmap_windows();
+        barrier(c);                                   // every rank has closed its mappings before any window is freed
+        free_window();
         const size_t cap = (need + need / 2 + (1u << 20)) / 512 * 512;   // two halves, each a multiple of 256 bytes
         uint64_t mine[9] = {0};
         cudaIpcMemHandle_t h;

@@ -49,6 +49,14 @@ struct Exchange {
     // for it); the walk stage gathers per-walk results and path pools out of their scratch buffers that way.
     struct Column { void *base; uint32_t elem; const void *src = nullptr; };
     virtual void gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, uint64_t mine0, const uint64_t *counts, const uint64_t *displs);
+    // COLLECTIVE.  A buffer of at least `bytes` bytes on every rank under `key`, owned by the exchange and kept until a
+    // larger one is asked for; ptrs[r] = rank r's buffer as addressable from THIS rank's device (ptrs[rank] = its own), so
+    // a kernel can write its results straight into the final tables of every GPU (peer stores over NVLink).  Returns
+    // false when the ranks cannot address each other's memory: then only ptrs[rank] is valid and the caller merges with
+    // all_reduce_sum_u32.  Every rank must ask for the same size.
+    virtual bool shared_buffers(Ctx &c, int key, size_t bytes, void **ptrs) = 0;
+    // In-place element-wise sum over the ranks (fallback of shared_buffers: the ranks filled disjoint parts of zeroed arrays).
+    virtual void all_reduce_sum_u32(Ctx &c, uint32_t *buf, size_t count) = 0;
     // Host barrier (after synchronising the context's stream).
     virtual void barrier(Ctx &c) = 0;
     // Called when this rank fails inside a collective call: wakes the ranks waiting for it.

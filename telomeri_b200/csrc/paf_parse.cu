@@ -1191,7 +1191,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     const uint64_t T = sharded ? tokens_all : hc.total_tokens;
     uint64_t records = T / 16 + ((T % 16) >= 12 ? 1 : 0);
     if (records > rec_limit) records = rec_limit;
-    uint64_t kept_new = hc.kept;
+    uint64_t kept_new = hc.kept, kept_global = 0;
     if (sharded) {
         const uint64_t *gathered = c.h_counters.p + 16 + ranks;
         std::vector<uint64_t> counts(ranks), displs(ranks);
@@ -1208,16 +1208,18 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
             cudaEventDestroy(ev2);
             throw Error{20, "irregular PAF record " + std::to_string(first_bad) + ": formatted extraction leaves the 16-token grid there; load this file unsharded"};
         }
-        c.kept.reserve(c.kept.n + total, c.stream, c.kept.n + counts[me]);
-        KeptTable &k = c.kept;
-        const uint64_t n0 = k.n;
-        const Exchange::Column cols[15] = {{k.qs.p, 4}, {k.qe.p, 4}, {k.ts.p, 4}, {k.te.p, 4}, {k.qlen.p, 4}, {k.tlen.p, 4}, {k.rec.p, 4},
-                                           {k.os.p, 4}, {k.si.p, 4}, {k.es.p, 4}, {k.flags.p, 1},
-                                           {k.qhash.p, 8}, {k.thash.p, 8}, {k.qname.p, 8}, {k.tname.p, 8}};
-        c.xch->gather_rows(c, cols, 15, n0, n0, counts.data(), displs.data());
+        // The kept rows stay where they were parsed (node ids and adjacency are built from every rank's own
+        // rows, see finalize_graph); only their number per rank is known everywhere.
+        LoadShape shape;
+        shape.global0 = c.rows_total;
+        shape.total = total;
+        shape.counts = counts;
+        shape.displs = displs;
+        c.load_shapes.push_back(shape);
         HERA_CUDA(cudaEventRecord(ev2, c.stream));
-        c.own_rows.push_back({n0 + displs[me], n0 + displs[me] + counts[me]});
-        kept_new = total;
+        c.own_rows.push_back({c.rows_total + displs[me], c.rows_total + displs[me] + counts[me]});
+        kept_new = counts[me];
+        kept_global = total;
     } else if (hc.first_bad_rec < records) {
         // truncate to the records before the irregular one, then continue serially from there
         unsigned long long *d_cut = reinterpret_cast<unsigned long long *>(c.counters.p + 12);
@@ -1234,13 +1236,29 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         records = hc.first_bad_rec + hc.tail_records;
         kept_new += hc.tail_kept;
     }
-    if (!sharded) c.own_rows.push_back({c.kept.n, c.kept.n + kept_new});
+    if (!sharded) {
+        // A whole text on a sharded context (the exact reader's fallback for an irregular file): every rank parsed the
+        // same rows; rank 0 keeps them, the others contribute none.
+        kept_global = kept_new;
+        if (me != 0) kept_new = 0;
+        c.own_rows.push_back({c.rows_total, c.rows_total + kept_new});
+        LoadShape shape;
+        shape.global0 = c.rows_total;
+        shape.total = kept_global;
+        shape.counts.assign(ranks, 0);
+        shape.counts[0] = kept_global;
+        shape.displs.assign(ranks, kept_global);
+        shape.displs[0] = 0;
+        c.load_shapes.push_back(shape);
+    }
     c.kept.n += kept_new;
+    c.rows_total += kept_global;
+    c.gathered.valid = false;
     c.g.ready = false;
     if (out) {
         out->records = records;
-        out->kept = kept_new;
-        out->kept_total = c.kept.n;
+        out->kept = kept_global;
+        out->kept_total = c.rows_total;
         out->bytes = n;
         HERA_CUDA(cudaEventElapsedTime(&out->parse_ms, ev0, ev1));
         out->exchange_ms = 0;

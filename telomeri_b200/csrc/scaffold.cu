@@ -205,6 +205,7 @@ void load_fasta(Ctx &c, const char *path, FastaFile &f) {
 
 void build_scaffold(Ctx &c, const char *reads_path, const char *contigs_path, uint64_t min_path_num, hera_scaffold_view *out) {
     HERA_REQUIRE(c.groups_valid, 41, "hera_scaffold: call hera_groups first");
+    const RowView rows = rows_view(c);   // coordinates of the path edges (collective on a sharded context)
     HERA_REQUIRE(reads_path && contigs_path, 101, "null path");
     const PathStore &ps = c.uniq_ready ? c.uniq : c.all;
     auto &m = c.grm;
@@ -305,7 +306,7 @@ void build_scaffold(Ctx &c, const char *reads_path, const char *contigs_path, ui
     HERA_CUDA(cudaMemcpyAsync(d_nodes, sm.nodes.data(), nn * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
     HERA_CUDA(cudaMemcpyAsync(d_slots, sm.slots.data(), ne * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
     HERA_LAUNCH(c, fa_lookup_kernel, div_up(nn, 128), 128, 0, nn, d_nodes, c.g.node_name_off.p, c.g.node_names.p, reads.dev(), contigs.dev(), keys, first_rec, cap - 1, d_refs);
-    HERA_LAUNCH(c, slot_ends_kernel, div_up(ne, 128), 128, 0, ne, d_slots, c.g.adj_pay.p, c.kept.qe.p, c.kept.te.p, c.kept.flags.p, d_ends);
+    HERA_LAUNCH(c, slot_ends_kernel, div_up(ne, 128), 128, 0, ne, d_slots, c.g.adj_pay.p, rows.qe, rows.te, rows.flags, d_ends);
     std::vector<SeqRef> refs(nn);
     std::vector<SlotEnds> ends(ne);
     HERA_CUDA(cudaMemcpyAsync(refs.data(), d_refs, nn * sizeof(SeqRef), cudaMemcpyDeviceToHost, c.stream));

@@ -15,6 +15,8 @@
 // addends non-negative finite multiples of 2^k and the total below 2^(k+53)): then any order
 // gives the sequential result bit for bit.  Otherwise the warp accumulates in list order.
 #include <algorithm>
+#include <chrono>
+#include <string>
 #include <vector>
 
 #include "ctx.cuh"
@@ -27,10 +29,8 @@ constexpr int WK_WARPS = WK_THREADS / 32;
 constexpr int WK_CACHE_MAX = 1024;  // list entries (metric values) a warp can keep in shared memory between the two roulette passes
 
 struct WalkGraph {
-    const uint32_t *off, *nbr, *canon, *rank, *node_len, *anchor_ids;
-    const float *metric;      // a_es or a_os
-    const int32_t *delta;
-    const uint4 *adj4;        // {nbr, es, os, delta} per slot
+    const uint32_t *off, *canon, *rank, *node_len, *anchor_ids;
+    const uint4 *adj4;        // {nbr | anchor bit 31, es, os, delta} per slot
     const uint8_t *node_exact;
     uint32_t N, anchors;
     int sqrt_metric;
@@ -85,9 +85,12 @@ __device__ __forceinline__ double mc_draw(uint64_t seed, uint32_t metric, uint32
 }
 
 __device__ __forceinline__ float walk_metric(const WalkGraph &g, uint32_t s) {
-    const float v = g.metric[s];
+    const uint4 e = __ldg(g.adj4 + s);
+    const float v = __uint_as_float(g.use_os ? e.z : e.y);
     return g.sqrt_metric ? __fsqrt_rn(v) : v;
 }
+__device__ __forceinline__ uint32_t slot_nbr(const WalkGraph &g, uint32_t s) { return __ldg(&reinterpret_cast<const uint32_t *>(g.adj4 + s)[0]); }
+__device__ __forceinline__ int32_t slot_delta(const WalkGraph &g, uint32_t s) { return static_cast<int32_t>(__ldg(&reinterpret_cast<const uint32_t *>(g.adj4 + s)[3])); }
 
 __device__ __forceinline__ bool bit_get(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1u; }
 
@@ -120,7 +123,8 @@ __device__ __forceinline__ void clear_visited(uint32_t *bm, uint32_t words, cons
 }
 
 // Visited-set probe: the walk's bitmap lives in shared memory when the graph is small enough
-// (SMEM_BM), else in the warp's slab of global scratch.
+// (SMEM_BM), else in the warp's slab of global scratch.  (A Bloom filter in shared memory in front of the global bitmap
+// was measured on configs[3] and gave nothing: the probes of a step are independent loads that hit L2.)
 template <bool SMEM_BM>
 __device__ __forceinline__ bool bm_get(const uint32_t *s_bm, const uint32_t *g_bm, uint32_t i) {
     if (SMEM_BM) return (s_bm[i >> 5] >> (i & 31)) & 1u;
@@ -219,12 +223,12 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
                     bool open = false;
                     do {
                         n_nodes--;
-                        sum_all -= g.delta[slots[n_nodes - 1]];
+                        sum_all -= slot_delta(g, slots[n_nodes - 1]);
                         const uint32_t back = nodes[n_nodes - 1];
                         const uint32_t bb = g.off[back], bd = g.off[back + 1] - bb;
                         for (uint32_t c0 = 0; c0 < bd && !open; c0 += 32) {
                             const uint32_t k = c0 + lane;
-                            const bool un = k < bd && !bm_get<SMEM_BM>(s_bm, g_bm, g.nbr[bb + k] & 0x7fffffffu);
+                            const bool un = k < bd && !bm_get<SMEM_BM>(s_bm, g_bm, slot_nbr(g, bb + k) & 0x7fffffffu);
                             open = __any_sync(0xffffffffu, un);
                         }
                         examined += bd;
@@ -277,7 +281,7 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
                     for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
                         const uint32_t k = c0 + lane;
                         const bool valid = k < deg;
-                        const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, g.nbr[base + k] & 0x7fffffffu);
+                        const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, slot_nbr(g, base + k) & 0x7fffffffu);
                         const float v = cand ? walk_metric(g, base + k) : 0.0f;
                         const uint32_t cb = __ballot_sync(0xffffffffu, cand);
                         for (uint32_t m = cb; m; m &= m - 1) total = __dadd_rn(total, static_cast<double>(__shfl_sync(0xffffffffu, v, __ffs(m) - 1)));
@@ -287,7 +291,7 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
                     for (uint32_t c0 = 0; c0 < deg && pick < 0; c0 += 32) {
                         const uint32_t k = c0 + lane;
                         const bool valid = k < deg;
-                        const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, g.nbr[base + k] & 0x7fffffffu);
+                        const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, slot_nbr(g, base + k) & 0x7fffffffu);
                         const float v = cand ? walk_metric(g, base + k) : 0.0f;
                         const uint32_t cb = __ballot_sync(0xffffffffu, cand);
                         for (uint32_t m = cb; m; m &= m - 1) {
@@ -325,7 +329,7 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
         }
         if (lane == 0) o.res_draws[local] = draws;
         if (accepted) {
-            const long long len = sum_all - g.delta[slots[n_nodes - 2]];
+            const long long len = sum_all - slot_delta(g, slots[n_nodes - 2]);
             if (len >= 0) emit_path(o, local, nodes, slots, n_nodes, len);
         }
         clear_visited(bm, sc.words, vlog, nlog);
@@ -340,7 +344,7 @@ __global__ void det_count_kernel(WalkGraph g, uint32_t *first_edges) {
     if (a >= g.anchors) return;
     const uint32_t x = g.anchor_ids[a], base = g.off[x], deg = g.off[x + 1] - base;
     uint32_t n = deg;
-    for (uint32_t k = 0; k < deg; k++) if (g.nbr[base + k] >> 31) { n = k + 1; break; }
+    for (uint32_t k = 0; k < deg; k++) if (slot_nbr(g, base + k) >> 31) { n = k + 1; break; }
     first_edges[a] = n;
 }
 
@@ -363,7 +367,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
         while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (walk_base[mid] <= walk) lo = mid; else hi = mid; }
         const uint32_t start = g.anchor_ids[lo];
         const uint32_t fs = g.off[start] + (walk - walk_base[lo]);
-        const uint32_t nbw0 = g.nbr[fs];
+        const uint32_t nbw0 = slot_nbr(g, fs);
         uint32_t cur = nbw0 & 0x7fffffffu;
         uint32_t n_nodes = 2, nlog = 2;
         if (lane == 0) {
@@ -387,7 +391,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
                         const uint32_t k = c0 + lane;
                         uint32_t s = 0;
                         bool un = false;
-                        if (k < deg - 1) { s = g.rank[base + k]; un = !bit_get(bm, g.nbr[s] & 0x7fffffffu); }
+                        if (k < deg - 1) { s = g.rank[base + k]; un = !bit_get(bm, slot_nbr(g, s) & 0x7fffffffu); }
                         const uint32_t ub = __ballot_sync(0xffffffffu, un);
                         if (ub) chosen = static_cast<int>(__shfl_sync(0xffffffffu, s, __ffs(ub) - 1));
                         examined += 32;
@@ -404,7 +408,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
                     __syncwarp();
                     continue;
                 }
-                const uint32_t nbw = g.nbr[chosen];
+                const uint32_t nbw = slot_nbr(g, chosen);
                 const uint32_t next = nbw & 0x7fffffffu;
                 if (nlog >= sc.cap) { if (lane == 0) *o.overflow = 1u; break; }
                 if (lane == 0) {
@@ -423,7 +427,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
             if (reached) {
                 // src/Path.cpp:6-16 over the final edge list
                 long long part = 0;
-                for (uint32_t i = lane; i + 2 < n_nodes; i += 32) part += g.delta[slots[i]];
+                for (uint32_t i = lane; i + 2 < n_nodes; i += 32) part += slot_delta(g, slots[i]);
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
                 const long long len = static_cast<long long>(g.node_len[start]) + part;
@@ -473,10 +477,8 @@ struct WalkRun {
 WalkGraph make_walk_graph(Ctx &c, int metric) {
     GraphTables &g = c.g;
     WalkGraph w{};
-    w.off = g.adj_off.p; w.nbr = g.a_nbr.p; w.canon = g.canon.p; w.rank = g.rank_ready[metric] ? g.rank[metric].p : nullptr;
+    w.off = g.adj_off.p; w.canon = g.canon.p; w.rank = g.rank_ready[metric] ? g.rank[metric].p : nullptr;
     w.node_len = g.node_len.p; w.anchor_ids = g.anchor_ids.p;
-    w.metric = (metric == HERA_EXTENSION_SCORE || metric == HERA_EXTENSION_SCORE_SQRT) ? g.a_es.p : g.a_os.p;
-    w.delta = g.a_delta.p;
     w.adj4 = g.adj4.p; w.node_exact = g.node_exact.p;
     w.use_os = (metric == HERA_OVERLAP_SCORE || metric == HERA_OVERLAP_SCORE_SQRT) ? 1 : 0;
     w.exact_bit = 1u << metric;
@@ -680,7 +682,9 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
             }
             job_launch_kernel(c, j);
         }
-        c.walk_work_hint[j.kind][j.metric] = j.h_ctr[1];
+        float ms_now = 0;
+        HERA_CUDA(cudaEventElapsedTime(&ms_now, j.ev0, j.ev1));
+        c.walk_work_hint[j.kind][j.metric] = static_cast<uint64_t>(static_cast<double>(ms_now) * 1e3 * static_cast<double>(j.warps)) + 1;   // warp-microseconds
         HERA_CUDA(cudaEventElapsedTime(&ms, j.ev0, j.ev1));
         steps = j.h_ctr[1];
         uint64_t &hint = c.walk_pool_hint[j.kind][j.metric];
@@ -790,27 +794,28 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
 void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_path_params &pp, uint64_t seed, hera_walk_stats *out) {
     HERA_REQUIRE(n >= 1 && n <= 8, 101, "hera_paths_build: between 1 and 8 calls");
     std::vector<WalkJob> jobs(n);
-    // resident warps are shared out: greedy jobs have few walks and get a small share
-    int mc = 0, det = 0;
-    for (int i = 0; i < n; i++) (kinds[i] == 0 ? mc : det)++;
+    // HERA_DEBUG_TIMING: host clock at the phase ends of the call (prepare = sizing + scratch, launch, finish i = wait + gather + append)
+    const bool debug = getenv("HERA_DEBUG_TIMING") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    std::string phases;
+    auto stamp = [&](const char *name) {
+        if (!debug) return;
+        char buf[64];
+        snprintf(buf, sizeof buf, " %s +%.3f", name, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
+        phases += buf;
+    };
     const int budget = c.opt_walk_warps_per_sm;
-    // Shares of the resident warps: in proportion to the adjacency entries the same call examined last time on this
-    // context (the kernels run side by side and the stage ends with the slowest one); equal Monte-Carlo shares and 4
-    // warps per greedy call when nothing is known yet.
-    double known = 0;
-    bool all_known = n > 1;
-    for (int i = 0; i < n; i++) {
-        const uint64_t w = c.walk_work_hint[kinds[i] ? 1 : 0][metrics[i] & 3];
-        all_known = all_known && w > 0;
-        known += static_cast<double>(w);
-    }
+    // Every call gets the whole budget of resident warps.  The kernels are persistent (walks are handed out by ticket), so
+    // the CTAs of a kernel launched later start as the CTAs of an earlier one run out of walks: back to back, with the
+    // tail of each kernel (its longest walks) hidden behind the next.  Measured on configs[3] (800 k walks per
+    // Monte-Carlo call): the four kernels alone take 21 + 60 + 13 + 13 ms, side by side with split budgets 127 ms.
+    // The budget is what fits at once: 64 registers per thread allow 32 warps per SM.
     for (int i = 0; i < n; i++) {
         WalkJob &j = jobs[i];
         j.kind = kinds[i] ? 1 : 0; j.metric = metrics[i]; j.pp = pp; j.seed = seed;
-        int share = n == 1 ? budget : (j.kind == 0 ? std::max(8, (budget - 4 * det) / std::max(1, mc)) : 4);
-        if (all_known) share = std::max(4, static_cast<int>(budget * static_cast<double>(c.walk_work_hint[j.kind][j.metric & 3]) / known + 0.5) / 4 * 4);
-        job_prepare(c, j, share, i);
+        job_prepare(c, j, budget, i);
     }
+    stamp("prepared");
     if (n == 1) {
         jobs[0].stream = c.stream;
         if (jobs[0].total_walks) job_launch_kernel(c, jobs[0]);
@@ -823,14 +828,29 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
         cudaEvent_t ready;
         HERA_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
         HERA_CUDA(cudaEventRecord(ready, c.stream));   // scratch allocation and the graph itself are ordered on the context's stream
-        for (int i = 0; i < n; i++) {
+        // longest first (warp-time of the same call the last time on this context; call order when nothing is known)
+        std::vector<int> order(n);
+        for (int i = 0; i < n; i++) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
+            return c.walk_work_hint[jobs[x].kind][jobs[x].metric & 3] > c.walk_work_hint[jobs[y].kind][jobs[y].metric & 3];
+        });
+        for (int i : order) {
             jobs[i].stream = c.aux_streams[i];
             HERA_CUDA(cudaStreamWaitEvent(jobs[i].stream, ready, 0));
             if (jobs[i].total_walks) job_launch_kernel(c, jobs[i]);
         }
         cudaEventDestroy(ready);
     }
-    for (int i = 0; i < n; i++) job_finish(c, jobs[i], out ? out + i : nullptr);
+    stamp("launched");
+    for (int i = 0; i < n; i++) {
+        job_finish(c, jobs[i], out ? out + i : nullptr);
+        stamp("finished");
+    }
+    if (debug) {
+        std::string shares;
+        for (int i = 0; i < n; i++) shares += " " + std::to_string(jobs[i].warps) + "w/cap" + std::to_string(jobs[i].cap);
+        fprintf(stderr, "[hera rank %d] paths_build host clock (ms):%s; warps / scratch capacity per job:%s\n", xch_rank(c), phases.c_str(), shares.c_str());
+    }
 }
 
 // ---- measured ceiling for list walking (north_star: "the pointer-chasing walks are reported against the measured

@@ -62,6 +62,8 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, bat
         if exports:
             out.update(h.export_graph())
             out.update(slot_sections(out))
+        elif h.size > 1:
+            h.gather_rows()   # the other ranks' export_graph is collective
         if stages == "graph":
             return out
         pp = capi.default_path_params(o["rb_att"], o["bt_att"], o["len_thr"], o["w_size"], o["r_thr"])

@@ -213,14 +213,14 @@ def test_batched_build_equals_separate_calls(case, oracle_bin, datasets, tmp_pat
 
 
 def test_rank_and_canon_of_long_lists(oracle_bin, tmp_path):
-    """K4b has three code paths by list length (<= 512: counting on 32-bit keys, <= 2048: bitonic sort in shared
-    memory, longer: counting from global memory); hubs of 40 / 700 / 2600 reads with many equal scores, parallel
-    edges (the same read twice) and all four metrics go through each of them."""
+    """K4b has code paths by list length (<= 64: all pairs, <= 512: one warp per node with sampled buckets, <= 4096: the
+    same with the whole CTA, longer: counting from global memory); hubs of 40 / 300 / 700 / 2600 / 4500 reads with many
+    equal scores, parallel edges (the same read twice) and all four metrics go through each of them."""
     import random
     from telomeri_b200 import pipeline
     rng = random.Random(5)
     lines = []
-    for hub, n in (("ctgA", 40), ("ctgB", 700), ("ctgC", 2600)):
+    for hub, n in (("ctgA", 40), ("ctgB", 700), ("ctgC", 2600), ("ctgD", 300), ("ctgE", 4500)):
         for k in range(n):
             name = f"{hub}r{rng.randrange(n * 3 // 4)}"          # repeats: parallel edges -> canon != slot
             qs = rng.choice((10, 20, 30))
@@ -237,6 +237,7 @@ def test_rank_and_canon_of_long_lists(oracle_bin, tmp_path):
         gpu = pipeline.run_hot_path(d, opts, stages="graph")
         ranks = [f"rank_{METRIC_ID[m]}" for m in metrics.split(",")]
         deg = np.diff(ora["adj_off"].astype(np.int64))
-        assert deg.max() > 2048 and ((deg > 512) & (deg <= 2048)).any() and (ora["canon"] != np.arange(ora["canon"].size)).any()
+        assert deg.max() > 4096 and ((deg > 512) & (deg <= 4096)).any() and ((deg > 64) & (deg <= 512)).any()
+        assert (ora["canon"] != np.arange(ora["canon"].size)).any()
         common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + ranks, f"hubs {metrics}")
 
