@@ -338,15 +338,18 @@ def measure(key, args, torch, dist, capi, h, rank, world, dev, local_rank, with_
         h.probe_list_gather(64, 64)
         gather_gbs, gather_ms = h.probe_list_gather(64, 256)
     # roofline leg: the dominant streaming kernel (paf_parse_kernel on this rank's rr text) timed alone by its own CUDA events
-    h.set_option("flush_l2", 1)
-    parse_ms = []
-    for _ in range(min(args.steps, 5) + 1):
-        h.graph_reset()
-        leg = h.load_device_view_ptr(rr.dev.data_ptr(), rr.avail if world == 1 else rr.owned & ~15, False)   # not collective: a stand-alone text
-        parse_ms.append(leg.parse_ms)
-    h.set_option("flush_l2", 0)
+    # (sharded run: rank 0's byte range as a stand-alone text -- it starts at a record boundary; the other ranks wait)
+    parse_ms, leg_bytes, leg_kept = 0.0, 0, 0
+    if rank == 0:
+        h.set_option("flush_l2", 1)
+        legs = []
+        for _ in range(min(args.steps, 5) + 1):
+            h.graph_reset()
+            leg = h.load_device_view_ptr(rr.dev.data_ptr(), rr.avail if world == 1 else rr.owned & ~15, False)   # not collective
+            legs.append(leg.parse_ms)
+        h.set_option("flush_l2", 0)
+        parse_ms, leg_bytes, leg_kept = statistics.mean(legs[1:]), int(leg.bytes), int(leg.kept)
     h.graph_reset()
-    parse_ms = statistics.mean(parse_ms[1:])
 
     def agg(steps, k):
         return sum(s[k] for s in steps)
@@ -372,8 +375,9 @@ def measure(key, args, torch, dist, capi, h, rank, world, dev, local_rank, with_
     matches = None if not want else all(int(want[k]) == v for k, v in digest.items())
     s0 = dev_steps[-1]
     res = {"key": key, "meta": meta, "stage": stage, "e2e_wall_ms": s[8] / args.steps, "e2e_graph_ms": s[9] / args.steps, "e2e_h2d_ms": s[10] / args.steps,
-           "parse_leg_ms": s[11], "parse_leg_bytes": int(leg.bytes), "parse_leg_kept": int(leg.kept),
+           "parse_leg_ms": s[11], "parse_leg_bytes": leg_bytes, "parse_leg_kept": leg_kept,
            "launches": counts[0].item(), "h2d_bytes": counts[1].item(), "d2h_bytes": counts[2].item(),
+           "parse_rr_ms": [round(x["parse_rr_ms"], 3) for x in dev_steps],
            "records": s0["records"], "kept": s0["kept"], "nodes": s0["nodes"], "walks": s0["walks"], "walk_entries": s0["walk_entries"], "found": s0["found"],
            "unique_paths": s0["unique_paths"], "pairs": s0["pairs"], "walk_ms": s0["walk_ms"], "gather_gbs": gather_gbs, "gather_ms": gather_ms,
            "clocks": clocks.summary(), "digest": digest, "ranks_agree": ranks_agree, "golden_matches": matches, "golden_note": golden.get("verified"),
@@ -500,6 +504,7 @@ def main():
             "paths_per_s": r["walks"] / (st["paths_ms"] * 1e-3), "accepted_paths_per_s": r["found"] / (st["paths_ms"] * 1e-3),
             "unique_paths_per_step": r["unique_paths"],
             "stages_ms_per_step": st,
+            "parse_rr_ms_per_step": r["parse_rr_ms"],
             "per_step": {"records": r["records"], "paf_bytes": r["bytes"], "kept_overlaps": r["kept"], "nodes": r["nodes"], "walks": r["walks"],
                          "adjacency_entries_examined": r["walk_entries"], "anchor_pairs": r["pairs"], "walk_kernel_ms": r["walk_ms"]},
             "gpu_launches": int(r["launches"]),

@@ -289,6 +289,7 @@ struct MailboxArgs {
 __global__ void __launch_bounds__(32) mailbox_all_gather_kernel(MailboxArgs a) {
     const int r = static_cast<int>(threadIdx.x);
     const int par = static_cast<int>(a.seq & 1ull);
+    __threadfence_system();   // what earlier kernels of this stream stored into peer memory is ordered before the tags below
     if (r < a.ranks) {
         unsigned long long *slot = a.box[r] + (static_cast<size_t>(par) * MB_MAX_RANKS + a.me) * MB_SLOT;
         for (int i = 0; i < a.count; i++) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(slot + 1 + i), "l"(a.in[i]) : "memory");

@@ -277,7 +277,6 @@ __global__ void csr_scatter_kernel(uint64_t S, uint32_t P, const uint32_t *__res
         t.adj4[r][dest] = entry;
         t.pay[r][dest] = pay;
     }
-    if (t.n > 1) __threadfence_system();
 }
 
 __device__ __forceinline__ float metric_value(int metric, float es, float os);
@@ -364,7 +363,20 @@ __device__ __forceinline__ float slot_metric(const uint4 *__restrict__ adj4, int
 //              `>` sees them).  A list with a NaN metric, or longer than CAP, is ranked by counting instead:
 //              position of slot i = #{j : m[j] > m[i]} + #{j < i : m[j] == m[i]}  (what `>` on NaN gives).
 // This kernel takes the lists longer than LOW entries (the short ones go to rank_small_kernel below).
-struct RankPtrs { uint32_t *p[4]; };
+// Where the permutations and canonical slots go: this rank's tables and -- sharded runs -- the same tables of every other
+// rank (peer memory): a rank computes the lists of its share of the nodes and stores the results everywhere, so the
+// transfer over NVLink overlaps the sorting instead of following it as a gather.
+struct RankPtrs {
+    uint32_t *p[4][MAX_PEERS];
+    uint32_t *canon[MAX_PEERS];
+    int n;
+    __device__ __forceinline__ void put_rank(int m, uint32_t at, uint32_t v) const {
+        for (int r = 0; r < n; r++) p[m][r][at] = v;
+    }
+    __device__ __forceinline__ void put_canon(uint32_t at, uint32_t v) const {
+        for (int r = 0; r < n; r++) canon[r][at] = v;
+    }
+};
 
 __device__ __forceinline__ uint64_t rank_key(float v, uint32_t i, bool &nan) {
     uint32_t bits = __float_as_uint(v);
@@ -374,13 +386,12 @@ __device__ __forceinline__ uint64_t rank_key(float v, uint32_t i, bool &nan) {
     return (static_cast<uint64_t>(u) << 32) | (0xffffffffu - i);
 }
 
-__device__ void rank_by_counting(const uint4 *__restrict__ adj4, int metric, uint32_t base, uint32_t deg,
-                                 uint32_t *__restrict__ rank) {
+__device__ void rank_by_counting(const uint4 *__restrict__ adj4, int metric, uint32_t base, uint32_t deg, const RankPtrs &out) {
     for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) {
         const float mi = slot_metric(adj4, metric, base + i);
         uint32_t r = 0;
         for (uint32_t j = 0; j < deg; j++) { const float mj = slot_metric(adj4, metric, base + j); r += (mj > mi) || (mj == mi && j < i); }
-        rank[base + r] = base + i;
+        out.put_rank(metric, base + r, base + i);
     }
 }
 
@@ -395,13 +406,12 @@ __device__ void rank_by_counting(const uint4 *__restrict__ adj4, int metric, uin
 // A list with a NaN is ranked with float compares (what `>` does with a NaN is not an order).
 constexpr int RB_WARPS = 4, RB_THREADS = RB_WARPS * 32;
 
-__device__ void rank_by_counting_warp(const uint4 *__restrict__ adj4, int metric, uint32_t base, uint32_t deg,
-                                      uint32_t *__restrict__ rank) {
+__device__ void rank_by_counting_warp(const uint4 *__restrict__ adj4, int metric, uint32_t base, uint32_t deg, const RankPtrs &out) {
     for (uint32_t i = threadIdx.x & 31u; i < deg; i += 32) {
         const float mi = slot_metric(adj4, metric, base + i);
         uint32_t r = 0;
         for (uint32_t j = 0; j < deg; j++) { const float mj = slot_metric(adj4, metric, base + j); r += (mj > mi) || (mj == mi && j < i); }
-        rank[base + r] = base + i;
+        out.put_rank(metric, base + r, base + i);
     }
 }
 
@@ -419,7 +429,7 @@ struct RankSmem {
 
 template <int GROUP, int CAP>
 __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const uint4 *__restrict__ adj4, uint32_t metrics_mask, const RankPtrs &rank,
-                                                 uint32_t *__restrict__ canon, uint32_t base, uint32_t deg) {
+                                                 uint32_t base, uint32_t deg) {
     constexpr int PER = CAP / GROUP;
     static_assert(GROUP == 32 || GROUP == RB_THREADS, "a warp or the CTA per node");
     const uint32_t t = threadIdx.x % GROUP, w = threadIdx.x / GROUP, lane = threadIdx.x & 31u;
@@ -447,7 +457,7 @@ __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const
             const uint32_t nbr = adj4[base + i].x;
             uint32_t h = (nbr * 2654435761u) >> shift;
             while (hkey[h] != nbr) h = (h + 1) & (T - 1);
-            canon[base + i] = base + hval[h];
+            rank.put_canon(base + i, base + hval[h]);
         }
     }
 
@@ -465,8 +475,8 @@ __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const
         if (nan) s_nan[w] = 1;
         group_sync();
         if (s_nan[w]) {
-            if (GROUP == 32) rank_by_counting_warp(adj4, m, base, deg, rank.p[m]);
-            else rank_by_counting(adj4, m, base, deg, rank.p[m]);
+            if (GROUP == 32) rank_by_counting_warp(adj4, m, base, deg, rank);
+            else rank_by_counting(adj4, m, base, deg, rank);
             continue;
         }
         uint32_t *out = reinterpret_cast<uint32_t *>(bkt);   // positions are staged here once the buckets have been read
@@ -553,7 +563,7 @@ __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const
             for (int e = 0; e < PER; e++) if (t + GROUP * e < deg) out[r[e]] = t + GROUP * e;
         }
         group_sync();
-        for (uint32_t p = t; p < deg; p += GROUP) rank.p[m][base + p] = base + out[p];
+        for (uint32_t p = t; p < deg; p += GROUP) rank.put_rank(m, base + p, base + out[p]);
     }
 }
 
@@ -562,14 +572,14 @@ __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const
 // and half the unrolled iterations.
 template <int CAP, int LOW>
 __global__ void __launch_bounds__(RB_THREADS) rank_warp_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t metrics_mask,
-                                                               RankPtrs rank, uint32_t *__restrict__ canon, uint32_t node0, uint32_t nodes) {
+                                                               RankPtrs rank, uint32_t node0, uint32_t nodes) {
     __shared__ __align__(16) RankSmem<32, CAP> sm;
     const uint32_t xi = blockIdx.x * RB_WARPS + (threadIdx.x >> 5);
     if (xi >= nodes) return;
     const uint32_t x = node0 + xi;
     const uint32_t base = off[x], deg = off[x + 1] - base;
     if (deg <= static_cast<uint32_t>(LOW) || deg > static_cast<uint32_t>(CAP)) return;
-    rank_bucket_node<32, CAP>(sm, adj4, metrics_mask, rank, canon, base, deg);
+    rank_bucket_node<32, CAP>(sm, adj4, metrics_mask, rank, base, deg);
 }
 
 // The nodes of a chunk of RB_THREADS nodes whose lists have LOW + 1 .. CAP entries (few): found with one coalesced
@@ -591,7 +601,7 @@ __device__ __forceinline__ uint32_t select_long_nodes(const uint32_t *__restrict
 constexpr int RS_SMALL = 512, RS_MID = 4096;
 template <int CAP, int LOW>
 __global__ void __launch_bounds__(RB_THREADS) rank_cta_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t metrics_mask,
-                                                              RankPtrs rank, uint32_t *__restrict__ canon, uint32_t node0, uint32_t nodes) {
+                                                              RankPtrs rank, uint32_t node0, uint32_t nodes) {
     extern __shared__ __align__(16) unsigned char rank_cta_smem[];
     RankSmem<RB_THREADS, CAP> &sm = *reinterpret_cast<RankSmem<RB_THREADS, CAP> *>(rank_cta_smem);
     __shared__ uint32_t s_nodes[RB_THREADS], s_n;
@@ -599,14 +609,14 @@ __global__ void __launch_bounds__(RB_THREADS) rank_cta_kernel(const uint32_t *__
     for (uint32_t q = 0; q < n; q++) {
         const uint32_t x = s_nodes[q];
         const uint32_t base = off[x], deg = off[x + 1] - base;
-        rank_bucket_node<RB_THREADS, CAP>(sm, adj4, metrics_mask, rank, canon, base, deg);
+        rank_bucket_node<RB_THREADS, CAP>(sm, adj4, metrics_mask, rank, base, deg);
         __syncthreads();
     }
 }
 
 // Lists longer than RS_MID entries (hubs): counting with float compares from global memory.
 __global__ void __launch_bounds__(RK_THREADS) rank_long_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t metrics_mask,
-                                                               RankPtrs rank, uint32_t *__restrict__ canon, uint32_t node0, uint32_t nodes) {
+                                                               RankPtrs rank, uint32_t node0, uint32_t nodes) {
     __shared__ uint32_t s_nodes[RK_THREADS], s_n;
     const uint32_t n = select_long_nodes<RS_MID, 0>(off, node0, nodes, s_nodes, &s_n);
     for (uint32_t q = 0; q < n; q++) {
@@ -616,10 +626,10 @@ __global__ void __launch_bounds__(RK_THREADS) rank_long_kernel(const uint32_t *_
             const uint32_t ni = adj4[base + i].x;
             uint32_t j = 0;
             while (adj4[base + j].x != ni) j++;
-            canon[base + i] = base + j;
+            rank.put_canon(base + i, base + j);
         }
         for (int m = 0; m < 4; m++)
-            if (metrics_mask & (1u << m)) rank_by_counting(adj4, m, base, deg, rank.p[m]);
+            if (metrics_mask & (1u << m)) rank_by_counting(adj4, m, base, deg, rank);
     }
 }
 
@@ -882,7 +892,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             g.adj_pay.reserve(S + 1);
             pt.adj4[0] = g.adj4.p; pt.pay[0] = g.adj_pay.p;
         }
-        g.canon.reserve(S); g.node_exact.reserve(N);
+        g.node_exact.reserve(N);
         if (SL) HERA_LAUNCH(c, csr_scatter_kernel, div_up(SL, 256), 256, 0, SL, P, keys32, vals32, run_start, g.adj_off.p, before, pc, g.e_q.p, g.e_t.p, c.kept.qs.p,
                             c.kept.ts.p, c.kept.es.p, c.kept.os.p, g.node_anchor.p, pt);
         if (merged_by_reduce) {
@@ -896,10 +906,37 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         log.mark("exact");
         HERA_CUDA(cudaEventRecord(ev[2], c.stream));
 
-        // ---- rank permutations + canonical slots: each rank does its share of the nodes, the slices are all-gathered
+        // ---- rank permutations + canonical slots: each rank does its share of the nodes and stores the results into every
+        // rank's tables (peer memory); when the ranks cannot address each other's memory the slices are all-gathered instead
         c.h_counters.reserve(64 + ranks);
+        RankPtrs rp{};
+        rp.n = 1;
+        bool rank_pushed = false;
+        if (ranks > 1) {
+            void *ptrs[5][MAX_PEERS];
+            bool mapped = c.xch->shared_buffers(c, 2, (S + 1) * sizeof(uint32_t), ptrs[4]);
+            g.canon.borrow(static_cast<uint32_t *>(ptrs[4][me]), S + 1);
+            for (int m = 0; m < 4; m++) {
+                if (!(metrics_mask & (1u << m))) continue;
+                mapped = c.xch->shared_buffers(c, 3 + m, (S + 1) * sizeof(uint32_t), ptrs[m]) && mapped;
+                g.rank[m].borrow(static_cast<uint32_t *>(ptrs[m][me]), S + 1);
+            }
+            if (mapped) {
+                rank_pushed = true;
+                rp.n = ranks;
+                // own tables first: the stores that stay on this GPU are issued before the ones that cross NVLink
+                for (int k = 0; k < ranks; k++) {
+                    const int r = (me + k) % ranks;
+                    rp.canon[k] = static_cast<uint32_t *>(ptrs[4][r]);
+                    for (int m = 0; m < 4; m++) if (metrics_mask & (1u << m)) rp.p[m][k] = static_cast<uint32_t *>(ptrs[m][r]);
+                }
+                c.xch->all_gather_dev(c, c.counters.p, c.counters.p + 1, 1);   // no rank still reads the previous graph's tables
+            }
+        } else {
+            g.canon.reserve(S);
+        }
         cudaEvent_t cuts_ready = nullptr;
-        if (ranks > 1) {   // slot ranges of the ranks' node ranges: read now, needed (on the host) once the rank kernels are queued
+        if (ranks > 1 && !rank_pushed) {   // slot ranges of the ranks' node ranges: read now, needed (on the host) once the rank kernels are queued
             uint64_t *d_cut = tmp.get<uint64_t>(ranks + 1);
             HERA_LAUNCH(c, node_cut_kernel, 1, 64, 0, g.adj_off.p, N, ranks, d_cut);
             HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 40, d_cut, (ranks + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
@@ -908,31 +945,34 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         }
         const uint64_t n_lo = N * me / ranks, n_hi = N * (me + 1) / ranks;
         const unsigned my_nodes = static_cast<unsigned>(n_hi - n_lo);
-        RankPtrs rp{};
         for (int m = 0; m < 4; m++) {
             if (!(metrics_mask & (1u << m))) continue;
-            g.rank[m].reserve(S);
-            rp.p[m] = g.rank[m].p;
+            if (ranks == 1) g.rank[m].reserve(S);
+            if (!rank_pushed) rp.p[m][0] = g.rank[m].p;
             g.rank_ready[m] = true;
         }
+        if (!rank_pushed) rp.canon[0] = g.canon.p;
         if (my_nodes) {
-            HERA_LAUNCH(c, (rank_warp_kernel<256, 0>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp, g.canon.p,
+            HERA_LAUNCH(c, (rank_warp_kernel<256, 0>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
-            HERA_LAUNCH(c, (rank_warp_kernel<RS_SMALL, 256>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp, g.canon.p,
+            HERA_LAUNCH(c, (rank_warp_kernel<RS_SMALL, 256>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
             log.mark("rank small");
             constexpr size_t smem1 = sizeof(RankSmem<RB_THREADS, 1024>), smem2 = sizeof(RankSmem<RB_THREADS, RS_MID>);
             HERA_CUDA(cudaFuncSetAttribute(rank_cta_kernel<RS_MID, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem2)));
-            HERA_LAUNCH(c, (rank_cta_kernel<1024, RS_SMALL>), div_up(my_nodes, RB_THREADS), RB_THREADS, smem1, g.adj_off.p, g.adj4.p, metrics_mask, rp, g.canon.p,
+            HERA_LAUNCH(c, (rank_cta_kernel<1024, RS_SMALL>), div_up(my_nodes, RB_THREADS), RB_THREADS, smem1, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
-            HERA_LAUNCH(c, (rank_cta_kernel<RS_MID, 1024>), div_up(my_nodes, RB_THREADS), RB_THREADS, smem2, g.adj_off.p, g.adj4.p, metrics_mask, rp, g.canon.p,
+            HERA_LAUNCH(c, (rank_cta_kernel<RS_MID, 1024>), div_up(my_nodes, RB_THREADS), RB_THREADS, smem2, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
             log.mark("rank mid");
-            HERA_LAUNCH(c, rank_long_kernel, div_up(my_nodes, RK_THREADS), RK_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp, g.canon.p,
+            HERA_LAUNCH(c, rank_long_kernel, div_up(my_nodes, RK_THREADS), RK_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
         }
         log.mark("rank long");
-        if (ranks > 1) {
+        if (rank_pushed) {
+            c.xch->all_gather_dev(c, c.counters.p, c.counters.p + 1, 1);   // stream-ordered rendezvous: every rank's stores have been issued
+            log.mark("rank rendezvous");
+        } else if (ranks > 1) {
             HERA_CUDA(cudaEventSynchronize(cuts_ready));   // the slice boundaries left the device before the rank kernels started
             cudaEventDestroy(cuts_ready);
             const uint64_t *cut = c.h_counters.p + 40;
