@@ -757,6 +757,15 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
     TileFrame f = frame_tile(a, tile, tv[0], s_excl[0], s_tokens[0], s_tok_base, s_rec_off);
     __syncthreads();
     int p = 0;
+    // The kept rows of a tile are written ONE ITERATION AFTER the tile was parsed: its count is published to chain 2 at once,
+    // but the chain is resolved (and the rows stored at their file-order place) only while the next tile's successor is
+    // staged.  Resolving in the same iteration left ~5 us between a tile's publication and its successor's look-up; the
+    // CTAs of an SM slow each other down by more than that, so on a long text almost every look-up met a predecessor
+    // that had not published yet and 57 % of all warp samples sat at the barrier behind warp 0's spin (ncu, configs[3]).
+    // The parked row lives in registers / local memory (the compiler's choice) for the length of one iteration.
+    uint32_t prev_tile = a.tiles, prev_kept = 0, e_prev = 0;
+    bool keep_prev = false;
+    StagedRecord mine_prev;
 
     while (tile < a.tiles) {
         const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
@@ -822,16 +831,31 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
         __syncthreads();   // everybody is done with cur's text and record offsets; the ticket is visible
         const uint32_t after = s_ticket;
         if (after < a.tiles) stage_issue(a, after, tv[p]);
-        stage_and_service(after, p, next, s_tokens[p ^ 1], rounds ? a.tiles : tile, tile_kept);
+        stage_and_service(after, p, next, s_tokens[p ^ 1], prev_tile, prev_kept);   // chain 2 of the tile parsed one iteration ago
         TileFrame fn{};
         if (next < a.tiles) fn = frame_tile(a, next, tv[p ^ 1], s_excl[p ^ 1], s_tokens[p ^ 1], s_tok_base, s_rec_off);
-        if (!rounds && keep0) store_record(a.kept, a.kept_base + s_kept_base + e0, mine);
-        __syncthreads();   // record offsets of next are complete
+        if (keep_prev) store_record(a.kept, a.kept_base + s_kept_base + e_prev, mine_prev);
+        __syncthreads();   // record offsets of next are complete; s_kept_base has been read
+        prev_tile = rounds ? a.tiles : tile;
+        prev_kept = tile_kept;
+        keep_prev = !rounds && keep0;
+        e_prev = e0;
+        mine_prev = mine;
         tile = next;
         next = after;
         f = fn;
         p ^= 1;
     }
+    // the rows of the last tile this CTA parsed
+    if (warp == 0 && prev_tile < a.tiles) {
+        const unsigned long long base = chain_resolve(a.kept_state, prev_tile, prev_kept, chain_probe(a.kept_state, prev_tile));
+        if (lane == 0) {
+            s_kept_base = base;
+            if (prev_tile == a.tiles - 1) a.ctr->kept = base + prev_kept;
+        }
+    }
+    __syncthreads();
+    if (keep_prev) store_record(a.kept, a.kept_base + s_kept_base + e_prev, mine_prev);
 }
 
 // ---- warp-autonomous variant (hera_set_option "parse_variant" = 1) -----------------------------------------------------
