@@ -544,6 +544,7 @@ static_assert(PF_RAW_BYTES % 16 == 0, "mask words must stay aligned");
 struct TileView {
     uint8_t *raw;        // PF_RAW_BYTES
     uint16_t *nonws;     // PF_CHUNKS + 6
+    uint32_t mbar;       // shared-memory address of the buffer's mbarrier (bulk copies complete on it)
     __device__ __forceinline__ uint8_t *text() const { return raw + 16; }
     __device__ __forceinline__ const uint32_t *mask() const { return reinterpret_cast<const uint32_t *>(nonws) + 1; }  // word i = bytes [32 i, 32 i + 32)
 };
@@ -570,12 +571,35 @@ __device__ __forceinline__ uint32_t token_starts(const ParseArgs &a, const uint3
     return n;
 }
 
-// Stage A of a tile, first half: asynchronous 16-byte copies of tile + halo into shared memory (the data is
-// looked at later, after the CTA has done other work).
+// A tile whose window lies inside the readable text is staged with ONE bulk copy (cp.async.bulk, the TMA unit: UBLKCP in
+// SASS) issued by one thread and completing on the buffer's mbarrier; only the last tiles of a caller's buffer
+// (hera_graph_load_device_view: nothing behind byte n may be read) fall back to per-thread 16-byte cp.async with zero fill.
+__device__ __forceinline__ bool tile_is_bulk(const ParseArgs &a, uint32_t tile) {
+    return !(a.bare && static_cast<uint64_t>(tile) * PF_TILE + PF_WIN > a.n);
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
+    } while (!done);
+}
+
+// Stage A of a tile, first half: asynchronous copy of tile + halo into shared memory (the data is looked at later,
+// after the CTA has done other work).  Called by all threads after a barrier: nobody reads the buffer any more.
 __device__ __forceinline__ void stage_issue(const ParseArgs &a, uint32_t tile, const TileView &tv) {
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
     const uint8_t *src = a.text + tile_byte0;
     const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(tv.text()));
+    if (tile_is_bulk(a, tile)) {
+        if (threadIdx.x == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the generic-proxy reads of the old tile come before the async-proxy writes
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tv.mbar), "r"(static_cast<uint32_t>(PF_WIN)) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst), "l"(src), "r"(static_cast<uint32_t>(PF_WIN)), "r"(tv.mbar) : "memory");
+        }
+        return;
+    }
     if (a.bare && tile_byte0 + PF_WIN > a.n) {
         // the window reaches behind the caller's buffer: chunks that start behind byte n are not read at all (zero filled)
         for (int ch = threadIdx.x; ch < PF_CHUNKS; ch += PF_THREADS) {
@@ -592,10 +616,11 @@ __device__ __forceinline__ void stage_issue(const ParseArgs &a, uint32_t tile, c
 
 // Second half, part one: byte classification (every thread reads back the chunks it copied).  The mask may be
 // read by other threads after the next barrier.
-__device__ __forceinline__ void stage_classify(const ParseArgs &a, uint32_t tile, const TileView &tv) {
+__device__ __forceinline__ void stage_classify(const ParseArgs &a, uint32_t tile, const TileView &tv, uint32_t parity) {
     const uint32_t tid = threadIdx.x;
     const uint64_t tile_byte0 = static_cast<uint64_t>(tile) * PF_TILE;
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (tile_is_bulk(a, tile)) mbar_wait(tv.mbar, parity);   // the whole window has landed (any thread may read any chunk)
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
     const uint8_t *s_text = tv.text();
     if (a.bare && tile_byte0 + PF_WIN > a.n) {
         // bytes at and behind n (whatever the last chunk of the caller's buffer holds there, zeros behind it) are white space
@@ -691,6 +716,7 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
     __shared__ uint32_t s_tokens[2];
     __shared__ unsigned int s_ticket;
     __shared__ unsigned long long s_tok_base, s_kept_base;
+    __shared__ __align__(8) unsigned long long s_mbar[2];
 
     const uint32_t tid = threadIdx.x, lane = lane_id(), warp = warp_id();
     TileView tv[2];
@@ -698,14 +724,22 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
     for (int p = 0; p < 2; p++) {
         tv[p].raw = s_dyn + p * PF_BUF_BYTES;
         tv[p].nonws = reinterpret_cast<uint16_t *>(s_dyn + p * PF_BUF_BYTES + PF_RAW_BYTES);
+        tv[p].mbar = static_cast<uint32_t>(__cvta_generic_to_shared(&s_mbar[p]));
     }
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tv[0].mbar) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tv[1].mbar) : "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    uint32_t phases = 0;   // bit q: parity of the next bulk copy into buffer q (same in every thread)
     // Classifies the copied tile `t` in buffer q, counts its tokens and lets warp 0 publish the count; warp 0 also
     // resolves chain 1 of tile `n` (-> s_tok_base) and chain 2 of tile `c` with aggregate kc (-> s_kept_base) while
     // the other warps wait at the closing barrier.  Tiles >= a.tiles are skipped.
     auto stage_and_service = [&](uint32_t t, int q, uint32_t n, uint32_t n_tokens, uint32_t c, uint32_t kc) {
         uint32_t my_tokens = 0, incl = 0;
         if (t < a.tiles) {
-            stage_classify(a, t, tv[q]);
+            stage_classify(a, t, tv[q], (phases >> q) & 1u);
+            if (tile_is_bulk(a, t)) phases ^= 1u << q;
             __syncthreads();
             uint32_t starts[PF_WPT];
             my_tokens = token_starts(a, tv[q].mask(), static_cast<uint64_t>(t) * PF_TILE, tid, starts);
