@@ -276,7 +276,7 @@ def hot_path_step(h, pp, rr, cr, device_resident, read_back):
     n_unique = h.unique()
     t_paths = h.timer_stop()
     h.timer_start()
-    g = h.groups(pp)
+    g = h.groups(pp, copy=False)   # views into the library's host tables
     t_groups = h.timer_stop()
     d2h = 0
     if read_back:  # the result a caller consumes: groups/consensus tables + the unique paths
@@ -287,7 +287,7 @@ def hot_path_step(h, pp, rr, cr, device_resident, read_back):
             "exchange_ms": r1.exchange_ms + r2.exchange_ms, "parse_rr_ms": r1.parse_ms, "intern_ms": info.intern_ms, "csr_ms": info.csr_ms, "rank_ms": info.rank_ms,
             "records": r1.records + r2.records, "kept": r2.kept_total, "nodes": info.nodes, "walks": sum(s.walks for s in stats),
             "walk_entries": sum(s.steps for s in stats), "found": sum(s.found for s in stats), "walk_ms": [round(s.ms, 3) for s in stats],
-            "unique_paths": n_unique, "unique_nodes": 0, "pairs": len(g["pair_a1"]), "launches": h.launches - launches0, "d2h": d2h, "wall_ms": wall_ms,
+            "unique_paths": n_unique, "groups_device_ms": g["ms"], "pairs": len(g["pair_a1"]), "launches": h.launches - launches0, "d2h": d2h, "wall_ms": wall_ms,
             "rr_bytes": r1.bytes, "rr_kept": r1.kept}
 
 
@@ -377,7 +377,7 @@ def measure(key, args, torch, dist, capi, h, rank, world, dev, local_rank, with_
     res = {"key": key, "meta": meta, "stage": stage, "e2e_wall_ms": s[8] / args.steps, "e2e_graph_ms": s[9] / args.steps, "e2e_h2d_ms": s[10] / args.steps,
            "parse_leg_ms": s[11], "parse_leg_bytes": leg_bytes, "parse_leg_kept": leg_kept,
            "launches": counts[0].item(), "h2d_bytes": counts[1].item(), "d2h_bytes": counts[2].item(),
-           "parse_rr_ms": [round(x["parse_rr_ms"], 3) for x in dev_steps],
+           "parse_rr_ms": [round(x["parse_rr_ms"], 3) for x in dev_steps], "groups_device_ms": round(statistics.mean(x["groups_device_ms"] for x in dev_steps), 3),
            "records": s0["records"], "kept": s0["kept"], "nodes": s0["nodes"], "walks": s0["walks"], "walk_entries": s0["walk_entries"], "found": s0["found"],
            "unique_paths": s0["unique_paths"], "pairs": s0["pairs"], "walk_ms": s0["walk_ms"], "gather_gbs": gather_gbs, "gather_ms": gather_ms,
            "clocks": clocks.summary(), "digest": digest, "ranks_agree": ranks_agree, "golden_matches": matches, "golden_note": golden.get("verified"),
@@ -504,7 +504,7 @@ def main():
             "paths_per_s": r["walks"] / (st["paths_ms"] * 1e-3), "accepted_paths_per_s": r["found"] / (st["paths_ms"] * 1e-3),
             "unique_paths_per_step": r["unique_paths"],
             "stages_ms_per_step": st,
-            "parse_rr_ms_per_step": r["parse_rr_ms"],
+            "parse_rr_ms_per_step": r["parse_rr_ms"], "groups_device_ms": r["groups_device_ms"],
             "per_step": {"records": r["records"], "paf_bytes": r["bytes"], "kept_overlaps": r["kept"], "nodes": r["nodes"], "walks": r["walks"],
                          "adjacency_entries_examined": r["walk_entries"], "anchor_pairs": r["pairs"], "walk_kernel_ms": r["walk_ms"]},
             "gpu_launches": int(r["launches"]),

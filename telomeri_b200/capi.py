@@ -366,16 +366,17 @@ class Hera:
                 "logged": _arr(v.logged_index, v.logged, np.uint32), "fasta": C.string_at(v.fasta, v.fasta_bytes),
                 "sequence_length": int(v.sequence_length), "ms": float(v.ms)}
 
-    def groups(self, pp):
+    def groups(self, pp, copy=True):
+        """copy=False: views into the library's host tables (valid until the next groups call)."""
         v = GroupsView()
         self._check(self.lib.hera_groups(self.h, C.byref(pp), C.byref(v)))
         K, G = v.pairs, v.groups
         return {
-            "pair_a1": _arr(v.pair_a1, K, np.uint32), "pair_a2": _arr(v.pair_a2, K, np.uint32), "pair_off": _arr(v.pair_off, K + 1, np.uint64),
-            "pair_sorted": _arr(v.pair_sorted, v.sorted_total, np.uint32), "grp_pair": _arr(v.grp_pair, G, np.uint32),
-            "grp_size0": _arr(v.grp_size0, G, np.uint32), "grp_pig_off": _arr(v.grp_pig_off, G + 1, np.uint64),
-            "grp_pig": _arr(v.grp_pig, v.pig_total, np.uint32), "grp_consensus": _arr(v.grp_consensus, G, np.int64),
-            "grp_valid": _arr(v.grp_valid, G, np.int32), "pair_consensus": _arr(v.pair_consensus, K, np.int64), "ms": float(v.ms),
+            "pair_a1": _arr(v.pair_a1, K, np.uint32, copy), "pair_a2": _arr(v.pair_a2, K, np.uint32, copy), "pair_off": _arr(v.pair_off, K + 1, np.uint64, copy),
+            "pair_sorted": _arr(v.pair_sorted, v.sorted_total, np.uint32, copy), "grp_pair": _arr(v.grp_pair, G, np.uint32, copy),
+            "grp_size0": _arr(v.grp_size0, G, np.uint32, copy), "grp_pig_off": _arr(v.grp_pig_off, G + 1, np.uint64, copy),
+            "grp_pig": _arr(v.grp_pig, v.pig_total, np.uint32, copy), "grp_consensus": _arr(v.grp_consensus, G, np.int64, copy),
+            "grp_valid": _arr(v.grp_valid, G, np.int32, copy), "pair_consensus": _arr(v.pair_consensus, K, np.int64, copy), "ms": float(v.ms),
         }
 
 

@@ -193,6 +193,7 @@ struct Ctx {
         std::vector<int64_t> grp_consensus, pair_consensus;
         std::vector<int32_t> grp_valid;
     } grm;
+    HBuf<uint32_t> grp_stage;    // pinned staging of hera_groups' device results
     bool groups_valid = false;   // grm describes the current paths
     struct ScaffoldMirror {
         std::vector<uint32_t> nodes, slots, logged;

@@ -363,9 +363,9 @@ __device__ __forceinline__ float slot_metric(const uint4 *__restrict__ adj4, int
 //              `>` sees them).  A list with a NaN metric, or longer than CAP, is ranked by counting instead:
 //              position of slot i = #{j : m[j] > m[i]} + #{j < i : m[j] == m[i]}  (what `>` on NaN gives).
 // This kernel takes the lists longer than LOW entries (the short ones go to rank_small_kernel below).
-// Where the permutations and canonical slots go: this rank's tables and -- sharded runs -- the same tables of every other
-// rank (peer memory): a rank computes the lists of its share of the nodes and stores the results everywhere, so the
-// transfer over NVLink overlaps the sorting instead of following it as a gather.
+// Where the permutations and canonical slots go.  (The kernels can store into several ranks' tables at once; measured on
+// 8 GPUs the 4-byte peer stores of the sorting warps reached 220 GB/s, so a rank now writes its own tables and
+// slice_push_kernel copies the finished slices to the peers with 16-byte stores.)
 struct RankPtrs {
     uint32_t *p[4][MAX_PEERS];
     uint32_t *canon[MAX_PEERS];
@@ -582,14 +582,17 @@ __global__ void __launch_bounds__(RB_THREADS) rank_warp_kernel(const uint32_t *_
     rank_bucket_node<32, CAP>(sm, adj4, metrics_mask, rank, base, deg);
 }
 
-// The nodes of a chunk of RB_THREADS nodes whose lists have LOW + 1 .. CAP entries (few): found with one coalesced
-// read of the offsets, then handled one after the other by the whole CTA.
+// The nodes of a chunk of RANK_CHUNK consecutive nodes whose lists have LOW + 1 .. CAP entries, handled one after the other
+// by the whole CTA.  The chunk is small: nodes with long lists come in runs (reads of one repeat copy are numbered
+// consecutively), and a CTA that had to work through 128 of them was the critical path of the whole stage (4 ms whatever
+// the number of nodes).
+constexpr int RANK_CHUNK = 8;
 template <int LOW, int CAP>
 __device__ __forceinline__ uint32_t select_long_nodes(const uint32_t *__restrict__ off, uint32_t node0, uint32_t nodes, uint32_t *s_nodes, uint32_t *s_n) {
     if (threadIdx.x == 0) *s_n = 0;
     __syncthreads();
-    const uint32_t xi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (xi < nodes) {
+    const uint32_t xi = blockIdx.x * RANK_CHUNK + threadIdx.x;
+    if (threadIdx.x < RANK_CHUNK && xi < nodes) {
         const uint32_t d = off[node0 + xi + 1] - off[node0 + xi];
         if (d > static_cast<uint32_t>(LOW) && (CAP == 0 || d <= static_cast<uint32_t>(CAP))) s_nodes[atomicAdd(s_n, 1u)] = node0 + xi;
     }
@@ -604,7 +607,7 @@ __global__ void __launch_bounds__(RB_THREADS) rank_cta_kernel(const uint32_t *__
                                                               RankPtrs rank, uint32_t node0, uint32_t nodes) {
     extern __shared__ __align__(16) unsigned char rank_cta_smem[];
     RankSmem<RB_THREADS, CAP> &sm = *reinterpret_cast<RankSmem<RB_THREADS, CAP> *>(rank_cta_smem);
-    __shared__ uint32_t s_nodes[RB_THREADS], s_n;
+    __shared__ uint32_t s_nodes[RANK_CHUNK], s_n;
     const uint32_t n = select_long_nodes<LOW, CAP>(off, node0, nodes, s_nodes, &s_n);
     for (uint32_t q = 0; q < n; q++) {
         const uint32_t x = s_nodes[q];
@@ -617,7 +620,7 @@ __global__ void __launch_bounds__(RB_THREADS) rank_cta_kernel(const uint32_t *__
 // Lists longer than RS_MID entries (hubs): counting with float compares from global memory.
 __global__ void __launch_bounds__(RK_THREADS) rank_long_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t metrics_mask,
                                                                RankPtrs rank, uint32_t node0, uint32_t nodes) {
-    __shared__ uint32_t s_nodes[RK_THREADS], s_n;
+    __shared__ uint32_t s_nodes[RANK_CHUNK], s_n;
     const uint32_t n = select_long_nodes<RS_MID, 0>(off, node0, nodes, s_nodes, &s_n);
     for (uint32_t q = 0; q < n; q++) {
         const uint32_t x = s_nodes[q];
@@ -633,6 +636,34 @@ __global__ void __launch_bounds__(RK_THREADS) rank_long_kernel(const uint32_t *_
     }
 }
 
+
+// The finished slices of this rank's node range (canon, rank permutations: contiguous slots [off[n_lo], off[n_hi])) go to
+// the same place in every other rank's tables: 16-byte loads from local memory, 16-byte stores into peer memory over
+// NVLink.  blockIdx.y = table, blockIdx.z = peer (visited in ring order so that no GPU is everybody's target at once).
+struct SlicePush {
+    const uint32_t *src[5];
+    uint32_t *dst[5][MAX_PEERS];
+    int tables, peers;
+};
+__global__ void __launch_bounds__(256) slice_push_kernel(SlicePush a, const uint32_t *__restrict__ off, uint32_t n_lo, uint32_t n_hi) {
+    const uint64_t lo = off[n_lo], hi = off[n_hi];
+    const uint32_t *src = a.src[blockIdx.y];
+    uint32_t *dst = a.dst[blockIdx.y][blockIdx.z];
+    const uint64_t up = (lo + 3) & ~3ull, down = hi & ~3ull;
+    const uint64_t head = up < hi ? up : hi, tail = down > head ? down : head;   // [head, tail) is 16-byte aligned on both sides
+    const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x, t = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    for (uint64_t i = lo + t; i < head; i += stride) dst[i] = src[i];
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+    uint64_t q = head / 4 + t;
+    const uint64_t q_end = tail / 4;
+    for (; q + 3 * stride < q_end; q += 4 * stride) {   // four loads in flight per thread
+        const uint4 v0 = s4[q], v1 = s4[q + stride], v2 = s4[q + 2 * stride], v3 = s4[q + 3 * stride];
+        d4[q] = v0; d4[q + stride] = v1; d4[q + 2 * stride] = v2; d4[q + 3 * stride] = v3;
+    }
+    for (; q < q_end; q += stride) d4[q] = s4[q];
+    for (uint64_t i = tail + t; i < hi; i += stride) dst[i] = src[i];
+}
 
 static int bits_for(uint64_t n) {
     int b = 1;
@@ -912,6 +943,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         RankPtrs rp{};
         rp.n = 1;
         bool rank_pushed = false;
+        SlicePush push{};
         if (ranks > 1) {
             void *ptrs[5][MAX_PEERS];
             bool mapped = c.xch->shared_buffers(c, 2, (S + 1) * sizeof(uint32_t), ptrs[4]);
@@ -923,12 +955,15 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             }
             if (mapped) {
                 rank_pushed = true;
-                rp.n = ranks;
-                // own tables first: the stores that stay on this GPU are issued before the ones that cross NVLink
-                for (int k = 0; k < ranks; k++) {
+                push.src[0] = static_cast<uint32_t *>(ptrs[4][me]);
+                push.tables = 1;
+                for (int m = 0; m < 4; m++) if (metrics_mask & (1u << m)) push.src[push.tables++] = static_cast<uint32_t *>(ptrs[m][me]);
+                push.peers = ranks - 1;
+                for (int k = 1; k < ranks; k++) {   // ring order: rank + 1 first
                     const int r = (me + k) % ranks;
-                    rp.canon[k] = static_cast<uint32_t *>(ptrs[4][r]);
-                    for (int m = 0; m < 4; m++) if (metrics_mask & (1u << m)) rp.p[m][k] = static_cast<uint32_t *>(ptrs[m][r]);
+                    int t = 0;
+                    push.dst[t++][k - 1] = static_cast<uint32_t *>(ptrs[4][r]);
+                    for (int m = 0; m < 4; m++) if (metrics_mask & (1u << m)) push.dst[t++][k - 1] = static_cast<uint32_t *>(ptrs[m][r]);
                 }
                 c.xch->all_gather_dev(c, c.counters.p, c.counters.p + 1, 1);   // no rank still reads the previous graph's tables
             }
@@ -948,10 +983,10 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         for (int m = 0; m < 4; m++) {
             if (!(metrics_mask & (1u << m))) continue;
             if (ranks == 1) g.rank[m].reserve(S);
-            if (!rank_pushed) rp.p[m][0] = g.rank[m].p;
+            rp.p[m][0] = g.rank[m].p;
             g.rank_ready[m] = true;
         }
-        if (!rank_pushed) rp.canon[0] = g.canon.p;
+        rp.canon[0] = g.canon.p;
         if (my_nodes) {
             HERA_LAUNCH(c, (rank_warp_kernel<256, 0>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
@@ -960,16 +995,18 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             log.mark("rank small");
             constexpr size_t smem1 = sizeof(RankSmem<RB_THREADS, 1024>), smem2 = sizeof(RankSmem<RB_THREADS, RS_MID>);
             HERA_CUDA(cudaFuncSetAttribute(rank_cta_kernel<RS_MID, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem2)));
-            HERA_LAUNCH(c, (rank_cta_kernel<1024, RS_SMALL>), div_up(my_nodes, RB_THREADS), RB_THREADS, smem1, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, (rank_cta_kernel<1024, RS_SMALL>), div_up(my_nodes, RANK_CHUNK), RB_THREADS, smem1, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
-            HERA_LAUNCH(c, (rank_cta_kernel<RS_MID, 1024>), div_up(my_nodes, RB_THREADS), RB_THREADS, smem2, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, (rank_cta_kernel<RS_MID, 1024>), div_up(my_nodes, RANK_CHUNK), RB_THREADS, smem2, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
             log.mark("rank mid");
-            HERA_LAUNCH(c, rank_long_kernel, div_up(my_nodes, RK_THREADS), RK_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, rank_long_kernel, div_up(my_nodes, RANK_CHUNK), RK_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
         }
         log.mark("rank long");
         if (rank_pushed) {
+            if (my_nodes) HERA_LAUNCH(c, slice_push_kernel, dim3(148, push.tables, push.peers), 256, 0, push, g.adj_off.p, static_cast<uint32_t>(n_lo), static_cast<uint32_t>(n_hi));
+            log.mark("rank push");
             c.xch->all_gather_dev(c, c.counters.p, c.counters.p + 1, 1);   // stream-ordered rendezvous: every rank's stores have been issued
             log.mark("rank rendezvous");
         } else if (ranks > 1) {

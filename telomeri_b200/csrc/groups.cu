@@ -257,6 +257,15 @@ __global__ void pair_offsets_kernel(uint32_t paths, const uint8_t *__restrict__ 
     if (i < paths && head[i]) { pair_off[head_scan[i]] = i; pair_key[head_scan[i]] = keys[i]; }
 }
 
+// Longest run of equal keys (= paths of the largest anchor pair): sizes the shared memory of group_pairs_kernel.
+__global__ void pair_max_kernel(uint32_t paths, const uint8_t *__restrict__ head, uint32_t *__restrict__ out_max) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= paths || !head[i]) return;
+    uint32_t e = i + 1;
+    while (e < paths && !head[e]) e++;
+    atomicMax(out_max, e - i);
+}
+
 static int bits_for_u64(uint64_t n) {
     int b = 1;
     while ((1ull << b) < n) b++;
@@ -266,7 +275,9 @@ static int bits_for_u64(uint64_t n) {
 void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out) {
     const PathStore &ps = c.uniq_ready ? c.uniq : c.all;
     auto &m = c.grm;
-    m = Ctx::GroupMirror{};
+    // (cleared, not rebuilt: the vectors keep their capacity from call to call)
+    m.pair_a1.clear(); m.pair_a2.clear(); m.pair_sorted.clear(); m.grp_pair.clear(); m.grp_size0.clear(); m.grp_pig.clear();
+    m.pair_off.clear(); m.grp_pig_off.clear(); m.grp_consensus.clear(); m.pair_consensus.clear(); m.grp_valid.clear();
     *out = hera_groups_view{};
     HERA_REQUIRE(pp.window_size > 0, 11, "window_size must be positive");
     HERA_REQUIRE(ps.paths < (1ull << 31), 12, "too many paths");
@@ -286,15 +297,18 @@ void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out) {
         uint32_t *keys = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t))), *vals = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t)));
         uint32_t *keys_alt = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t))), *vals_alt = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t)));
         uint8_t *head = static_cast<uint8_t *>(alloc(P));
-        uint32_t *head_scan = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t))), *d_pairs = static_cast<uint32_t *>(alloc(sizeof(uint32_t)));
+        uint32_t *head_scan = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t))), *d_pairs = static_cast<uint32_t *>(alloc(2 * sizeof(uint32_t)));   // [0] pairs [1] largest pair
         HERA_LAUNCH(c, anchor_rank_kernel, div_up(A, 128), 128, 0, A, c.g.anchor_ids.p, rank_of_node);
         HERA_LAUNCH(c, pair_keys_kernel, div_up(P, 256), 256, 0, P, A, ps.off.p, ps.node.p, rank_of_node, keys, vals);
         radix_sort_pairs(c, keys, vals, keys_alt, vals_alt, P, bits_for_u64(static_cast<uint64_t>(A) * A));
         HERA_LAUNCH(c, pair_heads_kernel, div_up(P, 256), 256, 0, P, keys, head);
         exclusive_scan_u8_to_u32(c, head, P, head_scan, d_pairs);
-        uint32_t K = 0;
-        HERA_CUDA(cudaMemcpyAsync(&K, d_pairs, sizeof(K), cudaMemcpyDeviceToHost, c.stream));
+        HERA_CUDA(cudaMemsetAsync(d_pairs + 1, 0, sizeof(uint32_t), c.stream));
+        HERA_LAUNCH(c, pair_max_kernel, div_up(P, 256), 256, 0, P, head, d_pairs + 1);
+        uint32_t h_pairs[2] = {0, 0};
+        HERA_CUDA(cudaMemcpyAsync(h_pairs, d_pairs, sizeof(h_pairs), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
+        const uint32_t K = h_pairs[0], max_pair = h_pairs[1];
         uint32_t *pair_off = static_cast<uint32_t *>(alloc((K + 1) * sizeof(uint32_t))), *pair_key = static_cast<uint32_t *>(alloc(K * sizeof(uint32_t)));
         HERA_LAUNCH(c, pair_offsets_kernel, div_up(P, 256), 256, 0, P, head, head_scan, keys, pair_off, pair_key, K);
 
@@ -308,28 +322,38 @@ void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out) {
         a.grp_count = static_cast<uint32_t *>(alloc(K * 4)); a.grp_size0 = static_cast<uint32_t *>(alloc(P * 4)); a.grp_kept = static_cast<uint32_t *>(alloc(P * 4));
         a.grp_cons = static_cast<long long *>(alloc(P * 8)); a.grp_valid = static_cast<int *>(alloc(P * 4)); a.pig = static_cast<uint32_t *>(alloc(P * 4));
         a.pair_cons = static_cast<long long *>(alloc(K * 8));
-        a.smem_items = std::min<uint32_t>(P, 10240);   // 16 B per path, up to 160 KB per CTA; larger pairs sort in global memory
+        // 16 B per path of the LARGEST pair, up to 160 KB per CTA (larger pairs sort in global memory): sized for all paths, the
+        // 46 844 pairs of configs[3] (26 paths on average) ran one CTA per SM
+        a.smem_items = std::min<uint32_t>(std::max<uint32_t>(max_pair, 32), 10240);
         const size_t smem = static_cast<size_t>(a.smem_items) * sizeof(SortItem);
         HERA_CUDA(cudaFuncSetAttribute(group_pairs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         HERA_LAUNCH(c, group_pairs_kernel, K, GP_THREADS, smem, a);
         HERA_CUDA(cudaEventRecord(ev1, c.stream));
 
         // flatten on the host (marshalling only)
-        std::vector<uint32_t> h_pair_off(K + 1), h_pair_key(K), h_ids(P), h_cnt(K), h_size0(P), h_kept(P), h_pig(P), h_anchor(A);
-        std::vector<long long> h_cons(P), h_pair_cons(K);
-        std::vector<int> h_valid(P);
+        // one pinned staging block (pageable destinations would make every copy a synchronous staged one: 34 MB on configs[3])
+        auto words = [](uint64_t n) { return (n + 1) / 2 * 2; };   // keep the 64-bit arrays aligned
+        const uint64_t w_total = words(K + 1) + words(K) + words(P) + words(K) + 3 * words(P) + words(A) + 2 * P + 2 * K + words(P);
+        c.grp_stage.reserve(w_total);
+        uint32_t *w = c.grp_stage.p;
+        auto take = [&](uint64_t n) { uint32_t *q = w; w += words(n); return q; };
+        uint32_t *h_pair_off = take(K + 1), *h_pair_key = take(K), *h_ids = take(P), *h_cnt = take(K), *h_size0 = take(P), *h_kept = take(P), *h_pig = take(P),
+                 *h_anchor = take(A);
+        long long *h_cons = reinterpret_cast<long long *>(take(2 * P)), *h_pair_cons = reinterpret_cast<long long *>(take(2 * K));
+        int *h_valid = reinterpret_cast<int *>(take(P));
         auto get = [&](void *dst, const void *src, size_t bytes) { if (bytes) HERA_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.stream)); };
-        get(h_pair_off.data(), pair_off, (K + 1) * 4); get(h_pair_key.data(), pair_key, K * 4); get(h_ids.data(), vals, P * 4);
-        get(h_cnt.data(), a.grp_count, K * 4); get(h_size0.data(), a.grp_size0, P * 4); get(h_kept.data(), a.grp_kept, P * 4);
-        get(h_pig.data(), a.pig, P * 4); get(h_cons.data(), a.grp_cons, P * 8); get(h_valid.data(), a.grp_valid, P * 4);
-        get(h_pair_cons.data(), a.pair_cons, K * 8); get(h_anchor.data(), c.g.anchor_ids.p, A * 4);
+        get(h_pair_off, pair_off, (K + 1) * 4); get(h_pair_key, pair_key, K * 4); get(h_ids, vals, P * 4);
+        get(h_cnt, a.grp_count, K * 4); get(h_size0, a.grp_size0, P * 4); get(h_kept, a.grp_kept, P * 4);
+        get(h_pig, a.pig, P * 4); get(h_cons, a.grp_cons, P * 8); get(h_valid, a.grp_valid, P * 4);
+        get(h_pair_cons, a.pair_cons, K * 8); get(h_anchor, c.g.anchor_ids.p, A * 4);
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         HERA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
         cudaEventDestroy(ev0);
         cudaEventDestroy(ev1);
         for (void *p : tmp) HERA_CUDA(cudaFreeAsync(p, c.stream));
 
-        m.pair_sorted = h_ids;
+        m.pair_sorted.assign(h_ids, h_ids + P);
+        m.pair_a1.reserve(K); m.pair_a2.reserve(K); m.pair_off.reserve(K + 1); m.pair_consensus.reserve(K); m.grp_pig.reserve(P);
         for (uint32_t k = 0; k < K; k++) {
             m.pair_a1.push_back(h_anchor[h_pair_key[k] / A]);
             m.pair_a2.push_back(h_anchor[h_pair_key[k] % A]);
@@ -340,7 +364,7 @@ void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out) {
             for (uint32_t g = 0; g < h_cnt[k]; g++) {
                 m.grp_pair.push_back(k);
                 m.grp_size0.push_back(h_size0[b + g]);
-                m.grp_pig.insert(m.grp_pig.end(), h_pig.begin() + b + gb, h_pig.begin() + b + gb + h_kept[b + g]);
+                m.grp_pig.insert(m.grp_pig.end(), h_pig + b + gb, h_pig + b + gb + h_kept[b + g]);
                 m.grp_pig_off.push_back(m.grp_pig.size());
                 m.grp_consensus.push_back(h_cons[b + g]);
                 m.grp_valid.push_back(h_valid[b + g]);

@@ -19,51 +19,58 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t *__r
     for (int i = threadIdx.x; i < RS_BINS; i += RS_THREADS) hist[static_cast<uint64_t>(i) * gridDim.x + blockIdx.x] = h[i];
 }
 
-// Stable scatter: elements of a tile keep their relative order inside each digit.  Ranking is
-// staged in shared memory: per chunk of RS_THREADS elements every warp ranks its lanes with
-// match.any, warps are ordered through a per-warp digit table, chunks through a running count.
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+// Stable scatter: elements of a tile keep their relative order inside each digit.  Every warp owns a CONTIGUOUS 512-key
+// stretch of the tile and ranks it on its own: per round of 32 keys the lanes with the same digit find each other with
+// match.any, the lowest of them advances the warp's private digit counter (shared memory, no atomics) and hands the
+// old value back, so a key's place among the warp's keys of its digit is known without any CTA-wide barrier.  One pass
+// over the digit table (thread d = digit d) then turns the per-warp counts into destinations -- tile base from the
+// scanned histogram + keys of earlier warps -- and the keys, still in registers, go out.  Three barriers per tile.
+__global__ void __launch_bounds__(RS_THREADS, 4) rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                                                                 uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n,
                                                                 int shift, const uint32_t *__restrict__ hist_scanned) {
-    __shared__ uint32_t run[RS_BINS];                 // global destination of the next key of each digit
-    __shared__ uint16_t warp_cnt[RS_WARPS][RS_BINS];  // per-warp digit counts of the current chunk
-    for (int i = threadIdx.x; i < RS_BINS; i += RS_THREADS) run[i] = hist_scanned[static_cast<uint64_t>(i) * gridDim.x + blockIdx.x];
+    __shared__ uint32_t warp_cnt[RS_WARPS][RS_BINS];   // per warp: keys of each digit seen so far, then destination of the warp's first key of the digit
+    static_assert(RS_BINS == RS_THREADS, "one thread per digit in the prefix pass");
     for (int i = threadIdx.x; i < RS_WARPS * RS_BINS; i += RS_THREADS) (&warp_cnt[0][0])[i] = 0;
     __syncthreads();
-    const uint64_t base = static_cast<uint64_t>(blockIdx.x) * RS_TILE;
     const uint32_t lane = lane_id(), warp = warp_id();
-    for (int k = 0; k < RS_ITEMS; k++) {
-        const uint64_t i = base + static_cast<uint64_t>(k) * RS_THREADS + threadIdx.x;
-        const bool live = i < n;
-        uint32_t key = 0, val = 0, d = RS_BINS;  // dead lanes get a digit nobody else has
-        if (live) {
-            key = keys_in[i];
-            val = vals_in[i];
-            d = (key >> shift) & (RS_BINS - 1);
-        }
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const uint32_t rank_in_warp = __popc(peers & ((1u << lane) - 1u));
-        if (live && rank_in_warp == 0) warp_cnt[warp][d] = static_cast<uint16_t>(__popc(peers));
-        __syncthreads();
-        uint32_t dst = 0;
-        if (live) {
-            uint32_t before = 0;
-            for (uint32_t w = 0; w < warp; w++) before += warp_cnt[w][d];
-            dst = run[d] + before + rank_in_warp;
-        }
-        __syncthreads();
-        // one thread per digit folds the chunk into the running count and clears the table
-        for (int b = threadIdx.x; b < RS_BINS; b += RS_THREADS) {
-            uint32_t s = 0;
+    const uint64_t base = static_cast<uint64_t>(blockIdx.x) * RS_TILE + static_cast<uint64_t>(warp) * (RS_ITEMS * 32);
+    uint32_t key[RS_ITEMS], val[RS_ITEMS];
+    uint16_t place[RS_ITEMS];
 #pragma unroll
-            for (int w = 0; w < RS_WARPS; w++) { s += warp_cnt[w][b]; warp_cnt[w][b] = 0; }
-            run[b] += s;
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const uint64_t i = base + static_cast<uint64_t>(k) * 32 + lane;
+        key[k] = i < n ? keys_in[i] : 0u;
+        val[k] = i < n ? vals_in[i] : 0u;
+    }
+    uint32_t *mine = warp_cnt[warp];
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const uint64_t i = base + static_cast<uint64_t>(k) * 32 + lane;
+        const uint32_t d = i < n ? ((key[k] >> shift) & (RS_BINS - 1)) : RS_BINS + lane;   // dead lanes match nobody
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (static_cast<int>(lane) == leader && i < n) { old = mine[d]; mine[d] = old + __popc(peers); }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        place[k] = static_cast<uint16_t>(old + __popc(peers & ((1u << lane) - 1u)));
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // digit d: destinations of the warps' first keys
+        const uint32_t d = threadIdx.x;
+        uint32_t run = hist_scanned[static_cast<uint64_t>(d) * gridDim.x + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) { const uint32_t t = warp_cnt[w][d]; warp_cnt[w][d] = run; run += t; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const uint64_t i = base + static_cast<uint64_t>(k) * 32 + lane;
+        if (i < n) {
+            const uint32_t dst = mine[(key[k] >> shift) & (RS_BINS - 1)] + place[k];
+            keys_out[dst] = key[k];
+            vals_out[dst] = val[k];
         }
-        if (live) {
-            keys_out[dst] = key;
-            vals_out[dst] = val;
-        }
-        __syncthreads();
     }
 }
 
