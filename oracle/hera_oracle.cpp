@@ -4,6 +4,9 @@
 #include "hera_oracle.hpp"
 
 #include <algorithm>
+#include <atomic>
+#include <cstdlib>
+#include <thread>
 #include <cfloat>
 #include <climits>
 #include <cmath>
@@ -286,17 +289,69 @@ int64_t path_length(const Graph &g, const std::vector<uint32_t> &nodes, const st
     return len;
 }
 
+// ---- running the anchors of a build call on several host threads (test infrastructure for the full-size configurations:
+// HERA_ORACLE_THREADS, default 1).  The walks of different anchors are independent in the reference except for the shared
+// std::mt19937 stream, so the mt19937 mode always runs on one thread; results are appended in anchor order either way.
+namespace {
+struct AnchorOut {
+    PathSet ps;
+    McStats st;
+    uint64_t found = 0;
+};
+
+int oracle_threads() {
+    const char *v = std::getenv("HERA_ORACLE_THREADS");
+    const int n = v ? std::atoi(v) : 1;
+    return n < 1 ? 1 : n;
+}
+
+void append_set(PathSet &dst, const PathSet &src) {
+    const uint64_t base = dst.nodes.size();
+    dst.nodes.insert(dst.nodes.end(), src.nodes.begin(), src.nodes.end());
+    dst.slots.insert(dst.slots.end(), src.slots.begin(), src.slots.end());
+    for (size_t i = 1; i < src.off.size(); i++) dst.off.push_back(base + src.off[i]);
+    dst.len.insert(dst.len.end(), src.len.begin(), src.len.end());
+}
+
+template <typename Body>
+uint64_t for_each_anchor(const Graph &g, int threads, PathSet &ps, McStats *stats, Body body) {
+    std::vector<uint32_t> anchors;
+    for (uint32_t x = 0; x < g.nodes(); x++) if (g.node_anchor[x]) anchors.push_back(x);
+    std::vector<AnchorOut> out(anchors.size());
+    std::atomic<size_t> next{0};
+    auto work = [&]() {
+        std::vector<uint8_t> visited(g.nodes(), 0);
+        for (size_t i = next.fetch_add(1); i < anchors.size(); i = next.fetch_add(1)) body(anchors[i], out[i], visited);
+    };
+    if (threads <= 1) {
+        work();
+    } else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; t++) pool.emplace_back(work);
+        for (auto &t : pool) t.join();
+    }
+    uint64_t found = 0;
+    for (AnchorOut &o : out) {
+        append_set(ps, o.ps);
+        found += o.found;
+        if (stats) {
+            stats->draws_per_walk.insert(stats->draws_per_walk.end(), o.st.draws_per_walk.begin(), o.st.draws_per_walk.end());
+            stats->draws.insert(stats->draws.end(), o.st.draws.begin(), o.st.draws.end());
+        }
+    }
+    return found;
+}
+}  // namespace
+
 uint64_t walk_monte_carlo(const Graph &g, int metric, const PathParams &pp, RngMode mode, uint64_t seed, PathSet &ps, McStats *stats) {
     std::mt19937 engine;  // default seed 5489, one per call (src/PathManager.cpp:13)
     std::uniform_real_distribution<> unit(0., 1.);
-    const size_t N = g.nodes();
-    uint64_t found = 0;
-    std::vector<uint8_t> visited;
-    std::vector<uint32_t> nodes, slots, cand;
-    for (uint32_t anchor = 0; anchor < N; anchor++) {
-        if (!g.node_anchor[anchor]) continue;
+    const int threads = mode == RNG_MT19937 ? 1 : oracle_threads();
+    return for_each_anchor(g, threads, ps, stats, [&](uint32_t anchor, AnchorOut &o, std::vector<uint8_t> &visited) {
+        std::vector<uint32_t> nodes, slots, cand, touched;
         for (int attempt = 0; attempt < pp.rebuild_attempts; attempt++) {
-            visited.assign(N, 0);
+            for (uint32_t x : touched) visited[x] = 0;   // (the reference allocates a fresh vector<bool>(N) per walk, src/PathManager.cpp:32)
+            touched.assign(1, anchor);
             visited[anchor] = 1;
             nodes.assign(1, anchor);
             slots.clear();
@@ -335,7 +390,7 @@ uint64_t walk_monte_carlo(const Graph &g, int metric, const PathParams &pp, RngM
                 } else {  // roulette, :102-115
                     double u = mode == RNG_MT19937 ? unit(engine) : mc_draw(seed, static_cast<uint32_t>(metric), anchor, static_cast<uint32_t>(attempt), draw_no);
                     draw_no++;
-                    if (stats) stats->draws.push_back(u);
+                    if (stats) o.st.draws.push_back(u);
                     double target = u * sum;
                     double acc = 0;
                     for (uint32_t s : cand) {
@@ -348,42 +403,40 @@ uint64_t walk_monte_carlo(const Graph &g, int metric, const PathParams &pp, RngM
                 nodes.push_back(cur);
                 slots.push_back(static_cast<uint32_t>(pick));
                 visited[cur] = 1;
+                touched.push_back(cur);
                 int64_t len = path_length(g, nodes, slots);
                 if (len <= 0) break;                        // :126
                 if (g.node_anchor[cur]) { accepted = true; break; }  // :131
                 if (len >= pp.len_threshold) break;         // :137
             }
-            if (stats) stats->draws_per_walk.push_back(draw_no);
+            if (stats) o.st.draws_per_walk.push_back(draw_no);
             if (accepted) {
                 int64_t len = path_length(g, nodes, slots);
                 if (len < 0) continue;
-                ps.append(nodes, slots, len);
-                found++;
+                o.ps.append(nodes, slots, len);
+                o.found++;
             }
         }
-    }
-    return found;
+        for (uint32_t x : touched) visited[x] = 0;
+    });
 }
 
 uint64_t walk_deterministic(const Graph &g, int metric, PathSet &ps) {
-    const size_t N = g.nodes();
     const std::vector<uint32_t> rank = rank_permutation(g, metric);
     const std::vector<uint32_t> canon = canonical_slots(g);
-    uint64_t found = 0;
-    std::vector<uint8_t> visited;
-    std::vector<uint32_t> nodes, slots;
-    for (uint32_t anchor = 0; anchor < N; anchor++) {
-        if (!g.node_anchor[anchor]) continue;
+    return for_each_anchor(g, oracle_threads(), ps, nullptr, [&](uint32_t anchor, AnchorOut &o, std::vector<uint8_t> &visited) {
+        std::vector<uint32_t> nodes, slots, touched;
         for (uint64_t fs = g.adj_off[anchor]; fs < g.adj_off[anchor + 1]; fs++) {  // :204
-            visited.assign(N, 0);
+            for (uint32_t x : touched) visited[x] = 0;   // (a fresh vector<bool>(N) per walk in the reference, src/PathManager.cpp:212)
             visited[anchor] = 1;
             uint32_t cur = g.slot_neighbour(fs);
             visited[cur] = 1;
+            touched = {anchor, cur};
             nodes = {anchor, cur};
             slots = {static_cast<uint32_t>(fs)};
             if (g.node_anchor[cur]) {  // :224-229 -- and no further first edges for this anchor
-                ps.append(nodes, slots, path_length(g, nodes, slots));
-                found++;
+                o.ps.append(nodes, slots, path_length(g, nodes, slots));
+                o.found++;
                 break;
             }
             bool reached = false, went_back = false;
@@ -411,6 +464,7 @@ uint64_t walk_deterministic(const Graph &g, int metric, PathSet &ps) {
                 }
                 slots.push_back(canon[static_cast<size_t>(chosen)]);  // first parallel edge, :340-347
                 visited[cur] = 1;
+                touched.push_back(cur);
                 cur = g.slot_neighbour(static_cast<uint64_t>(chosen));
                 nodes.push_back(cur);
                 if (g.node_anchor[cur]) { reached = true; break; }
@@ -419,12 +473,12 @@ uint64_t walk_deterministic(const Graph &g, int metric, PathSet &ps) {
             if (reached) {
                 int64_t len = path_length(g, nodes, slots);
                 if (len < 0) continue;
-                ps.append(nodes, slots, len);
-                found++;
+                o.ps.append(nodes, slots, len);
+                o.found++;
             }
         }
-    }
-    return found;
+        for (uint32_t x : touched) visited[x] = 0;
+    });
 }
 
 PathSet filter_unique(const PathSet &ps) {
