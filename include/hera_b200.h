@@ -235,6 +235,36 @@ int hera_graph_load_cache(hera_ctx *ctx, const char *path);
 int hera_graph_export(hera_ctx *ctx, hera_graph_view *out);
 int hera_graph_gather_rows(hera_ctx *ctx);
 
+/* ---- allocation-free variant of the tokenizer ------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * The tokenizer / filter / score kernel of hera_graph_load_* over a PAF text resident in device memory, with its
+ * scratch (counter block + the two look-back chains, one 64-bit word per 30 KiB tile and chain) in a file-scope
+ * device array instead of the context's growable buffer: the call makes NO cudaMalloc / cudaFree / cudaMallocAsync
+ * and needs no hera_ctx.  Limit: n <= HERA_NOALLOC_MAX_TEXT_BYTES (480 MiB of text; the array is ~256 KB and every
+ * GPU that loads the library holds it until the process exits); longer texts are rejected with code 60.
+ * The caller passes everything else: device_text (16-byte aligned, in a cudaMalloc'ed allocation; the 16-byte chunk
+ * holding byte n-1 is read whole, nothing behind it), the 15 output columns in device memory with room for
+ * `capacity` >= n / 24 + 2 rows (code 61 otherwise; rows are written in file order: what edges_ holds before node
+ * ids exist -- qname/tname are {file:4 = 0, byte offset:44, length:16} references into the text, qhash/thash the
+ * 64-bit name hashes, flags bit 0 = strand '-', bit 1 = anchors load, bit 2 = query name starts with "ctg"),
+ * d_result = 4 words in DEVICE memory: records consumed, kept overlaps, index of the first record formatted
+ * extraction would fail or desynchronise on (UINT64_MAX = none; otherwise only rows with rec below it are
+ * meaningful: load such a text with hera_graph_load_*), tokens; and the CUDA stream (cudaStream_t, may be NULL)
+ * everything is queued on -- nothing is synchronised, results are valid once the stream has passed the call.
+ * All calls on a GPU SHARE the scratch array, which keeps the previous call's contents: each call first clears
+ * the part it uses, and two calls whose kernels can overlap on the GPU (different streams without a
+ * dependency) race -- order them.  On failure returns a non-zero code and writes a message to err (may be NULL). */
+#define HERA_NOALLOC_MAX_TEXT_BYTES (16384ull * 30720ull - 30720ull)
+typedef struct {
+    uint32_t *qs, *qe, *ts, *te, *qlen, *tlen, *rec;
+    float *os, *si, *es;
+    uint8_t *flags;
+    uint64_t *qhash, *thash, *qname, *tname;
+} hera_kept_columns;
+int hera_paf_parse_noalloc(int device, const void *device_text, uint64_t n, int anchors, const hera_filter_params *fp, uint32_t test_load_num,
+                           const hera_kept_columns *out, uint64_t capacity, uint64_t *d_result, void *stream, char *err, uint64_t err_cap);
+
 /* ---- PathManager ------------------------------------------------------------------------- */
 /* PathManager::buildMonteCarlo (src/PathManager.cpp:12-177).  Draws come from Philox4x32-10 with
  * counter (anchor node, attempt, draw number, metric) and key = seed instead of one shared

@@ -65,6 +65,14 @@ class ScaffoldView(C.Structure):
                 ("fasta_bytes", C.c_uint64), ("sequence_length", C.c_uint64), ("fasta", C.POINTER(C.c_char)), ("ms", C.c_float)]
 
 
+class KeptColumns(C.Structure):
+    _fields_ = [(k, u32p) for k in ("qs", "qe", "ts", "te", "qlen", "tlen", "rec")] + [(k, f32p) for k in ("os", "si", "es")] + [("flags", u8p)] + \
+               [(k, u64p) for k in ("qhash", "thash", "qname", "tname")]
+
+
+NOALLOC_MAX_TEXT_BYTES = 16384 * 30720 - 30720
+
+
 class WalkStats(C.Structure):
     _fields_ = [("walks", C.c_uint64), ("found", C.c_uint64), ("steps", C.c_uint64), ("ms", C.c_float), ("launches", C.c_uint32)]
 
@@ -80,6 +88,8 @@ SIGNATURES = {
     "hera_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "hera_probe_list_gather": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
     "hera_digest": (C.c_int, [C.c_void_p, u64p]),
+    "hera_paf_parse_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(FilterParams), C.c_uint32, C.POINTER(KeptColumns), C.c_uint64,
+                                         C.c_void_p, C.c_void_p, C.c_char_p, C.c_uint64]),
     "hera_graph_set_filter": (C.c_int, [C.c_void_p, C.POINTER(FilterParams)]),
     "hera_graph_load_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
     "hera_graph_load_bytes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_uint32, C.POINTER(LoadResult)]),
@@ -378,6 +388,20 @@ class Hera:
             "grp_pig": _arr(v.grp_pig, v.pig_total, np.uint32, copy), "grp_consensus": _arr(v.grp_consensus, G, np.int64, copy),
             "grp_valid": _arr(v.grp_valid, G, np.int32, copy), "pair_consensus": _arr(v.pair_consensus, K, np.int64, copy), "ms": float(v.ms),
         }
+
+
+def paf_parse_noalloc(device, text_ptr, n, anchors, fp, columns, capacity, result_ptr, stream=0, test_load_num=0):
+    """hera_paf_parse_noalloc: columns = {name: device pointer} for the 15 KeptColumns fields, result_ptr = 4 u64 in device
+    memory.  Queues the work on `stream` (a cudaStream_t handle, 0 = default stream); raises HeraError on rejection."""
+    lib = load_library()
+    cols = KeptColumns()
+    for name, ctype in KeptColumns._fields_:
+        setattr(cols, name, C.cast(C.c_void_p(int(columns[name])), ctype))
+    err = C.create_string_buffer(512)
+    rc = lib.hera_paf_parse_noalloc(int(device), C.c_void_p(int(text_ptr)), int(n), int(anchors), C.byref(fp), int(test_load_num), C.byref(cols), int(capacity),
+                                    C.c_void_p(int(result_ptr)), C.c_void_p(int(stream)), err, 512)
+    if rc != 0:
+        raise HeraError(rc, err.value.decode())
 
 
 def nccl_unique_id():

@@ -10,6 +10,8 @@
 
 namespace hera {
 uint64_t padded_text_size(uint64_t n);  // paf_parse.cu
+void paf_parse_noalloc(int device, const void *device_text, uint64_t n, int anchors, const hera_filter_params &fp, uint32_t test_load_num,
+                       const hera_kept_columns &out, uint64_t capacity, uint64_t *d_result, cudaStream_t stream);   // paf_parse.cu
 
 __global__ void l2_flush_kernel(uint4 *p, uint64_t n) {
     for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<uint64_t>(gridDim.x) * blockDim.x) p[i] = make_uint4(i, 0, 0, 0);
@@ -210,6 +212,24 @@ int hera_digest(hera_ctx *ctx, uint64_t *out) {
     HERA_REQUIRE(out != nullptr, 101, "null output");
     hera::digest_tables(c, out);
     HERA_API_END
+}
+
+int hera_paf_parse_noalloc(int device, const void *device_text, uint64_t n, int anchors, const hera_filter_params *fp, uint32_t test_load_num,
+                           const hera_kept_columns *out, uint64_t capacity, uint64_t *d_result, void *stream, char *err, uint64_t err_cap) {
+    auto fail = [&](int code, const std::string &msg) {
+        if (err && err_cap) { std::strncpy(err, msg.c_str(), err_cap - 1); err[err_cap - 1] = 0; }
+        cudaGetLastError();
+        return code;
+    };
+    try {
+        if (!fp || !out) throw hera::Error{101, "hera_paf_parse_noalloc: null filter parameters or output columns"};
+        hera::paf_parse_noalloc(device, device_text, n, anchors, *fp, test_load_num, *out, capacity, d_result, static_cast<cudaStream_t>(stream));
+        return 0;
+    } catch (const hera::Error &e) {
+        return fail(e.code, e.msg);
+    } catch (const std::exception &e) {
+        return fail(99, e.what());
+    }
 }
 
 int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp) {

@@ -26,6 +26,7 @@
 // desynchronise there) ends the parallel part; a one-thread tail kernel continues from its byte
 // offset with the exact character-stream rules of formatted extraction.
 #include <algorithm>
+#include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <string>
@@ -1328,6 +1329,99 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
     cudaEventDestroy(ev2);
+}
+
+// ---- hera_paf_parse_noalloc: the tokenizer / filter / score kernel for callers that cannot allocate ---------------------
+// (No counterpart in the reference.)  The parse kernel needs scratch memory --
+// the ParseCounters block and the two look-back chains, one 64-bit state word per tile and chain -- which the ordinary entry
+// points keep in a growable cudaMalloc'ed buffer of the context.  This variant takes it from a file-scope device array of
+// fixed size, so the call path contains no cudaMalloc / cudaFree / stream-ordered allocation at all: usable under CUDA
+// graph capture, in serving loops and in harnesses that forbid allocation.  The array limits the text to
+// HERA_NOALLOC_MAX_TEXT_BYTES per call; every GPU that loads the library holds the array (~256 KB) until the process exits.
+// All calls on a device share it and it keeps the previous call's contents: every call clears what it uses first, and two
+// calls whose kernels overlap on the GPU (different streams, no dependency) race.
+constexpr uint32_t NA_MAX_TILES = static_cast<uint32_t>(HERA_NOALLOC_MAX_TEXT_BYTES / PF_TILE) + 1;
+constexpr uint32_t NA_HEAD_WORDS = 16;   // ParseCounters (8 words) + spare
+constexpr uint64_t NA_WORDS = NA_HEAD_WORDS + 2ull * NA_MAX_TILES;
+static_assert(sizeof(ParseCounters) <= NA_HEAD_WORDS * sizeof(unsigned long long), "counter block fits the head of the scratch array");
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[NA_WORDS];
+
+// Clears the words this call uses (the head and 2 * tiles chain states) and arms the "first irregular record" minima.
+__global__ void __launch_bounds__(256) noalloc_init_kernel(unsigned long long *scratch, uint64_t words) {
+    const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < words; i += stride) scratch[i] = 0;
+}
+__global__ void noalloc_arm_kernel(ParseCounters *ctr) {
+    ctr->first_bad_rec = ~0ull;
+    ctr->first_bad_off = ~0ull;
+}
+// result[0] records consumed ("ctr", src/OverlapGraph.cpp:128), [1] kept overlaps, [2] index of the first record formatted
+// extraction would fail or desynchronise on (UINT64_MAX: none), [3] tokens in the text
+__global__ void noalloc_result_kernel(const ParseCounters *ctr, uint64_t rec_limit, unsigned long long *result) {
+    const unsigned long long T = ctr->total_tokens;
+    unsigned long long records = T / 16 + ((T % 16) >= 12 ? 1 : 0);
+    if (records > rec_limit) records = rec_limit;
+    result[0] = records;
+    result[1] = ctr->kept;
+    result[2] = ctr->first_bad_rec < records ? ctr->first_bad_rec : ~0ull;
+    result[3] = T;
+}
+
+namespace {
+struct NoAllocDevice {
+    bool ready = false;
+    unsigned long long *scratch = nullptr;   // DEVICE address of g_noalloc_scratch on this device (cudaGetSymbolAddress)
+    int sms = 0;
+};
+NoAllocDevice g_noalloc_dev[64];
+std::mutex g_noalloc_mutex;
+}  // namespace
+
+// Once per device, with that device current: the device address of the scratch array (in host code the array's name is
+// only a stand-in for the symbol, not an address a kernel could use) and the launch attributes of the kernel.
+static const NoAllocDevice &noalloc_setup(int device) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mutex);
+    HERA_REQUIRE(device >= 0 && device < 64, 101, "hera_paf_parse_noalloc: device index out of range");
+    NoAllocDevice &d = g_noalloc_dev[device];
+    if (!d.ready) {
+        void *ptr = nullptr;
+        HERA_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        HERA_REQUIRE(ptr != nullptr, 2, "cudaGetSymbolAddress returned a null address for the scratch array");
+        d.scratch = static_cast<unsigned long long *>(ptr);
+        HERA_CUDA(cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, device));
+        HERA_CUDA(cudaFuncSetAttribute(paf_parse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM_BYTES));
+        d.ready = true;
+    }
+    return d;
+}
+
+void paf_parse_noalloc(int device, const void *device_text, uint64_t n, int anchors, const hera_filter_params &fp, uint32_t test_load_num,
+                       const hera_kept_columns &out, uint64_t capacity, uint64_t *d_result, cudaStream_t stream) {
+    HERA_REQUIRE(n <= HERA_NOALLOC_MAX_TEXT_BYTES, 60, "hera_paf_parse_noalloc: the text is longer than HERA_NOALLOC_MAX_TEXT_BYTES (" +
+                 std::to_string(static_cast<unsigned long long>(HERA_NOALLOC_MAX_TEXT_BYTES)) + " bytes): use hera_graph_load_device_view");
+    HERA_REQUIRE(device_text != nullptr && n > 0, 101, "hera_paf_parse_noalloc: empty text");
+    HERA_REQUIRE((reinterpret_cast<uintptr_t>(device_text) & 15u) == 0, 101, "hera_paf_parse_noalloc: the text must start at a 16-byte aligned address");
+    HERA_REQUIRE(d_result != nullptr, 101, "hera_paf_parse_noalloc: null result pointer");
+    HERA_REQUIRE(capacity >= n / 24 + 2, 61, "hera_paf_parse_noalloc: the output columns must hold n / 24 + 2 rows (every record could be kept)");
+    HERA_REQUIRE(out.qs && out.qe && out.ts && out.te && out.qlen && out.tlen && out.rec && out.os && out.si && out.es && out.flags && out.qhash &&
+                 out.thash && out.qname && out.tname, 101, "hera_paf_parse_noalloc: null output column");
+    HERA_CUDA(cudaSetDevice(device));
+    const NoAllocDevice &d = noalloc_setup(device);
+    const uint32_t tiles = static_cast<uint32_t>(n / PF_TILE + 1);
+    ParseCounters *ctr = reinterpret_cast<ParseCounters *>(d.scratch);
+    unsigned long long *tok_state = d.scratch + NA_HEAD_WORDS, *kept_state = tok_state + tiles;
+    const uint64_t words = NA_HEAD_WORDS + 2ull * tiles;
+    noalloc_init_kernel<<<std::min<unsigned>(div_up(words, 256), 148u), 256, 0, stream>>>(d.scratch, words);
+    noalloc_arm_kernel<<<1, 1, 0, stream>>>(ctr);
+    FilterDev fd{fp.mode, static_cast<float>(fp.min_overlap_length), fp.min_overlap_percentage, static_cast<float>(fp.max_overhang_length), fp.max_overhang_percentage};
+    const uint64_t rec_limit = test_load_num > 0 ? static_cast<uint64_t>(test_load_num) + 1 : ~0ull;
+    const KeptPtrs kp{out.qs, out.qe, out.ts, out.te, out.qlen, out.tlen, out.rec, out.os, out.si, out.es, out.flags,
+                      reinterpret_cast<uint64_t *>(out.qhash), reinterpret_cast<uint64_t *>(out.thash), reinterpret_cast<uint64_t *>(out.qname),
+                      reinterpret_cast<uint64_t *>(out.tname)};
+    ParseArgs a{static_cast<const uint8_t *>(device_text), 1, n, n, 0, nullptr, 0, 1, tiles, 0u, anchors ? 1 : 0, rec_limit, 0, fd, kp, tok_state, kept_state, ctr};
+    paf_parse_kernel<<<std::min<uint32_t>(tiles, static_cast<uint32_t>(d.sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, stream>>>(a);
+    noalloc_result_kernel<<<1, 1, 0, stream>>>(ctr, rec_limit, reinterpret_cast<unsigned long long *>(d_result));
+    HERA_CUDA(cudaGetLastError());
 }
 
 }  // namespace hera
