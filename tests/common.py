@@ -150,6 +150,11 @@ def assert_sections_equal(a, b, names=None, what=""):
             raise AssertionError(f"{what}: section {k} differs at {bad}: {x[bad]} vs {y[bad]}")
 
 
+def golden_cases():
+    """Fixture names under tests/golden (bench_digests.json is bench.py's digest golden, not a fixture)."""
+    return sorted(p.stem for p in GOLDEN.glob("*.json") if not p.stem.startswith("bench_"))
+
+
 def load_golden(name):
     with open(GOLDEN / f"{name}.json") as f:
         return json.load(f)

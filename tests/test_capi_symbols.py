@@ -54,3 +54,14 @@ def test_create_without_gpu_fails_loudly(lib_path):
     from telomeri_b200 import capi
     with pytest.raises(capi.HeraError):
         capi.Hera(0)
+
+
+def test_bench_digest_golden_covers_the_bench_workloads():
+    """bench.py proves parity of its own run (any number of GPUs) by comparing hera_digest with these oracle-verified words."""
+    import json
+    import bench
+    from telomeri_b200 import capi
+    golden = json.loads(bench.DIGEST_GOLDEN.read_text())
+    for key in bench.WORKLOADS:
+        assert sorted(golden[key]["digests"]) == sorted(capi.DIGEST_NAMES), key
+        assert "bit-exact against oracle" in golden[key]["verified"] and int(golden[key]["digests"]["u_len"]) != 0

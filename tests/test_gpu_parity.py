@@ -16,7 +16,7 @@ GROUP_SECTIONS = ["pair_a1", "pair_a2", "pair_off", "pair_sorted", "grp_pair", "
                   "grp_consensus", "grp_valid", "pair_consensus"]
 METRIC_ID = {"es": 0, "os": 1, "es_sqrt": 2, "os_sqrt": 3}
 
-CASES = sorted(p.stem for p in common.GOLDEN.glob("*.json"))
+CASES = common.golden_cases()
 
 
 def run_both(case, oracle_bin, datasets, tmp_path, seed):
