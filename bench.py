@@ -494,8 +494,8 @@ def main():
         achieved = algo_bytes / (r["parse_leg_ms"] * 1e-3) / 1e9
         tr = parse_traffic()
         traffic = None
-        if tr and tr.get("text_bytes"):   # per launch like `achieved`: the capture's DRAM bytes per PAF byte x this launch's text
-            traffic = int((int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])) / int(tr["text_bytes"]) * r["parse_leg_bytes"])
+        if tr and tr.get("algorithmic_bytes"):   # per launch like `achieved`: the capture's DRAM bytes per algorithmic byte x this launch's
+            traffic = int((int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])) / int(tr["algorithmic_bytes"]) * algo_bytes)
         step_ms = st["graph_ms"] + st["paths_ms"] + st["groups_ms"]
         line = {
             "metric": "overlaps/s graph build", "value": r["records"] / (st["graph_ms"] * 1e-3), "unit": "overlaps/s", "n_gpus": world, "steps": args.steps,
