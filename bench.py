@@ -517,13 +517,13 @@ def main():
                          "algorithmic_bytes": algo_bytes, "kernel_ms": r["parse_leg_ms"], "traffic": traffic},
             "roofline_stages": stage_rooflines(r, peak, world),
             # north_star: the pointer-chasing walks are reported against a measured ceiling: an L2-resident *streaming* probe of
-            # whole adjacency lists with dependent hops (not a random 32-byte-sector gather), 16-byte entries
+            # whole adjacency lists (8-byte entries) with dependent hops, not a random 32-byte-sector gather
             "roofline_walks": {"bound": "dependent list gather (L2/HBM latency)", "kernel": "walk_mc_kernel x2 + walk_det_kernel x2 in flight together",
-                               "achieved": r["walk_entries"] * 16 / (st["paths_ms"] * 1e-3) / 1e9 / world,
+                               "achieved": r["walk_entries"] * 8 / (st["paths_ms"] * 1e-3) / 1e9 / world,
                                "peak": r["gather_gbs"], "unit": "GB/s per GPU", "frac": None,
                                "peak_source": f"hera_probe_list_gather(64 warps/SM, 256 hops) on this graph: {r['gather_ms']:.3f} ms",
-                               "algorithmic_bytes": int(r["walk_entries"]) * 16,
-                               "algorithmic_bytes_survey_8d": int(r["walk_entries"]) * 8},
+                               "algorithmic_bytes": int(r["walk_entries"]) * 8,
+                               "bytes_model": "SURVEY 8(d): 8 B per adjacency entry examined (neighbour | anchor bit + fp32 score), the 8-byte tables the roulette scan streams"},
             "parity_checked": {"ranks_agree": bool(r["ranks_agree"]), "matches_oracle_verified_digests": r["golden_matches"],
                                "verified_by": r["golden_note"], "tables": list(r["digest"].keys())},
             "clocks": r["clocks"],

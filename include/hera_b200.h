@@ -130,7 +130,9 @@ uint64_t hera_kernel_launches(hera_ctx *ctx);    /* kernels launched by this con
  * Options: "flush_l2" (1 = write a buffer larger than L2 before every event-timed kernel region,
  * outside the timed region), "walk_warps_per_sm" (resident walk warps per SM shared by the walk kernels in flight, default 32), "walk_smem_bitmap" (0 = visited
  * bitmaps of the Monte-Carlo walks stay in global memory even when they would fit in shared memory),
- * "walk_variant" (chunks in flight x resident CTAs of the Monte-Carlo kernel, tuning), "walk_cap_small" (nodes a walk may
+ * "walk_variant" (chunks in flight x resident CTAs of the Monte-Carlo kernel, tuning), "parse_count_rows" (a load whose worst case, bytes / 24 rows, exceeds this many rows does not reserve that worst case: it
+ * counts the tokens first or, on a context that already holds enough rows, tries with those and repeats the load if they
+ * do not suffice; default 64 Mi), "walk_cap_small" (nodes a walk may
  * visit before its call is repeated with per-warp scratch for every node of the graph, default 16384), "parse_variant" (0 = the
  * CTA-tile tokenizer, default; 1 = the warp-autonomous tokenizer -- same results, see DESIGN.md K1+K2). */
 int hera_timer_start(hera_ctx *ctx);

@@ -45,6 +45,7 @@ struct KeptPtrs {
     float *os, *si, *es;
     uint8_t *flags;
     uint64_t *qhash, *thash, *qname, *tname;
+    uint64_t cap = ~0ull;   // rows the columns can hold
 };
 
 // A byte-range slice of a PAF file (sharded load): which of its tokens are this rank's.
@@ -112,6 +113,7 @@ struct GraphTables {
     // walk-facing view of a slot: {neighbour id | bit 31 = neighbour is an anchor, es, os, q_start - t_start (src/Path.cpp:13)},
     // one 128-bit load per entry.  Sharded runs: every rank writes its entries into every rank's array (peer memory).
     DBuf<uint4> adj4;
+    DBuf<uint2> a8[2];                       // {neighbour | anchor bit, es} and {neighbour | anchor bit, os}: what the roulette scan streams (8 B / entry; derived from adj4 on every rank)
     DBuf<uint8_t> node_exact;                // bit m: the fp64 sum of metric m over any subset of the node's list is exact in any order
     DBuf<uint32_t> rank[4];                  // per metric; empty if not built
     bool rank_ready[4] = {false, false, false, false};
@@ -150,6 +152,8 @@ struct Ctx {
     std::vector<std::unique_ptr<LoadedText>> texts;
     std::vector<std::unique_ptr<LoadedText>> text_pool;   // buffers of texts dropped by hera_graph_reset, reused by the next loads
     KeptTable kept;                   // LOCAL rows: the kept overlaps this rank parsed itself (all of them on a single rank)
+    int64_t opt_parse_count_rows = 64ll << 20;   // loads whose worst-case row count (bytes / 24) exceeds this size their rows by counting tokens / by what the context already holds
+    bool parse_force_count = false;   // the optimistic row reservation of a load overflowed: count the tokens first this time
     bool cache_loaded = false;        // kept overlaps + node table came from hera_graph_load_cache: finalize skips K3
     std::vector<RowRange> own_rows;   // per load: the GLOBAL rows this rank parsed itself
     std::vector<LoadShape> load_shapes;   // per load: every rank's kept count

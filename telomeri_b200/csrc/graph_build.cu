@@ -287,8 +287,12 @@ __device__ __forceinline__ float metric_value(int metric, float es, float os);
 // sum of ALL of them stays below 2^53 * q, then every partial sum over every subset is an integer
 // multiple of q below 2^53 * q: exactly representable, so any summation order gives the sequential
 // result bit for bit.  Bit m of node_exact[x] records that for metric m.
+// The same pass writes the 8-byte views {neighbour | anchor bit, metric} the Monte-Carlo walks stream (one per stored score;
+// the walk stage is bound by the bytes it reads per examined entry, and a roulette scan needs neither the other score nor
+// the coordinate delta of an entry it does not take).
 __global__ void __launch_bounds__(128) node_exact_kernel(uint32_t N, const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4,
-                                                         uint8_t *__restrict__ node_exact, uint32_t *__restrict__ max_deg) {
+                                                         uint8_t *__restrict__ node_exact, uint32_t *__restrict__ max_deg, uint2 *__restrict__ a8_es,
+                                                         uint2 *__restrict__ a8_os) {
     const uint32_t x = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (x >= N) return;
     const uint32_t base = off[x], deg = off[x + 1] - base;
@@ -300,6 +304,8 @@ __global__ void __launch_bounds__(128) node_exact_kernel(uint32_t N, const uint3
     double part[4] = {0.0, 0.0, 0.0, 0.0};
     for (uint32_t k = lane; k < deg; k += 32) {
         const uint4 e = adj4[base + k];
+        a8_es[base + k] = make_uint2(e.x, e.y);
+        a8_os[base + k] = make_uint2(e.x, e.z);
         anchor_nbr |= (e.x >> 31) != 0;
 #pragma unroll
         for (int m = 0; m < 4; m++) {
@@ -924,6 +930,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             pt.adj4[0] = g.adj4.p; pt.pay[0] = g.adj_pay.p;
         }
         g.node_exact.reserve(N);
+        g.a8[0].reserve(S + 1); g.a8[1].reserve(S + 1);
         if (SL) HERA_LAUNCH(c, csr_scatter_kernel, div_up(SL, 256), 256, 0, SL, P, keys32, vals32, run_start, g.adj_off.p, before, pc, g.e_q.p, g.e_t.p, c.kept.qs.p,
                             c.kept.ts.p, c.kept.es.p, c.kept.os.p, g.node_anchor.p, pt);
         if (merged_by_reduce) {
@@ -933,7 +940,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             c.xch->all_gather_dev(c, c.counters.p, c.counters.p + 1, 1);   // stream-ordered rendezvous: every rank's stores have been issued and fenced
         }
         log.mark("scatter");
-        HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.adj4.p, g.node_exact.p, d_late + 2);
+        HERA_LAUNCH(c, node_exact_kernel, div_up(N * 32, 128), 128, 0, static_cast<uint32_t>(N), g.adj_off.p, g.adj4.p, g.node_exact.p, d_late + 2, g.a8[0].p, g.a8[1].p);
         log.mark("exact");
         HERA_CUDA(cudaEventRecord(ev[2], c.stream));
 

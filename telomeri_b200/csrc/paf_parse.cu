@@ -235,6 +235,7 @@ __device__ __forceinline__ bool make_record(const FilterDev &f, const uint8_t *t
 }
 
 __device__ __forceinline__ void store_record(const KeptPtrs &k, uint64_t i, const StagedRecord &s) {
+    if (i >= k.cap) return;   // the table was sized optimistically and this text keeps more rows: the host sees kept > room and runs again
     k.qs[i] = s.qs; k.qe[i] = s.qe; k.ts[i] = s.ts; k.te[i] = s.te; k.qlen[i] = s.qlen; k.tlen[i] = s.tlen; k.rec[i] = s.rec;
     k.os[i] = s.os; k.si[i] = s.si; k.es[i] = s.es; k.flags[i] = s.flags;
     k.qhash[i] = s.qhash; k.thash[i] = s.thash; k.qname[i] = s.qname; k.tname[i] = s.tname;
@@ -1041,6 +1042,12 @@ __global__ void __launch_bounds__(WW_THREADS, WW_MIN_CTAS) paf_parse_warp_kernel
     }
 }
 
+// More rows were kept than the table has room for (optimistic reservation): marked in the top bit of the count.
+constexpr unsigned long long KEPT_OVERFLOW = 1ull << 63;
+__global__ void kept_overflow_kernel(ParseCounters *ctr, uint64_t room) {
+    if (ctr->kept > room) ctr->kept |= KEPT_OVERFLOW;
+}
+
 // Finds how many kept records of this load precede the first irregular record.
 __global__ void kept_before_kernel(const uint32_t *__restrict__ rec, uint64_t base, uint64_t n, uint64_t bad_rec, unsigned long long *out) {
     const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -1103,7 +1110,8 @@ __global__ void pad_text_kernel(uint8_t *text, uint64_t n, uint64_t padded) {
 }
 
 static KeptPtrs kept_ptrs(KeptTable &k) {
-    return KeptPtrs{k.qs.p, k.qe.p, k.ts.p, k.te.p, k.qlen.p, k.tlen.p, k.rec.p, k.os.p, k.si.p, k.es.p, k.flags.p, k.qhash.p, k.thash.p, k.qname.p, k.tname.p};
+    return KeptPtrs{k.qs.p, k.qe.p, k.ts.p, k.te.p, k.qlen.p, k.tlen.p, k.rec.p, k.os.p, k.si.p, k.es.p, k.flags.p, k.qhash.p, k.thash.p, k.qname.p, k.tname.p,
+                    k.qs.cap};
 }
 
 uint64_t padded_text_size(uint64_t n) { return (n / PF_TILE + 2) * static_cast<uint64_t>(PF_TILE); }
@@ -1153,8 +1161,17 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     // worst case every record is kept: records <= bytes / 24 (12 one-byte tokens + separators).  For a large text that
     // bound would reserve far more rows than the file can hold records (42 GB of PAF -> 128 GB of rows), so the tokens
     // are counted first (one more pass over the text) and the rows are reserved for tokens / 16 records.
+    // A context that has loaded a text of this kind before skips the counting pass: the rows it holds already are taken as
+    // the reservation (a PAF record has > 100 bytes; owned / 160 rows is the least that is worth trying), the kernel drops
+    // rows that do not fit, the overflow is noticed right after the kernel (on every rank of a sharded load: the mark
+    // travels with the kept counts) and the load is done again with the count.
     uint64_t max_new = owned / 24 + 2;
-    if (max_new > (64ull << 20)) {
+    const uint64_t room_now = c.kept.qs.cap > c.kept.n ? c.kept.qs.cap - c.kept.n : 0;
+    const uint64_t count_rows = static_cast<uint64_t>(c.opt_parse_count_rows);
+    const bool optimistic = max_new > count_rows && !c.parse_force_count && room_now >= owned / 160 + 2;
+    if (optimistic) {
+        max_new = room_now;
+    } else if (max_new > count_rows) {
         c.counters.reserve(16);
         unsigned long long *d_tok = reinterpret_cast<unsigned long long *>(c.counters.p + 13);
         HERA_CUDA(cudaMemsetAsync(d_tok, 0, sizeof(unsigned long long), c.stream));
@@ -1164,7 +1181,8 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         max_new = std::min<uint64_t>(max_new, c.h_counters.p[13] / 16 + 2);
     }
-    c.kept.reserve(c.kept.n + max_new, c.stream);
+    if (!optimistic) c.kept.reserve(c.kept.n + max_new, c.stream);
+    const uint64_t room = c.kept.qs.cap - c.kept.n;
 
     // device block: [0, 8) ParseCounters, [12] cut, [13] my token count, [14] tokens before my slice, [15] tokens of all
     // slices, [16, 16 + 2 tiles) chain states, then what the ranks tell each other: token counts, {kept, first bad} pairs
@@ -1218,6 +1236,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     }
     HERA_CUDA(cudaEventRecord(ev1, c.stream));
     mark("parse");
+    HERA_LAUNCH(c, kept_overflow_kernel, 1, 1, 0, ctr, room);
 
     if (sharded) {   // every rank learns every rank's kept count and whether anybody met an irregular record
         c.xch->all_gather_dev(c, c.counters.p + 2, d_kb_all, 2);   // ParseCounters::kept, first_bad_rec
@@ -1244,6 +1263,23 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
                 me, pre, krn, t_entry, t_gather - t_entry, t_launched - t_entry, host_now_ms() - t_entry);
     }
     ParseCounters hc = *reinterpret_cast<ParseCounters *>(c.h_counters.p);
+    bool overflow = (hc.kept & KEPT_OVERFLOW) != 0;
+    for (int r = 0; sharded && r < ranks; r++) overflow = overflow || (c.h_counters.p[16 + ranks + 2 * r] & KEPT_OVERFLOW) != 0;
+    if (overflow) {   // (only after an optimistic reservation; the same decision on every rank)
+        cudaEventDestroy(ev0);
+        cudaEventDestroy(ev1);
+        cudaEventDestroy(ev2);
+        HERA_REQUIRE(!c.parse_force_count, 3, "internal: kept rows overflowed a counted reservation");
+        c.parse_force_count = true;
+        try {
+            load_text_resident(c, text, file_id, anchors, test_load_num, shard, out);
+        } catch (...) {
+            c.parse_force_count = false;
+            throw;
+        }
+        c.parse_force_count = false;
+        return;
+    }
     uint64_t tokens_all = 0;
     for (int r = 0; sharded && r < ranks; r++) tokens_all += c.h_counters.p[16 + r];
 

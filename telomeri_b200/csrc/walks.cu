@@ -31,6 +31,7 @@ constexpr int WK_CACHE_MAX = 1024;  // list entries (metric values) a warp can k
 struct WalkGraph {
     const uint32_t *off, *canon, *rank, *node_len, *anchor_ids;
     const uint4 *adj4;        // {nbr | anchor bit 31, es, os, delta} per slot
+    const uint2 *a8;          // {nbr | anchor bit 31, this call's stored score} per slot: what the roulette scan reads
     const uint8_t *node_exact;
     uint32_t N, anchors;
     int sqrt_metric;
@@ -178,15 +179,14 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
             int forced = -1;
             bool any_cand = false;
             uint32_t forced_nbw = 0;
-            int32_t forced_dl = 0;
             // four 32-entry chunks in flight per round trip: the step latency of a single walk is what
             // bounds the kernel (the longest walk is its critical path), not the entries per second
             for (uint32_t c0 = 0; c0 < deg && forced < 0; c0 += 32 * WK_MLP) {
-                uint4 a[WK_MLP];
+                uint2 a[WK_MLP];
 #pragma unroll
                 for (int j = 0; j < WK_MLP; j++) {
                     const uint32_t k = c0 + 32 * j + lane;
-                    a[j] = k < deg ? __ldg(g.adj4 + base + k) : make_uint4(0, 0, 0, 0);
+                    a[j] = k < deg ? __ldg(g.a8 + base + k) : make_uint2(0, 0);
                 }
 #pragma unroll
                 for (int j = 0; j < WK_MLP; j++) {
@@ -200,14 +200,13 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
                         const int src = __ffs(fb) - 1;
                         forced = static_cast<int>(c0) + 32 * j + src;
                         forced_nbw = __shfl_sync(0xffffffffu, a[j].x, src);
-                        forced_dl = static_cast<int32_t>(__shfl_sync(0xffffffffu, a[j].w, src));
                         continue;
                     }
                     const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, nb);
                     any_cand |= cand;
                     // entry k keeps its place in the cache: its metric if it is a candidate, else -0.0f
                     // (adding -0.0 to a sum changes nothing, and the sign bit tells the two apart)
-                    float v = __uint_as_float(g.use_os ? a[j].z : a[j].y);
+                    float v = __uint_as_float(a[j].y);
                     if (g.sqrt_metric) v = __fsqrt_rn(v);
                     if (k < WK_CACHE) s_cval[k] = cand ? v : -0.0f;
                 }
@@ -306,13 +305,10 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
             }
             // ---- take the edge (src/PathManager.cpp:117-142)
             const uint32_t slot = base + static_cast<uint32_t>(pick);
-            uint32_t nbw = forced_nbw;
-            int32_t dl = forced_dl;
-            if (forced < 0) {   // roulette pick: its entry left the registers, it is an L1/L2 hit
-                const uint4 taken = __ldg(g.adj4 + slot);
-                nbw = taken.x;
-                dl = static_cast<int32_t>(taken.w);
-            }
+            // the taken entry's coordinate delta (and, for a roulette pick, its neighbour) from the full 16-byte entry
+            const uint4 taken = __ldg(g.adj4 + slot);
+            const uint32_t nbw = forced >= 0 ? forced_nbw : taken.x;
+            const int32_t dl = static_cast<int32_t>(taken.w);
             cur = nbw & 0x7fffffffu;
             if (nlog >= sc.cap) { if (lane == 0) *o.overflow = 1u; break; }   // scratch sized for typical walks: the host re-runs the job with cap = N + 1
             if (lane == 0) {
@@ -339,13 +335,17 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
 
 // Greedy walk ids: prefix over anchors of the number of first edges tried
 // (src/PathManager.cpp:204,224-229: the first edge that lands on an anchor ends the loop).
-__global__ void det_count_kernel(WalkGraph g, uint32_t *first_edges) {
-    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void det_count_kernel(WalkGraph g, uint32_t *first_edges) {   // one warp per anchor
+    const uint32_t a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (a >= g.anchors) return;
     const uint32_t x = g.anchor_ids[a], base = g.off[x], deg = g.off[x + 1] - base;
     uint32_t n = deg;
-    for (uint32_t k = 0; k < deg; k++) if (slot_nbr(g, base + k) >> 31) { n = k + 1; break; }
-    first_edges[a] = n;
+    for (uint32_t c0 = 0; c0 < deg; c0 += 32) {
+        const uint32_t k = c0 + lane;
+        const uint32_t hit = __ballot_sync(0xffffffffu, k < deg && (__ldg(&g.a8[base + k].x) >> 31));
+        if (hit) { n = c0 + __ffs(hit); break; }
+    }
+    if (lane == 0) first_edges[a] = n;
 }
 
 __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkScratch sc, WalkOut o, uint32_t total_walks, const uint32_t *__restrict__ walk_base) {
@@ -480,6 +480,7 @@ WalkGraph make_walk_graph(Ctx &c, int metric) {
     w.off = g.adj_off.p; w.canon = g.canon.p; w.rank = g.rank_ready[metric] ? g.rank[metric].p : nullptr;
     w.node_len = g.node_len.p; w.anchor_ids = g.anchor_ids.p;
     w.adj4 = g.adj4.p; w.node_exact = g.node_exact.p;
+    w.a8 = g.a8[(metric == HERA_OVERLAP_SCORE || metric == HERA_OVERLAP_SCORE_SQRT) ? 1 : 0].p;
     w.use_os = (metric == HERA_OVERLAP_SCORE || metric == HERA_OVERLAP_SCORE_SQRT) ? 1 : 0;
     w.exact_bit = 1u << metric;
     w.N = static_cast<uint32_t>(g.N); w.anchors = static_cast<uint32_t>(g.anchors);
@@ -618,7 +619,7 @@ void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm, int slot) {
             HERA_CUDA(cudaMallocAsync(&j.first_edges, g.anchors * sizeof(uint32_t), c.stream));
             HERA_CUDA(cudaMallocAsync(&j.walk_base, g.anchors * sizeof(uint32_t), c.stream));
             HERA_CUDA(cudaMallocAsync(&d_total, sizeof(uint32_t), c.stream));
-            HERA_LAUNCH(c, det_count_kernel, div_up(g.anchors, 128), 128, 0, j.wg, j.first_edges);
+            HERA_LAUNCH(c, det_count_kernel, div_up(g.anchors * 32, 128), 128, 0, j.wg, j.first_edges);
             exclusive_scan_u32(c, j.first_edges, g.anchors, j.walk_base, d_total);
             HERA_CUDA(cudaMemcpyAsync(&j.total_walks, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
             HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -856,9 +857,9 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
 // ---- measured ceiling for list walking (north_star: "the pointer-chasing walks are reported against the measured
 // random-gather roofline") -------------------------------------------------------------------------------------
 // The same memory behaviour as a walk step and nothing else: a warp reads the whole adjacency list of its current
-// node as 16-byte entries, then hops to a neighbour it found there (the next address depends on loaded data), with
+// node as 8-byte entries (what the roulette scan reads), then hops to a neighbour it found there (the next address depends on loaded data), with
 // the walk kernels' number of resident warps.  No roulette, no visited set, no random numbers.
-__global__ void __launch_bounds__(WK_THREADS) list_gather_probe_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t N,
+__global__ void __launch_bounds__(WK_THREADS) list_gather_probe_kernel(const uint32_t *__restrict__ off, const uint2 *__restrict__ adj, uint32_t N,
                                                                        uint32_t hops, unsigned long long *bytes_out, uint32_t *sink) {
     const uint32_t lane = threadIdx.x & 31u, w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     uint32_t x = (w * 2654435761u) % N, acc = 0;
@@ -868,11 +869,11 @@ __global__ void __launch_bounds__(WK_THREADS) list_gather_probe_kernel(const uin
         const uint32_t pick = deg ? ((w + h) * 0x9E3779B1u >> 8) % deg : 0;
         uint32_t cand = x;
         for (uint32_t k = lane; k < deg; k += 32) {
-            const uint4 e = adj4[base + k];
-            acc ^= e.y + e.z;
+            const uint2 e = adj[base + k];
+            acc ^= e.y;
             if (k == pick) cand = e.x & 0x7fffffffu;
         }
-        bytes += static_cast<unsigned long long>(deg) * 16;
+        bytes += static_cast<unsigned long long>(deg) * 8;
         x = deg ? __shfl_sync(0xffffffffu, cand, pick & 31u) : (x + 1) % N;
     }
     if (lane == 0) atomicAdd(bytes_out, bytes);
@@ -892,7 +893,7 @@ void probe_list_gather(Ctx &c, uint32_t warps_per_sm, uint32_t hops, double *gby
     HERA_CUDA(cudaEventCreate(&e0));
     HERA_CUDA(cudaEventCreate(&e1));
     HERA_CUDA(cudaEventRecord(e0, c.stream));
-    HERA_LAUNCH(c, list_gather_probe_kernel, div_up(static_cast<uint64_t>(warps) * 32, WK_THREADS), WK_THREADS, 0, g.adj_off.p, g.adj4.p,
+    HERA_LAUNCH(c, list_gather_probe_kernel, div_up(static_cast<uint64_t>(warps) * 32, WK_THREADS), WK_THREADS, 0, g.adj_off.p, g.a8[0].p,
                 static_cast<uint32_t>(g.N), hops, d_bytes, reinterpret_cast<uint32_t *>(d_bytes + 1));
     HERA_CUDA(cudaEventRecord(e1, c.stream));
     unsigned long long h_bytes = 0;

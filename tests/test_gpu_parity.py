@@ -133,6 +133,34 @@ def test_reader_edge_cases_gpu(oracle_bin, tmp_path):
     assert gpu["node_anchor"].sum() == 0
 
 
+def test_optimistic_row_reservation_and_its_overflow(oracle_bin, datasets, tmp_path):
+    """Large loads do not reserve bytes / 24 rows: the first one counts its tokens, later ones on the same context try with the
+    rows the context already holds and are repeated (with the count) when the text keeps more rows than that.  Forced here at
+    small size with the "parse_count_rows" option: a context sized by 58 % of a file then loads the whole file."""
+    from telomeri_b200 import capi
+    ds = datasets["small"]
+    full = (ds / "rr_overlaps.paf").read_bytes()
+    cut = full.rfind(b"\n", 0, int(len(full) * 0.58)) + 1
+    d = tmp_path / "prefix"
+    d.mkdir()
+    (d / "rr_overlaps.paf").write_bytes(full[:cut])
+    (d / "cr_overlaps.paf").write_bytes(b"")
+    ora_full = common.run_dump(oracle_bin, ds, tmp_path / "f.bin", [], extra=["--stage", "graph"])
+    ora_pre = common.run_dump(oracle_bin, d, tmp_path / "p.bin", [], extra=["--stage", "graph"])
+    cols = ["node_len", "e_q", "e_t", "e_qs", "e_te", "e_os", "e_es", "adj_off", "adj_rec", "canon", "rank_0"]
+    with capi.Hera(0) as h:
+        h.set_option("parse_count_rows", 1000)
+        h.set_filter(capi.default_filter())
+        for rep, (path, ora) in enumerate([(d, ora_pre), (ds, ora_full), (ds, ora_full), (d, ora_pre)]):
+            # 1: counted; 2: optimistic, overflows (more rows than the prefix left room for), repeated; 3: optimistic, fits; 4: optimistic, fits
+            h.graph_reset()
+            r1 = h.load_file(path / "rr_overlaps.paf", False)
+            r2 = h.load_file(path / "cr_overlaps.paf", True)
+            assert [r1.records, r2.records] == ora["load_ctr"].tolist() and [r1.kept_total, r2.kept_total] == ora["load_cum_edges"].tolist(), rep
+            h.finalize(["es"])
+            common.assert_sections_equal(ora, h.export_graph(), cols, f"load {rep}")
+
+
 def test_device_view_loads_match_oracle(oracle_bin, tmp_path):
     """hera_graph_load_device_view parses the caller's device buffer in place: nothing behind byte n is readable, so
     texts whose end falls on / next to a tile, halo or 16-byte chunk boundary (the tokenizer stages 30 KiB tiles + 1 KiB

@@ -30,7 +30,7 @@ for warps in (32, 16):
         s = h.monte_carlo(m, pp, bench.WALK_SEED) if kind == "mc" else h.deterministic(m)
         out.append(f"{kind}_{m} {s.ms:.1f} ms ({s.walks} walks, {s.steps / 1e6:.0f}M entries)")
     print(f"alone, {warps} warps/SM: " + " | ".join(out))
-for variant, warps in ((0, 32), (1, 48), (2, 64)):
+for variant, warps in ((0, 32), (0, 40)):
     h.set_option("walk_variant", variant)
     h.set_option("walk_warps_per_sm", warps)
     h.set_option("walk_hints_reset", 1)
