@@ -152,7 +152,7 @@ def assert_sections_equal(a, b, names=None, what=""):
 
 def golden_cases():
     """Fixture names under tests/golden (bench_digests.json is bench.py's digest golden, not a fixture)."""
-    return sorted(p.stem for p in GOLDEN.glob("*.json") if not p.stem.startswith("bench_"))
+    return sorted(p.stem for p in GOLDEN.glob("*.json") if not p.stem.startswith(("bench_", "config_")))
 
 
 def load_golden(name):
