@@ -63,7 +63,7 @@ struct FilterDev {
 
 struct ParseCounters {  // device block, zeroed per load
     unsigned int ticket;
-    unsigned int pad;
+    unsigned int name_too_long;         // a kept record has a sequence name of 65536 bytes or more (the name reference holds 16 bits of length)
     unsigned long long total_tokens;
     unsigned long long kept;
     unsigned long long first_bad_rec;   // min record index that is irregular (init UINT64_MAX)
@@ -219,9 +219,10 @@ __device__ __forceinline__ bool is_ctg(const uint8_t *text, uint64_t off, uint32
 
 // Turns parsed fields into a staged record; returns keep flag.
 __device__ __forceinline__ bool make_record(const FilterDev &f, const uint8_t *text, uint32_t file_id, bool anchors, const SerialRecord &r,
-                                            uint32_t rec_idx, StagedRecord &out) {
+                                            uint32_t rec_idx, StagedRecord &out, ParseCounters *ctr) {
     if (r.qhash == r.thash && r.qnlen == r.tnlen && names_equal(text, r.qoff, r.toff, r.qnlen)) return false;  // :157
     if (!filter_fields(f, r.qlen, r.qs, r.qe, r.tlen, r.ts, r.te)) return false;
+    if ((r.qnlen | r.tnlen) > 0xffffu) ctr->name_too_long = 1;   // (the reference takes names of any length; here the load fails with code 22)
     out.qs = static_cast<uint32_t>(r.qs); out.qe = static_cast<uint32_t>(r.qe);
     out.ts = static_cast<uint32_t>(r.ts); out.te = static_cast<uint32_t>(r.te);
     out.qlen = static_cast<uint32_t>(r.qlen); out.tlen = static_cast<uint32_t>(r.tlen);
@@ -510,7 +511,7 @@ __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, 
         atomicMin(&a.ctr->first_bad_off, static_cast<unsigned long long>(tile_byte0 + p0));
         return false;
     }
-    return make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), out);
+    return make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), out, a.ctr);
 }
 
 // Position of the k-th (0-based) set bit of a mask that has more than k bits set.
@@ -1066,7 +1067,7 @@ __global__ void paf_tail_kernel(const uint8_t *text, uint64_t n, uint64_t start_
         SerialRecord r;
         if (!serial_read_record(cur, r)) break;
         StagedRecord s;
-        if (make_record(filter, text, file_id, anchors != 0, r, static_cast<uint32_t>(rec), s)) {
+        if (make_record(filter, text, file_id, anchors != 0, r, static_cast<uint32_t>(rec), s, ctr)) {
             if (kept_pos + nk < kept_cap) store_record(kept, kept_pos + nk, s);
             nk++;
         }
@@ -1345,6 +1346,14 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         shape.displs.assign(ranks, kept_global);
         shape.displs[0] = 0;
         c.load_shapes.push_back(shape);
+    }
+    if (hc.name_too_long || records >= (1ull << 32)) {
+        cudaEventDestroy(ev0);
+        cudaEventDestroy(ev1);
+        cudaEventDestroy(ev2);
+        if (!c.own_rows.empty()) { c.own_rows.pop_back(); c.load_shapes.pop_back(); }
+        HERA_REQUIRE(!hc.name_too_long, 22, "a kept record has a sequence name of 65536 bytes or more: not supported (name references hold 16 bits of length)");
+        HERA_REQUIRE(records < (1ull << 32), 23, "more than 2^32 records in one load: not supported (record indices are 32 bits)");
     }
     c.kept.n += kept_new;
     c.rows_total += kept_global;

@@ -161,6 +161,24 @@ def test_optimistic_row_reservation_and_its_overflow(oracle_bin, datasets, tmp_p
             common.assert_sections_equal(ora, h.export_graph(), cols, f"load {rep}")
 
 
+def test_names_of_65536_bytes_are_refused(tmp_path):
+    """Name references hold 16 bits of length: a kept record with a longer name fails the load (code 22) instead of
+    producing a truncated node name; the reference has no such limit (documented in INTEGRATION.md)."""
+    from telomeri_b200 import capi
+    rec = "r1 1000 10 990 + ctg1 5000 0 980 970 980 0 tp:A:S cm:i:1 s1:i:1 dv:f:0.1\n"
+    text = rec + rec.replace("r1", "r" * 70000) + rec
+    f = tmp_path / "long.paf"
+    f.write_text(text)
+    with capi.Hera(0) as h:
+        h.set_filter(capi.default_filter("max"))
+        with pytest.raises(capi.HeraError) as e:
+            h.load_file(f, True)
+        assert e.value.code == 22
+        h.graph_reset()
+        (tmp_path / "ok.paf").write_text(rec)
+        assert h.load_file(tmp_path / "ok.paf", True).kept == 1   # the context stays usable
+
+
 def test_device_view_loads_match_oracle(oracle_bin, tmp_path):
     """hera_graph_load_device_view parses the caller's device buffer in place: nothing behind byte n is readable, so
     texts whose end falls on / next to a tile, halo or 16-byte chunk boundary (the tokenizer stages 30 KiB tiles + 1 KiB
