@@ -93,7 +93,5 @@ constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 16;                 // chunks of RS_THREADS elements per tile
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
-constexpr int RS_BITS = 8;
-constexpr int RS_BINS = 1 << RS_BITS;
 
 }  // namespace hera

@@ -133,6 +133,20 @@ def test_reader_edge_cases_gpu(oracle_bin, tmp_path):
     assert gpu["node_anchor"].sum() == 0
 
 
+@pytest.mark.parametrize("digit", [9, 10, 11])
+def test_radix_sort_digit_widths(digit, oracle_bin, datasets, tmp_path):
+    """radix_sort_pairs picks 8- to 11-bit digits from the key width (two 10-bit passes for configs[3]'s 20-bit keys); small
+    inputs only ever meet 8 bits, so the other widths are forced here: CSR order, pair order and groups must not change."""
+    from telomeri_b200 import capi, pipeline
+    golden = common.load_golden("mixed_default")
+    ds = datasets[golden["dataset"]]
+    ora = common.run_dump(oracle_bin, ds, tmp_path / "o.bin", golden["options"], extra=["--rng", "philox", "--seed", "3"])
+    with capi.Hera(0) as h:
+        h.set_option("radix_digit_bits", digit)
+        gpu = pipeline.run_hot_path(ds, golden["options"], seed=3, hera=h, batched=True)
+    common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + ["rank_0", "rank_1"] + PATH_SECTIONS + GROUP_SECTIONS, f"digit {digit}")
+
+
 def test_optimistic_row_reservation_and_its_overflow(oracle_bin, datasets, tmp_path):
     """Large loads do not reserve bytes / 24 rows: the first one counts its tokens, later ones on the same context try with the
     rows the context already holds and are repeated (with the count) when the text keeps more rows than that.  Forced here at
