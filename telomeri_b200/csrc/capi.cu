@@ -204,6 +204,7 @@ int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
     else if (k == "walk_variant") c.opt_walk_variant = static_cast<int>(value);
     else if (k == "parse_variant") c.opt_parse_variant = static_cast<int>(value);
     else if (k == "walk_smem_bitmap") c.opt_walk_smem_bitmap = value != 0;
+    else if (k == "verify_ctas_per_sm") c.opt_verify_ctas_per_sm = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(8, value)));
     else if (k == "radix_digit_bits") c.opt_radix_digit_bits = static_cast<int>(value);
     else if (k == "parse_count_rows") c.opt_parse_count_rows = std::max<int64_t>(1, value);
     else if (k == "walk_hints_reset") { for (auto &a : c.walk_work_hint) for (uint64_t &w : a) w = 0; }

@@ -152,6 +152,7 @@ struct Ctx {
     std::vector<std::unique_ptr<LoadedText>> texts;
     std::vector<std::unique_ptr<LoadedText>> text_pool;   // buffers of texts dropped by hera_graph_reset, reused by the next loads
     KeptTable kept;                   // LOCAL rows: the kept overlaps this rank parsed itself (all of them on a single rank)
+    int opt_verify_ctas_per_sm = 4;   // resident CTAs per SM of the name verification (side stream beside the CSR build)
     int opt_radix_digit_bits = 0;   // 0 = chosen from the key width; 8..11 forces the digit width of radix_sort_pairs (tests)
     int64_t opt_parse_count_rows = 64ll << 20;   // loads whose worst-case row count (bytes / 24) exceeds this size their rows by counting tokens / by what the context already holds
     bool parse_force_count = false;   // the optimistic row reservation of a load overflowed: count the tokens first this time

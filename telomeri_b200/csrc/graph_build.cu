@@ -184,21 +184,24 @@ __global__ void name_merge_kernel(uint64_t bytes, int parts, const char *__restr
 __global__ void intern_verify_kernel(uint64_t L, const uint32_t *__restrict__ e_q, const uint32_t *__restrict__ e_t,
                                      const uint64_t *__restrict__ qname, const uint64_t *__restrict__ tname, const uint64_t *__restrict__ name_off_tab,
                                      const char *__restrict__ blob, TextPtrs texts, unsigned int *collision) {
-    const uint64_t e = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (e >= L) return;
-    const uint64_t mine[2] = {qname[e], tname[e]};
-    const uint32_t ids[2] = {e_q[e], e_t[e]};
+    // a small persistent grid (grid-stride loop): the kernel runs on a side stream beside the CSR build; a grid of L / 256 CTAs
+    // would all be issued before the main stream's next kernels, which then wait for it
+    const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+    for (uint64_t e = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < L; e += stride) {
+        const uint64_t mine[2] = {qname[e], tname[e]};
+        const uint32_t ids[2] = {e_q[e], e_t[e]};
 #pragma unroll
-    for (int s = 0; s < 2; s++) {
-        const uint64_t o = name_off_tab[ids[s]];
-        const uint32_t len = static_cast<uint32_t>(name_off_tab[ids[s] + 1] - o);
-        bool same = len == name_len(mine[s]);
-        if (same) {
-            const char *a = blob + o;
-            const uint8_t *b = texts.p[name_file(mine[s])] + name_off(mine[s]);
-            for (uint32_t i = 0; i < len; i++) if (static_cast<uint8_t>(a[i]) != b[i]) { same = false; break; }
+        for (int s = 0; s < 2; s++) {
+            const uint64_t o = name_off_tab[ids[s]];
+            const uint32_t len = static_cast<uint32_t>(name_off_tab[ids[s] + 1] - o);
+            bool same = len == name_len(mine[s]);
+            if (same) {
+                const char *a = blob + o;
+                const uint8_t *b = texts.p[name_file(mine[s])] + name_off(mine[s]);
+                for (uint32_t i = 0; i < len; i++) if (static_cast<uint8_t>(a[i]) != b[i]) { same = false; break; }
+            }
+            if (!same) *collision = 1;
         }
-        if (!same) *collision = 1;
     }
 }
 
@@ -860,7 +863,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
                 HERA_CUDA(cudaEventRecord(names_ready, c.stream));
                 HERA_CUDA(cudaStreamWaitEvent(c.aux_streams[0], names_ready, 0));
                 cudaEventDestroy(names_ready);
-                intern_verify_kernel<<<div_up(L, 256), 256, 0, c.aux_streams[0]>>>(L, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p, g.node_name_off.p,
+                intern_verify_kernel<<<std::min<unsigned>(div_up(L, 256), 148u * static_cast<unsigned>(c.opt_verify_ctas_per_sm)), 256, 0, c.aux_streams[0]>>>(L, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p, g.node_name_off.p,
                                                                                   g.node_names.p, tp, d_late);
                 c.launches.count++;
                 HERA_CUDA(cudaGetLastError());
