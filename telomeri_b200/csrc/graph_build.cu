@@ -359,9 +359,12 @@ __device__ __forceinline__ float metric_value(int metric, float es, float os) {
         default: return __fsqrt_rn(os);
     }
 }
-__device__ __forceinline__ float slot_metric(const uint4 *__restrict__ adj4, int metric, uint32_t s) {
-    const uint4 e = adj4[s];
-    return metric_value(metric, __uint_as_float(e.y), __uint_as_float(e.z));
+// The rank kernels read the 8-byte views {neighbour | anchor bit, score} (node_exact_kernel wrote them just before): a list
+// is read once per metric and once for the canonical slots, 8 bytes per entry instead of the 16-byte walk entry.
+struct SlotView { const uint2 *es, *os; };
+__device__ __forceinline__ float slot_metric(const SlotView &v, int metric, uint32_t s) {
+    const float x = __uint_as_float(((metric & 1) ? v.os : v.es)[s].y);   // metrics: 0 ES, 1 OS, 2 sqrt(ES), 3 sqrt(OS)
+    return metric >= 2 ? __fsqrt_rn(x) : x;
 }
 
 // K4b: canonical slots and rank permutations of every node's list, staged in shared memory.
@@ -395,7 +398,7 @@ __device__ __forceinline__ uint64_t rank_key(float v, uint32_t i, bool &nan) {
     return (static_cast<uint64_t>(u) << 32) | (0xffffffffu - i);
 }
 
-__device__ void rank_by_counting(const uint4 *__restrict__ adj4, int metric, uint32_t base, uint32_t deg, const RankPtrs &out) {
+__device__ void rank_by_counting(const SlotView adj4, int metric, uint32_t base, uint32_t deg, const RankPtrs &out) {
     for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) {
         const float mi = slot_metric(adj4, metric, base + i);
         uint32_t r = 0;
@@ -415,7 +418,7 @@ __device__ void rank_by_counting(const uint4 *__restrict__ adj4, int metric, uin
 // A list with a NaN is ranked with float compares (what `>` does with a NaN is not an order).
 constexpr int RB_WARPS = 4, RB_THREADS = RB_WARPS * 32;
 
-__device__ void rank_by_counting_warp(const uint4 *__restrict__ adj4, int metric, uint32_t base, uint32_t deg, const RankPtrs &out) {
+__device__ void rank_by_counting_warp(const SlotView adj4, int metric, uint32_t base, uint32_t deg, const RankPtrs &out) {
     for (uint32_t i = threadIdx.x & 31u; i < deg; i += 32) {
         const float mi = slot_metric(adj4, metric, base + i);
         uint32_t r = 0;
@@ -437,7 +440,7 @@ struct RankSmem {
 };
 
 template <int GROUP, int CAP>
-__device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const uint4 *__restrict__ adj4, uint32_t metrics_mask, const RankPtrs &rank,
+__device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const SlotView adj4, uint32_t metrics_mask, const RankPtrs &rank,
                                                  uint32_t base, uint32_t deg) {
     constexpr int PER = CAP / GROUP;
     static_assert(GROUP == 32 || GROUP == RB_THREADS, "a warp or the CTA per node");
@@ -453,7 +456,7 @@ __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const
         for (uint32_t i = t; i < T; i += GROUP) { hkey[i] = 0xffffffffu; hval[i] = 0xffffffffu; }
         group_sync();
         for (uint32_t i = t; i < deg; i += GROUP) {
-            const uint32_t nbr = adj4[base + i].x;
+            const uint32_t nbr = adj4.es[base + i].x;
             uint32_t h = (nbr * 2654435761u) >> shift;
             for (;;) {
                 const uint32_t prev = atomicCAS(&hkey[h], 0xffffffffu, nbr);
@@ -463,7 +466,7 @@ __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const
         }
         group_sync();
         for (uint32_t i = t; i < deg; i += GROUP) {
-            const uint32_t nbr = adj4[base + i].x;
+            const uint32_t nbr = adj4.es[base + i].x;
             uint32_t h = (nbr * 2654435761u) >> shift;
             while (hkey[h] != nbr) h = (h + 1) & (T - 1);
             rank.put_canon(base + i, base + hval[h]);
@@ -580,7 +583,7 @@ __device__ __forceinline__ void rank_bucket_node(RankSmem<GROUP, CAP> &sm, const
 // leaves at once).  Two instances (CAP 256 and 512): the shorter lists are the majority and need half the shared memory
 // and half the unrolled iterations.
 template <int CAP, int LOW>
-__global__ void __launch_bounds__(RB_THREADS) rank_warp_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t metrics_mask,
+__global__ void __launch_bounds__(RB_THREADS) rank_warp_kernel(const uint32_t *__restrict__ off, const SlotView adj4, uint32_t metrics_mask,
                                                                RankPtrs rank, uint32_t node0, uint32_t nodes) {
     __shared__ __align__(16) RankSmem<32, CAP> sm;
     const uint32_t xi = blockIdx.x * RB_WARPS + (threadIdx.x >> 5);
@@ -612,7 +615,7 @@ __device__ __forceinline__ uint32_t select_long_nodes(const uint32_t *__restrict
 // Lists of LOW + 1 .. CAP entries, the whole CTA per node (instances: CAP 1024 and 4096; dynamic shared memory).
 constexpr int RS_SMALL = 512, RS_MID = 4096;
 template <int CAP, int LOW>
-__global__ void __launch_bounds__(RB_THREADS) rank_cta_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t metrics_mask,
+__global__ void __launch_bounds__(RB_THREADS) rank_cta_kernel(const uint32_t *__restrict__ off, const SlotView adj4, uint32_t metrics_mask,
                                                               RankPtrs rank, uint32_t node0, uint32_t nodes) {
     extern __shared__ __align__(16) unsigned char rank_cta_smem[];
     RankSmem<RB_THREADS, CAP> &sm = *reinterpret_cast<RankSmem<RB_THREADS, CAP> *>(rank_cta_smem);
@@ -627,7 +630,7 @@ __global__ void __launch_bounds__(RB_THREADS) rank_cta_kernel(const uint32_t *__
 }
 
 // Lists longer than RS_MID entries (hubs): counting with float compares from global memory.
-__global__ void __launch_bounds__(RK_THREADS) rank_long_kernel(const uint32_t *__restrict__ off, const uint4 *__restrict__ adj4, uint32_t metrics_mask,
+__global__ void __launch_bounds__(RK_THREADS) rank_long_kernel(const uint32_t *__restrict__ off, const SlotView adj4, uint32_t metrics_mask,
                                                                RankPtrs rank, uint32_t node0, uint32_t nodes) {
     __shared__ uint32_t s_nodes[RANK_CHUNK], s_n;
     const uint32_t n = select_long_nodes<RS_MID, 0>(off, node0, nodes, s_nodes, &s_n);
@@ -635,9 +638,9 @@ __global__ void __launch_bounds__(RK_THREADS) rank_long_kernel(const uint32_t *_
         const uint32_t x = s_nodes[q];
         const uint32_t base = off[x], deg = off[x + 1] - base;
         for (uint32_t i = threadIdx.x; i < deg; i += RK_THREADS) {
-            const uint32_t ni = adj4[base + i].x;
+            const uint32_t ni = adj4.es[base + i].x;
             uint32_t j = 0;
-            while (adj4[base + j].x != ni) j++;
+            while (adj4.es[base + j].x != ni) j++;
             rank.put_canon(base + i, base + j);
         }
         for (int m = 0; m < 4; m++)
@@ -997,20 +1000,21 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             g.rank_ready[m] = true;
         }
         rp.canon[0] = g.canon.p;
+        const SlotView views{g.a8[0].p, g.a8[1].p};
         if (my_nodes) {
-            HERA_LAUNCH(c, (rank_warp_kernel<256, 0>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, (rank_warp_kernel<256, 0>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, views, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
-            HERA_LAUNCH(c, (rank_warp_kernel<RS_SMALL, 256>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, (rank_warp_kernel<RS_SMALL, 256>), div_up(my_nodes, RB_WARPS), RB_THREADS, 0, g.adj_off.p, views, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
             log.mark("rank small");
             constexpr size_t smem1 = sizeof(RankSmem<RB_THREADS, 1024>), smem2 = sizeof(RankSmem<RB_THREADS, RS_MID>);
             HERA_CUDA(cudaFuncSetAttribute(rank_cta_kernel<RS_MID, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem2)));
-            HERA_LAUNCH(c, (rank_cta_kernel<1024, RS_SMALL>), div_up(my_nodes, RANK_CHUNK), RB_THREADS, smem1, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, (rank_cta_kernel<1024, RS_SMALL>), div_up(my_nodes, RANK_CHUNK), RB_THREADS, smem1, g.adj_off.p, views, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
-            HERA_LAUNCH(c, (rank_cta_kernel<RS_MID, 1024>), div_up(my_nodes, RANK_CHUNK), RB_THREADS, smem2, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, (rank_cta_kernel<RS_MID, 1024>), div_up(my_nodes, RANK_CHUNK), RB_THREADS, smem2, g.adj_off.p, views, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
             log.mark("rank mid");
-            HERA_LAUNCH(c, rank_long_kernel, div_up(my_nodes, RANK_CHUNK), RK_THREADS, 0, g.adj_off.p, g.adj4.p, metrics_mask, rp,
+            HERA_LAUNCH(c, rank_long_kernel, div_up(my_nodes, RANK_CHUNK), RK_THREADS, 0, g.adj_off.p, views, metrics_mask, rp,
                         static_cast<uint32_t>(n_lo), my_nodes);
         }
         log.mark("rank long");
