@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <chrono>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "ctx.cuh"
@@ -144,6 +145,10 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
     const uint32_t wslot = blockIdx.x * WK_WARPS + wib;
     uint32_t *g_bm = sc.bitmap + (SMEM_BM ? 0ull : static_cast<uint64_t>(wslot) * sc.words);
     uint32_t *bm = SMEM_BM ? s_bm : g_bm;
+    // the probe address is bmw + 4 (nb >> 5): keep the warp's bitmap base in registers (the compiler otherwise rebuilds
+    // slab index x words + base from the kernel parameters for every probe: 7 instructions)
+    const uint32_t *bmw = bm;
+    if (!SMEM_BM) asm volatile("" : "+l"(bmw));
     uint32_t *nodes = sc.nodes + static_cast<uint64_t>(wslot) * sc.cap;
     uint32_t *slots = sc.slots + static_cast<uint64_t>(wslot) * sc.cap;
     uint32_t *vlog = sc.vlog + static_cast<uint64_t>(wslot) * sc.cap;
@@ -179,38 +184,49 @@ __global__ void __launch_bounds__(WK_THREADS, MIN_CTAS) walk_mc_kernel(WalkGraph
             int forced = -1;
             bool any_cand = false;
             uint32_t forced_nbw = 0;
-            // four 32-entry chunks in flight per round trip: the step latency of a single walk is what
-            // bounds the kernel (the longest walk is its critical path), not the entries per second
-            for (uint32_t c0 = 0; c0 < deg && forced < 0; c0 += 32 * WK_MLP) {
-                uint2 a[WK_MLP];
+            // WK_MLP 32-entry chunks in flight per round trip.  The loop body is branch-free inside a chunk group (ncu on
+            // configs[3]: the kernel is issue-bound, 94 warp instructions per 32 entries with the forced-edge test as a branch
+            // per chunk and the bitmap address recomputed per probe): per-lane pointers are hoisted, the probe of an entry
+            // behind the list's end reads nothing and sees "visited", the forced-edge ballots are looked at once per group.
+            const uint2 *lp = g.a8 + base + lane;
+            float *cp = s_cval + lane;
+            // (two instances of the loop: only nodes next to an anchor -- few -- need the forced-edge ballots)
+            auto scan_list = [&](auto with_force) {
+                constexpr bool FORCE = decltype(with_force)::value;
+                for (uint32_t c0 = 0; c0 < deg; c0 += 32 * WK_MLP) {
+                    uint2 a[WK_MLP];
 #pragma unroll
-                for (int j = 0; j < WK_MLP; j++) {
-                    const uint32_t k = c0 + 32 * j + lane;
-                    a[j] = k < deg ? __ldg(g.a8 + base + k) : make_uint2(0, 0);
-                }
+                    for (int j = 0; j < WK_MLP; j++) a[j] = c0 + 32 * j + lane < deg ? __ldg(lp + c0 + 32 * j) : make_uint2(0, 0);
+                    uint32_t fb[WK_MLP];
 #pragma unroll
-                for (int j = 0; j < WK_MLP; j++) {
-                    const uint32_t k = c0 + 32 * j + lane;
-                    if (c0 + 32 * j >= deg || forced >= 0) continue;   // warp-uniform
-                    const bool valid = k < deg;
-                    const uint32_t nb = a[j].x & 0x7fffffffu;
-                    const bool force = may_force && valid && (a[j].x >> 31) && nb != start;
-                    const uint32_t fb = may_force ? __ballot_sync(0xffffffffu, force) : 0u;
-                    if (fb) {
-                        const int src = __ffs(fb) - 1;
-                        forced = static_cast<int>(c0) + 32 * j + src;
-                        forced_nbw = __shfl_sync(0xffffffffu, a[j].x, src);
-                        continue;
+                    for (int j = 0; j < WK_MLP; j++) {
+                        const uint32_t k = c0 + 32 * j + lane;
+                        const bool valid = k < deg;
+                        const uint32_t nbw = a[j].x, nb = nbw & 0x7fffffffu;
+                        const uint32_t word = valid ? bmw[nb >> 5] : 0xffffffffu;
+                        const bool cand = ((word >> (nb & 31u)) & 1u) == 0u;
+                        fb[j] = FORCE ? __ballot_sync(0xffffffffu, valid && (nbw >> 31) && nb != start) : 0u;
+                        any_cand |= cand;
+                        // entry k keeps its place in the cache: its metric if it is a candidate, else -0.0f
+                        // (adding -0.0 to a sum changes nothing, and the sign bit tells the two apart)
+                        float v = __uint_as_float(a[j].y);
+                        if (g.sqrt_metric) v = __fsqrt_rn(v);
+                        if (k < WK_CACHE) cp[c0 + 32 * j] = cand ? v : -0.0f;
                     }
-                    const bool cand = valid && !bm_get<SMEM_BM>(s_bm, g_bm, nb);
-                    any_cand |= cand;
-                    // entry k keeps its place in the cache: its metric if it is a candidate, else -0.0f
-                    // (adding -0.0 to a sum changes nothing, and the sign bit tells the two apart)
-                    float v = __uint_as_float(a[j].y);
-                    if (g.sqrt_metric) v = __fsqrt_rn(v);
-                    if (k < WK_CACHE) s_cval[k] = cand ? v : -0.0f;
+                    if (FORCE) {   // first forced edge of the group, if any: entries behind it do not matter
+#pragma unroll
+                        for (int j = 0; j < WK_MLP; j++) {
+                            if (forced < 0 && fb[j]) {
+                                const int src = __ffs(fb[j]) - 1;
+                                forced = static_cast<int>(c0) + 32 * j + src;
+                                forced_nbw = __shfl_sync(0xffffffffu, a[j].x, src);
+                            }
+                        }
+                        if (forced >= 0) break;
+                    }
                 }
-            }
+            };
+            if (may_force) scan_list(std::true_type{}); else scan_list(std::false_type{});
             const uint32_t ncand = __any_sync(0xffffffffu, any_cand) ? 1u : 0u;   // only "none / some" matters below
             examined += deg;
             int pick = -1;
