@@ -102,7 +102,10 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-__device__ __forceinline__ void emit_path(const WalkOut &o, uint32_t local, const uint32_t *nodes, const uint32_t *slots, uint32_t n_nodes, int64_t len) {
+// canon != nullptr: slots[1..] still hold the slots the greedy walk chose; the path stores their canonical slots (first
+// parallel edge, src/PathManager.cpp:340-347) -- looked up here, once per accepted path, instead of inside every step.
+__device__ __forceinline__ void emit_path(const WalkOut &o, uint32_t local, const uint32_t *nodes, const uint32_t *slots, uint32_t n_nodes, int64_t len,
+                                          const uint32_t *__restrict__ canon = nullptr) {
     const uint32_t lane = lane_id();
     unsigned long long base = 0;
     if (lane == 0) base = atomicAdd(o.pool_used, static_cast<unsigned long long>(n_nodes));
@@ -110,7 +113,7 @@ __device__ __forceinline__ void emit_path(const WalkOut &o, uint32_t local, cons
     if (lane == 0) { o.res_n[local] = n_nodes; o.res_off[local] = base; o.res_len[local] = len; }
     if (base + n_nodes <= o.pool_cap) {
         for (uint32_t i = lane; i < n_nodes; i += 32) o.pool_nodes[base + i] = nodes[i];
-        for (uint32_t i = lane; i + 1 < n_nodes; i += 32) o.pool_slots[base + i] = slots[i];
+        for (uint32_t i = lane; i + 1 < n_nodes; i += 32) o.pool_slots[base + i] = (canon && i) ? canon[slots[i]] : slots[i];
     }
 }
 
@@ -428,7 +431,7 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
                 const uint32_t next = nbw & 0x7fffffffu;
                 if (nlog >= sc.cap) { if (lane == 0) *o.overflow = 1u; break; }
                 if (lane == 0) {
-                    slots[n_nodes - 1] = g.canon[chosen];
+                    slots[n_nodes - 1] = static_cast<uint32_t>(chosen);   // canonical slot: when the path is accepted (emit_path)
                     bm[cur >> 5] |= 1u << (cur & 31);
                     nodes[n_nodes] = next;
                     vlog[nlog] = next;
@@ -443,11 +446,11 @@ __global__ void __launch_bounds__(WK_THREADS) walk_det_kernel(WalkGraph g, WalkS
             if (reached) {
                 // src/Path.cpp:6-16 over the final edge list
                 long long part = 0;
-                for (uint32_t i = lane; i + 2 < n_nodes; i += 32) part += slot_delta(g, slots[i]);
+                for (uint32_t i = lane; i + 2 < n_nodes; i += 32) part += slot_delta(g, i ? g.canon[slots[i]] : slots[i]);
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
                 const long long len = static_cast<long long>(g.node_len[start]) + part;
-                if (len >= 0) emit_path(o, local, nodes, slots, n_nodes, len);
+                if (len >= 0) emit_path(o, local, nodes, slots, n_nodes, len, g.canon);
             }
         }
         if (lane == 0) o.res_draws[local] = 0;
