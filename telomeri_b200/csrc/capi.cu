@@ -63,9 +63,8 @@ static uint64_t digest_host_words(const std::vector<T> &v) {
 
 static void digest_tables(Ctx &c, uint64_t *out) {
     for (int i = 0; i < HERA_DIGEST_WORDS; i++) out[i] = 0;
-    unsigned long long *d = nullptr;
-    HERA_CUDA(cudaMallocAsync(&d, HERA_DIGEST_WORDS * sizeof(unsigned long long), c.stream));
-    HERA_CUDA(cudaMemsetAsync(d, 0, HERA_DIGEST_WORDS * sizeof(unsigned long long), c.stream));
+    TempPool tmp(c.stream);
+    unsigned long long *d = tmp.zeroed<unsigned long long>(HERA_DIGEST_WORDS);
     const GraphTables &g = c.g;
     if (g.ready && g.E) {
         const RowView rows = rows_view(c);   // (collective on a sharded context)
@@ -88,7 +87,6 @@ static void digest_tables(Ctx &c, uint64_t *out) {
     }
     HERA_CUDA(cudaMemcpyAsync(out, d, HERA_DIGEST_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
-    HERA_CUDA(cudaFreeAsync(d, c.stream));
     if (c.groups_valid) {   // the group tables are marshalled on the host by hera_groups
         const auto &m = c.grm;
         out[16] = digest_host_words(m.pair_a1); out[17] = digest_host_words(m.pair_a2); out[18] = digest_host_words(m.pair_sorted);
@@ -287,24 +285,15 @@ static void commit_text(Ctx &c, std::unique_ptr<hera::LoadedText> t, int anchors
 static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard,
                         hera_load_result *out) {
     std::unique_ptr<hera::LoadedText> t = acquire_text(c, n);
-    cudaEvent_t e0, e1;
-    HERA_CUDA(cudaEventCreate(&e0));
-    HERA_CUDA(cudaEventCreate(&e1));
+    hera::Events<2> ev;
+    const cudaEvent_t e0 = ev[0], e1 = ev[1];
     HERA_CUDA(cudaEventRecord(e0, c.stream));
     if (n) HERA_CUDA(cudaMemcpyAsync(t->bytes.p, src, n, kind, c.stream));
     HERA_CUDA(cudaEventRecord(e1, c.stream));
     hera_load_result tmp{};
-    try {
-        commit_text(c, std::move(t), anchors, test_load_num, shard, &tmp);
-    } catch (...) {
-        cudaEventDestroy(e0);
-        cudaEventDestroy(e1);
-        throw;
-    }
+    commit_text(c, std::move(t), anchors, test_load_num, shard, &tmp);
     float copy_ms = 0;
     HERA_CUDA(cudaEventElapsedTime(&copy_ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     tmp.h2d_ms = kind == cudaMemcpyHostToDevice ? copy_ms : 0.0f;
     if (out) *out = tmp;
 }

@@ -4,6 +4,7 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -30,6 +31,56 @@ struct Error {
     do {                                               \
         if (!(cond)) throw ::hera::Error{(code), (text)}; \
     } while (0)
+
+// Stream-ordered temporaries, freed (stream-ordered) when the scope ends, exception or not.
+struct TempPool {
+    cudaStream_t s;
+    std::vector<void *> ptrs;
+    explicit TempPool(cudaStream_t st) : s(st) {}
+    ~TempPool() { for (void *p : ptrs) if (p) cudaFreeAsync(p, s); }
+    TempPool(const TempPool &) = delete;
+    TempPool &operator=(const TempPool &) = delete;
+    template <typename T>
+    T *get(uint64_t n) {
+        void *p = nullptr;
+        HERA_CUDA(cudaMallocAsync(&p, std::max<uint64_t>(n, 1) * sizeof(T), s));
+        ptrs.push_back(p);
+        return static_cast<T *>(p);
+    }
+    void release(void *p) {   // before the scope ends (stream-ordered like the rest)
+        for (auto &q : ptrs)
+            if (q == p && p) { cudaFreeAsync(p, s); q = nullptr; }
+    }
+    template <typename T>
+    T *zeroed(uint64_t n) {
+        T *p = get<T>(n);
+        HERA_CUDA(cudaMemsetAsync(p, 0, std::max<uint64_t>(n, 1) * sizeof(T), s));
+        return p;
+    }
+};
+
+// N CUDA events, destroyed when the scope ends, exception or not.
+template <int N>
+struct Events {
+    cudaEvent_t e[N] = {};
+    explicit Events(unsigned flags = cudaEventDefault) {
+        for (int i = 0; i < N; i++) {
+            cudaError_t err = cudaEventCreateWithFlags(&e[i], flags);
+            if (err != cudaSuccess) {
+                destroy();
+                throw ::hera::Error{2, std::string("cudaEventCreateWithFlags: ") + cudaGetErrorString(err)};
+            }
+        }
+    }
+    ~Events() { destroy(); }
+    Events(const Events &) = delete;
+    Events &operator=(const Events &) = delete;
+    cudaEvent_t operator[](int i) const { return e[i]; }
+    void destroy() {
+        for (int i = 0; i < N; i++)
+            if (e[i]) { cudaEventDestroy(e[i]); e[i] = nullptr; }
+    }
+};
 
 // Growable device array.  grow() keeps the contents when asked to.
 template <typename T>

@@ -180,11 +180,12 @@ void Exchange::gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, u
     bool any_inplace = false;
     for (int k = 0; k < ncols; k++) any_inplace = any_inplace || cols[k].src == nullptr;
     const bool staged = any_inplace && mine0 != n0 + displs[rank] && counts[rank] != 0;
+    TempPool pool(c.stream);
     char *tmp0 = nullptr;
     if (staged) {
         size_t bytes = 0;
         for (int k = 0; k < ncols; k++) bytes += (counts[rank] * cols[k].elem + 255) / 256 * 256;
-        HERA_CUDA(cudaMallocAsync(&tmp0, bytes, c.stream));
+        tmp0 = pool.get<char>(bytes);
     }
     char *tmp = tmp0;
     begin_batch();
@@ -199,7 +200,6 @@ void Exchange::gather_rows(Ctx &c, const Column *cols, int ncols, uint64_t n0, u
         all_gatherv(c, send, col, counts, displs, cols[k].elem);
     }
     end_batch();
-    if (tmp0) HERA_CUDA(cudaFreeAsync(tmp0, c.stream));
 }
 
 namespace {

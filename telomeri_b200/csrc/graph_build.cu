@@ -714,24 +714,15 @@ struct PhaseLog {
     }
 };
 
-// Stream-ordered temporaries, freed (stream-ordered) when the scope ends, exception or not.
-struct TempPool {
+// An event a later point of a scope waits for.  Left early (exception), the scope still makes the stream wait for it
+// before the temporaries declared in front of the guard go back to the pool (a kernel on a side stream may read them).
+struct PendingEvent {
     cudaStream_t s;
-    std::vector<void *> ptrs;
-    explicit TempPool(cudaStream_t st) : s(st) {}
-    ~TempPool() { for (void *p : ptrs) cudaFreeAsync(p, s); }
-    template <typename T>
-    T *get(uint64_t n) {
-        void *p = nullptr;
-        HERA_CUDA(cudaMallocAsync(&p, std::max<uint64_t>(n, 1) * sizeof(T), s));
-        ptrs.push_back(p);
-        return static_cast<T *>(p);
-    }
-    template <typename T>
-    T *zeroed(uint64_t n) {
-        T *p = get<T>(n);
-        HERA_CUDA(cudaMemsetAsync(p, 0, std::max<uint64_t>(n, 1) * sizeof(T), s));
-        return p;
+    cudaEvent_t e = nullptr;
+    ~PendingEvent() {
+        if (!e) return;
+        cudaStreamWaitEvent(s, e, 0);
+        cudaEventDestroy(e);
     }
 };
 }  // namespace
@@ -761,7 +752,8 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         TempPool tmp(c.stream);
         uint64_t N = 0;
         uint32_t *d_late = tmp.zeroed<uint32_t>(4);   // [0] collision flag, [1] anchors, [2] max degree: looked at when the build is over
-        cudaEvent_t verify_done = nullptr;
+        PendingEvent verify_guard{c.stream};
+        cudaEvent_t &verify_done = verify_guard.e;
         TextPtrs tp{};
         for (size_t i = 0; i < c.texts.size(); i++) tp.p[i] = c.texts[i]->data();
         if (!c.cache_loaded) {
@@ -777,8 +769,8 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
             std::vector<uint64_t> ecount(ranks), edispl(ranks);
             c.h_counters.reserve(64 + ranks);
             for (;;) {
-                HERA_CUDA(cudaMallocAsync(&keys, cap * sizeof(unsigned long long), c.stream));
-                HERA_CUDA(cudaMallocAsync(&minpos, cap * sizeof(uint32_t), c.stream));
+                keys = tmp.get<unsigned long long>(cap);
+                minpos = tmp.get<uint32_t>(cap);
                 HERA_CUDA(cudaMemsetAsync(keys, 0, cap * sizeof(unsigned long long), c.stream));
                 HERA_CUDA(cudaMemsetAsync(minpos, 0xff, cap * sizeof(uint32_t), c.stream));
                 HERA_CUDA(cudaMemsetAsync(d_small, 0, 8 * sizeof(unsigned int), c.stream));
@@ -794,13 +786,11 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
                 T = 0;
                 for (int r = 0; r < ranks; r++) { ecount[r] = all[2 * r]; edispl[r] = T; T += ecount[r]; overflow = overflow || all[2 * r + 1] != 0; }
                 if (!overflow && T * 2 <= cap) break;
-                HERA_CUDA(cudaFreeAsync(keys, c.stream));
-                HERA_CUDA(cudaFreeAsync(minpos, c.stream));
+                tmp.release(keys);
+                tmp.release(minpos);
                 while (cap < 4 * T) cap <<= 1;   // table too full: probe chains get long, rebuild larger
                 if (overflow) cap <<= 1;
             }
-            tmp.ptrs.push_back(keys);
-            tmp.ptrs.push_back(minpos);
             log.mark("insert");
             // this rank's distinct names -> entries, all ranks' entries -> every table
             const uint64_t mine_n = ecount[me];
@@ -861,11 +851,11 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
                 c.aux_streams.push_back(st);
             }
             if (L) {
-                cudaEvent_t names_ready;
-                HERA_CUDA(cudaEventCreateWithFlags(&names_ready, cudaEventDisableTiming));
-                HERA_CUDA(cudaEventRecord(names_ready, c.stream));
-                HERA_CUDA(cudaStreamWaitEvent(c.aux_streams[0], names_ready, 0));
-                cudaEventDestroy(names_ready);
+                {
+                    Events<1> names_ready(cudaEventDisableTiming);
+                    HERA_CUDA(cudaEventRecord(names_ready[0], c.stream));
+                    HERA_CUDA(cudaStreamWaitEvent(c.aux_streams[0], names_ready[0], 0));
+                }
                 intern_verify_kernel<<<std::min<unsigned>(div_up(L, 256), 148u * static_cast<unsigned>(c.opt_verify_ctas_per_sm)), 256, 0, c.aux_streams[0]>>>(L, g.e_q.p, g.e_t.p, c.kept.qname.p, c.kept.tname.p, g.node_name_off.p,
                                                                                   g.node_names.p, tp, d_late);
                 c.launches.count++;
@@ -983,7 +973,8 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         } else {
             g.canon.reserve(S);
         }
-        cudaEvent_t cuts_ready = nullptr;
+        PendingEvent cuts_guard{c.stream};
+        cudaEvent_t &cuts_ready = cuts_guard.e;
         if (ranks > 1 && !rank_pushed) {   // slot ranges of the ranks' node ranges: read now, needed (on the host) once the rank kernels are queued
             uint64_t *d_cut = tmp.get<uint64_t>(ranks + 1);
             HERA_LAUNCH(c, node_cut_kernel, 1, 64, 0, g.adj_off.p, N, ranks, d_cut);
@@ -1026,6 +1017,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         } else if (ranks > 1) {
             HERA_CUDA(cudaEventSynchronize(cuts_ready));   // the slice boundaries left the device before the rank kernels started
             cudaEventDestroy(cuts_ready);
+            cuts_ready = nullptr;
             const uint64_t *cut = c.h_counters.p + 40;
             std::vector<uint64_t> counts(ranks), displs(ranks);
             for (int r = 0; r < ranks; r++) { displs[r] = cut[r]; counts[r] = cut[r + 1] - cut[r]; }
@@ -1040,6 +1032,7 @@ void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out) {
         if (verify_done) {
             HERA_CUDA(cudaStreamWaitEvent(c.stream, verify_done, 0));
             cudaEventDestroy(verify_done);
+            verify_done = nullptr;
         }
         HERA_CUDA(cudaMemcpyAsync(c.h_counters.p + 36, d_late, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
         HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -1154,8 +1147,8 @@ void export_graph(Ctx &c, hera_graph_view *out) {
         d2h(c, m.node_len, g.node_len.p, N);
         d2h(c, m.node_anchor, g.node_anchor.p, N);
         // names
-        uint64_t *offs = nullptr; uint8_t *tmp8 = nullptr; uint32_t *tmp32 = nullptr;
-        HERA_CUDA(cudaMallocAsync(&offs, (N + 1) * sizeof(uint64_t), c.stream));
+        TempPool tmp(c.stream);
+        uint64_t *offs = tmp.get<uint64_t>(N + 1);
         d2h(c, m.node_name_off, g.node_name_off.p, N + 1);
         m.node_names.reserve(g.name_bytes + 1);
         if (g.name_bytes) HERA_CUDA(cudaMemcpyAsync(m.node_names.p, g.node_names.p, g.name_bytes, cudaMemcpyDeviceToHost, c.stream));
@@ -1163,8 +1156,8 @@ void export_graph(Ctx &c, hera_graph_view *out) {
         d2h(c, m.e_q, rv.e_q, E); d2h(c, m.e_t, rv.e_t, E);
         d2h(c, m.e_qs, rv.qs, E); d2h(c, m.e_qe, rv.qe, E); d2h(c, m.e_ts, rv.ts, E); d2h(c, m.e_te, rv.te, E);
         d2h(c, m.e_os, rv.os, E); d2h(c, m.e_si, rv.si, E); d2h(c, m.e_es, rv.es, E);
-        HERA_CUDA(cudaMallocAsync(&tmp8, S + 1, c.stream));
-        HERA_CUDA(cudaMallocAsync(&tmp32, (S + 1) * sizeof(uint32_t), c.stream));
+        uint8_t *tmp8 = tmp.get<uint8_t>(S + 1);
+        uint32_t *tmp32 = tmp.get<uint32_t>(S + 1);
         HERA_LAUNCH(c, export_strand_kernel, div_up(E, 256), 256, 0, E, rv.flags, tmp8);
         d2h(c, m.e_strand, tmp8, E);
         HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -1175,8 +1168,6 @@ void export_graph(Ctx &c, hera_graph_view *out) {
         d2h(c, m.canon, g.canon.p, S);
         for (int k = 0; k < 4; k++) if (g.rank_ready[k]) d2h(c, m.rank[k], g.rank[k].p, S);
         HERA_CUDA(cudaStreamSynchronize(c.stream));
-        HERA_CUDA(cudaFreeAsync(offs, c.stream));
-        HERA_CUDA(cudaFreeAsync(tmp8, c.stream)); HERA_CUDA(cudaFreeAsync(tmp32, c.stream));
     }
     out->node_len = m.node_len.p; out->node_anchor = m.node_anchor.p; out->node_name_off = m.node_name_off.p; out->node_names = m.node_names.p;
     out->e_q = m.e_q.p; out->e_t = m.e_t.p; out->e_qs = m.e_qs.p; out->e_qe = m.e_qe.p; out->e_ts = m.e_ts.p; out->e_te = m.e_te.p;
@@ -1307,13 +1298,11 @@ void load_graph_cache(Ctx &c, const char *path) {
     get_array(c, f, g.node_len, N, buf, cs); get_array(c, f, g.node_anchor, N, buf, cs);
     get_array(c, f, g.node_name_off, N + 1, buf, cs); get_array(c, f, g.node_names, h.name_bytes, buf, cs);
     HERA_REQUIRE(cs.sum == h.payload_sum, 52, "graph cache: checksum mismatch (truncated or corrupt file)");
-    unsigned int *d_bad = nullptr, h_bad = 0;
-    HERA_CUDA(cudaMallocAsync(&d_bad, sizeof(unsigned int), c.stream));
-    HERA_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(unsigned int), c.stream));
+    TempPool tmp(c.stream);
+    unsigned int *d_bad = tmp.zeroed<unsigned int>(1), h_bad = 0;
     HERA_LAUNCH(c, cache_check_kernel, div_up(std::max<uint64_t>(std::max(E, N), 1), 256), 256, 0, E, N, h.name_bytes, g.e_q.p, g.e_t.p, g.node_name_off.p, d_bad);
     HERA_CUDA(cudaMemcpyAsync(&h_bad, d_bad, sizeof(unsigned int), cudaMemcpyDeviceToHost, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
-    HERA_CUDA(cudaFreeAsync(d_bad, c.stream));
     HERA_REQUIRE(!h_bad, 52, "graph cache: node ids or name offsets out of range");
     k.n = E;
     c.rows_total = E;

@@ -287,12 +287,11 @@ void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out) {
     float ms = 0;
     if (P > 0) {
         HERA_REQUIRE(static_cast<uint64_t>(A) * A < (1ull << 32), 13, "too many anchors for 32-bit pair keys");
-        cudaEvent_t ev0, ev1;
-        HERA_CUDA(cudaEventCreate(&ev0));
-        HERA_CUDA(cudaEventCreate(&ev1));
+        Events<2> ev;   // events and temporaries go when the scope ends, exception or not
+        const cudaEvent_t ev0 = ev[0], ev1 = ev[1];
         HERA_CUDA(cudaEventRecord(ev0, c.stream));
-        std::vector<void *> tmp;
-        auto alloc = [&](size_t bytes) { void *p = nullptr; HERA_CUDA(cudaMallocAsync(&p, bytes ? bytes : 4, c.stream)); tmp.push_back(p); return p; };
+        TempPool tmp(c.stream);
+        auto alloc = [&](size_t bytes) { return static_cast<void *>(tmp.get<uint8_t>(bytes)); };
         uint32_t *rank_of_node = static_cast<uint32_t *>(alloc(c.g.N * sizeof(uint32_t)));
         uint32_t *keys = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t))), *vals = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t)));
         uint32_t *keys_alt = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t))), *vals_alt = static_cast<uint32_t *>(alloc(P * sizeof(uint32_t)));
@@ -348,9 +347,6 @@ void group_paths(Ctx &c, const hera_path_params &pp, hera_groups_view *out) {
         get(h_pair_cons, a.pair_cons, K * 8); get(h_anchor, c.g.anchor_ids.p, A * 4);
         HERA_CUDA(cudaStreamSynchronize(c.stream));
         HERA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
-        cudaEventDestroy(ev0);
-        cudaEventDestroy(ev1);
-        for (void *p : tmp) HERA_CUDA(cudaFreeAsync(p, c.stream));
 
         m.pair_sorted.assign(h_ids, h_ids + P);
         m.pair_a1.reserve(K); m.pair_a2.reserve(K); m.pair_off.reserve(K + 1); m.pair_consensus.reserve(K); m.grp_pig.reserve(P);

@@ -1203,10 +1203,8 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
                  static_cast<float>(c.fp.max_overhang_length), c.fp.max_overhang_percentage};
     const uint64_t rec_limit = test_load_num > 0 ? static_cast<uint64_t>(test_load_num) + 1 : ~0ull;
 
-    cudaEvent_t ev0, ev1, ev2;
-    HERA_CUDA(cudaEventCreate(&ev0));
-    HERA_CUDA(cudaEventCreate(&ev1));
-    HERA_CUDA(cudaEventCreate(&ev2));
+    Events<3> ev;   // destroyed when the scope ends, exception or not
+    const cudaEvent_t ev0 = ev[0], ev1 = ev[1], ev2 = ev[2];
     maybe_flush_l2(c);
     mark("setup");
     HERA_CUDA(cudaEventRecord(ev0, c.stream));
@@ -1267,9 +1265,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     bool overflow = (hc.kept & KEPT_OVERFLOW) != 0;
     for (int r = 0; sharded && r < ranks; r++) overflow = overflow || (c.h_counters.p[16 + ranks + 2 * r] & KEPT_OVERFLOW) != 0;
     if (overflow) {   // (only after an optimistic reservation; the same decision on every rank)
-        cudaEventDestroy(ev0);
-        cudaEventDestroy(ev1);
-        cudaEventDestroy(ev2);
+        ev.destroy();
         HERA_REQUIRE(!c.parse_force_count, 3, "internal: kept rows overflowed a counted reservation");
         c.parse_force_count = true;
         try {
@@ -1299,9 +1295,6 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
             first_bad = std::min(first_bad, gathered[2 * r + 1]);
         }
         if (first_bad < records) {
-            cudaEventDestroy(ev0);
-            cudaEventDestroy(ev1);
-            cudaEventDestroy(ev2);
             throw Error{20, "irregular PAF record " + std::to_string(first_bad) + ": formatted extraction leaves the 16-token grid there; load this file unsharded"};
         }
         // The kept rows stay where they were parsed (node ids and adjacency are built from every rank's own
@@ -1348,9 +1341,6 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         c.load_shapes.push_back(shape);
     }
     if (hc.name_too_long || records >= (1ull << 32)) {
-        cudaEventDestroy(ev0);
-        cudaEventDestroy(ev1);
-        cudaEventDestroy(ev2);
         if (!c.own_rows.empty()) { c.own_rows.pop_back(); c.load_shapes.pop_back(); }
         HERA_REQUIRE(!hc.name_too_long, 22, "a kept record has a sequence name of 65536 bytes or more: not supported (name references hold 16 bits of length)");
         HERA_REQUIRE(records < (1ull << 32), 23, "more than 2^32 records in one load: not supported (record indices are 32 bits)");
@@ -1371,9 +1361,6 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
             HERA_CUDA(cudaEventElapsedTime(&out->exchange_ms, ev1, ev2));
         }
     }
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
-    cudaEventDestroy(ev2);
 }
 
 // ---- hera_paf_parse_noalloc: the tokenizer / filter / score kernel for callers that cannot allocate ---------------------

@@ -43,15 +43,10 @@ void unique_paths(Ctx &c, uint64_t *n_unique) {
     PathStore &a = c.all, &u = c.uniq;
     u.paths = 0; u.nodes = 0;
     if (a.paths > 0) {
-        uint8_t *keep = nullptr;
-        uint32_t *kept_nodes = nullptr, *path_scan = nullptr, *d_np = nullptr;
-        uint64_t *node_scan = nullptr, *d_nn = nullptr;
-        HERA_CUDA(cudaMallocAsync(&keep, a.paths, c.stream));
-        HERA_CUDA(cudaMallocAsync(&kept_nodes, a.paths * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&path_scan, a.paths * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&node_scan, a.paths * sizeof(uint64_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&d_np, sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&d_nn, sizeof(uint64_t), c.stream));
+        TempPool tmp(c.stream);
+        uint8_t *keep = tmp.get<uint8_t>(a.paths);
+        uint32_t *kept_nodes = tmp.get<uint32_t>(a.paths), *path_scan = tmp.get<uint32_t>(a.paths), *d_np = tmp.get<uint32_t>(1);
+        uint64_t *node_scan = tmp.get<uint64_t>(a.paths), *d_nn = tmp.get<uint64_t>(1);
         HERA_LAUNCH(c, unique_flags_kernel, div_up(a.paths * 32, 128), 128, 0, a.paths, a.off.p, a.node.p, keep, kept_nodes);
         exclusive_scan_u8_to_u32(c, keep, a.paths, path_scan, d_np);
         exclusive_scan_u32_to_u64(c, kept_nodes, a.paths, node_scan, d_nn);
@@ -65,8 +60,6 @@ void unique_paths(Ctx &c, uint64_t *n_unique) {
                     u.off.p, u.node.p, u.slot.p, u.len.p);
         u.paths = np; u.nodes = nn;
         HERA_CUDA(cudaStreamSynchronize(c.stream));
-        HERA_CUDA(cudaFreeAsync(keep, c.stream)); HERA_CUDA(cudaFreeAsync(kept_nodes, c.stream)); HERA_CUDA(cudaFreeAsync(path_scan, c.stream));
-        HERA_CUDA(cudaFreeAsync(node_scan, c.stream)); HERA_CUDA(cudaFreeAsync(d_np, c.stream)); HERA_CUDA(cudaFreeAsync(d_nn, c.stream));
     }
     c.uniq_ready = true;
     c.groups_valid = false;

@@ -94,12 +94,11 @@ void scan_impl(Ctx &c, const TIn *in, uint64_t n, TOut *out, TOut *d_total, int 
         return;
     }
     // tile sums live in a scratch allocation private to this recursion level
-    TOut *sums = nullptr;
-    HERA_CUDA(cudaMallocAsync(&sums, sizeof(TOut) * tiles, c.stream));
+    TempPool tmp(c.stream);
+    TOut *sums = tmp.get<TOut>(tiles);
     HERA_LAUNCH(c, (scan_tile_sums_kernel<TIn, TOut>), tiles, SCAN_THREADS, 0, in, n, sums);
     scan_impl<TOut, TOut>(c, sums, tiles, sums, static_cast<TOut *>(nullptr), depth + 1);
     HERA_LAUNCH(c, (scan_apply_kernel<TIn, TOut>), tiles, SCAN_THREADS, 0, in, n, static_cast<const TOut *>(sums), out, d_total);
-    HERA_CUDA(cudaFreeAsync(sums, c.stream));
 }
 
 }  // namespace
@@ -129,8 +128,8 @@ void radix_sort_pairs(Ctx &c, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt
         digit = c.opt_radix_digit_bits;
         passes = std::max(1, (bits + digit - 1) / digit);
     }
-    uint32_t *hist = nullptr;
-    HERA_CUDA(cudaMallocAsync(&hist, sizeof(uint32_t) * (static_cast<size_t>(1) << digit) * tiles, c.stream));
+    TempPool tmp(c.stream);
+    uint32_t *hist = tmp.get<uint32_t>((static_cast<size_t>(1) << digit) * tiles);
     uint32_t *kin = keys, *vin = vals, *kout = keys_alt, *vout = vals_alt;
     for (int p = 0; p < passes; p++) {
         const int shift = p * digit;
@@ -147,7 +146,6 @@ void radix_sort_pairs(Ctx &c, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt
         HERA_CUDA(cudaMemcpyAsync(keys, keys_alt, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c.stream));
         HERA_CUDA(cudaMemcpyAsync(vals, vals_alt, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c.stream));
     }
-    HERA_CUDA(cudaFreeAsync(hist, c.stream));
 }
 
 }  // namespace hera

@@ -184,9 +184,8 @@ void load_fasta(Ctx &c, const char *path, FastaFile &f) {
     f.records = 0;
     if (f.n == 0) { HERA_CUDA(cudaStreamSynchronize(c.stream)); return; }
     const uint64_t chunks = (f.n + FA_CHUNK - 1) / FA_CHUNK;
-    uint32_t *counts = nullptr, *d_total = nullptr;
-    HERA_CUDA(cudaMallocAsync(&counts, chunks * sizeof(uint32_t), c.stream));
-    HERA_CUDA(cudaMallocAsync(&d_total, sizeof(uint32_t), c.stream));
+    TempPool tmp(c.stream);
+    uint32_t *counts = tmp.get<uint32_t>(chunks), *d_total = tmp.get<uint32_t>(1);
     HERA_LAUNCH(c, fa_count_kernel, div_up(chunks, 128), 128, 0, f.text.p, f.n, counts);
     exclusive_scan_u32(c, counts, chunks, counts, d_total);
     uint32_t newlines = 0;
@@ -196,8 +195,6 @@ void load_fasta(Ctx &c, const char *path, FastaFile &f) {
     HERA_LAUNCH(c, fa_lines_kernel, div_up(chunks, 128), 128, 0, f.text.p, f.n, counts, f.line_start.p);
     f.lines = newlines + (staging.p[f.n - 1] != '\n' ? 1 : 0);   // std::getline: a trailing newline does not open another line
     f.records = (f.lines + f.step - 1) / f.step;
-    HERA_CUDA(cudaFreeAsync(counts, c.stream));
-    HERA_CUDA(cudaFreeAsync(d_total, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
 }
 
@@ -212,9 +209,9 @@ void build_scaffold(Ctx &c, const char *reads_path, const char *contigs_path, ui
     auto &sm = c.scm;
     sm.nodes.clear(); sm.slots.clear(); sm.logged.clear();
     *out = hera_scaffold_view{};
-    cudaEvent_t ev0, ev1;
-    HERA_CUDA(cudaEventCreate(&ev0));
-    HERA_CUDA(cudaEventCreate(&ev1));
+    Events<2> ev;   // events and temporaries go when the scope ends, exception or not
+    const cudaEvent_t ev0 = ev[0], ev1 = ev[1];
+    TempPool tmp(c.stream);
 
     // ---- the chain of consensus paths (src/PathManager.cpp:664-767), host bookkeeping over the group tables
     using Key = std::pair<uint32_t, uint32_t>;
@@ -232,10 +229,7 @@ void build_scaffold(Ctx &c, const char *reads_path, const char *contigs_path, ui
         pool[k] = {m.pair_consensus[p], num};
         if (best_num < num) { best_num = num; best_key = k; }
     }
-    if (!pool.count(best_key)) {   // the reference's map::at throws here; main() prints "No consensus found!" when no group has one
-        cudaEventDestroy(ev0); cudaEventDestroy(ev1);
-        throw Error{40, "No consensus found!"};
-    }
+    if (!pool.count(best_key)) throw Error{40, "No consensus found!"};   // the reference's map::at throws here; main() prints this when no group has a consensus
     std::vector<uint64_t> h_off(ps.paths + 1);
     HERA_CUDA(cudaMemcpyAsync(h_off.data(), ps.off.p, (ps.paths + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
@@ -289,20 +283,15 @@ void build_scaffold(Ctx &c, const char *reads_path, const char *contigs_path, ui
     HERA_REQUIRE(records < (1ull << 31), 43, "too many FASTA records");
     uint64_t cap = 1024;
     while (cap < 2 * records) cap <<= 1;
-    unsigned long long *keys = nullptr;
-    uint32_t *first_rec = nullptr, *d_nodes = nullptr, *d_slots = nullptr;
-    SeqRef *d_refs = nullptr;
-    SlotEnds *d_ends = nullptr;
-    HERA_CUDA(cudaMallocAsync(&keys, cap * sizeof(unsigned long long), c.stream));
-    HERA_CUDA(cudaMallocAsync(&first_rec, cap * sizeof(uint32_t), c.stream));
+    unsigned long long *keys = tmp.get<unsigned long long>(cap);
+    uint32_t *first_rec = tmp.get<uint32_t>(cap);
     HERA_CUDA(cudaMemsetAsync(keys, 0, cap * sizeof(unsigned long long), c.stream));
     HERA_CUDA(cudaMemsetAsync(first_rec, 0xff, cap * sizeof(uint32_t), c.stream));
     if (reads.records) HERA_LAUNCH(c, fa_insert_kernel, div_up(reads.records, 128), 128, 0, reads.dev(), 0u, keys, first_rec, cap - 1);
     if (contigs.records) HERA_LAUNCH(c, fa_insert_kernel, div_up(contigs.records, 128), 128, 0, contigs.dev(), static_cast<uint32_t>(reads.records), keys, first_rec, cap - 1);
-    HERA_CUDA(cudaMallocAsync(&d_nodes, nn * sizeof(uint32_t), c.stream));
-    HERA_CUDA(cudaMallocAsync(&d_slots, ne * sizeof(uint32_t), c.stream));
-    HERA_CUDA(cudaMallocAsync(&d_refs, nn * sizeof(SeqRef), c.stream));
-    HERA_CUDA(cudaMallocAsync(&d_ends, ne * sizeof(SlotEnds), c.stream));
+    uint32_t *d_nodes = tmp.get<uint32_t>(nn), *d_slots = tmp.get<uint32_t>(ne);
+    SeqRef *d_refs = tmp.get<SeqRef>(nn);
+    SlotEnds *d_ends = tmp.get<SlotEnds>(ne);
     HERA_CUDA(cudaMemcpyAsync(d_nodes, sm.nodes.data(), nn * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
     HERA_CUDA(cudaMemcpyAsync(d_slots, sm.slots.data(), ne * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
     HERA_LAUNCH(c, fa_lookup_kernel, div_up(nn, 128), 128, 0, nn, d_nodes, c.g.node_name_off.p, c.g.node_names.p, reads.dev(), contigs.dev(), keys, first_rec, cap - 1, d_refs);
@@ -360,26 +349,17 @@ void build_scaffold(Ctx &c, const char *reads_path, const char *contigs_path, ui
     sm.fasta.reserve(hl + seq_len + 2);
     std::memcpy(sm.fasta.p, header, hl);
     if (seq_len) {
-        Segment *d_seg = nullptr;
-        char *d_out = nullptr;
-        HERA_CUDA(cudaMallocAsync(&d_seg, segs.size() * sizeof(Segment), c.stream));
-        HERA_CUDA(cudaMallocAsync(&d_out, seq_len, c.stream));
+        Segment *d_seg = tmp.get<Segment>(segs.size());
+        char *d_out = tmp.get<char>(seq_len);
         HERA_CUDA(cudaMemcpyAsync(d_seg, segs.data(), segs.size() * sizeof(Segment), cudaMemcpyHostToDevice, c.stream));
         HERA_LAUNCH(c, stitch_kernel, div_up(seq_len, 256), 256, 0, seq_len, static_cast<uint32_t>(segs.size()), d_seg, reads.text.p, contigs.text.p, d_out);
         HERA_CUDA(cudaMemcpyAsync(sm.fasta.p + hl, d_out, seq_len, cudaMemcpyDeviceToHost, c.stream));
-        HERA_CUDA(cudaFreeAsync(d_seg, c.stream));
-        HERA_CUDA(cudaFreeAsync(d_out, c.stream));
     }
     HERA_CUDA(cudaEventRecord(ev1, c.stream));
-    for (void *p : {static_cast<void *>(keys), static_cast<void *>(first_rec), static_cast<void *>(d_nodes), static_cast<void *>(d_slots),
-                    static_cast<void *>(d_refs), static_cast<void *>(d_ends)})
-        HERA_CUDA(cudaFreeAsync(p, c.stream));
     HERA_CUDA(cudaStreamSynchronize(c.stream));
     sm.fasta.p[hl + seq_len] = '\n';
     float ms = 0;
     HERA_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
     out->nodes = nn; out->node = sm.nodes.data(); out->slot = sm.slots.data();
     out->logged = sm.logged.size(); out->logged_index = sm.logged.data();
     out->fasta_bytes = hl + seq_len + 1; out->fasta = sm.fasta.p; out->sequence_length = seq_len; out->ms = ms;

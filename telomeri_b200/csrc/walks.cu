@@ -543,10 +543,35 @@ struct WalkJob {
     uint32_t cap = 0, words = 0;
     int warps_per_sm = 1;
     unsigned blocks = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;   // the stream the job's kernel runs on
+    cudaStream_t home = nullptr;     // the context's stream: the job's memory is allocated and freed in its order
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     unsigned long long *h_ctr = nullptr;   // pinned: [0] pool used [1] entries examined [2] ticket [3] scratch overflow
     uint64_t launches = 0;
+
+    WalkJob() = default;
+    WalkJob(const WalkJob &) = delete;
+    WalkJob &operator=(const WalkJob &) = delete;
+    // A job that goes while it still holds memory (an exception between job_prepare and the end of job_finish) waits for
+    // its kernel and gives everything back.
+    ~WalkJob() { release(true); }
+    void release(bool wait_for_kernel) {
+        void **held[] = {reinterpret_cast<void **>(&r.res_n), reinterpret_cast<void **>(&r.res_draws), reinterpret_cast<void **>(&r.res_off),
+                         reinterpret_cast<void **>(&r.res_len), reinterpret_cast<void **>(&r.d_ctr), reinterpret_cast<void **>(&r.bitmap),
+                         reinterpret_cast<void **>(&r.nodes), reinterpret_cast<void **>(&r.slots), reinterpret_cast<void **>(&r.vlog),
+                         reinterpret_cast<void **>(&r.pool_nodes), reinterpret_cast<void **>(&r.pool_slots), reinterpret_cast<void **>(&first_edges),
+                         reinterpret_cast<void **>(&walk_base)};
+        bool any = false;
+        for (void **q : held) any = any || *q != nullptr;
+        if (any && wait_for_kernel && stream) cudaStreamSynchronize(stream);
+        for (void **q : held) {
+            if (*q) cudaFreeAsync(*q, home);
+            *q = nullptr;
+        }
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        ev0 = ev1 = nullptr;
+    }
 };
 
 uint32_t walk_share(uint32_t total_walks, int ranks, int r) { return static_cast<uint32_t>((static_cast<uint64_t>(total_walks) + ranks - 1 - r) / ranks); }
@@ -625,6 +650,7 @@ void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm, int slot) {
     const int ranks = xch_size(c), me = xch_rank(c);
     HERA_REQUIRE(ranks <= WK_MAX_RANKS, 37, "more than 16 ranks are not supported");
     j.wg = make_walk_graph(c, j.metric);
+    j.home = c.stream;
     const uint64_t launches0 = c.launches.count;
     if (j.kind == 0) {
         const uint64_t total = g.anchors * static_cast<uint64_t>(j.pp.rebuild_attempts > 0 ? j.pp.rebuild_attempts : 0);
@@ -634,15 +660,14 @@ void job_prepare(Ctx &c, WalkJob &j, int warps_per_sm, int slot) {
         HERA_REQUIRE(g.E == 0 || g.rank_ready[j.metric], 10, "rank permutation for this metric was not built (metrics_mask of hera_graph_finalize)");
         j.total_walks = 0;
         if (g.anchors) {
-            uint32_t *d_total = nullptr;
+            TempPool tmp(c.stream);
+            uint32_t *d_total = tmp.get<uint32_t>(1);
             HERA_CUDA(cudaMallocAsync(&j.first_edges, g.anchors * sizeof(uint32_t), c.stream));
             HERA_CUDA(cudaMallocAsync(&j.walk_base, g.anchors * sizeof(uint32_t), c.stream));
-            HERA_CUDA(cudaMallocAsync(&d_total, sizeof(uint32_t), c.stream));
             HERA_LAUNCH(c, det_count_kernel, div_up(g.anchors * 32, 128), 128, 0, j.wg, j.first_edges);
             exclusive_scan_u32(c, j.first_edges, g.anchors, j.walk_base, d_total);
             HERA_CUDA(cudaMemcpyAsync(&j.total_walks, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
             HERA_CUDA(cudaStreamSynchronize(c.stream));
-            HERA_CUDA(cudaFreeAsync(d_total, c.stream));
         }
     }
     j.my_walks = walk_share(j.total_walks, ranks, me);
@@ -689,13 +714,17 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
             if (scratch_overflow) {   // some walk visited more nodes than the small scratch holds: again with room for every node
                 HERA_REQUIRE(j.cap < c.g.N + 1, 38, "internal: walk scratch overflow at full capacity");
                 c.walk_full_cap[j.kind][j.metric] = 1;
-                for (void *q : {static_cast<void *>(r.bitmap), static_cast<void *>(r.nodes), static_cast<void *>(r.slots), static_cast<void *>(r.vlog)})
-                    HERA_CUDA(cudaFreeAsync(q, j.stream));
+                for (uint32_t **q : {&r.bitmap, &r.nodes, &r.slots, &r.vlog}) {
+                    HERA_CUDA(cudaFreeAsync(*q, j.stream));
+                    *q = nullptr;
+                }
                 job_alloc_scratch(c, j, true, j.stream);
             }
             if (j.h_ctr[0] > j.pool_cap) {
-                HERA_CUDA(cudaFreeAsync(r.pool_nodes, j.stream));
-                HERA_CUDA(cudaFreeAsync(r.pool_slots, j.stream));
+                for (uint32_t **q : {&r.pool_nodes, &r.pool_slots}) {
+                    HERA_CUDA(cudaFreeAsync(*q, j.stream));
+                    *q = nullptr;
+                }
                 j.pool_cap = j.h_ctr[0] + 1024;
                 HERA_CUDA(cudaMallocAsync(&r.pool_nodes, j.pool_cap * sizeof(uint32_t), j.stream));
                 HERA_CUDA(cudaMallocAsync(&r.pool_slots, j.pool_cap * sizeof(uint32_t), j.stream));
@@ -715,7 +744,7 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
         uint32_t *res_n = r.res_n, *res_draws = r.res_draws, *pool_nodes = r.pool_nodes, *pool_slots = r.pool_slots;
         uint64_t *res_off = r.res_off;
         int64_t *res_len = r.res_len;
-        std::vector<void *> gathered;
+        TempPool tmp(c.stream);   // gathered copies, flags and scans: gone when the scope ends, exception or not
         if (ranks > 1) {
             // exchange step: all-gather of the ranks' accepted paths
             const uint64_t mine[2] = {j.h_ctr[0], j.h_ctr[1]};
@@ -734,10 +763,7 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
             uint32_t *g_n, *g_draws, *g_pn, *g_ps, *o_n, *o_draws;
             uint64_t *g_off, *o_off;
             int64_t *g_len, *o_len;
-            auto alloc = [&](auto **p, uint64_t n) {
-                HERA_CUDA(cudaMallocAsync(p, std::max<uint64_t>(n, 1) * sizeof(**p), c.stream));
-                gathered.push_back(*p);
-            };
+            auto alloc = [&](auto **p, uint64_t n) { *p = tmp.get<std::remove_pointer_t<std::remove_pointer_t<decltype(p)>>>(n); };
             alloc(&g_n, wtot); alloc(&g_draws, wtot); alloc(&g_off, wtot); alloc(&g_len, wtot); alloc(&g_pn, ptot); alloc(&g_ps, ptot);
             alloc(&o_n, wtot); alloc(&o_draws, wtot); alloc(&o_off, wtot); alloc(&o_len, wtot);
             // two row gathers (per-walk results, path pools): over peer windows on the NCCL transport (pack, mailbox
@@ -753,13 +779,9 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
         }
 
         // order by walk id and append to the path store
-        uint8_t *flags = nullptr;
-        uint32_t *acc_scan = nullptr, *d_found = nullptr;
-        uint64_t *node_scan = nullptr;
-        HERA_CUDA(cudaMallocAsync(&flags, total_walks, c.stream));
-        HERA_CUDA(cudaMallocAsync(&acc_scan, total_walks * sizeof(uint32_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&node_scan, total_walks * sizeof(uint64_t), c.stream));
-        HERA_CUDA(cudaMallocAsync(&d_found, sizeof(uint32_t), c.stream));
+        uint8_t *flags = tmp.get<uint8_t>(total_walks);
+        uint32_t *acc_scan = tmp.get<uint32_t>(total_walks), *d_found = tmp.get<uint32_t>(1);
+        uint64_t *node_scan = tmp.get<uint64_t>(total_walks);
         HERA_LAUNCH(c, flag_nonzero_kernel, div_up(total_walks, 256), 256, 0, total_walks, res_n, flags);
         exclusive_scan_u8_to_u32(c, flags, total_walks, acc_scan, d_found);
         exclusive_scan_u32_to_u64(c, res_n, total_walks, node_scan, nullptr);
@@ -785,16 +807,8 @@ void job_finish(Ctx &c, WalkJob &j, hera_walk_stats *out) {
             HERA_CUDA(cudaMemcpyAsync(c.mc_draws.data() + before, res_draws, total_walks * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
         }
         HERA_CUDA(cudaStreamSynchronize(c.stream));
-        for (void *p : gathered) HERA_CUDA(cudaFreeAsync(p, c.stream));
-        for (void *p : {static_cast<void *>(flags), static_cast<void *>(acc_scan), static_cast<void *>(node_scan), static_cast<void *>(d_found),
-                        static_cast<void *>(r.res_n), static_cast<void *>(r.res_draws), static_cast<void *>(r.res_off), static_cast<void *>(r.res_len),
-                        static_cast<void *>(r.d_ctr), static_cast<void *>(r.bitmap), static_cast<void *>(r.nodes), static_cast<void *>(r.slots),
-                        static_cast<void *>(r.vlog), static_cast<void *>(r.pool_nodes), static_cast<void *>(r.pool_slots)})
-            HERA_CUDA(cudaFreeAsync(p, c.stream));
     }
-    if (j.first_edges) { HERA_CUDA(cudaFreeAsync(j.first_edges, c.stream)); HERA_CUDA(cudaFreeAsync(j.walk_base, c.stream)); }
-    cudaEventDestroy(j.ev0);
-    cudaEventDestroy(j.ev1);
+    j.release(false);   // (the job's kernel has finished: the stream was synchronised above)
     j.h_ctr = nullptr;
     c.uniq_ready = false;
     c.groups_valid = false;
@@ -845,8 +859,8 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
             HERA_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
             c.aux_streams.push_back(s);
         }
-        cudaEvent_t ready;
-        HERA_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+        Events<1> ready_ev(cudaEventDisableTiming);
+        const cudaEvent_t ready = ready_ev[0];
         HERA_CUDA(cudaEventRecord(ready, c.stream));   // scratch allocation and the graph itself are ordered on the context's stream
         // longest first (warp-time of the same call the last time on this context; call order when nothing is known)
         std::vector<int> order(n);
@@ -859,7 +873,6 @@ void walk_build(Ctx &c, int n, const int *kinds, const int *metrics, const hera_
             HERA_CUDA(cudaStreamWaitEvent(jobs[i].stream, ready, 0));
             if (jobs[i].total_walks) job_launch_kernel(c, jobs[i]);
         }
-        cudaEventDestroy(ready);
     }
     stamp("launched");
     for (int i = 0; i < n; i++) {
@@ -905,12 +918,10 @@ void probe_list_gather(Ctx &c, uint32_t warps_per_sm, uint32_t hops, double *gby
     int sms = 148;
     HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
     const unsigned warps = static_cast<unsigned>(sms) * std::max(1u, std::min(64u, warps_per_sm));
-    unsigned long long *d_bytes = nullptr;
-    HERA_CUDA(cudaMallocAsync(&d_bytes, 2 * sizeof(unsigned long long), c.stream));
-    HERA_CUDA(cudaMemsetAsync(d_bytes, 0, 2 * sizeof(unsigned long long), c.stream));
-    cudaEvent_t e0, e1;
-    HERA_CUDA(cudaEventCreate(&e0));
-    HERA_CUDA(cudaEventCreate(&e1));
+    TempPool tmp(c.stream);
+    unsigned long long *d_bytes = tmp.zeroed<unsigned long long>(2);
+    Events<2> ev;
+    const cudaEvent_t e0 = ev[0], e1 = ev[1];
     HERA_CUDA(cudaEventRecord(e0, c.stream));
     HERA_LAUNCH(c, list_gather_probe_kernel, div_up(static_cast<uint64_t>(warps) * 32, WK_THREADS), WK_THREADS, 0, g.adj_off.p, g.a8[0].p,
                 static_cast<uint32_t>(g.N), hops, d_bytes, reinterpret_cast<uint32_t *>(d_bytes + 1));
@@ -920,9 +931,6 @@ void probe_list_gather(Ctx &c, uint32_t warps_per_sm, uint32_t hops, double *gby
     HERA_CUDA(cudaStreamSynchronize(c.stream));
     float ms = 0;
     HERA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    HERA_CUDA(cudaFreeAsync(d_bytes, c.stream));
     if (gbytes_per_s) *gbytes_per_s = ms > 0 ? static_cast<double>(h_bytes) / (ms * 1e-3) / 1e9 : 0.0;
     if (ms_out) *ms_out = ms;
 }
