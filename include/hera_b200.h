@@ -134,7 +134,9 @@ uint64_t hera_kernel_launches(hera_ctx *ctx);    /* kernels launched by this con
  * counts the tokens first or, on a context that already holds enough rows, tries with those and repeats the load if they
  * do not suffice; default 64 Mi), "walk_cap_small" (nodes a walk may
  * visit before its call is repeated with per-warp scratch for every node of the graph, default 16384), "parse_variant" (0 = the
- * CTA-tile tokenizer, default; 1 = the warp-autonomous tokenizer -- same results, see DESIGN.md K1+K2). */
+ * CTA-tile tokenizer, default; 1 = the warp-autonomous tokenizer -- same results, see DESIGN.md K1+K2),
+ * "load_chunk_bytes" (hera_graph_load_bytes copies and parses a host text in chunks of this size, rounded to whole
+ * 30 720-byte tiles, at least 8 of them; 0 = one copy, then one launch; default 256 Mi). */
 int hera_timer_start(hera_ctx *ctx);
 int hera_timer_stop(hera_ctx *ctx, float *ms);   /* synchronises the stream */
 int hera_set_option(hera_ctx *ctx, const char *key, int64_t value);
@@ -206,7 +208,10 @@ int hera_graph_set_filter(hera_ctx *ctx, const hera_filter_params *fp);
  * to the device, tokenizes / filters / scores there, appends to the graph.  test_load_num as
  * OverlapGraph::test_load_num_ (0 = whole file).  A file that cannot be opened returns 1. */
 int hera_graph_load_file(hera_ctx *ctx, const char *path, int anchors, uint32_t test_load_num, hera_load_result *out);
-/* Same, PAF text already in host memory (copied H2D inside) ... */
+/* Same, PAF text already in host memory.  The text is copied to the device in chunks ("load_chunk_bytes", default
+ * 256 MiB) on a copy stream of the context and every chunk is parsed by its own launch as soon as it has landed: the
+ * tokenizer hides behind the copy (out->h2d_ms = the copies; out->parse_ms = first launch to last, waits for the
+ * copy included).  Pinned host memory makes the copies asynchronous; pageable memory works, without the overlap. ... */
 int hera_graph_load_bytes(hera_ctx *ctx, const void *host_text, uint64_t n, int anchors, uint32_t test_load_num, hera_load_result *out);
 /* ... or already resident in device memory (n bytes at a cudaMalloc'ed address; the library
  * copies it device-to-device into its own padded buffer). */

@@ -163,6 +163,7 @@ void hera_destroy(hera_ctx *ctx) {
     cudaStreamSynchronize(ctx->c.stream);
     cudaStream_t s = ctx->c.stream;
     for (cudaStream_t a : ctx->c.aux_streams) { cudaStreamSynchronize(a); cudaStreamDestroy(a); }
+    if (ctx->c.copy_stream) { cudaStreamSynchronize(ctx->c.copy_stream); cudaStreamDestroy(ctx->c.copy_stream); }
     delete ctx;
     cudaStreamDestroy(s);
 }
@@ -205,6 +206,7 @@ int hera_set_option(hera_ctx *ctx, const char *key, int64_t value) {
     else if (k == "verify_ctas_per_sm") c.opt_verify_ctas_per_sm = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(8, value)));
     else if (k == "radix_digit_bits") c.opt_radix_digit_bits = static_cast<int>(value);
     else if (k == "parse_count_rows") c.opt_parse_count_rows = std::max<int64_t>(1, value);
+    else if (k == "load_chunk_bytes") c.opt_load_chunk_bytes = std::max<int64_t>(0, value);
     else if (k == "walk_hints_reset") { for (auto &a : c.walk_work_hint) for (uint64_t &w : a) w = 0; }
     else if (k == "walk_cap_small") { c.opt_walk_cap_small = static_cast<int>(std::max<int64_t>(2, value)); for (auto &a : c.walk_full_cap) for (int &f : a) f = 0; }
     else throw hera::Error{102, "unknown option: " + k};
@@ -259,7 +261,8 @@ static std::unique_ptr<hera::LoadedText> acquire_text(Ctx &c, uint64_t n) {
 }
 
 // Parses a text whose bytes are (being copied) on the device, in stream order.
-static void commit_text(Ctx &c, std::unique_ptr<hera::LoadedText> t, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard, hera_load_result *out) {
+static void commit_text(Ctx &c, std::unique_ptr<hera::LoadedText> t, int anchors, uint32_t test_load_num, const hera::ShardSpec *shard, hera_load_result *out,
+                        const hera::HostSource *host = nullptr) {
     if (c.cache_loaded) {
         cudaStreamSynchronize(c.stream);
         if (!t->view) c.text_pool.push_back(std::move(t));
@@ -273,9 +276,10 @@ static void commit_text(Ctx &c, std::unique_ptr<hera::LoadedText> t, int anchors
     }
     c.texts.push_back(std::move(t));
     try {
-        hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, shard, out);
+        hera::load_text_resident(c, *c.texts.back(), file_id, anchors != 0, test_load_num, shard, out, host);
     } catch (...) {
         cudaStreamSynchronize(c.stream);
+        if (c.copy_stream) cudaStreamSynchronize(c.copy_stream);
         if (!c.texts.back()->view) c.text_pool.push_back(std::move(c.texts.back()));
         c.texts.pop_back();   // the failed load leaves no trace
         throw;
@@ -287,14 +291,21 @@ static void load_common(Ctx &c, const void *src, uint64_t n, cudaMemcpyKind kind
     std::unique_ptr<hera::LoadedText> t = acquire_text(c, n);
     hera::Events<2> ev;
     const cudaEvent_t e0 = ev[0], e1 = ev[1];
+    // A whole text in host memory is copied in chunks on the copy stream and parsed chunk by chunk as it lands
+    // (load_text_resident): the parse hides behind the copy.  Slices of a sharded load and device sources: one copy, then parse.
+    const uint64_t grains = static_cast<uint64_t>(std::max<int64_t>(0, c.opt_load_chunk_bytes)) / hera::LOAD_CHUNK_GRAIN;
+    const bool chunked = kind == cudaMemcpyHostToDevice && !shard && grains > 0 && n > 0;
+    const hera::HostSource host{static_cast<const uint8_t *>(src), std::max(grains, hera::LOAD_CHUNK_MIN_GRAINS) * hera::LOAD_CHUNK_GRAIN};
     HERA_CUDA(cudaEventRecord(e0, c.stream));
-    if (n) HERA_CUDA(cudaMemcpyAsync(t->bytes.p, src, n, kind, c.stream));
+    if (n && !chunked) HERA_CUDA(cudaMemcpyAsync(t->bytes.p, src, n, kind, c.stream));
     HERA_CUDA(cudaEventRecord(e1, c.stream));
     hera_load_result tmp{};
-    commit_text(c, std::move(t), anchors, test_load_num, shard, &tmp);
-    float copy_ms = 0;
-    HERA_CUDA(cudaEventElapsedTime(&copy_ms, e0, e1));
-    tmp.h2d_ms = kind == cudaMemcpyHostToDevice ? copy_ms : 0.0f;
+    commit_text(c, std::move(t), anchors, test_load_num, shard, &tmp, chunked ? &host : nullptr);
+    if (!chunked) {
+        float copy_ms = 0;
+        HERA_CUDA(cudaEventElapsedTime(&copy_ms, e0, e1));
+        tmp.h2d_ms = kind == cudaMemcpyHostToDevice ? copy_ms : 0.0f;
+    }
     if (out) *out = tmp;
 }
 

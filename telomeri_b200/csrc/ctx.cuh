@@ -128,6 +128,14 @@ struct PathStore {
     DBuf<int64_t> len;
 };
 
+// A text that is still in host memory (hera_graph_load_bytes): copied and parsed chunk by chunk.
+constexpr uint64_t LOAD_CHUNK_GRAIN = 30720;      // the parse kernel's tile
+constexpr uint64_t LOAD_CHUNK_MIN_GRAINS = 8;     // a record (two names below 64 KiB each) ends inside the chunk behind the one it starts in
+struct HostSource {
+    const uint8_t *text;
+    uint64_t chunk_bytes;   // a multiple of LOAD_CHUNK_GRAIN, at least LOAD_CHUNK_MIN_GRAINS of them
+};
+
 struct Ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -146,6 +154,8 @@ struct Ctx {
     uint64_t walk_work_hint[2][4] = {};   // per (kind, metric): warp-microseconds the last call took (shares of the resident warps)
     int walk_full_cap[2][4] = {};         // per (kind, metric): a walk outgrew the small per-warp scratch once, size it for N nodes
     std::vector<cudaStream_t> aux_streams;   // hera_paths_build: one stream per walk kernel in flight
+    cudaStream_t copy_stream = nullptr;      // hera_graph_load_bytes: host-to-device copies of the chunks of a text
+    int64_t opt_load_chunk_bytes = 256ll << 20;   // chunk of a host text (rounded to whole tiles; 0 = one copy, then parse)
     DBuf<uint8_t> l2_flush_buf;
     std::unique_ptr<Exchange> xch;   // null = single rank
 
@@ -220,7 +230,10 @@ void radix_sort_pairs(Ctx &c, uint32_t *keys, uint32_t *vals, uint32_t *keys_alt
 void maybe_flush_l2(Ctx &c);
 
 // ---- stages ------------------------------------------------------------------------------
-void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out);
+// host != nullptr: the bytes are still in host memory; they are copied in chunks on the context's copy stream and every
+// chunk is parsed as it lands (whole texts only; see chunk_carry_kernel).
+void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out,
+                        const HostSource *host = nullptr);
 void finalize_graph(Ctx &c, uint32_t metrics_mask, hera_graph_info *out);
 RowPieces row_pieces(const Ctx &c);
 RowView rows_view(Ctx &c);   // COLLECTIVE on a sharded context the first time after a finalize (all-gather of the rows)

@@ -219,7 +219,7 @@ __device__ __forceinline__ bool is_ctg(const uint8_t *text, uint64_t off, uint32
 
 // Turns parsed fields into a staged record; returns keep flag.
 __device__ __forceinline__ bool make_record(const FilterDev &f, const uint8_t *text, uint32_t file_id, bool anchors, const SerialRecord &r,
-                                            uint32_t rec_idx, StagedRecord &out, ParseCounters *ctr) {
+                                            uint32_t rec_idx, StagedRecord &out, ParseCounters *ctr, uint64_t name_off0 = 0) {
     if (r.qhash == r.thash && r.qnlen == r.tnlen && names_equal(text, r.qoff, r.toff, r.qnlen)) return false;  // :157
     if (!filter_fields(f, r.qlen, r.qs, r.qe, r.tlen, r.ts, r.te)) return false;
     if ((r.qnlen | r.tnlen) > 0xffffu) ctr->name_too_long = 1;   // (the reference takes names of any length; here the load fails with code 22)
@@ -229,8 +229,8 @@ __device__ __forceinline__ bool make_record(const FilterDev &f, const uint8_t *t
     out.rec = rec_idx;
     score_fields(r.qlen, r.qs, r.qe, r.tlen, r.ts, r.te, r.matches, out.si, out.os, out.es);
     out.qhash = r.qhash; out.thash = r.thash;
-    out.qname = pack_name(file_id, r.qoff, r.qnlen);
-    out.tname = pack_name(file_id, r.toff, r.tnlen);
+    out.qname = pack_name(file_id, name_off0 + r.qoff, r.qnlen);   // (name_off0: where `text` starts in the loaded text, chunked loads)
+    out.tname = pack_name(file_id, name_off0 + r.toff, r.tnlen);
     out.flags = (r.strand == '-' ? KF_MINUS : 0) | (anchors ? KF_CR : 0) | ((anchors && is_ctg(text, r.qoff, r.qnlen)) ? KF_QCTG : 0);
     return true;
 }
@@ -347,6 +347,10 @@ struct ParseArgs {
     KeptPtrs kept;
     unsigned long long *tok_state, *kept_state;
     ParseCounters *ctr;
+    // chunked load (a host text parsed chunk by chunk as it lands, one launch per chunk): rows kept by the earlier chunks
+    // of this load, a device value (paf_parse_kernel only; ctr->kept and the chains stay relative to the chunk)
+    const unsigned long long *kept_base_dev;
+    uint64_t name_off0;         // where `text` starts in the loaded text: name references hold offsets into the whole text
 };
 
 // Exact reader for a record that does not fit the shared-memory window (very long names).
@@ -511,7 +515,7 @@ __device__ __forceinline__ bool parse_one(const ParseArgs &a, const uint8_t *s, 
         atomicMin(&a.ctr->first_bad_off, static_cast<unsigned long long>(tile_byte0 + p0));
         return false;
     }
-    return make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), out, a.ctr);
+    return make_record(a.filter, a.text, a.file_id, a.anchors != 0, r, static_cast<uint32_t>(rec_idx), out, a.ctr, a.name_off0);
 }
 
 // Position of the k-th (0-based) set bit of a mask that has more than k bits set.
@@ -769,7 +773,7 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
             if (c < a.tiles) {
                 const unsigned long long base = chain_resolve(a.kept_state, c, kc, probe_kept);
                 if (lane == 0) {
-                    s_kept_base = base;
+                    s_kept_base = base + (a.kept_base_dev ? *a.kept_base_dev : 0ull);
                     if (c == a.tiles - 1) a.ctr->kept = base + kc;
                 }
             }
@@ -841,7 +845,7 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
             if (warp == 0) {
                 const unsigned long long base = chain_resolve(a.kept_state, tile, tile_kept, chain_probe(a.kept_state, tile));
                 if (lane == 0) {
-                    s_kept_base = base;
+                    s_kept_base = base + (a.kept_base_dev ? *a.kept_base_dev : 0ull);
                     if (tile == a.tiles - 1) a.ctr->kept = base + tile_kept;
                 }
             }
@@ -887,7 +891,7 @@ __global__ void __launch_bounds__(PF_THREADS, PF_MIN_CTAS) paf_parse_kernel(cons
     if (warp == 0 && prev_tile < a.tiles) {
         const unsigned long long base = chain_resolve(a.kept_state, prev_tile, prev_kept, chain_probe(a.kept_state, prev_tile));
         if (lane == 0) {
-            s_kept_base = base;
+            s_kept_base = base + (a.kept_base_dev ? *a.kept_base_dev : 0ull);
             if (prev_tile == a.tiles - 1) a.ctr->kept = base + prev_kept;
         }
     }
@@ -1049,6 +1053,30 @@ __global__ void kept_overflow_kernel(ParseCounters *ctr, uint64_t room) {
     if (ctr->kept > room) ctr->kept |= KEPT_OVERFLOW;
 }
 
+// ---- chunked load: a host text is copied in chunks and every chunk is parsed by its own launch as soon as it (and the
+// head of its successor) has landed, so the parse hides behind the host-to-device copy.  A chunk is what a rank's slice is
+// in a sharded load: it starts at an arbitrary byte, counts the tokens that START inside it and completes its last record
+// from the bytes behind it.  Where a slice learns the tokens in front of it from the other ranks, a chunk reads them -- and
+// the rows kept so far -- from the `carry` words the previous chunk's launch left behind.
+__global__ void chunk_init_kernel(ParseCounters *part, uint32_t chunks) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= chunks) return;
+    part[k].first_bad_rec = ~0ull;
+    part[k].first_bad_off = ~0ull;
+}
+// merged: the counters of the whole load (what an unchunked launch leaves); carry[0] tokens, carry[1] kept rows so far
+__global__ void chunk_carry_kernel(ParseCounters *merged, const ParseCounters *part, unsigned long long *carry, uint64_t byte0) {
+    carry[0] += part->total_tokens;
+    carry[1] += part->kept;
+    merged->total_tokens = carry[0];
+    merged->kept = carry[1];
+    if (part->first_bad_rec < merged->first_bad_rec) {   // record indices are global; chunks come in file order
+        merged->first_bad_rec = part->first_bad_rec;
+        merged->first_bad_off = part->first_bad_off + byte0;
+    }
+    if (part->name_too_long) merged->name_too_long = 1;
+}
+
 // Finds how many kept records of this load precede the first irregular record.
 __global__ void kept_before_kernel(const uint32_t *__restrict__ rec, uint64_t base, uint64_t n, uint64_t bad_rec, unsigned long long *out) {
     const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -1117,13 +1145,17 @@ static KeptPtrs kept_ptrs(KeptTable &k) {
 
 uint64_t padded_text_size(uint64_t n) { return (n / PF_TILE + 2) * static_cast<uint64_t>(PF_TILE); }
 
+static_assert(LOAD_CHUNK_GRAIN == PF_TILE, "chunks of a host text are whole tiles");
+static bool host_is_space(uint8_t ch) { return ch == ' ' || (ch >= 9 && ch <= 13); }
+
 static double host_now_ms() {   // wall clock shared by the ranks of one box (HERA_DEBUG_TIMING)
     timespec ts;
     clock_gettime(CLOCK_REALTIME, &ts);
     return static_cast<double>(ts.tv_sec % 1000) * 1e3 + static_cast<double>(ts.tv_nsec) * 1e-6;
 }
 
-void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out) {
+void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors, uint32_t test_load_num, const ShardSpec *shard, hera_load_result *out,
+                        const HostSource *host) {
     const bool debug_timing = getenv("HERA_DEBUG_TIMING") != nullptr;
     const double t_entry = debug_timing ? host_now_ms() : 0.0;
     double t_gather = 0.0, t_launched = 0.0;
@@ -1153,12 +1185,48 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     }
     const bool sharded = shard != nullptr;
     const int ranks = xch_size(c), me = xch_rank(c);
+    // The text is still in host memory: copy it on the copy stream, chunk by chunk, an event behind every chunk.
+    struct Chunk { uint64_t off, owned; uint32_t tiles, tile0; cudaEvent_t landed; };
+    std::vector<Chunk> chunks;
+    struct ChunkEvents {
+        std::vector<Chunk> &v;
+        cudaEvent_t t0 = nullptr, t1 = nullptr;
+        ~ChunkEvents() {
+            for (Chunk &k : v) if (k.landed) cudaEventDestroy(k.landed);
+            if (t0) cudaEventDestroy(t0);
+            if (t1) cudaEventDestroy(t1);
+        }
+    } chunk_events{chunks};
+    if (host) {
+        HERA_REQUIRE(!bare && !sharded && host->chunk_bytes >= LOAD_CHUNK_MIN_GRAINS * PF_TILE && host->chunk_bytes % PF_TILE == 0, 3, "internal: chunked load of a view / a slice");
+        if (!c.copy_stream) HERA_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
+        HERA_CUDA(cudaEventCreate(&chunk_events.t0));
+        HERA_CUDA(cudaEventCreate(&chunk_events.t1));
+        {   // the buffer may be one an earlier graph of this context was parsed from: the copy starts behind the stream's work
+            Events<1> entry(cudaEventDisableTiming);
+            HERA_CUDA(cudaEventRecord(entry[0], c.stream));
+            HERA_CUDA(cudaStreamWaitEvent(c.copy_stream, entry[0], 0));
+        }
+        HERA_CUDA(cudaEventRecord(chunk_events.t0, c.copy_stream));
+        uint32_t tile0 = 0;
+        for (uint64_t off = 0; off < n; off += host->chunk_bytes) {
+            Chunk k{off, std::min<uint64_t>(host->chunk_bytes, n - off), 0, tile0, nullptr};
+            k.tiles = static_cast<uint32_t>(k.owned / PF_TILE + 1);
+            tile0 += k.tiles;
+            chunks.push_back(k);
+            HERA_CUDA(cudaEventCreateWithFlags(&chunks.back().landed, cudaEventDisableTiming));
+            HERA_CUDA(cudaMemcpyAsync(text.bytes.p + off, host->text + off, k.owned, cudaMemcpyHostToDevice, c.copy_stream));
+            HERA_CUDA(cudaEventRecord(chunks.back().landed, c.copy_stream));
+        }
+        HERA_CUDA(cudaEventRecord(chunk_events.t1, c.copy_stream));
+    }
     HERA_REQUIRE(!sharded || c.xch, 21, "hera_graph_load_shard needs a communicator (hera_comm_init_nccl / hera_comm_attach_local)");
     const uint64_t owned = sharded ? shard->owned : n;
     HERA_REQUIRE(owned <= n, 101, "shard: owned bytes exceed the bytes provided");
 
     const bool warp_variant = c.opt_parse_variant == 1;
-    const uint32_t tiles = static_cast<uint32_t>(owned / (warp_variant ? WW_TILE : PF_TILE) + 1);
+    bool chunked = chunks.size() > 1 && !warp_variant;
+    uint32_t tiles = static_cast<uint32_t>(owned / (warp_variant ? WW_TILE : PF_TILE) + 1);
     // worst case every record is kept: records <= bytes / 24 (12 one-byte tokens + separators).  For a large text that
     // bound would reserve far more rows than the file can hold records (42 GB of PAF -> 128 GB of rows), so the tokens
     // are counted first (one more pass over the text) and the rows are reserved for tokens / 16 records.
@@ -1170,6 +1238,12 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     const uint64_t room_now = c.kept.qs.cap > c.kept.n ? c.kept.qs.cap - c.kept.n : 0;
     const uint64_t count_rows = static_cast<uint64_t>(c.opt_parse_count_rows);
     const bool optimistic = max_new > count_rows && !c.parse_force_count && room_now >= owned / 160 + 2;
+    if (!chunks.empty() && !(chunked && (optimistic || max_new <= count_rows))) {
+        // one chunk, or the tokens are counted first (a pass over the whole text): wait for the text, then as for a resident one
+        HERA_CUDA(cudaStreamWaitEvent(c.stream, chunks.back().landed, 0));
+        chunked = false;
+    }
+    if (chunked) tiles = chunks.back().tile0 + chunks.back().tiles;
     if (optimistic) {
         max_new = room_now;
     } else if (max_new > count_rows) {
@@ -1188,11 +1262,14 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     // device block: [0, 8) ParseCounters, [12] cut, [13] my token count, [14] tokens before my slice, [15] tokens of all
     // slices, [16, 16 + 2 tiles) chain states, then what the ranks tell each other: token counts, {kept, first bad} pairs
     const uint64_t gather_at = 16 + 2ull * tiles;
-    c.counters.reserve(gather_at + 3ull * ranks + 8);
+    const uint64_t parts_at = gather_at + 3ull * ranks + 8, part_words = sizeof(ParseCounters) / sizeof(uint64_t);   // per-chunk counters, then carry[2]
+    static_assert(sizeof(ParseCounters) % sizeof(uint64_t) == 0, "counter blocks are laid out in 64-bit words");
+    const uint64_t block_words = parts_at + (chunked ? chunks.size() * part_words + 2 : 0);
+    c.counters.reserve(block_words);
     ParseCounters *ctr = reinterpret_cast<ParseCounters *>(c.counters.p);
     unsigned long long *tok_state = reinterpret_cast<unsigned long long *>(c.counters.p + 16);
     unsigned long long *kept_state = tok_state + tiles;
-    HERA_CUDA(cudaMemsetAsync(c.counters.p, 0, (gather_at + 3ull * ranks) * sizeof(uint64_t), c.stream));
+    HERA_CUDA(cudaMemsetAsync(c.counters.p, 0, (chunked ? block_words : gather_at + 3ull * ranks) * sizeof(uint64_t), c.stream));
     ParseCounters init{};
     init.first_bad_rec = ~0ull;
     init.first_bad_off = ~0ull;
@@ -1228,7 +1305,31 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
     int sms = 148;
     HERA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.device));
     HERA_CUDA(cudaFuncSetAttribute(paf_parse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM_BYTES));   // per device: cheap, idempotent
-    if (warp_variant) {
+    if (chunked) {
+        ParseCounters *part = reinterpret_cast<ParseCounters *>(c.counters.p + parts_at);
+        unsigned long long *carry = reinterpret_cast<unsigned long long *>(c.counters.p + parts_at + chunks.size() * part_words);
+        HERA_LAUNCH(c, chunk_init_kernel, div_up(chunks.size(), 128), 128, 0, part, static_cast<uint32_t>(chunks.size()));
+        for (size_t k = 0; k < chunks.size(); k++) {
+            const Chunk &ck = chunks[k];
+            // a chunk's last record ends in the bytes behind it: wait for the next chunk too (PF_HALO << a chunk)
+            HERA_CUDA(cudaStreamWaitEvent(c.stream, chunks[std::min(k + 1, chunks.size() - 1)].landed, 0));
+            ParseArgs ak = a;
+            ak.text = text_p + ck.off;
+            ak.n = n - ck.off;
+            ak.owned = ck.owned;
+            ak.tok_base0_dev = carry;
+            ak.prev_nonws = ck.off > 0 && !host_is_space(host->text[ck.off - 1]) ? 1 : 0;
+            ak.at_eof = 1;   // text[n] is the end of the file for every chunk: ak.n reaches to the end of the text
+            ak.tiles = ck.tiles;
+            ak.tok_state = tok_state + ck.tile0;
+            ak.kept_state = kept_state + ck.tile0;
+            ak.ctr = part + k;
+            ak.kept_base_dev = carry + 1;
+            ak.name_off0 = ck.off;
+            HERA_LAUNCH(c, paf_parse_kernel, std::min<uint32_t>(ck.tiles, static_cast<uint32_t>(sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, ak);
+            HERA_LAUNCH(c, chunk_carry_kernel, 1, 1, 0, ctr, part + k, carry, ck.off);
+        }
+    } else if (warp_variant) {
         HERA_LAUNCH(c, paf_parse_warp_kernel, std::min<uint32_t>(div_up(tiles, WW_WARPS), static_cast<uint32_t>(sms) * WW_MIN_CTAS), WW_THREADS, 0, a);
     } else {
         HERA_LAUNCH(c, paf_parse_kernel, std::min<uint32_t>(tiles, static_cast<uint32_t>(sms) * PF_MIN_CTAS), PF_THREADS, PF_SMEM_BYTES, a);
@@ -1269,7 +1370,7 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         HERA_REQUIRE(!c.parse_force_count, 3, "internal: kept rows overflowed a counted reservation");
         c.parse_force_count = true;
         try {
-            load_text_resident(c, text, file_id, anchors, test_load_num, shard, out);
+            load_text_resident(c, text, file_id, anchors, test_load_num, shard, out, nullptr);   // (the text has landed by now)
         } catch (...) {
             c.parse_force_count = false;
             throw;
@@ -1354,7 +1455,8 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         out->kept = kept_global;
         out->kept_total = c.rows_total;
         out->bytes = n;
-        HERA_CUDA(cudaEventElapsedTime(&out->parse_ms, ev0, ev1));
+        HERA_CUDA(cudaEventElapsedTime(&out->parse_ms, ev0, ev1));   // (a chunked load: from the first chunk's launch to the last one's end, waits for the copy included)
+        if (host) HERA_CUDA(cudaEventElapsedTime(&out->h2d_ms, chunk_events.t0, chunk_events.t1));
         out->exchange_ms = 0;
         if (sharded) {
             HERA_CUDA(cudaEventSynchronize(ev2));

@@ -30,7 +30,8 @@ def parse_options(opts):
 def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, batched=False, exports=True, loader="file"):
     """exports=False: make every (collective) call but copy no table back -- the other ranks of a gang at large sizes.
     loader="device_view": the PAF files are put into device tensors of exactly their size and parsed in place
-    (hera_graph_load_device_view) instead of going through hera_graph_load_file."""
+    (hera_graph_load_device_view) instead of going through hera_graph_load_file; loader="bytes": host arrays through
+    hera_graph_load_bytes."""
     o = parse_options(list(opts))
     ds_dir = Path(ds_dir)
     own = hera is None
@@ -48,6 +49,10 @@ def run_hot_path(ds_dir, opts=(), seed=0, device=0, stages="all", hera=None, bat
                 held.append(t)
                 return h.load_device_view_ptr(t.data_ptr() if data.size else 0, int(data.size), anchors, o["test_load_num"])
             out["_held"] = held
+        elif loader == "bytes":   # host arrays through hera_graph_load_bytes (copied and parsed chunk by chunk)
+            def load(name, anchors):
+                data = np.fromfile(ds_dir / name, dtype=np.uint8)
+                return h.load_host_ptr(data.ctypes.data if data.size else 0, int(data.size), anchors, o["test_load_num"])
         else:
             def load(name, anchors):
                 return h.load_file(ds_dir / name, anchors, o["test_load_num"])

@@ -175,6 +175,62 @@ def test_optimistic_row_reservation_and_its_overflow(oracle_bin, datasets, tmp_p
             common.assert_sections_equal(ora, h.export_graph(), cols, f"load {rep}")
 
 
+def test_host_text_is_parsed_chunk_by_chunk_as_it_lands(oracle_bin, datasets, tmp_path):
+    """hera_graph_load_bytes copies a host text in chunks on a copy stream and parses every chunk with its own launch as soon
+    as it has landed (tokens and kept rows of the earlier chunks are carried on the device).  Forced here at small size with
+    "load_chunk_bytes" = 8 tiles: dozens of chunks per file, records across every chunk border, texts that end on / next to
+    a border, an irregular record in a late chunk (exact reader from there), --test-load-num, and the row reservations of
+    large loads (counted = the text is awaited whole; optimistic; optimistic with overflow and repeat)."""
+    from telomeri_b200 import capi, pipeline
+    chunk = 8 * 30720
+    # whole datasets, walks and groups included
+    for name in ("small", "mixed"):
+        ds = datasets[name]
+        assert (ds / "rr_overlaps.paf").stat().st_size > 3 * chunk
+        ora = common.run_dump(oracle_bin, ds, tmp_path / f"{name}.bin", [], extra=["--rng", "philox", "--seed", "5"])
+        with capi.Hera(0) as h:
+            h.set_option("load_chunk_bytes", chunk)
+            gpu = pipeline.run_hot_path(ds, [], seed=5, hera=h, loader="bytes")
+        common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS + PATH_SECTIONS + GROUP_SECTIONS, f"{name} in chunks")
+    # ends of text around the chunk borders, an irregular record, a record limit
+    rec = "read%05d 9000 10 8990 + ctg%d 50000 %d %d 8000 8980 0 tp:A:S cm:i:1 s1:i:1 dv:f:0.1\n"
+    body = "".join(rec % (i, i % 3, i % 7, 8980 + i % 7) for i in range(11000))
+    assert len(body) > 3 * chunk + 4096
+    texts = {f"cut{k}{d:+d}": body[:k * chunk + d] for k in (1, 2, 3) for d in (-1, 0, 1, 16, 1500)}
+    late = body.find("\n", 2 * chunk + 9000) + 1
+    texts["irregular"] = body[:late] + "x" + body[late:]
+    texts["no_newline"] = body.rstrip("\n")
+    with capi.Hera(0) as h:
+        h.set_option("load_chunk_bytes", chunk)
+        for name, text in texts.items():
+            for opts in ([], ["--test-load-num", "7000"]) if name in ("cut3+0", "irregular") else ([],):
+                d = tmp_path / (name + "_" + str(len(opts)))
+                d.mkdir()
+                (d / "rr_overlaps.paf").write_text(text, newline="")
+                (d / "cr_overlaps.paf").write_text(body[:5000], newline="")
+                ora = common.run_dump(oracle_bin, d, d / "o.bin", ["--mode", "max"] + opts, extra=["--stage", "graph"])
+                h.graph_reset()
+                gpu = pipeline.run_hot_path(d, ["--mode", "max"] + opts, stages="graph", hera=h, loader="bytes")
+                common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS, f"{name} {opts}")
+    # the reservations of large loads
+    ds = datasets["small"]
+    full = (ds / "rr_overlaps.paf").read_bytes()
+    pre = full[:full.rfind(b"\n", 0, int(len(full) * 0.58)) + 1]
+    d = tmp_path / "prefix"
+    d.mkdir()
+    (d / "rr_overlaps.paf").write_bytes(pre)
+    (d / "cr_overlaps.paf").write_bytes(b"")
+    ora_full = common.run_dump(oracle_bin, ds, tmp_path / "f.bin", [], extra=["--stage", "graph"])
+    ora_pre = common.run_dump(oracle_bin, d, tmp_path / "p.bin", [], extra=["--stage", "graph"])
+    with capi.Hera(0) as h:
+        h.set_option("load_chunk_bytes", chunk)
+        h.set_option("parse_count_rows", 1000)
+        for rep, (path, ora) in enumerate([(d, ora_pre), (ds, ora_full), (ds, ora_full), (d, ora_pre)]):   # counted; overflow + repeat; fits; fits
+            h.graph_reset()
+            gpu = pipeline.run_hot_path(path, [], stages="graph", hera=h, loader="bytes")
+            common.assert_sections_equal(ora, gpu, GRAPH_SECTIONS, f"reservation {rep}")
+
+
 def test_names_of_65536_bytes_are_refused(tmp_path):
     """Name references hold 16 bits of length: a kept record with a longer name fails the load (code 22) instead of
     producing a truncated node name; the reference has no such limit (documented in INTEGRATION.md)."""
