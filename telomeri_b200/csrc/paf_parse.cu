@@ -1456,7 +1456,10 @@ void load_text_resident(Ctx &c, LoadedText &text, uint32_t file_id, bool anchors
         out->kept_total = c.rows_total;
         out->bytes = n;
         HERA_CUDA(cudaEventElapsedTime(&out->parse_ms, ev0, ev1));   // (a chunked load: from the first chunk's launch to the last one's end, waits for the copy included)
-        if (host) HERA_CUDA(cudaEventElapsedTime(&out->h2d_ms, chunk_events.t0, chunk_events.t1));
+        if (host) {
+            HERA_CUDA(cudaEventSynchronize(chunk_events.t1));   // recorded right behind the last chunk's event, which the stream has waited for
+            HERA_CUDA(cudaEventElapsedTime(&out->h2d_ms, chunk_events.t0, chunk_events.t1));
+        }
         out->exchange_ms = 0;
         if (sharded) {
             HERA_CUDA(cudaEventSynchronize(ev2));
